@@ -1,0 +1,109 @@
+"""Pins the CPU oracle (oracle/) on the reference's own known answers.
+
+  * Wigner-3j buffers stored in tests/data/checkpoints/cp_0.pth
+  * test_train.py:284-316 metric goldens of cp_0.pth on hfo2.extxyz
+  * edge counts of test_data.py:48
+  * SH / w3j self-consistency (SURVEY Appendix A rules 2-3)
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import e3nn_ref as o3
+from oracle import sevenn_ref as S
+
+
+def test_w3j_matches_reference_goldens(golden_dir):
+    gold = torch.load(os.path.join(golden_dir, 'w3j_cp0.pt'))
+    assert len(gold) == 8
+    for name, ref in gold.items():
+        l1, l2, l3 = (int(t) for t in name.split('_')[-3:])
+        mine = o3.wigner_3j(l1, l2, l3)
+        assert torch.equal(mine, ref) or torch.allclose(mine, ref, atol=1e-7), name
+        assert abs(ref.norm().item() - 1) < 1e-6
+
+
+@pytest.mark.parametrize('lmax', [1, 2, 3])
+def test_sh_closed_forms_vs_recursion(lmax):
+    g = torch.Generator().manual_seed(0)
+    v = torch.randn(50, 3, generator=g, dtype=torch.float64)
+    a = o3.spherical_harmonics(lmax, v, normalize=False)
+    b = o3.spherical_harmonics_recursive(lmax, v)
+    assert torch.allclose(a, b, atol=1e-10)
+    u = torch.nn.functional.normalize(v, dim=-1)
+    y = o3.spherical_harmonics(lmax, u, normalize=True)
+    off = 0
+    for l in range(lmax + 1):
+        blk = y[:, off:off + 2 * l + 1]
+        assert torch.allclose((blk ** 2).sum(-1), torch.full((50,), 2.0 * l + 1, dtype=torch.float64))
+        off += 2 * l + 1
+
+
+def test_normalize2mom_constant():
+    c = o3.Normalize2Mom(torch.nn.functional.silu).cst
+    assert abs(c - 1.6791767923989418) < 1e-12
+
+
+def _cp0_metrics(golden_dir):
+    model, cfg = S.load_checkpoint(os.path.join(golden_dir, 'cp0_model.pt'))
+    model.eval()
+    fr = np.load(os.path.join(golden_dir, 'hfo2_frames.npz'))
+    dE, dF, dS = [], [], []
+    for k in range(2):
+        num, pos, cell, pbc = (fr[f'f{k}_{n}'] for n in ('numbers', 'pos', 'cell', 'pbc'))
+        g = S.atoms_to_graph(num, pos, cell, pbc, cfg['cutoff'])
+        out = model(g)
+        s = fr[f'f{k}_stress3x3']
+        voigt = np.array([s[0, 0], s[1, 1], s[2, 2], s[1, 2], s[0, 2], s[0, 1]])
+        y_stress = -voigt[[0, 1, 2, 5, 3, 4]]   # train/dataload.py:275-300
+        dE.append((out[S.E_TOT].item() - float(fr[f'f{k}_energy'])) / len(num))
+        dF.append(out[S.FORCE].detach().numpy() - fr[f'f{k}_forces'])
+        dS.append(out[S.STRESS].detach().numpy() - y_stress)
+    dF = np.concatenate(dF)
+    return (math.sqrt(np.mean(np.square(dE))), math.sqrt(np.mean((dF ** 2).sum(1))),
+            math.sqrt(np.mean((np.array(dS) ** 2).sum(1))) * 1602.1766208)
+
+
+def test_cp0_known_answer_metrics(golden_dir):
+    """reference tests/unit_tests/test_train.py:284-316 (eval half)."""
+    e, f, s = _cp0_metrics(golden_dir)
+    # the reference compares 6-decimal strings with np.allclose (rtol 1e-5); we are far tighter
+    assert abs(e - 28.977758) < 2e-6
+    assert abs(f - 0.214107) < 1e-6
+    assert abs(s - 190.014237) < 5e-6
+
+
+def test_edge_counts_reference_test_data():
+    """reference tests/unit_tests/test_data.py:48: NaCl prim 36, sc Cu(a=3.35) 18 at rc=4."""
+    a = 5.64 / 2   # ase bulk('NaCl','rocksalt',a=5.64) primitive fcc vectors
+    cell = np.array([[0, a, a], [a, 0, a], [a, a, 0]])
+    pos = np.array([[0, 0, 0], [a, a, a]])
+    i, j, D, Sh = S.neighbor_list_bruteforce(pos, cell, [True] * 3, 4.0)
+    assert len(i) == 36
+    cell = np.eye(3) * 3.35
+    i, j, D, Sh = S.neighbor_list_bruteforce(np.zeros((1, 3)), cell, [True] * 3, 4.0)
+    assert len(i) == 18
+
+
+def test_oracle_forces_are_energy_gradient_fp64(golden_dir):
+    torch.set_default_dtype(torch.float64)
+    try:
+        model, cfg = S.load_checkpoint(os.path.join(golden_dir, 'cp0_model.pt'))
+        model = model.double().eval()
+        fr = np.load(os.path.join(golden_dir, 'hfo2_frames.npz'))
+        num, pos, cell, pbc = (fr[f'f0_{n}'] for n in ('numbers', 'pos', 'cell', 'pbc'))
+        g = S.atoms_to_graph(num, pos, cell, pbc, cfg['cutoff'], dtype=torch.float64)
+        out = model(g)
+        F = out[S.FORCE].detach().numpy()
+        h = 1e-5
+        for (a, d) in [(0, 0), (5, 2)]:
+            es = []
+            for sgn in (+1, -1):
+                p = pos.copy(); p[a, d] += sgn * h
+                es.append(model(S.atoms_to_graph(num, p, cell, pbc, cfg['cutoff'], dtype=torch.float64))[S.E_TOT].item())
+            assert abs(-(es[0] - es[1]) / (2 * h) - F[a, d]) < 1e-6
+    finally:
+        torch.set_default_dtype(torch.float32)
