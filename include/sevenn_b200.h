@@ -1,0 +1,114 @@
+/* sevenn_b200.h -- C ABI of the B200 (sm_100a) SevenNet energy/force/stress kernels.
+ *
+ * Drop-in boundary for the hot path of hexagonrose/SevenNet_exp (sevenn 0.11): everything the
+ * reference obtains from e3nn/ATen/torch.autograd inside AtomGraphSequential.forward
+ * (sevenn/nn/sequential.py:178, call stack in SURVEY.md section 3.1) is reachable through the plain-C
+ * launchers below.  Conventions:
+ *   - all pointers are DEVICE pointers unless the parameter is documented "host";
+ *   - the caller owns every buffer (no hidden allocation), passes the cudaStream_t as void*;
+ *   - launchers are asynchronous and return 0 or a cudaError_t / SEVENN_ERR_* code; they never exit();
+ *   - node tensors are fp32 rows in the "ir_mul" layout described in sevennet_exp_b200/irreps.py;
+ *   - indices are int32 on the device (E < 2^31); the torch boundary converts from int64.
+ * Each entry cites the reference interface it replaces (paths relative to /root/reference).
+ */
+#ifndef SEVENN_B200_H
+#define SEVENN_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SEVENN_ERR_BAD_ARG 10001
+#define SEVENN_MAX_GATE_PIECES 16
+
+int sevenn_abi_version(void);
+
+/* ---- neighbor list: replaces sevenn/train/dataload.py:32-130 (_graph_build_ase/_matscipy,
+ * unlabeled_atoms_to_graph) and the CPU edge loop of sevenn/pair_e3gnn/pair_e3gnn.cpp:157-195.
+ * dpar (host, 25 doubles): cell[9] rows=lattice vectors, inv[9] (frac = pos.inv), bin origin lo[3],
+ * 1/extent inv_span[3] (fractional), rc^2.   ipar (host, 9 ints): pbc[3], nbins[3], stencil R[3]. */
+int sevenn_scan_i32(const int* in, int* out /* n+1 */, int n, int* tmp, void* stream);
+long long sevenn_scan_tmp_ints(int n);
+int sevenn_nl_bin(const double* pos, int n, const double* dpar, const int* ipar, double* pos_wrapped,
+                  int* wrap, int* atom_bin, int* bin_count /* zeroed, nbins+1 */, void* stream);
+int sevenn_nl_scatter(const int* atom_bin, int n, const int* bin_start, int* bin_fill /* zeroed */,
+                      int* bin_atoms, void* stream);
+int sevenn_nl_count(const double* pos_wrapped, const int* wrap, const int* atom_bin, const int* bin_start,
+                    const int* bin_atoms, int n, const double* dpar, const int* ipar, int* count, void* stream);
+int sevenn_nl_fill(const double* pos_wrapped, const int* wrap, const int* atom_bin, const int* bin_start,
+                   const int* bin_atoms, int n, const double* dpar, const int* ipar, const int* rowptr,
+                   unsigned long long* keys /* E */, const double* pos, int* center /* E: edge_index[0] */,
+                   int* col /* E: edge_index[1] */, int* shift /* E,3 */, float* edge_vec /* E,3 */, void* stream);
+/* edges grouped by neighbour (edge_index[1]); segments sorted by edge id */
+int sevenn_csc_build(const int* col, long long n_edges, int n_nodes, int* cnt /* zeroed n_nodes+1 */,
+                     int* fill /* zeroed n_nodes */, int* cptr /* n_nodes+1 */, unsigned long long* keys /* E */,
+                     int* cedge /* E */, int* scan_tmp, void* stream);
+
+/* ---- edge embedding: replaces sevenn/nn/edge_embedding.py:81-217 (BesselBasis, PolynomialCutoff,
+ * XPLORCutoff, SphericalEncoding, EdgeEmbedding.forward).  cutoff_kind 0 = poly_cut(p), 1 = XPLOR(r_on). */
+int sevenn_edge_fwd(const float* edge_vec, long long n_edges, int lmax, int normalize, int n_basis,
+                    int cutoff_kind, float rc, float p, float r_on, const float* bessel_coeffs,
+                    float* Y /* E,(lmax+1)^2 */, float* emb /* E,n_basis */, void* stream);
+/* analytic d/d(edge_vec): replaces autograd through the same modules (sevenn/nn/force_output.py:173-178) */
+int sevenn_edge_bwd(const float* edge_vec, long long n_edges, int lmax, int normalize, int n_basis,
+                    int cutoff_kind, float rc, float p, float r_on, const float* bessel_coeffs,
+                    const float* dY, const float* demb, float* f_edge /* E,3 */, void* stream);
+
+/* ---- dense contractions: replaces e3nn o3.Linear (sevenn/nn/linear.py:49-63,94), the radial MLP
+ * e3nn FullyConnectedNet (sevenn/nn/convolution.py:92-101,121) and their input gradients. */
+typedef struct {
+  const float* A; long long sAn; int sAm;   /* row (n,m) at A + n*sAn + m*sAm, K contiguous */
+  const float* B; int ldb;                   /* [K, N] row-major */
+  float* C; long long sCn; int sCm;          /* row (n,m) at C + n*sCn + m*sCm */
+  long long M; int R; int N; int K;          /* M = nodes*R rows */
+  int epi;                                   /* 0 store, 1 accumulate, 2 pre->C & cst*act->C2, 3 acc*cst*act'(P) */
+  int act; float cst;                        /* activation id (0 silu,1 tanh,2 abs,3 relu,4 sigmoid,5 ssp) */
+  float* C2; const float* P;                 /* aux out / aux in, strides of C */
+} sevenn_gemm_args;
+int sevenn_gemm_f32(const sevenn_gemm_args* args /* host */, void* stream);   /* exact fp32 (SIMT) */
+
+/* species-indexed linear = FullyConnectedTensorProduct(x, one_hot): sevenn/nn/self_connection.py:10-64 */
+int sevenn_linear_by_type(const float* A, long long sAn, int sAm, const float* W /* S,K,N */, const int* types,
+                          float* C, long long sCn, int sCm, long long n_nodes, int R, int K, int N,
+                          int accumulate, void* stream);
+
+/* ---- node kernels */
+/* OnehotEmbedding + onehot_to_feature_x: sevenn/nn/node_embedding.py:15-53, model_build.py:453-458 */
+int sevenn_embed(const int* types, long long n, int dim, const float* table /* S,dim */, float* out, void* stream);
+typedef struct {
+  int kind;       /* 0 scalar, 1 gated */
+  int l, mul;
+  int in_off, in_stride, gate_off;
+  int out_off, out_stride;
+  int act; float cst;
+} sevenn_gate_piece;
+/* EquivariantGate / e3nn nn.Gate: sevenn/nn/equivariant_gate.py:13-61 */
+int sevenn_gate_fwd(const float* pre, int din, float* out, int dout, long long n,
+                    const sevenn_gate_piece* pieces /* host */, int n_pieces, void* stream);
+int sevenn_gate_bwd(const float* pre, int din, const float* dout, int dout_dim, float* dpre, long long n,
+                    const sevenn_gate_piece* pieces /* host */, int n_pieces, void* stream);
+/* Rescale / SpeciesWiseRescale: sevenn/nn/scale.py:22-161 ; also emits dE/de_i (= scale) */
+int sevenn_rescale(const float* e_scaled, const int* types, long long n, const float* scale, const float* shift,
+                   int species_wise, float* atomic_energy, float* seed, void* stream);
+/* AtomReduce (sevenn/nn/linear.py:104-141) and the stress sum: deterministic column sums in fp64 */
+int sevenn_colsum_f64(const float* a, long long n, int D, double* part /* >= 296*D */, double* out, void* stream);
+/* ForceStressOutputFromEdge scatter part: sevenn/nn/force_output.py:185-222 */
+int sevenn_force_virial(const float* f_edge, const float* edge_vec, const int* rowptr, int n_rows, const int* cptr,
+                        const int* cedge, long long n_nodes, float* F /* n_nodes,3 */, float* vir /* n_nodes,6 */,
+                        void* stream);
+int sevenn_segment_gather_sum(const float* src, int D, const int* cptr, const int* cedge, long long n_nodes,
+                              float* out, int accumulate, void* stream);
+/* halo pack / unpack-add: sevenn/pair_e3gnn/pair_e3gnn_parallel.cpp:787-897 */
+int sevenn_gather_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream);
+int sevenn_scatter_add_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream);
+
+/* ---- fused gather + uvu CG tensor product + segment sum (generated per irreps signature <sig>):
+ *   int sevenn_conv_fwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo, stream)
+ *   int sevenn_conv_bwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY, stream)
+ *   int sevenn_conv_info_<sig>(&x_dim, &mid_dim, &wn, &sh_dim)
+ * replaces IrrepsConvolution.forward's TensorProduct + message_gather (sevenn/nn/convolution.py:16-25,118-137). */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

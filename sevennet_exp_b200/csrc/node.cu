@@ -1,0 +1,269 @@
+// Per-node elementwise / gather kernels of the SevenNet evaluation path (fp32, ir_mul layout).
+//   embed            : OnehotEmbedding + onehot_to_feature_x  (sevenn/nn/node_embedding.py:15-53, model_build.py:453-458)
+//   gate fwd/bwd     : EquivariantGate -> e3nn nn.Gate        (sevenn/nn/equivariant_gate.py:13-61)
+//   energy / seed    : Rescale / SpeciesWiseRescale + AtomReduce (sevenn/nn/scale.py:22-161, nn/linear.py:104-141)
+//   force_virial     : ForceStressOutputFromEdge scatter part (sevenn/nn/force_output.py:185-222)
+//   segment_gather_sum: source-side reduction of per-edge dE/dx_j (replaces autograd's index backward, atomics-free)
+//   linear_by_type   : SelfConnectionIntro (FullyConnectedTensorProduct x (x) one-hot) (nn/self_connection.py:10-64)
+//   gather_rows / scatter_add_rows : halo pack / unpack-add (pair_e3gnn_parallel.cpp:787-897)
+// All HBM-bound; grid-stride, coalesced along the channel index.
+#include "sevenn_common.cuh"
+#include "../../include/sevenn_b200.h"
+
+HD float act_f(int id, float x) {
+  switch (id) {
+    case 0: return x / (1.f + expf(-x));
+    case 1: return tanhf(x);
+    case 2: return fabsf(x);
+    case 3: return x > 0.f ? x : 0.f;
+    case 4: return 1.f / (1.f + expf(-x));
+    default: return (x > 20.f ? x : log1pf(expf(x))) - 0.6931471805599453f;
+  }
+}
+HD float dact_f(int id, float x) {
+  switch (id) {
+    case 0: { const float s = 1.f / (1.f + expf(-x)); return s * (1.f + x * (1.f - s)); }
+    case 1: { const float t = tanhf(x); return 1.f - t * t; }
+    case 2: return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f);
+    case 3: return x > 0.f ? 1.f : 0.f;
+    case 4: { const float s = 1.f / (1.f + expf(-x)); return s * (1.f - s); }
+    default: return 1.f / (1.f + expf(-x));
+  }
+}
+
+GKERNEL(embed_kernel)(const int* __restrict__ types, long long n, int dim, const float* __restrict__ table,
+                      float* __restrict__ out) {
+  GRID_STRIDE_LOOP(t, n * dim) {
+    const long long i = t / dim; const int c = (int)(t % dim);
+    out[t] = LDGF(table + (size_t)types[i] * dim + c);
+  }
+}
+
+struct GateTable { int n; sevenn_gate_piece p[SEVENN_MAX_GATE_PIECES]; };
+
+GKERNEL(gate_fwd_kernel)(const float* __restrict__ pre, int din, float* __restrict__ out, int dout, long long n,
+                         GateTable T) {
+  GRID_STRIDE_LOOP(t, n * dout) {
+    const long long i = t / dout; int c = (int)(t % dout);
+    const float* row = pre + i * din;
+    for (int q = 0; q < T.n; ++q) {
+      const sevenn_gate_piece& P = T.p[q];
+      const int sz = P.mul * (2 * P.l + 1);
+      // pieces tile the output row; inside a piece the output block is [2l+1][out_stride] at out_off
+      // (out_stride == mul because gate outputs are simplified entries)
+      if (c < sz) {
+        const int m = c / P.mul, u = c % P.mul;
+        float v;
+        if (P.kind == 0) v = P.cst * act_f(P.act, row[P.in_off + u]);
+        else v = P.cst * act_f(P.act, row[P.gate_off + u]) * row[P.in_off + m * P.in_stride + u];
+        out[i * dout + P.out_off + m * P.out_stride + u] = v;
+        break;
+      }
+      c -= sz;
+    }
+  }
+}
+
+// one thread per (node, piece channel)
+GKERNEL(gate_bwd_kernel)(const float* __restrict__ pre, int din, const float* __restrict__ dout_, int dout,
+                         float* __restrict__ dpre, long long n, GateTable T, int nch) {
+  GRID_STRIDE_LOOP(t, n * nch) {
+    const long long i = t / nch; int c = (int)(t % nch);
+    const float* row = pre + i * din; const float* go = dout_ + i * dout; float* gi = dpre + i * din;
+    for (int q = 0; q < T.n; ++q) {
+      const sevenn_gate_piece& P = T.p[q];
+      if (c < P.mul) {
+        const int u = c;
+        if (P.kind == 0) {
+          gi[P.in_off + u] = go[P.out_off + u] * P.cst * dact_f(P.act, row[P.in_off + u]);
+        } else {
+          const float gpre = row[P.gate_off + u];
+          const float gate = P.cst * act_f(P.act, gpre);
+          float acc = 0.f;
+          for (int m = 0; m < 2 * P.l + 1; ++m) {
+            const float g = go[P.out_off + m * P.out_stride + u];
+            acc += g * row[P.in_off + m * P.in_stride + u];
+            gi[P.in_off + m * P.in_stride + u] = g * gate;
+          }
+          gi[P.gate_off + u] = acc * P.cst * dact_f(P.act, gpre);
+        }
+        break;
+      }
+      c -= P.mul;
+    }
+  }
+}
+
+static int load_gate(GateTable& T, const sevenn_gate_piece* pieces, int n_pieces) {
+  if (n_pieces < 0 || n_pieces > SEVENN_MAX_GATE_PIECES) return SEVENN_ERR_BAD_ARG;
+  T.n = n_pieces;
+  for (int k = 0; k < n_pieces; ++k) T.p[k] = pieces[k];
+  return 0;
+}
+
+extern "C" int sevenn_embed(const int* types, long long n, int dim, const float* table, float* out, void* stream) {
+  if (n <= 0) return 0;
+  LAUNCH1D(embed_kernel, n * dim, stream)(types, n, dim, table, out);
+  return LAUNCH_STATUS();
+}
+extern "C" int sevenn_gate_fwd(const float* pre, int din, float* out, int dout, long long n,
+                               const sevenn_gate_piece* pieces, int n_pieces, void* stream) {
+  GateTable T; int rc = load_gate(T, pieces, n_pieces); if (rc) return rc;
+  if (n <= 0) return 0;
+  LAUNCH1D(gate_fwd_kernel, n * dout, stream)(pre, din, out, dout, n, T);
+  return LAUNCH_STATUS();
+}
+extern "C" int sevenn_gate_bwd(const float* pre, int din, const float* dout_, int dout, float* dpre, long long n,
+                               const sevenn_gate_piece* pieces, int n_pieces, void* stream) {
+  GateTable T; int rc = load_gate(T, pieces, n_pieces); if (rc) return rc;
+  if (n <= 0) return 0;
+  int nch = 0; for (int k = 0; k < n_pieces; ++k) nch += pieces[k].mul;
+  LAUNCH1D(gate_bwd_kernel, n * nch, stream)(pre, din, dout_, dout, dpre, n, T, nch);
+  return LAUNCH_STATUS();
+}
+
+// ---- energy: E_i = e_i * scale[t_i] + shift[t_i]; seed of the backward pass dE/de_i = scale[t_i]
+GKERNEL(rescale_kernel)(const float* __restrict__ e_scaled, const int* __restrict__ types, long long n,
+                        const float* __restrict__ scale, const float* __restrict__ shift, int species_wise,
+                        float* __restrict__ atomic_energy, float* __restrict__ seed) {
+  GRID_STRIDE_LOOP(i, n) {
+    const int t = species_wise ? types[i] : 0;
+    const float s = LDGF(scale + t);
+    atomic_energy[i] = e_scaled[i] * s + LDGF(shift + t);
+    seed[i] = s;
+  }
+}
+extern "C" int sevenn_rescale(const float* e_scaled, const int* types, long long n, const float* scale,
+                              const float* shift, int species_wise, float* atomic_energy, float* seed, void* stream) {
+  if (n <= 0) return 0;
+  LAUNCH1D(rescale_kernel, n, stream)(e_scaled, types, n, scale, shift, species_wise, atomic_energy, seed);
+  return LAUNCH_STATUS();
+}
+
+// ---- deterministic column sums of a [n, D] fp32 matrix into D doubles (two stages, D <= 8)
+#ifndef SEVENN_EMU
+#define COLSUM_BLOCKS 296
+__global__ void colsum_stage1(const float* __restrict__ a, long long n, int D, double* __restrict__ part) {
+  __shared__ double sh[256];
+  for (int d = 0; d < D; ++d) {
+    double s = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+      s += (double)a[i * D + d];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) { if (threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o]; __syncthreads(); }
+    if (threadIdx.x == 0) part[blockIdx.x * D + d] = sh[0];
+    __syncthreads();
+  }
+}
+__global__ void colsum_stage2(const double* __restrict__ part, int nb, int D, double* __restrict__ out) {
+  const int d = threadIdx.x;
+  if (d < D) { double s = 0.0; for (int b = 0; b < nb; ++b) s += part[b * D + d]; out[d] = s; }
+}
+#endif
+extern "C" int sevenn_colsum_f64(const float* a, long long n, int D, double* part /* >= 296*D */, double* out,
+                                 void* stream) {
+  if (D < 1 || D > 8) return SEVENN_ERR_BAD_ARG;
+#ifdef SEVENN_EMU
+  for (int d = 0; d < D; ++d) { double s = 0; for (long long i = 0; i < n; ++i) s += a[i * D + d]; out[d] = s; }
+  return 0;
+#else
+  colsum_stage1<<<COLSUM_BLOCKS, 256, 0, (cudaStream_t)stream>>>(a, n, D, part);
+  colsum_stage2<<<1, 32, 0, (cudaStream_t)stream>>>(part, COLSUM_BLOCKS, D, out);
+  return (int)cudaGetLastError();
+#endif
+}
+
+// ---- forces and virial from per-edge dE/d(edge_vec)
+// F_k = sum_{e: centre k} f_e - sum_{e: neighbour k} f_e ; w_k[6] = sum_{e: centre k} (rx fx, ry fy, rz fz, rx fy, ry fz, rz fx)
+GKERNEL(force_virial_kernel)(const float* __restrict__ fvec, const float* __restrict__ vec,
+                             const int* __restrict__ rowptr, int n_rows, const int* __restrict__ cptr,
+                             const int* __restrict__ cedge, long long n_nodes, float* __restrict__ F,
+                             float* __restrict__ vir) {
+  GRID_STRIDE_LOOP(k, n_nodes) {
+    float fx = 0.f, fy = 0.f, fz = 0.f, w0 = 0.f, w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f, w5 = 0.f;
+    if (k < n_rows) {
+      for (int e = rowptr[k]; e < rowptr[k + 1]; ++e) {
+        const float ax = fvec[3 * e], ay = fvec[3 * e + 1], az = fvec[3 * e + 2];
+        const float rx = vec[3 * e], ry = vec[3 * e + 1], rz = vec[3 * e + 2];
+        fx += ax; fy += ay; fz += az;
+        w0 += rx * ax; w1 += ry * ay; w2 += rz * az; w3 += rx * ay; w4 += ry * az; w5 += rz * ax;
+      }
+    }
+    for (int a = cptr[k]; a < cptr[k + 1]; ++a) {
+      const int e = cedge[a];
+      fx -= fvec[3 * e]; fy -= fvec[3 * e + 1]; fz -= fvec[3 * e + 2];
+    }
+    F[3 * k] = fx; F[3 * k + 1] = fy; F[3 * k + 2] = fz;
+    float* w = vir + 6 * k;
+    w[0] = w0; w[1] = w1; w[2] = w2; w[3] = w3; w[4] = w4; w[5] = w5;
+  }
+}
+extern "C" int sevenn_force_virial(const float* fvec, const float* vec, const int* rowptr, int n_rows,
+                                   const int* cptr, const int* cedge, long long n_nodes, float* F, float* vir,
+                                   void* stream) {
+  if (n_nodes <= 0) return 0;
+  LAUNCH1D(force_virial_kernel, n_nodes, stream)(fvec, vec, rowptr, n_rows, cptr, cedge, n_nodes, F, vir);
+  return LAUNCH_STATUS();
+}
+
+// ---- out[j, :] (+)= sum_{a in csc(j)} src[cedge[a], :]
+GKERNEL(segment_gather_sum_kernel)(const float* __restrict__ src, int D, const int* __restrict__ cptr,
+                                   const int* __restrict__ cedge, long long n_nodes, float* __restrict__ out,
+                                   int accumulate) {
+  GRID_STRIDE_LOOP(t, n_nodes * D) {
+    const long long j = t / D; const int c = (int)(t % D);
+    float s = accumulate ? out[t] : 0.f;
+    for (int a = cptr[j]; a < cptr[j + 1]; ++a) s += src[(size_t)cedge[a] * D + c];
+    out[t] = s;
+  }
+}
+extern "C" int sevenn_segment_gather_sum(const float* src, int D, const int* cptr, const int* cedge,
+                                         long long n_nodes, float* out, int accumulate, void* stream) {
+  if (n_nodes <= 0) return 0;
+  LAUNCH1D(segment_gather_sum_kernel, n_nodes * D, stream)(src, D, cptr, cedge, n_nodes, out, accumulate);
+  return LAUNCH_STATUS();
+}
+
+// ---- species-indexed linear: C[(n,m), w] (+)= sum_u A[(n,m), u] * W[type_n][u][w]
+GKERNEL(linear_by_type_kernel)(const float* __restrict__ A, long long sAn, int sAm, const float* __restrict__ W,
+                               const int* __restrict__ types, float* __restrict__ C, long long sCn, int sCm,
+                               long long n_nodes, int R, int K, int N, int accumulate) {
+  GRID_STRIDE_LOOP(t, n_nodes * R * N) {
+    const int w = (int)(t % N); const long long r = t / N; const long long nn = r / R; const int m = (int)(r % R);
+    const float* a = A + nn * sAn + m * sAm;
+    const float* wt = W + (size_t)types[nn] * K * N + w;
+    float s = 0.f;
+    for (int u = 0; u < K; ++u) s += a[u] * wt[(size_t)u * N];
+    float* c = C + nn * sCn + m * sCm + w;
+    *c = accumulate ? *c + s : s;
+  }
+}
+extern "C" int sevenn_linear_by_type(const float* A, long long sAn, int sAm, const float* W, const int* types,
+                                     float* C, long long sCn, int sCm, long long n_nodes, int R, int K, int N,
+                                     int accumulate, void* stream) {
+  if (n_nodes <= 0) return 0;
+  LAUNCH1D(linear_by_type_kernel, n_nodes * R * N, stream)(A, sAn, sAm, W, types, C, sCn, sCm, n_nodes, R, K, N, accumulate);
+  return LAUNCH_STATUS();
+}
+
+// ---- halo pack / unpack
+GKERNEL(gather_rows_kernel)(const float* __restrict__ src, int D, const int* __restrict__ idx, long long n,
+                            float* __restrict__ out) {
+  GRID_STRIDE_LOOP(t, n * D) { out[t] = src[(size_t)idx[t / D] * D + (t % D)]; }
+}
+GKERNEL(scatter_add_rows_kernel)(const float* __restrict__ src, int D, const int* __restrict__ idx, long long n,
+                                 float* __restrict__ out) {
+  // idx must not repeat inside one call (one message per peer) -> plain read-modify-write
+  GRID_STRIDE_LOOP(t, n * D) { out[(size_t)idx[t / D] * D + (t % D)] += src[t]; }
+}
+extern "C" int sevenn_gather_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream) {
+  if (n <= 0) return 0;
+  LAUNCH1D(gather_rows_kernel, n * D, stream)(src, D, idx, n, out);
+  return LAUNCH_STATUS();
+}
+extern "C" int sevenn_scatter_add_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream) {
+  if (n <= 0) return 0;
+  LAUNCH1D(scatter_add_rows_kernel, n * D, stream)(src, D, idx, n, out);
+  return LAUNCH_STATUS();
+}

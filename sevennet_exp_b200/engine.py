@@ -1,0 +1,321 @@
+"""Whole-model launcher: energy, forces and virial of one atomic graph on one GPU.
+
+Straight-line replacement of ``AtomGraphSequential.forward`` (sevenn/nn/sequential.py:178; call
+stack SURVEY.md section 3.1) including the reverse pass that the reference gets from
+``torch.autograd.grad(E, edge_vec)`` (sevenn/nn/force_output.py:173-178): every step is one of
+the C-ABI launchers of include/sevenn_b200.h, no autograd, no e3nn, no CPU fallback.
+
+Nodes are ``n_local`` owned atoms followed by ghosts (single GPU: no ghosts).  Rows of the
+CSR edge list exist for owned atoms only; ``halo`` (domain.py) fills ghost rows of the
+convolution input before each layer >= 1 and returns ghost gradients to their owners.
+"""
+import ctypes
+import math
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from .spec import ACT_ID, LinearSpec, ModelSpec, nequip_sc_dense
+from . import irreps as ir
+
+
+class Graph:
+    """Device-side graph: CSR by centre (edge_index[0]) + CSC by neighbour (edge_index[1])."""
+
+    def __init__(self, types, edge_vec, rowptr, col, cptr, cedge, n_local, volume):
+        self.types, self.edge_vec, self.rowptr, self.col = types, edge_vec, rowptr, col
+        self.cptr, self.cedge = cptr, cedge
+        self.n_local, self.n_nodes, self.n_edges = int(n_local), int(types.shape[0]), int(col.shape[0])
+        self.volume = float(volume)
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class _Lin:
+    """Device weights of one o3.Linear (or nequip FCTP) in block form."""
+
+    def __init__(self, spec: LinearSpec, flat: np.ndarray, dev, by_type_S: int = 0):
+        self.spec, self.by_type = spec, by_type_S
+        self.W, self.WT = [], []
+        for b in spec.blocks:
+            if by_type_S:
+                w = nequip_sc_dense(spec, flat, b, by_type_S)              # [S,K,N]
+                wt = np.ascontiguousarray(w.transpose(0, 2, 1))
+            else:
+                w = spec.dense(flat, b)
+                wt = np.ascontiguousarray(w.T)
+            self.W.append(torch.tensor(w, dtype=torch.float32, device=dev).contiguous())
+            self.WT.append(torch.tensor(wt, dtype=torch.float32, device=dev).contiguous())
+        cover = [0] * len(spec.lin.groups)
+        for b in spec.blocks:
+            cover[b.g_in] += 1
+        self.bwd_needs_zero = any(c != 1 for c in cover)
+        cover_o = {}
+        for b in spec.blocks:
+            cover_o[(b.g_out, b.u_off_out)] = 1
+        self.fwd_full = sum(b.N * (2 * b.l + 1) for b in spec.blocks) == spec.lout.dim
+
+
+class Engine:
+    def __init__(self, spec: ModelSpec, state_dict: Dict[str, torch.Tensor], lib: Optional[_lib.Lib] = None,
+                 device='cuda', keep_weights: bool = True):
+        self.spec, self.dev = spec, torch.device(device)
+        self.lib = lib if lib is not None else _lib.load()
+        self.keep_w = keep_weights
+        sd = {k: v.detach().cpu().numpy().astype(np.float64) for k, v in state_dict.items()
+              if k in spec.expected_keys()}
+        missing = [k for k in spec.expected_keys() if k not in sd]
+        if missing:
+            raise KeyError(f'state_dict misses {missing}')
+        for k, shp in spec.expected_keys().items():
+            if tuple(sd[k].shape) != shp:
+                raise ValueError(f'{k}: shape {sd[k].shape} != expected {shp}')
+        dev = self.dev
+        f32 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32, device=dev).contiguous()  # noqa: E731
+        self.coeffs = f32(sd['edge_embedding.basis_function.coeffs'])
+        # embedding table [S, d0]
+        emb = spec.embed
+        table = np.zeros((spec.n_species, emb.lout.dim))
+        for b in emb.blocks:
+            assert b.l == 0
+            o = emb.lout.group_off[b.g_out] + b.u_off_out
+            table[:, o:o + b.N] = emb.dense(sd[emb.key], b)
+        self.embed_table = f32(table)
+        self.d0 = emb.lout.dim
+        self.layers = []
+        for L in spec.layers:
+            h = L.conv.hidden
+            Wm = [sd[f'{L.conv.name}.weight_nn.layer{k}.weight'] / math.sqrt(h[k]) for k in range(len(h) - 1)]
+            lay = {
+                'spec': L,
+                'sc': _Lin(L.sc, sd[L.sc.key], dev, spec.n_species if L.sc_type == 'nequip' else 0),
+                'si1': _Lin(L.si1, sd[L.si1.key], dev),
+                'si2': _Lin(L.si2, sd[L.si2.key], dev),
+                'mlp': [f32(w) for w in Wm],
+                'mlpT': [f32(np.ascontiguousarray(w.T)) for w in Wm],
+                'inv_denom': 1.0 / float(sd[f'{L.conv.name}.denominator'][0]),
+                'sig': L.conv.signature(),
+                'pieces': (_lib.GatePiece * len(L.gate.pieces))(*[
+                    _lib.GatePiece(p.kind, p.l, p.mul, p.in_off, p.in_stride, p.gate_off, p.out_off,
+                                   p.out_stride, p.act, p.cst) for p in L.gate.pieces]),
+            }
+            if not self.lib.has_conv(lay['sig']):
+                raise _lib.SevennError(
+                    f"no prebuilt conv kernel for signature {lay['sig']} ({ir.irreps_str(L.conv.lx.groups)}); "
+                    'build it with sevennet_exp_b200.build.build(extra_specs=...)')
+            self.layers.append(lay)
+        self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev)
+        self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev)
+        self.scale = f32(sd['rescale_atomic_energy.scale'])
+        self.shift = f32(sd['rescale_atomic_energy.shift'])
+        self.act_radial = ACT_ID[spec.act_radial]
+        self.cst_radial = ir.normalize2mom_const(spec.act_radial)
+        self.n_launch = 0
+
+    # ------------------------------------------------------------------ helpers
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream) if self.dev.type == 'cuda' else None
+
+    def _empty(self, *shape, dtype=torch.float32):
+        return torch.empty(*shape, dtype=dtype, device=self.dev)
+
+    def _zeros(self, *shape, dtype=torch.float32):
+        return torch.zeros(*shape, dtype=dtype, device=self.dev)
+
+    def _gemm(self, A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi=0, act=0, cst=1.0, C2=None, P=None):
+        g = _lib.GemmArgs(A.data_ptr() + 4 * a_off, sAn, sAm, B.data_ptr(), N, C.data_ptr() + 4 * c_off, sCn, sCm,
+                          M, R, N, K, epi, act, cst,
+                          (C2.data_ptr() + 4 * c_off) if C2 is not None else None,
+                          (P.data_ptr() + 4 * c_off) if P is not None else None)
+        self.lib.call('sevenn_gemm_f32', ctypes.byref(g), self._stream())
+        self.n_launch += 1
+
+    def _linear_fwd(self, lin: _Lin, x, n, y, accumulate=False, types=None):
+        sp = lin.spec
+        for b, W in zip(sp.blocks, lin.W):
+            a_off = sp.lin.group_off[b.g_in]
+            c_off = sp.lout.group_off[b.g_out] + b.u_off_out
+            R = 2 * b.l + 1
+            if lin.by_type:
+                self.lib.call('sevenn_linear_by_type', ctypes.c_void_p(x.data_ptr() + 4 * a_off), sp.lin.dim, b.K,
+                              _p(W), _p(types), ctypes.c_void_p(y.data_ptr() + 4 * c_off), sp.lout.dim,
+                              sp.lout.groups[b.g_out][0], n, R, b.K, b.N, int(accumulate), self._stream())
+                self.n_launch += 1
+            else:
+                self._gemm(x, a_off, sp.lin.dim, b.K, W, y, c_off, sp.lout.dim, sp.lout.groups[b.g_out][0],
+                           n * R, R, b.N, b.K, epi=1 if accumulate else 0)
+
+    def _linear_bwd(self, lin: _Lin, dy, n, dx, accumulate=False, types=None):
+        """dx (+)= dy @ W^T ; dx must be zero-initialised by the caller when lin.bwd_needs_zero."""
+        sp = lin.spec
+        acc = accumulate or lin.bwd_needs_zero
+        for b, WT in zip(sp.blocks, lin.WT):
+            a_off = sp.lout.group_off[b.g_out] + b.u_off_out
+            c_off = sp.lin.group_off[b.g_in]
+            R = 2 * b.l + 1
+            if lin.by_type:
+                self.lib.call('sevenn_linear_by_type', ctypes.c_void_p(dy.data_ptr() + 4 * a_off), sp.lout.dim,
+                              sp.lout.groups[b.g_out][0], _p(WT), _p(types),
+                              ctypes.c_void_p(dx.data_ptr() + 4 * c_off), sp.lin.dim, b.K, n, R, b.N, b.K,
+                              int(acc), self._stream())
+                self.n_launch += 1
+            else:
+                self._gemm(dy, a_off, sp.lout.dim, sp.lout.groups[b.g_out][0], WT, dx, c_off, sp.lin.dim, b.K,
+                           n * R, R, b.K, b.N, epi=1 if acc else 0)
+
+    def _mlp_fwd(self, lay, emb, E):
+        """radial MLP (e3nn FullyConnectedNet): returns (pre-activations, activations, w)."""
+        Ws = lay['mlp']
+        pres, acts, cur = [], [], emb
+        for k, W in enumerate(Ws):
+            K, N = W.shape
+            if k < len(Ws) - 1:
+                pre, act = self._empty(E, N), self._empty(E, N)
+                self._gemm(cur, 0, K, 0, W, pre, 0, N, 0, E, 1, N, K, epi=2, act=self.act_radial,
+                           cst=self.cst_radial, C2=act)
+                pres.append(pre); acts.append(act); cur = act
+            else:
+                w = self._empty(E, N)
+                self._gemm(cur, 0, K, 0, W, w, 0, N, 0, E, 1, N, K)
+        return pres, acts, w
+
+    def _mlp_last(self, lay, h_last, E):
+        W = lay['mlp'][-1]
+        K, N = W.shape
+        w = self._empty(E, N)
+        self._gemm(h_last, 0, K, 0, W, w, 0, N, 0, E, 1, N, K)
+        return w
+
+    def _mlp_bwd(self, lay, dW, pres, demb, E):
+        """demb += d(emb) given dE/dw (no weight gradients: inference)."""
+        WT = lay['mlpT']
+        cur = dW
+        for k in range(len(WT) - 1, -1, -1):
+            N, K = WT[k].shape   # WT[k] is [h_out, h_in]
+            if k > 0:
+                nxt = self._empty(E, K)
+                self._gemm(cur, 0, N, 0, WT[k], nxt, 0, K, 0, E, 1, K, N, epi=3, act=self.act_radial,
+                           cst=self.cst_radial, P=pres[k - 1])
+                cur = nxt
+            else:
+                self._gemm(cur, 0, N, 0, WT[k], demb, 0, K, 0, E, 1, K, N, epi=1)
+
+    # ------------------------------------------------------------------ evaluation
+    def evaluate(self, g: Graph, halo=None, want_forces: bool = True, debug: Optional[dict] = None):
+        """Returns dict(energy (0-d fp64 tensor), atomic_energy [n_local], forces [n_nodes,3],
+        virial6 (fp64 [6] = sum_e (rx fx, ry fy, rz fz, rx fy, ry fz, rz fx))).  Ghost rows of
+        `forces` hold the contributions owed to their owners (domain.py folds them back)."""
+        sp, lib, st = self.spec, self.lib, self._stream()
+        nl, nn, E = g.n_local, g.n_nodes, g.n_edges
+        S = (sp.lmax_sh + 1) ** 2
+        ckind = 0 if sp.cutoff_fn == 'poly_cut' else 1
+        edge_args = (sp.lmax_sh, int(sp.normalize_sph), sp.n_basis, ckind, sp.cutoff, sp.cutoff_p, sp.cutoff_on,
+                     _p(self.coeffs))
+        Y, emb = self._empty(max(E, 1), S), self._empty(max(E, 1), sp.n_basis)
+        lib.call('sevenn_edge_fwd', _p(g.edge_vec), E, *edge_args, _p(Y), _p(emb), st)
+        x = self._empty(nn, self.d0)
+        lib.call('sevenn_embed', _p(g.types), nn, self.d0, _p(self.embed_table), _p(x), st)
+        self.n_launch += 2
+        saved = []
+        n_x = nn                      # rows of x that are valid (all nodes for layer 0, owned afterwards)
+        for t, lay in enumerate(self.layers):
+            L = lay['spec']
+            dx_in, dmid, dgi, dout = L.conv.lx.dim, L.conv.lmid.dim, L.gate.lin.dim, L.gate.lout.dim
+            # self connection (owned atoms)
+            pre = self._empty(nl, dgi) if lay['sc'].fwd_full else self._zeros(nl, dgi)
+            self._linear_fwd(lay['sc'], x, nl, pre, types=g.types)
+            # self interaction 1 -> convolution input for all nodes
+            h = self._empty(nn, dx_in) if lay['si1'].fwd_full else self._zeros(nn, dx_in)
+            self._linear_fwd(lay['si1'], x, n_x, h)
+            if n_x < nn:
+                halo.forward(t, h)    # fills rows [n_local, n_nodes)
+            pres, acts, w = self._mlp_fwd(lay, emb, E)
+            agg = self._empty(nl, dmid)
+            fwd, _ = lib.conv(lay['sig'])
+            rc = fwd(_p(h), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(agg), dmid, st)
+            if rc:
+                raise _lib.SevennError(f'conv_fwd {lay["sig"]} failed with status {rc}')
+            self.n_launch += len(L.conv.lx.groups)
+            # self interaction 2 accumulates onto the self connection; then the gate
+            self._linear_fwd(lay['si2'], agg, nl, pre, accumulate=True)
+            xo = self._empty(nl, dout)
+            lib.call('sevenn_gate_fwd', _p(pre), dgi, _p(xo), dout, nl, lay['pieces'], len(L.gate.pieces), st)
+            self.n_launch += 1
+            saved.append({'pre': pre, 'h': h, 'w': w if self.keep_w else None, 'pres': pres,
+                          'h_last': acts[-1] if acts else emb})
+            if debug is not None:
+                debug[f'{t}_x'] = xo
+                debug[f'{t}_agg'] = agg
+                debug[f'{t}_h'] = h
+            x, n_x = xo, nl
+        # readout
+        r1 = self._empty(nl, sp.read1.lout.dim)
+        self._linear_fwd(self.read1, x, nl, r1)
+        es = self._empty(nl, 1)
+        self._linear_fwd(self.read2, r1, nl, es)
+        ae, seed = self._empty(nl), self._empty(nl, 1)
+        lib.call('sevenn_rescale', _p(es), _p(g.types), nl, _p(self.scale), _p(self.shift),
+                 int(sp.rescale_species_wise), _p(ae), _p(seed), st)
+        part = self._empty(296 * 8, dtype=torch.float64)
+        etot = self._empty(1, dtype=torch.float64)
+        lib.call('sevenn_colsum_f64', _p(ae), nl, 1, _p(part), _p(etot), st)
+        self.n_launch += 3
+        out = {'energy': etot[0], 'atomic_energy': ae}
+        if not want_forces:
+            return out
+
+        # ---------------- reverse pass: dE/d(edge_vec) --------------------------------------
+        dY, demb = self._zeros(max(E, 1), S), self._zeros(max(E, 1), sp.n_basis)
+        dr1 = self._empty(nl, sp.read1.lout.dim)
+        self._linear_bwd(self.read2, seed, nl, dr1)
+        dx = self._zeros(nl, sp.read1.lin.dim) if self.read1.bwd_needs_zero else self._empty(nl, sp.read1.lin.dim)
+        self._linear_bwd(self.read1, dr1, nl, dx)
+        for t in range(len(self.layers) - 1, -1, -1):
+            lay, sv = self.layers[t], saved[t]
+            L = lay['spec']
+            dx_in, dmid, dgi, dout = L.conv.lx.dim, L.conv.lmid.dim, L.gate.lin.dim, L.gate.lout.dim
+            dpre = self._empty(nl, dgi)
+            lib.call('sevenn_gate_bwd', _p(sv['pre']), dgi, _p(dx), dout, _p(dpre), nl, lay['pieces'],
+                     len(L.gate.pieces), st)
+            self.n_launch += 1
+            dagg = self._zeros(nl, dmid) if lay['si2'].bwd_needs_zero else self._empty(nl, dmid)
+            self._linear_bwd(lay['si2'], dpre, nl, dagg)
+            w = sv['w'] if sv['w'] is not None else self._mlp_last(lay, sv['h_last'], E)
+            dW = self._empty(max(E, 1), L.conv.wn)
+            unused = any(not any(p.gx == gi for p in L.conv.paths) for gi in range(len(L.conv.lx.groups)))
+            dxe = self._zeros(max(E, 1), dx_in) if unused else self._empty(max(E, 1), dx_in)
+            _, bwd = lib.conv(lay['sig'])
+            rc = bwd(_p(sv['h']), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(dagg), dmid,
+                     _p(dW), _p(dxe), dx_in, _p(dY), st)
+            if rc:
+                raise _lib.SevennError(f'conv_bwd {lay["sig"]} failed with status {rc}')
+            self.n_launch += len(L.conv.lx.groups)
+            del w
+            self._mlp_bwd(lay, dW, sv['pres'], demb, E)
+            del dW
+            if t == 0:
+                break                 # layer-0 inputs do not depend on positions
+            dh = self._empty(nn, dx_in)
+            lib.call('sevenn_segment_gather_sum', _p(dxe), dx_in, _p(g.cptr), _p(g.cedge), nn, _p(dh), 0, st)
+            self.n_launch += 1
+            del dxe
+            if nl < nn:
+                halo.backward(t, dh)  # ghost rows -> owners (added into rows [0, n_local))
+            dxn = self._zeros(nl, dx_in) if lay['si1'].bwd_needs_zero else self._empty(nl, dx_in)
+            self._linear_bwd(lay['si1'], dh, nl, dxn)
+            self._linear_bwd(lay['sc'], dpre, nl, dxn, accumulate=True, types=g.types)
+            dx = dxn
+        fvec = self._empty(max(E, 1), 3)
+        lib.call('sevenn_edge_bwd', _p(g.edge_vec), E, *edge_args, _p(dY), _p(demb), _p(fvec), st)
+        F, vir = self._empty(nn, 3), self._empty(nn, 6)
+        lib.call('sevenn_force_virial', _p(fvec), _p(g.edge_vec), _p(g.rowptr), nl, _p(g.cptr), _p(g.cedge), nn,
+                 _p(F), _p(vir), st)
+        v6 = self._empty(6, dtype=torch.float64)
+        lib.call('sevenn_colsum_f64', _p(vir), nn, 6, _p(part), _p(v6), st)
+        self.n_launch += 4
+        out.update({'forces': F, 'virial6': v6, 'f_edge': fvec})
+        return out

@@ -1,0 +1,62 @@
+"""Whole E/F/S pipeline of sevennet_exp_b200.engine (weight packing, layouts, launch order, analytic
+reverse pass) against the oracle, run through the EMULATION build of the kernel sources (g++, no GPU).
+The GPU parity tests (test_gpu_*.py) repeat this through the real CUDA library."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import sevenn_ref as S
+from sevennet_exp_b200 import presets, spec as sp
+from sevennet_exp_b200.engine import Engine
+from tests.emu_util import build_full_emu, graph_from_edges
+from tests.structures import random_cell
+
+KBAR = 1602.1766208
+
+
+def _compare(cfg, sd, numbers, pos, cell, pbc, oracle_model, tol_e=1e-5, tol_f=1e-4, tol_s=1e-3):
+    spec = sp.build_spec(cfg)
+    lib = build_full_emu([L.conv for L in spec.layers])
+    eng = Engine(spec, sd, lib=lib, device='cpu')
+    g = S.atoms_to_graph(numbers, pos, cell, pbc, cfg['cutoff'])
+    ref = oracle_model(dict(g))
+    tmap = cfg['_type_map']
+    types = np.array([tmap[int(z)] for z in numbers])
+    vol = float(g[S.VOL])
+    gr = graph_from_edges(types, g[S.EDGE_IDX].numpy(), g[S.EDGE_VEC].detach().numpy(), len(numbers), vol)
+    out = eng.evaluate(gr)
+    n = len(numbers)
+    dE = abs(out['energy'].item() - ref[S.E_TOT].item()) / n
+    dF = (out['forces'] - ref[S.FORCE].detach()).abs().max().item()
+    stress = -(out['virial6'] / vol).float()
+    dS = (stress - ref[S.STRESS].detach()).abs().max().item() * KBAR
+    assert dE < tol_e, dE
+    assert dF < tol_f, dF
+    assert dS < tol_s * max(1.0, ref[S.STRESS].abs().max().item() * KBAR * 1e-3), dS
+    return dE, dF, dS
+
+
+def test_engine_emu_cp0_hfo2(golden_dir):
+    model, cfg = S.load_checkpoint(os.path.join(golden_dir, 'cp0_model.pt'))
+    model.eval()
+    cp = torch.load(os.path.join(golden_dir, 'cp0_model.pt'))
+    from sevennet_exp_b200.checkpoint import patch_state_dict
+    spec = sp.build_spec(cfg)
+    sd = patch_state_dict(spec, cp['model_state_dict'], cfg.get('version', '0.0.0'))
+    fr = np.load(os.path.join(golden_dir, 'hfo2_frames.npz'))
+    for k in range(2):
+        num, pos, cell, pbc = (fr[f'f{k}_{n}'] for n in ('numbers', 'pos', 'cell', 'pbc'))
+        print(_compare(cfg, sd, num, pos, cell, pbc, model))
+
+
+@pytest.mark.parametrize('name', ['test-so3-l2', 'test-so3-l3'])
+def test_engine_emu_so3_random_weights(name):
+    cfg = dict(presets.PRESETS[name])
+    torch.manual_seed(777)
+    model = S.build_model(cfg).eval()
+    with torch.no_grad():
+        model.edge_embedding.basis_function.coeffs.mul_(1.03)
+    numbers, pos, cell = random_cell(24, list(cfg['_type_map']), density=0.05, seed=3)
+    print(_compare(cfg, model.state_dict(), numbers, pos, cell, [True] * 3, model))
