@@ -1,0 +1,264 @@
+#!/usr/bin/env python
+"""bench.py -- atom-steps/s of one SevenNet-0 energy+forces+stress evaluation (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+N = 1  : BASELINE config 2 -- 4,096-atom synthetic bulk HfO2 cell (fluorite 7x7x7, a = 4.80 A, 20 vacancies,
+         sigma = 0.05 A rattle, ~50 neighbours/atom at rc = 5 A), SevenNet-0 hyper-parameters, random-init
+         weights (torch.manual_seed(777)); a step = neighbour list + forward + analytic reverse pass.
+N > 1  : the same cell replicated over a brick of N sub-domains (weak scaling, 4,096 owned atoms per GPU),
+         LAMMPS-style spatial decomposition with ghost-atom feature exchange per layer (domain.py).
+--impl reference : the CPU restatement oracle (oracle/, kind "port": the reference itself needs e3nn/ase,
+         which are not installable here) on the host cores, bounded sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from sevennet_exp_b200 import presets  # noqa: E402
+from tests.structures import fluorite_hfo2  # noqa: E402
+
+METRIC = 'atom-steps/s (E+F+S) SevenNet-0'
+UNIT = 'atom-steps/s'
+A_LAT = 4.80
+
+
+def workload(reps=(7, 7, 7), n_remove=20):
+    numbers, pos, cell = fluorite_hfo2(reps, a=A_LAT, sigma=0.05, seed=0, n_remove=n_remove)
+    return numbers, pos, cell
+
+
+def model_config():
+    cfg = dict(presets.PRESETS['7net-0'])
+    cfg['version'] = '0.11.0'
+    return cfg
+
+
+def random_state_dict(cfg):
+    """Random-init weights at the real hyper-parameters, keyed like the reference state_dict."""
+    from sevennet_exp_b200.spec import build_spec
+    spec = build_spec(cfg)
+    g = torch.Generator().manual_seed(777)
+    sd = {}
+    for k, shp in spec.expected_keys().items():
+        sd[k] = torch.randn(*shp, generator=g)
+    nb = spec.n_basis
+    sd['edge_embedding.basis_function.coeffs'] = torch.arange(1, nb + 1, dtype=torch.float32) * np.pi / spec.cutoff
+    for L in spec.layers:
+        sd[f'{L.conv.name}.denominator'] = torch.tensor([L.denominator])
+    sd['rescale_atomic_energy.shift'] = torch.randn(spec.n_species, generator=g)
+    sd['rescale_atomic_energy.scale'] = torch.ones(spec.n_species) * 1.7
+    return sd
+
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index=0):
+        super().__init__(daemon=True)
+        self.rows, self.stop_flag, self.index = [], False, index
+
+    def run(self):
+        q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+        while not self.stop_flag:
+            try:
+                o = subprocess.run(['nvidia-smi', f'--query-gpu={q}', '--format=csv,noheader,nounits', '-i',
+                                    str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([t.strip() for t in o.split(',')])
+            except Exception:  # noqa: BLE001
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        if not self.rows:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace('.', '').isdigit())
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k] == 'Active' for r in self.rows)]
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': float(self.rows[0][1]),
+                'reasons': reasons, 'samples': len(self.rows)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        return float(json.load(open(p))['hbm_gbs']), 'measured'
+    return 6650.0, 'fallback'
+
+
+def conv_bwd_algorithmic_bytes(conv, n_dst, n_edges):
+    """each tensor the launch group must touch, once; gathers per edge."""
+    S = (conv.lmax_sh + 1) ** 2
+    per_edge = 4 * (2 * conv.wn + 2 * S + 1 + 2 * conv.lx.dim)      # w, dW, Y, dY, col, x_j gather, dx_e
+    return n_edges * per_edge + n_dst * (4 * conv.lmid.dim + 4)
+
+
+def conv_fwd_algorithmic_bytes(conv, n_dst, n_edges):
+    S = (conv.lmax_sh + 1) ** 2
+    return n_edges * 4 * (conv.wn + S + 1 + conv.lx.dim) + n_dst * (4 * conv.lmid.dim + 4)
+
+
+def cpu_oracle_sample(reps, steps, warmup):
+    """Times the CPU restatement (oracle/) on a bounded HfO2 sample of the same density."""
+    from oracle import sevenn_ref as S
+    cfg = model_config()
+    torch.manual_seed(777)
+    model = S.build_model(cfg).eval()
+    numbers, pos, cell = fluorite_hfo2(reps, a=A_LAT, sigma=0.05, seed=0)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ts = []
+    for k in range(warmup + steps):
+        t0 = time.perf_counter()
+        g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+        out = model(g)
+        float(out[S.E_TOT]); out[S.FORCE].sum().item()
+        if k >= warmup:
+            ts.append(time.perf_counter() - t0)
+    t = float(np.mean(ts))
+    return len(numbers) / t, t, cores, len(numbers), int(g[S.EDGE_IDX].shape[1])
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    v, t, cores, n, e = cpu_oracle_sample((2, 2, 2), args.steps, args.warmup)
+    sample = (f'{n}-atom fluorite HfO2 2x2x2 cell at the workload density ({e / n:.1f} neighbours/atom), full '
+              f'neighbour list + forward + autograd forces/stress per step')
+    line = {'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': UNIT, 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': t * 1e3, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': 'SevenNet-0 E+F+S, bulk HfO2, ~50 neighbours/atom, rc=5A (CPU sample: 96 atoms)'},
+            'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_single(args):
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    dev = torch.device('cuda:0')
+    torch.cuda.set_device(dev)
+    cfg = model_config()
+    sd = random_state_dict(cfg)
+    calc = SevenNetCalculator((cfg, sd), file_type='model_instance', device=dev)
+    numbers, pos, cell = workload()
+    n = len(numbers)
+    pbc = [True] * 3
+    types_dev = torch.from_numpy(calc._lut[numbers].astype(np.int32)).to(dev)
+    pos_dev = torch.from_numpy(pos).to(dev)
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+
+    def step():
+        g = calc.nl.graph(types_dev, None, cell, pbc, calc.cutoff, pos_dev=pos_dev)
+        return g, calc.engine.evaluate(g)
+
+    for _ in range(args.warmup):
+        g, out = step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler()
+    sampler.start()
+    l0 = calc.engine.n_launch + calc.nl.n_launch
+    evs = []
+    torch.cuda.synchronize()
+    for _ in range(args.steps):
+        flush.fill_(1.0)                       # L2 flush, outside the timed events
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        g, out = step()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+    launches = calc.engine.n_launch + calc.nl.n_launch - l0
+    ms_step = total_ms / args.steps
+    value = n / (ms_step * 1e-3)
+
+    # end to end through the public calculator call: host arrays in, host E/F/S out
+    for _ in range(2):
+        calc.compute(numbers, pos, cell, pbc)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.fill_(1.0)
+        res = calc.compute(numbers, pos, cell, pbc)
+    torch.cuda.synchronize()
+    e2e_t = (time.perf_counter() - t0) / args.steps
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    # per-stage device times (separate pass, CUDA events on the launch stream)
+    stage = {}
+    reps_prof = 5
+    for _ in range(reps_prof):
+        flush.fill_(1.0)
+        calc.engine.prof = []
+        calc.engine.evaluate(g)
+        torch.cuda.synchronize()
+        for k, v in calc.engine.profile_summary().items():
+            stage[k] = stage.get(k, 0.0) + v / reps_prof
+    calc.engine.prof = None
+    inner = calc.spec.layers[1].conv
+    key_b, key_f = f'conv_bwd_{inner.signature()}', f'conv_fwd_{inner.signature()}'
+    n_inner = sum(1 for L in calc.spec.layers if L.conv.signature() == inner.signature())
+    peak, how = measured_peak()
+    E = g.n_edges
+    dom_ms = stage[key_b] / n_inner
+    alg = conv_bwd_algorithmic_bytes(inner, n, E)
+    achieved = alg / (dom_ms * 1e-3) / 1e9
+    fwd_ach = conv_fwd_algorithmic_bytes(inner, n, E) / (stage[key_f] / n_inner * 1e-3) / 1e9
+    stage_sorted = dict(sorted(((k, round(v, 4)) for k, v in stage.items()), key=lambda kv: -kv[1]))
+
+    cpu_v, cpu_t, cores, cn, ce = cpu_oracle_sample((3, 3, 3), 1, 0)
+    line = {
+        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': 1, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {'workload': f'SevenNet-0 (lmax2, 5 layers, 128x0e+64x1e+32x2e, rc=5A, random-init weights) E+F+S, '
+                               f'{n}-atom bulk HfO2 (fluorite 7x7x7, a={A_LAT}A, 20 vacancies), {E / n:.1f} neighbours/atom',
+                   'n_atoms': n, 'n_edges': E, 'step': 'device neighbour list + forward + analytic reverse pass',
+                   'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)'},
+        'e2e': {'value': n / e2e_t, 'unit': UNIT, 'ms_per_step': e2e_t * 1e3,
+                'h2d_bytes_per_step': int(pos.nbytes + n * 4), 'd2h_bytes_per_step': int((1 + 6 + 3 * n + n) * 8)},
+        'gpu_launches': int(launches),
+        'clocks': sampler.summary(),
+        'roofline': {'bound': 'hbm', 'kernel': f'conv_bwd (inner layer, {len(inner.lx.groups)} group launches)',
+                     'achieved': achieved, 'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': achieved / peak,
+                     'algorithmic_bytes': alg, 'ms': dom_ms, 'traffic': None,
+                     'conv_fwd_achieved': fwd_ach, 'conv_fwd_frac': fwd_ach / peak},
+        'stage_ms': stage_sorted,
+        'cpu_baseline': {'value': cpu_v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+                         'sample': f'oracle (CPU restatement of the reference path) on a {cn}-atom HfO2 3x3x3 cell, '
+                                   f'{ce / cn:.1f} neighbours/atom, 1 evaluation = {cpu_t:.1f} s'},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl != 'reference' else args.warmup
+    if args.impl == 'reference':
+        return run_reference(args)
+    if args.gpus > 1 or int(os.environ.get('WORLD_SIZE', '1')) > 1:
+        from sevennet_exp_b200 import bench_multi
+        return bench_multi.run(args)
+    run_single(args)
+
+
+if __name__ == '__main__':
+    main()

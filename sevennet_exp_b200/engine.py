@@ -115,8 +115,22 @@ class Engine:
         self.act_radial = ACT_ID[spec.act_radial]
         self.cst_radial = ir.normalize2mom_const(spec.act_radial)
         self.n_launch = 0
+        self.prof = None          # list of (name, cuda event) when profiling is on (bench.py)
 
     # ------------------------------------------------------------------ helpers
+    def _mark(self, name):
+        if self.prof is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.prof.append((name, ev))
+
+    def profile_summary(self):
+        """{stage: milliseconds} summed over the marks recorded since self.prof = [] (after a sync)."""
+        out = {}
+        for (a, ea), (_, eb) in zip(self.prof[:-1], self.prof[1:]):
+            out[a] = out.get(a, 0.0) + ea.elapsed_time(eb)
+        return out
+
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream) if self.dev.type == 'cuda' else None
 
@@ -215,6 +229,7 @@ class Engine:
         ckind = 0 if sp.cutoff_fn == 'poly_cut' else 1
         edge_args = (sp.lmax_sh, int(sp.normalize_sph), sp.n_basis, ckind, sp.cutoff, sp.cutoff_p, sp.cutoff_on,
                      _p(self.coeffs))
+        self._mark('edge_fwd')
         Y, emb = self._empty(max(E, 1), S), self._empty(max(E, 1), sp.n_basis)
         lib.call('sevenn_edge_fwd', _p(g.edge_vec), E, *edge_args, _p(Y), _p(emb), st)
         x = self._empty(nn, self.d0)
@@ -225,23 +240,29 @@ class Engine:
         for t, lay in enumerate(self.layers):
             L = lay['spec']
             dx_in, dmid, dgi, dout = L.conv.lx.dim, L.conv.lmid.dim, L.gate.lin.dim, L.gate.lout.dim
+            self._mark('sc_fwd')
             # self connection (owned atoms)
             pre = self._empty(nl, dgi) if lay['sc'].fwd_full else self._zeros(nl, dgi)
             self._linear_fwd(lay['sc'], x, nl, pre, types=g.types)
+            self._mark('si1_fwd')
             # self interaction 1 -> convolution input for all nodes
             h = self._empty(nn, dx_in) if lay['si1'].fwd_full else self._zeros(nn, dx_in)
             self._linear_fwd(lay['si1'], x, n_x, h)
             if n_x < nn:
                 halo.forward(t, h)    # fills rows [n_local, n_nodes)
+            self._mark('mlp_fwd')
             pres, acts, w = self._mlp_fwd(lay, emb, E)
+            self._mark(f'conv_fwd_{lay["sig"]}')
             agg = self._empty(nl, dmid)
             fwd, _ = lib.conv(lay['sig'])
             rc = fwd(_p(h), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(agg), dmid, st)
             if rc:
                 raise _lib.SevennError(f'conv_fwd {lay["sig"]} failed with status {rc}')
             self.n_launch += len(L.conv.lx.groups)
+            self._mark('si2_fwd')
             # self interaction 2 accumulates onto the self connection; then the gate
             self._linear_fwd(lay['si2'], agg, nl, pre, accumulate=True)
+            self._mark('gate_fwd')
             xo = self._empty(nl, dout)
             lib.call('sevenn_gate_fwd', _p(pre), dgi, _p(xo), dout, nl, lay['pieces'], len(L.gate.pieces), st)
             self.n_launch += 1
@@ -252,6 +273,7 @@ class Engine:
                 debug[f'{t}_agg'] = agg
                 debug[f'{t}_h'] = h
             x, n_x = xo, nl
+        self._mark('readout')
         # readout
         r1 = self._empty(nl, sp.read1.lout.dim)
         self._linear_fwd(self.read1, x, nl, r1)
@@ -266,9 +288,11 @@ class Engine:
         self.n_launch += 3
         out = {'energy': etot[0], 'atomic_energy': ae}
         if not want_forces:
+            self._mark('end')
             return out
 
         # ---------------- reverse pass: dE/d(edge_vec) --------------------------------------
+        self._mark('readout_bwd')
         dY, demb = self._zeros(max(E, 1), S), self._zeros(max(E, 1), sp.n_basis)
         dr1 = self._empty(nl, sp.read1.lout.dim)
         self._linear_bwd(self.read2, seed, nl, dr1)
@@ -278,13 +302,17 @@ class Engine:
             lay, sv = self.layers[t], saved[t]
             L = lay['spec']
             dx_in, dmid, dgi, dout = L.conv.lx.dim, L.conv.lmid.dim, L.gate.lin.dim, L.gate.lout.dim
+            self._mark('gate_bwd')
             dpre = self._empty(nl, dgi)
             lib.call('sevenn_gate_bwd', _p(sv['pre']), dgi, _p(dx), dout, _p(dpre), nl, lay['pieces'],
                      len(L.gate.pieces), st)
             self.n_launch += 1
+            self._mark('si2_bwd')
             dagg = self._zeros(nl, dmid) if lay['si2'].bwd_needs_zero else self._empty(nl, dmid)
             self._linear_bwd(lay['si2'], dpre, nl, dagg)
+            self._mark('mlp_recompute')
             w = sv['w'] if sv['w'] is not None else self._mlp_last(lay, sv['h_last'], E)
+            self._mark(f'conv_bwd_{lay["sig"]}')
             dW = self._empty(max(E, 1), L.conv.wn)
             unused = any(not any(p.gx == gi for p in L.conv.paths) for gi in range(len(L.conv.lx.groups)))
             dxe = self._zeros(max(E, 1), dx_in) if unused else self._empty(max(E, 1), dx_in)
@@ -295,20 +323,24 @@ class Engine:
                 raise _lib.SevennError(f'conv_bwd {lay["sig"]} failed with status {rc}')
             self.n_launch += len(L.conv.lx.groups)
             del w
+            self._mark('mlp_bwd')
             self._mlp_bwd(lay, dW, sv['pres'], demb, E)
             del dW
             if t == 0:
                 break                 # layer-0 inputs do not depend on positions
+            self._mark('dx_reduce')
             dh = self._empty(nn, dx_in)
             lib.call('sevenn_segment_gather_sum', _p(dxe), dx_in, _p(g.cptr), _p(g.cedge), nn, _p(dh), 0, st)
             self.n_launch += 1
             del dxe
             if nl < nn:
                 halo.backward(t, dh)  # ghost rows -> owners (added into rows [0, n_local))
+            self._mark('si1_sc_bwd')
             dxn = self._zeros(nl, dx_in) if lay['si1'].bwd_needs_zero else self._empty(nl, dx_in)
             self._linear_bwd(lay['si1'], dh, nl, dxn)
             self._linear_bwd(lay['sc'], dpre, nl, dxn, accumulate=True, types=g.types)
             dx = dxn
+        self._mark('edge_bwd_force')
         fvec = self._empty(max(E, 1), 3)
         lib.call('sevenn_edge_bwd', _p(g.edge_vec), E, *edge_args, _p(dY), _p(demb), _p(fvec), st)
         F, vir = self._empty(nn, 3), self._empty(nn, 6)
@@ -317,5 +349,6 @@ class Engine:
         v6 = self._empty(6, dtype=torch.float64)
         lib.call('sevenn_colsum_f64', _p(vir), nn, 6, _p(part), _p(v6), st)
         self.n_launch += 4
+        self._mark('end')
         out.update({'forces': F, 'virial6': v6, 'f_edge': fvec})
         return out

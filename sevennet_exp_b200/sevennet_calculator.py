@@ -1,0 +1,121 @@
+"""ASE-style entry point: mirrors sevenn/sevennet_calculator.py:22-202.
+
+``SevenNetCalculator(model, file_type, device, ...)`` keeps the reference's constructor and fills
+``results`` with energy, free_energy, energies, forces, stress (ASE Voigt order, same sign
+convention: ``-inferred_stress[[0,1,2,4,5,3]]``).  The neighbour list, the model and the reverse
+pass all run on the GPU through the C ABI; only E/F/S come back to the host.  ``ase`` itself is
+optional: without it the class still works on any object with ``get_positions/get_cell/get_pbc/
+get_atomic_numbers`` (or through :meth:`compute` with plain arrays)."""
+import os
+from typing import Dict, Optional, Union
+
+import numpy as np
+import torch
+
+from . import presets
+from .checkpoint import load_checkpoint, patch_old_config, patch_state_dict
+from .engine import Engine
+from .neighbor import NeighborList
+from .spec import build_spec
+
+try:  # pragma: no cover - ase is not part of this image
+    from ase.calculators.calculator import Calculator as _AseCalculator, all_changes
+except Exception:  # noqa: BLE001
+    all_changes = ['positions', 'numbers', 'cell', 'pbc']
+
+    class _AseCalculator:  # minimal stand-in with the attributes SevenNetCalculator relies on
+        implemented_properties = []
+
+        def __init__(self, **kwargs):
+            self.results, self.atoms = {}, None
+
+        def calculate(self, atoms=None, properties=None, system_changes=all_changes):
+            self.atoms = atoms
+
+        def get_potential_energy(self, atoms=None):
+            self.calculate(atoms)
+            return self.results['energy']
+
+        def get_forces(self, atoms=None):
+            self.calculate(atoms)
+            return self.results['forces']
+
+        def get_stress(self, atoms=None):
+            self.calculate(atoms)
+            return self.results['stress']
+
+
+class SevenNetCalculator(_AseCalculator):
+    implemented_properties = ['free_energy', 'energy', 'forces', 'stress', 'energies']
+
+    def __init__(self, model: Union[str, tuple] = '7net-0', file_type: str = 'checkpoint',
+                 device: Union[torch.device, str] = 'auto', modal: Optional[str] = None,
+                 enable_cueq: bool = False, sevennet_config: Optional[Dict] = None, **kwargs):
+        super().__init__(**kwargs)
+        if enable_cueq:
+            raise ValueError('enable_cueq: the B200 backend replaces cuEquivariance, not combines with it')
+        if modal is not None:
+            raise NotImplementedError('multi-modal checkpoints are outside this hot path')
+        file_type = file_type.lower()
+        if file_type not in ('checkpoint', 'model_instance', 'torchscript'):
+            raise ValueError('file_type should be checkpoint, model_instance or torchscript')
+        if file_type == 'torchscript':
+            raise NotImplementedError('deployed TorchScript files freeze the e3nn graph; load the checkpoint')
+        if device == 'auto':
+            device = 'cuda'
+        self.device = torch.device(device)
+        if self.device.type != 'cuda':
+            raise RuntimeError('sevennet_exp_b200 runs on CUDA devices only (no CPU fallback)')
+        if file_type == 'checkpoint':
+            if isinstance(model, str) and os.path.isfile(model):
+                spec, sd, cfg = load_checkpoint(model)
+            elif isinstance(model, str) and model in presets.PRESETS:
+                raise FileNotFoundError(
+                    f'pretrained weights of {model} are not shipped here (reference blobs are absent); '
+                    'pass a checkpoint path or file_type="model_instance" with (config, state_dict)')
+            else:
+                raise FileNotFoundError(str(model))
+        else:
+            cfg, sd = model
+            cfg = patch_old_config(cfg)
+            spec = build_spec(cfg)
+            sd = patch_state_dict(spec, sd, cfg.get('version', '0.11.0'))
+        self.sevennet_config = sevennet_config or cfg
+        self.spec, self.cutoff = spec, spec.cutoff
+        self.type_map = spec.type_map
+        self.engine = Engine(spec, sd, device=self.device)
+        self.nl = NeighborList(device=self.device)
+        lut = -np.ones(120, dtype=np.int64)
+        for z, i in self.type_map.items():
+            lut[int(z)] = i
+        self._lut = lut
+
+    # ---- plain-array API (also what bench.py times end to end)
+    def compute(self, numbers, positions, cell, pbc):
+        numbers = np.asarray(numbers)
+        types = self._lut[numbers]
+        if (types < 0).any():
+            bad = sorted({int(z) for z in numbers[types < 0]})
+            raise ValueError(f'Unknown atomic numbers {bad} for this model')   # sevennet_calculator.py:153-161
+        pos = np.ascontiguousarray(np.asarray(positions, dtype=np.float64))
+        types_dev = torch.from_numpy(types.astype(np.int32)).to(self.device, non_blocking=True)
+        g = self.nl.graph(types_dev, pos, cell, pbc, self.cutoff)
+        out = self.engine.evaluate(g)
+        n = len(numbers)
+        host = torch.cat([out['energy'].reshape(1), out['virial6'],
+                          out['forces'][:n].reshape(-1).double(), out['atomic_energy'].double()]).cpu().numpy()
+        energy, vir = float(host[0]), host[1:7]
+        forces = host[7:7 + 3 * n].reshape(n, 3)
+        energies = host[7 + 3 * n:]
+        stress_model = -vir / g.volume                      # (xx,yy,zz,xy,yz,zx), force_output.py:194-222
+        stress = -stress_model[[0, 1, 2, 4, 5, 3]]           # ASE Voigt, sevennet_calculator.py:196-201
+        return {'energy': energy, 'free_energy': energy, 'forces': forces, 'stress': stress,
+                'energies': energies, 'inferred_stress': stress_model, 'n_edges': g.n_edges}
+
+    def calculate(self, atoms=None, properties=None, system_changes=all_changes):
+        super().calculate(atoms, properties, system_changes)
+        if atoms is None:
+            raise ValueError('No atoms to evaluate')
+        res = self.compute(atoms.get_atomic_numbers(), atoms.get_positions(), np.asarray(atoms.get_cell()),
+                           atoms.get_pbc())
+        self.results = {k: res[k] for k in ('free_energy', 'energy', 'energies', 'forces', 'stress')}

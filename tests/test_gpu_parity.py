@@ -1,0 +1,192 @@
+"""GPU parity tests proper: the CUDA library (through the C ABI) against the CPU oracle.
+Tolerances are north_star's: edge set bit-exact; E 1e-5 eV/atom; F 1e-4 eV/A; stress 1e-3 kbar (fp32)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import sevenn_ref as S
+from sevennet_exp_b200 import presets, spec as sp
+from tests.structures import diamond_si, fluorite_hfo2, random_cell
+
+pytestmark = pytest.mark.gpu
+KBAR = 1602.1766208
+
+
+@pytest.fixture(scope='module')
+def lib():
+    from sevennet_exp_b200 import _lib
+    return _lib.load()
+
+
+def _nl_check(pos, cell, pbc, rc):
+    from sevennet_exp_b200.neighbor import NeighborList
+    r = NeighborList().build(pos, cell, pbc, rc)
+    i, j, D, Sh = S.neighbor_list_bruteforce(pos, cell, pbc, rc)
+    assert r['n_edges'] == len(i)
+    assert np.array_equal(r['center'].cpu().numpy(), i)
+    assert np.array_equal(r['col'].cpu().numpy(), j)
+    assert np.array_equal(r['shift'].cpu().numpy(), Sh.astype(np.int64))
+    assert np.array_equal(r['edge_vec'].cpu().numpy(), D.astype(np.float32))
+    cp, ce = r['cptr'].cpu().numpy(), r['cedge'].cpu().numpy()
+    assert np.array_equal(np.sort(ce), np.arange(len(i)))
+    assert np.array_equal(j[ce], np.sort(j, kind='stable'))
+    assert np.array_equal(np.diff(cp), np.bincount(j, minlength=len(pos)))
+    return r
+
+
+def test_nl_bit_exact_edge_sets(lib):
+    num, pos, cell = random_cell(200, [1, 2], density=0.05, seed=1)
+    _nl_check(pos, cell, [True] * 3, 4.0)
+    num, pos, cell = random_cell(30, [1], density=0.04, seed=2)
+    pos = pos + np.array([2.3, -1.7, 0.4]) @ cell
+    _nl_check(pos, cell, [True] * 3, 4.5)
+    c = np.array([[0, 2.815, 2.815], [2.815, 0, 2.815], [2.815, 2.815, 0]])
+    assert _nl_check(np.array([[0, 0, 0], [2.815] * 3]), c, [True] * 3, 4.0)['n_edges'] == 36
+    _nl_check(np.zeros((1, 3)), np.eye(3) * 1.7, [True] * 3, 5.0)
+    num, pos, cell = diamond_si((3, 3, 3))
+    _nl_check(pos, cell, [True] * 3, 5.0)
+    num, pos, cell = random_cell(40, [1], density=0.05, seed=5, triclinic=False)
+    for pbc in ([False] * 3, [True, True, False]):
+        _nl_check(pos, cell, pbc, 4.0)
+    assert _nl_check(np.zeros((1, 3)), np.zeros((3, 3)), [False] * 3, 4.0)['n_edges'] == 0
+
+
+def test_nl_large_property(lib):
+    """4,116-atom HfO2 (cfg2 size): symmetric edge set, every |D| < rc, count equals the O(N^2)-free check."""
+    from sevennet_exp_b200.neighbor import NeighborList
+    num, pos, cell = fluorite_hfo2((7, 7, 7), a=5.0)
+    r = NeighborList().build(pos, cell, [True] * 3, 5.0)
+    i, j = r['center'].cpu().numpy().astype(np.int64), r['col'].cpu().numpy().astype(np.int64)
+    sh, D = r['shift'].cpu().numpy(), r['edge_vec'].cpu().numpy().astype(np.float64)
+    assert (np.linalg.norm(D, axis=1) < 5.0).all()
+    assert np.all(np.diff(i) >= 0)
+    fwd = set(zip(i.tolist(), j.tolist(), map(tuple, sh.tolist())))
+    assert len(fwd) == len(i)
+    assert all((b, a, (-s[0], -s[1], -s[2])) in fwd for a, b, s in list(fwd)[::37])
+    ref = pos[j] + sh @ cell - pos[i]
+    assert np.abs(ref - D).max() < 1e-5
+    # count against a KD-free brute force on a slab of atoms
+    sub = np.arange(0, len(pos), 97)
+    for a in sub:
+        d = pos - pos[a]
+        f = d @ np.linalg.inv(cell)
+        f -= np.round(f)
+        cnt = (np.linalg.norm(f @ cell, axis=1) < 5.0).sum() - 1
+        assert cnt == (i == a).sum()
+
+
+def _engine_vs_oracle(cfg, sd, model, numbers, pos, cell, pbc):
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    calc = SevenNetCalculator((cfg, sd), file_type='model_instance')
+    res = calc.compute(numbers, pos, cell, pbc)
+    g = S.atoms_to_graph(numbers, pos, cell, pbc, cfg['cutoff'])
+    ref = model(dict(g))
+    n = len(numbers)
+    assert res['n_edges'] == g[S.EDGE_IDX].shape[1]
+    dE = abs(res['energy'] - ref[S.E_TOT].item()) / n
+    dF = np.abs(res['forces'] - ref[S.FORCE].detach().numpy()).max()
+    dS = np.abs(res['inferred_stress'] - ref[S.STRESS].detach().numpy()).max() * KBAR
+    dAE = np.abs(res['energies'] - ref[S.AE].detach().numpy().ravel()).max()
+    assert dE < 1e-5, f'energy/atom {dE}'
+    assert dAE < 1e-4, f'atomic energies {dAE}'
+    assert dF < 1e-4, f'forces {dF}'
+    assert dS < 1e-3 * max(1.0, np.abs(ref[S.STRESS].detach().numpy()).max() * KBAR * 1e-3), f'stress {dS} kbar'
+    # ASE Voigt convention of the calculator (sevennet_calculator.py:196-201)
+    assert np.allclose(res['stress'], -res['inferred_stress'][[0, 1, 2, 4, 5, 3]])
+    return dE, dF, dS
+
+
+def test_cp0_checkpoint_hfo2_known_answer(lib, golden_dir):
+    """reference test_train.py:284-316: cp_0.pth on hfo2.extxyz -> Energy/Force/Stress RMSE goldens, on the GPU."""
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cp = torch.load(os.path.join(golden_dir, 'cp0_model.pt'))
+    calc = SevenNetCalculator((cp['config'], cp['model_state_dict']), file_type='model_instance')
+    fr = np.load(os.path.join(golden_dir, 'hfo2_frames.npz'))
+    dE, dF, dS = [], [], []
+    for k in range(2):
+        num, pos, cell, pbc = (fr[f'f{k}_{n}'] for n in ('numbers', 'pos', 'cell', 'pbc'))
+        res = calc.compute(num, pos, cell, pbc)
+        s = fr[f'f{k}_stress3x3']
+        voigt = np.array([s[0, 0], s[1, 1], s[2, 2], s[1, 2], s[0, 2], s[0, 1]])
+        dE.append((res['energy'] - float(fr[f'f{k}_energy'])) / len(num))
+        dF.append(res['forces'] - fr[f'f{k}_forces'])
+        dS.append(res['inferred_stress'] - (-voigt[[0, 1, 2, 5, 3, 4]]))
+    dF = np.concatenate(dF)
+    assert abs(np.sqrt(np.mean(np.square(dE))) - 28.977758) < 2e-5
+    assert abs(np.sqrt(np.mean((dF ** 2).sum(1))) - 0.214107) < 1e-5
+    assert abs(np.sqrt(np.mean((np.array(dS) ** 2).sum(1))) * KBAR - 190.014237) < 1e-3
+
+
+def test_cp0_vs_oracle(lib, golden_dir):
+    model, cfg = S.load_checkpoint(os.path.join(golden_dir, 'cp0_model.pt'))
+    cp = torch.load(os.path.join(golden_dir, 'cp0_model.pt'))
+    fr = np.load(os.path.join(golden_dir, 'hfo2_frames.npz'))
+    num, pos, cell, pbc = (fr[f'f0_{n}'] for n in ('numbers', 'pos', 'cell', 'pbc'))
+    print(_engine_vs_oracle(cp['config'], cp['model_state_dict'], model.eval(), num, pos, cell, pbc))
+
+
+def _random_model(name, seed=777):
+    cfg = dict(presets.PRESETS[name])
+    cfg['version'] = '0.11.0'
+    cfg['scale'] = [40.0] * cfg['_number_of_species']      # forces of O(0.1-1 eV/A) with random weights
+    torch.manual_seed(seed)
+    model = S.build_model(cfg).eval()
+    with torch.no_grad():
+        model.edge_embedding.basis_function.coeffs.mul_(1.03)
+    return cfg, model
+
+
+@pytest.mark.parametrize('name', ['test-so3-l2', 'test-so3-l3'])
+def test_small_so3_models(lib, name):
+    cfg, model = _random_model(name)
+    numbers, pos, cell = random_cell(48, list(cfg['_type_map']), density=0.05, seed=3)
+    print(_engine_vs_oracle(cfg, model.state_dict(), model, numbers, pos, cell, [True] * 3))
+
+
+def test_sevennet0_shape_si64(lib):
+    """BASELINE config 1: SevenNet-0 hyper-parameters (random weights), 64-atom bulk Si."""
+    cfg, model = _random_model('7net-0')
+    numbers, pos, cell = diamond_si((2, 2, 2))
+    print(_engine_vs_oracle(cfg, model.state_dict(), model, numbers, pos, cell, [True] * 3))
+
+
+def test_l3i5_shape_small(lib):
+    """SevenNet-l3i5 hyper-parameters (lmax 3, random weights) on a 40-atom Li-P-S-like cell."""
+    cfg, model = _random_model('7net-l3i5')
+    numbers, pos, cell = random_cell(40, [3, 15, 16], density=0.048, seed=1, rmin=1.9)
+    print(_engine_vs_oracle(cfg, model.state_dict(), model, numbers, pos, cell, [True] * 3))
+
+
+def test_bitwise_reproducible_and_edge_cases(lib):
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cfg, model = _random_model('test-so3-l2')
+    calc = SevenNetCalculator((cfg, model.state_dict()), file_type='model_instance')
+    numbers, pos, cell = random_cell(64, list(cfg['_type_map']), density=0.05, seed=4)
+    a = calc.compute(numbers, pos, cell, [True] * 3)
+    b = calc.compute(numbers, pos, cell, [True] * 3)
+    assert a['energy'] == b['energy'] and np.array_equal(a['forces'], b['forces'])   # no atomics on the path
+    assert np.abs(a['forces'].sum(0)).max() < 1e-3
+    # isolated atom: no edges -> energy is the species shift, zero force
+    one = calc.compute(numbers[:1], np.zeros((1, 3)), np.eye(3) * 30.0, [True] * 3)
+    assert one['n_edges'] == 0 and np.all(one['forces'] == 0)
+    ref = model(S.atoms_to_graph(numbers[:1], np.zeros((1, 3)), np.eye(3) * 30.0, [True] * 3, 5.0))
+    assert abs(one['energy'] - ref[S.AE].sum().item()) < 1e-5
+    with pytest.raises(ValueError):
+        calc.compute(np.array([99]), np.zeros((1, 3)), np.eye(3) * 30.0, [True] * 3)
+
+
+def test_gemm_against_torch(lib):
+    import ctypes
+    from sevennet_exp_b200 import _lib as L
+    torch.manual_seed(0)
+    for (n, R, K, N) in [(1000, 1, 8, 64), (777, 3, 64, 96), (513, 5, 352, 32), (4096, 1, 64, 960)]:
+        ldn = R * K + 7
+        A = torch.randn(n, ldn, device='cuda')
+        B = torch.randn(K, N, device='cuda')
+        C = torch.zeros(n, R * N, device='cuda')
+        g = L.GemmArgs(A.data_ptr(), ldn, K, B.data_ptr(), N, C.data_ptr(), R * N, N, n * R, R, N, K, 0, 0, 1.0, None, None)
+        lib.call('sevenn_gemm_f32', ctypes.byref(g), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+        ref = torch.einsum('nrk,kc->nrc', A[:, :R * K].reshape(n, R, K).double(), B.double()).reshape(n, R * N)
+        assert (C.double() - ref).abs().max() < 1e-4 * max(1.0, ref.abs().max().item())
