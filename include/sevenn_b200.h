@@ -66,6 +66,11 @@ typedef struct {
   float* C2; const float* P;                 /* aux out / aux in, strides of C */
 } sevenn_gemm_args;
 int sevenn_gemm_f32(const sevenn_gemm_args* args /* host */, void* stream);   /* exact fp32 (SIMT) */
+/* tcgen05/TMEM 3xTF32 arm (fp32-accurate).  B is passed as the pre-swizzled (hi, lo) K-major image
+ * [n_tiles][KB][2][Nt][32] whose geometry sevenn_gemm_tc_plan returns; args->B is ignored.
+ * Needs K % 4 == 0 and 16-byte aligned A rows; returns SEVENN_ERR_BAD_ARG otherwise. */
+int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, long long* img_floats);
+int sevenn_gemm_tc(const sevenn_gemm_args* args /* host */, const float* Bimg, void* stream);
 
 /* species-indexed linear = FullyConnectedTensorProduct(x, one_hot): sevenn/nn/self_connection.py:10-64 */
 int sevenn_linear_by_type(const float* A, long long sAn, int sAm, const float* W /* S,K,N */, const int* types,

@@ -37,6 +37,9 @@ SIGNATURES = {
     'sevenn_edge_fwd': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_p], c_i),
     'sevenn_edge_bwd': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_p, c_p], c_i),
     'sevenn_gemm_f32': ([ctypes.POINTER(GemmArgs), c_p], c_i),
+    'sevenn_gemm_tc_plan': ([c_i, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_i), ctypes.POINTER(c_i),
+                             ctypes.POINTER(c_ll)], c_i),
+    'sevenn_gemm_tc': ([ctypes.POINTER(GemmArgs), c_p, c_p], c_i),
     'sevenn_linear_by_type': ([c_p, c_ll, c_i, c_p, c_p, c_p, c_ll, c_i, c_ll, c_i, c_i, c_i, c_i, c_p], c_i),
     'sevenn_embed': ([c_p, c_ll, c_i, c_p, c_p, c_p], c_i),
     'sevenn_gate_fwd': ([c_p, c_i, c_p, c_i, c_ll, ctypes.POINTER(GatePiece), c_i, c_p], c_i),

@@ -17,7 +17,7 @@ LIB = os.path.join(LIBDIR, 'libsevenn_b200.so')
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '-Xcompiler', '-fPIC', '--use_fast_math=false']
 NVCC_FLAGS = [f for f in NVCC_FLAGS if f != '--use_fast_math=false']
-STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu']
+STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu']
 
 
 def nvcc():

@@ -1,0 +1,493 @@
+// tcgen05 / TMEM GEMM in 3xTF32 (fp32-accurate) with the same argument contract as gemm_simt.cu.
+//
+//   C[(n,m), :N] = epi( A[(n,m), :K] @ B[K, N] )        A, C fp32 with (node, m)-strided rows
+//
+// Replaces the cuBLAS calls behind e3nn's FullyConnectedNet (radial MLP, sevenn/nn/convolution.py:92-101,121)
+// and o3.Linear (sevenn/nn/linear.py:49-63,94) and their input-gradients.  Precision: every fp32 operand is
+// split x = hi + lo with hi = tf32(x); D += A_hi.B_hi + A_lo.B_hi + A_hi.B_lo accumulates in fp32 in TMEM,
+// which keeps ~2^-21 relative error per product (north_star tolerances are fp32 ones).
+//
+// Structure (persistent CTAs, grid = (SMs / n_tiles, n_tiles), 416 threads, one CTA per SM):
+//   warps 0-7  producers : A rows global -> smem by cp.async (ring, stages-1 k-blocks in flight per thread),
+//                          then an in-place (hi, lo) split into SWIZZLE_128B K-major tiles.
+//                          B arrives as a pre-swizzled (hi, lo) image through TMA bulk copies (cp.async.bulk):
+//                          "resident" mode = the whole [K, Nt] image once per CTA (radial-MLP forward, K = 64),
+//                          "streaming" mode = one k-block image per stage (large K).
+//   warp  12   MMA issuer: 4 k-steps x 3 tcgen05.mma.kind::tf32 (M=128, N=Nt<=256, K=8) per 32-wide k-block,
+//                          tcgen05.commit frees the stage / publishes the accumulator
+//   warps 8-11 epilogue  : tcgen05.ld 32 columns at a time -> swizzled smem transpose -> full-line coalesced
+//                          16 B accesses with the fused epilogue (store / accumulate / act / act-gradient)
+//   TMEM: 2 x 256 fp32 columns, double buffered so the epilogue of tile i overlaps loads+MMA of tile i+1.
+#include "sevenn_common.cuh"
+#include "../../include/sevenn_b200.h"
+
+#ifndef SEVENN_EMU
+#include <cuda.h>
+#include <cstdlib>
+#include <cstdio>
+
+#define TC_BM 128
+#define TC_BK 32                      // fp32 per k-block = one 128 B swizzle row
+#define TC_PRODUCERS 256
+#define TC_THREADS 416
+#define TC_MMA_WARP 12
+#define TC_EPI_WARP0 8
+#define TC_EPI_BYTES (4 * 32 * 128)  // per-warp 32 rows x 128 B transpose buffers
+
+struct TcParams {
+  sevenn_gemm_args g;
+  const float* Bimg;    // [n_tiles][KB][2][Nt][32] pre-swizzled hi/lo images
+  int Nt, n_tiles, KB, stages, vec4, mode, resident, dslack;
+  long long m_tiles;
+  long long* dbg;       // optional clock64 trace of CTA (0,0) (SEVENN_TC_DBG=1)
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {   // no arrival: only raises tx-count
+  asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_LOOP:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE;\n\t"
+      "bra WAIT_LOOP;\n\t"
+      "DONE:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+  // K-major, SWIZZLE_128B, 8-row groups 1024 B apart (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp)
+  return (uint64_t)((saddr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// row r = n*R + m -> n*sn + m*sm ; 32-bit division (rows < 2^31), none at all for edge matrices (R == 1)
+__device__ __forceinline__ long long row_offset(long long r, int R, long long sn, int sm) {
+  if (R == 1) return r * sn;
+  const unsigned n = (unsigned)r / (unsigned)R, m = (unsigned)r - n * (unsigned)R;
+  return (long long)n * sn + (long long)m * sm;
+}
+__device__ __forceinline__ float4 lds128(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, float4 v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// the tcgen05 arm fuses SiLU only (act_radial default, sevenn/_const.py:102); other activations use the SIMT arm
+__device__ __forceinline__ float silu_f(float x) { return x / (1.f + expf(-x)); }
+__device__ __forceinline__ float dsilu_f(float x) { const float s = 1.f / (1.f + expf(-x)); return s * (1.f + x * (1.f - s)); }
+__device__ __forceinline__ float tc_act_unused(int id, float x) {
+  switch (id) {
+    case 0: return x / (1.f + expf(-x));
+    case 1: return tanhf(x);
+    case 2: return fabsf(x);
+    case 3: return x > 0.f ? x : 0.f;
+    case 4: return 1.f / (1.f + expf(-x));
+    default: return (x > 20.f ? x : log1pf(expf(x))) - 0.6931471805599453f;
+  }
+}
+__device__ __forceinline__ float tc_dact_unused(int id, float x) {
+  switch (id) {
+    case 0: { const float s = 1.f / (1.f + expf(-x)); return s * (1.f + x * (1.f - s)); }
+    case 1: { const float t = tanhf(x); return 1.f - t * t; }
+    case 2: return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f);
+    case 3: return x > 0.f ? 1.f : 0.f;
+    case 4: { const float s = 1.f / (1.f + expf(-x)); return s * (1.f - s); }
+    default: return 1.f / (1.f + expf(-x));
+  }
+}
+
+#define DBG(role, it, ev) do { if (P.dbg && blockIdx.x == 0 && blockIdx.y == 0 && (it) < 6 && (threadIdx.x & 31) == 0) \
+  P.dbg[((role) * 6 + (it)) * 8 + (ev)] = clock64(); } while (0)
+
+template <int EPI>
+__global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcParams P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const sevenn_gemm_args& g = P.g;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t a_bytes = TC_BM * 128, b_bytes = (uint32_t)P.Nt * 128;
+  // stage = A_hi | A_lo | (streaming: B_hi | B_lo)
+  const uint32_t stage_bytes = 2 * a_bytes + (P.resident ? 0u : 2 * b_bytes);
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* bres = smem + (size_t)P.stages * stage_bytes;                     // resident B image [KB][2][Nt][32]
+  uint8_t* epi_buf = bres + (P.resident ? (size_t)P.KB * 2 * b_bytes : 0);
+  uint64_t* bars = (uint64_t*)(epi_buf + TC_EPI_BYTES);
+  // bars: full[stages], empty[stages], tmem_full[2], tmem_empty[2], b_full; then the TMEM base address
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (P.stages + s); };
+  auto tfull_bar = [&](int b) { return bar0 + 8u * (2 * P.stages + b); };
+  auto tempty_bar = [&](int b) { return bar0 + 8u * (2 * P.stages + 2 + b); };
+  const uint32_t bfull_bar = bar0 + 8u * (2 * P.stages + 4);
+  uint32_t* tmem_slot = (uint32_t*)(bars + 2 * P.stages + 5);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < P.stages; ++s) { mbar_init(full_bar(s), TC_PRODUCERS); mbar_init(empty_bar(s), 1); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 128); }
+    mbar_init(bfull_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == TC_MMA_WARP) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  // this CTA owns column tile nt and the row tiles mt = blockIdx.x, blockIdx.x + gridDim.x, ...
+  const int nt = blockIdx.y;
+  const long long my_items = (P.m_tiles > blockIdx.x) ? (P.m_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const float* bimg_nt = P.Bimg + (size_t)nt * P.KB * (size_t)(2 * P.Nt * 32);
+
+  if (warp < TC_PRODUCERS / 32) {
+    // ================= producers: cp.async (LDGSTS) ring, depth stages-1, in-place hi/lo split ==========
+    const int tid = threadIdx.x;
+    const int c = tid & 7;                  // 16 B chunk inside the 128 B k-block row
+    const long long total_q = my_items * P.KB;
+    // k-blocks in flight per thread; one slot of slack so that the slot being refilled was released by a
+    // tcgen05.commit issued a full iteration earlier (its round trip is off the critical path)
+    int D = P.stages > 2 ? P.stages - 2 : 1;
+    if (P.dslack == 0) D = P.stages - 1;
+    if (D > 4) D = 4;
+    if (P.resident && tid == 0 && my_items > 0) {
+      const uint32_t bytes = (uint32_t)P.KB * 2 * b_bytes;
+      mbar_expect_tx(bfull_bar, bytes);
+      bulk_g2s(smem_u32(bres), bimg_nt, bytes, bfull_bar);
+      mbar_arrive(bfull_bar);
+    }
+    long long q_i = 0, it_i = 0; int kb_i = 0;
+    const float* rowp[4];
+    auto set_rows = [&](long long it) {
+      const long long mt = blockIdx.x + it * gridDim.x;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const long long r = mt * TC_BM + i * 32 + (tid >> 3);
+        rowp[i] = (r < g.M) ? g.A + row_offset(r, g.R, g.sAn, g.sAm) : nullptr;
+      }
+    };
+    if (total_q > 0) set_rows(0);
+    auto issue = [&]() {
+      if (q_i < total_q) {
+        const int slot = (int)(q_i % P.stages);
+        const uint32_t ph = (uint32_t)((q_i / P.stages) & 1);
+        mbar_wait(empty_bar(slot), ph ^ 1);
+        uint8_t* sbase = smem + (size_t)slot * stage_bytes;
+        if (!P.resident && tid == 0) {
+          mbar_expect_tx(full_bar(slot), 2 * b_bytes);
+          bulk_g2s(smem_u32(sbase + 2 * a_bytes), bimg_nt + (size_t)kb_i * (size_t)(2 * P.Nt * 32), 2 * b_bytes,
+                   full_bar(slot));
+        }
+        const int k = kb_i * TC_BK + c * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int row = i * 32 + (tid >> 3);
+          const uint32_t dst = smem_u32(sbase) + row * 128 + ((c ^ (row & 7)) << 4);
+          const bool ok = rowp[i] != nullptr && k < g.K;
+          const float* src = ok ? rowp[i] + k : g.A;
+          const uint32_t nbytes = ok ? 16u : 0u;        // src-size 0 -> zero fill
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
+        }
+        ++q_i;
+        if (++kb_i == P.KB) { kb_i = 0; ++it_i; if (q_i < total_q) set_rows(it_i); }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    for (int d = 0; d < D; ++d) issue();
+    for (long long q = 0; q < total_q; ++q) {
+      // groups q .. q+D-1 are outstanding: allow the newest D-1 to stay in flight -> k-block q has landed
+      if (D == 1) asm volatile("cp.async.wait_group 0;" ::: "memory");
+      else if (D == 2) asm volatile("cp.async.wait_group 1;" ::: "memory");
+      else if (D == 3) asm volatile("cp.async.wait_group 2;" ::: "memory");
+      else asm volatile("cp.async.wait_group 3;" ::: "memory");
+      if (warp == 0) DBG(0, q, 1);
+      const int slot = (int)(q % P.stages);
+      uint8_t* sbase = smem + (size_t)slot * stage_bytes;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = i * 32 + (tid >> 3);
+        const uint32_t off = row * 128 + ((c ^ (row & 7)) << 4);
+        const uint32_t sa = smem_u32(sbase) + off;
+        const float4 v = lds128(sa);
+        float4 hi, lo;
+        hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); lo.x = v.x - hi.x;
+        hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
+        hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
+        hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
+        sts128(sa, hi);
+        sts128(sa + a_bytes, lo);
+      }
+      if (!(P.mode & 8)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> UMMA (async proxy)
+      mbar_arrive(full_bar(slot));                                  // 128 arrivals (+ B bytes) complete the phase
+      if (warp == 0) DBG(0, q, 2);
+      issue();                                                      // refill: k-block q + D (blocks only on MMA back-pressure)
+      if (warp == 0) DBG(0, q, 0);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  } else if (warp == TC_MMA_WARP) {
+    // ================= MMA issuer =================
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(P.Nt >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    int stage = 0; uint32_t phase = 0;
+    if (P.resident && my_items > 0) mbar_wait(bfull_bar, 0);
+    for (long long it = 0; it < my_items; ++it) {
+      const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
+      DBG(1, it, 0);
+      mbar_wait(tempty_bar(ab), aphase ^ 1);
+      DBG(1, it, 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t d_tmem = tmem_base + (uint32_t)ab * 256;
+      for (int kb = 0; kb < P.KB; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        if (kb == 0) DBG(1, it, 2);
+        if (kb == P.KB - 1) DBG(1, it, 3);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (lane == 0) {
+          const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint32_t sb = P.resident ? smem_u32(bres) + (uint32_t)kb * 2 * b_bytes : sa + 2 * a_bytes;
+          const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + a_bytes);
+          const uint64_t b_hi = make_desc(sb), b_lo = make_desc(sb + b_bytes);
+#pragma unroll
+          for (int j = 0; j < TC_BK / 8; ++j) {
+            const uint64_t adv = (uint64_t)(j * 2);     // 32 B per k-step, in 16 B units
+            if (P.mode & 4) {
+            } else if (!(P.mode & 1)) {
+              umma_tf32(d_tmem, a_lo + adv, b_hi + adv, idesc, (kb | j) != 0);
+              umma_tf32(d_tmem, a_hi + adv, b_lo + adv, idesc, 1);
+              umma_tf32(d_tmem, a_hi + adv, b_hi + adv, idesc, 1);
+            } else {
+              umma_tf32(d_tmem, a_hi + adv, b_hi + adv, idesc, (kb | j) != 0);   // diagnostic: plain TF32
+            }
+          }
+          umma_commit(empty_bar(stage));
+          if (kb == P.KB - 1) umma_commit(tfull_bar(ab));
+        }
+        __syncwarp();
+        if (kb == P.KB - 1) DBG(1, it, 4);
+        if (++stage == P.stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else {
+    // ================= epilogue (warps 4..7 -> TMEM lanes 32*(warp-4) ..) =================
+    const int ew = warp - TC_EPI_WARP0;
+    uint8_t* tb = epi_buf + ew * (32 * 128);             // this warp's 32 rows x 128 B transpose buffer
+    const int n0 = nt * P.Nt;
+    const int ncols = min(P.Nt, g.N - n0);
+    const int sub = lane >> 3, ch = lane & 7;            // read phase: row 4*i + sub, 16 B chunk ch
+    for (long long it = 0; it < my_items; ++it) {
+      const long long mt = blockIdx.x + it * gridDim.x;
+      const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
+      long long roff[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const long long r = mt * TC_BM + ew * 32 + 4 * i + sub;
+        roff[i] = (r < g.M) ? row_offset(r, g.R, g.sCn, g.sCm) : -1;
+      }
+      if (ew == 0) DBG(2, it, 0);
+      mbar_wait(tfull_bar(ab), aphase);
+      if (ew == 0) DBG(2, it, 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      for (int cc = 0; cc < ncols; cc += 32) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(ab * 256 + cc);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr) : "memory");
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (ew == 0 && cc == 0) DBG(2, it, 2);
+        if (P.mode & 2) continue;
+        // transpose through smem: thread = row writes 8 chunks, XOR-swizzled (conflict free both ways)
+        const uint32_t tbs = smem_u32(tb);
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          sts128(tbs + lane * 128 + ((q ^ (lane & 7)) << 4),
+                 make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                             __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])));
+        __syncwarp();
+        const int col = cc + ch * 4;                     // first of this lane's 4 columns (tile-relative)
+        const int nvalid = ncols - col;                  // >= 4 -> whole float4 valid
+        float4 x[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int row = 4 * i + sub;
+          x[i] = lds128(tbs + row * 128 + ((ch ^ (row & 7)) << 4));
+        }
+        if (P.vec4 && nvalid >= 4) {
+          float4 aux[8];
+          if (EPI == 1 || EPI == 3) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              if (roff[i] >= 0)
+                aux[i] = *reinterpret_cast<const float4*>((EPI == 1 ? g.C : g.P) + roff[i] + n0 + col);
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (roff[i] < 0) continue;
+            float4* c4 = reinterpret_cast<float4*>(g.C + roff[i] + n0 + col);
+            const float4 xv = x[i];
+            if (EPI == 0) {
+              *c4 = xv;
+            } else if (EPI == 1) {
+              *c4 = make_float4(aux[i].x + xv.x, aux[i].y + xv.y, aux[i].z + xv.z, aux[i].w + xv.w);
+            } else if (EPI == 2) {
+              *c4 = xv;
+              *reinterpret_cast<float4*>(g.C2 + roff[i] + n0 + col) =
+                  make_float4(g.cst * silu_f(xv.x), g.cst * silu_f(xv.y), g.cst * silu_f(xv.z), g.cst * silu_f(xv.w));
+            } else {
+              *c4 = make_float4(xv.x * g.cst * dsilu_f(aux[i].x), xv.y * g.cst * dsilu_f(aux[i].y),
+                                xv.z * g.cst * dsilu_f(aux[i].z), xv.w * g.cst * dsilu_f(aux[i].w));
+            }
+          }
+        } else if (nvalid > 0) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (roff[i] < 0) continue;
+            const float xs[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (e >= nvalid) break;
+              float* cp = g.C + roff[i] + n0 + col + e;
+              if (EPI == 0) *cp = xs[e];
+              else if (EPI == 1) *cp += xs[e];
+              else if (EPI == 2) { *cp = xs[e]; g.C2[roff[i] + n0 + col + e] = g.cst * silu_f(xs[e]); }
+              else *cp = xs[e] * g.cst * dsilu_f(g.P[roff[i] + n0 + col + e]);
+            }
+          }
+        }
+        __syncwarp();
+      }
+      if (ew == 0) DBG(2, it, 3);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      mbar_arrive(tempty_bar(ab));
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == TC_MMA_WARP) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
+// geometry shared by the host-side image builder (engine.tc_weight_image) and the kernel
+static int tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, int* resident) {
+  if (N <= 0 || K <= 0) return SEVENN_ERR_BAD_ARG;
+  const int kb = (K + TC_BK - 1) / TC_BK;
+  int res = 0, nt = 0, tiles = 0;
+  for (int t = (N + 255) / 256;; ++t) {
+    nt = (((N + t - 1) / t) + 15) / 16 * 16;
+    if ((long long)kb * nt * 256 <= 84 * 1024) { res = 1; tiles = t; break; }
+    if (nt <= 64) break;
+  }
+  if (!res) { tiles = (N + 255) / 256; nt = (((N + tiles - 1) / tiles) + 15) / 16 * 16; }
+  *Nt = nt; *n_tiles = tiles; *KB = kb; *resident = res;
+  return 0;
+}
+
+extern "C" int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, long long* img_floats) {
+  int res;
+  int rc = tc_plan(N, K, Nt, n_tiles, KB, &res);
+  if (rc) return rc;
+  *img_floats = (long long)(*n_tiles) * (*KB) * 2 * (*Nt) * 32;
+  return 0;
+}
+
+extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, void* stream) {
+  TcParams P;
+  P.g = *args;
+  const sevenn_gemm_args& g = P.g;
+  if (g.M <= 0 || g.N <= 0) return 0;
+  if (g.K <= 0 || g.R <= 0 || g.epi < 0 || g.epi > 3 || (g.K & 3) || (g.sAn & 3) || (g.sAm & 3) ||
+      ((uintptr_t)g.A & 15) || (g.epi >= 2 && g.act != 0))
+    return SEVENN_ERR_BAD_ARG;
+  tc_plan(g.N, g.K, &P.Nt, &P.n_tiles, &P.KB, &P.resident);
+  P.Bimg = Bimg;
+  P.m_tiles = (g.M + TC_BM - 1) / TC_BM;
+  const size_t b_bytes = (size_t)P.Nt * 128;
+  const size_t budget = 227 * 1024 - 1024 - TC_EPI_BYTES - 256;
+  const size_t stage_bytes = 2 * TC_BM * 128 + (P.resident ? 0 : 2 * b_bytes);
+  const size_t fixed = P.resident ? (size_t)P.KB * 2 * b_bytes : 0;
+  int stages = (int)((budget - fixed) / stage_bytes);
+  if (stages > 6) stages = 6;
+  if (stages < 2) return SEVENN_ERR_BAD_ARG;
+  P.stages = stages;
+  { const char* e = getenv("SEVENN_TC_MMA_MODE"); P.mode = e ? atoi(e) : 0; }
+  { const char* e = getenv("SEVENN_TC_DSLACK"); P.dslack = e ? atoi(e) : 1; }
+  P.vec4 = !((g.sCn & 3) || (g.sCm & 3) || ((uintptr_t)g.C & 15) || (g.C2 && ((uintptr_t)g.C2 & 15)) ||
+             (g.P && ((uintptr_t)g.P & 15)));
+  const size_t smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * stages + 5) + 16;
+  void (*kern)(const TcParams) = g.epi == 0 ? gemm_tc_kernel<0> : g.epi == 1 ? gemm_tc_kernel<1>
+                               : g.epi == 2 ? gemm_tc_kernel<2> : gemm_tc_kernel<3>;
+  static bool attr_set[4] = {false, false, false, false};
+  if (!attr_set[g.epi]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return (int)e;
+    attr_set[g.epi] = true;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long gx = sms / P.n_tiles;
+  if (gx < 1) gx = 1;
+  if (gx > P.m_tiles) gx = P.m_tiles;
+  dim3 grid((unsigned)gx, (unsigned)P.n_tiles);
+  static long long* dbg_dev = nullptr;
+  const bool dbg = getenv("SEVENN_TC_DBG") != nullptr;
+  if (dbg && !dbg_dev) cudaMalloc(&dbg_dev, 3 * 6 * 8 * sizeof(long long));
+  if (dbg) cudaMemset(dbg_dev, 0, 3 * 6 * 8 * sizeof(long long));
+  P.dbg = dbg ? dbg_dev : nullptr;
+  kern<<<grid, TC_THREADS, smem, (cudaStream_t)stream>>>(P);
+  if (dbg) {
+    long long h[3 * 6 * 8];
+    cudaDeviceSynchronize();
+    cudaMemcpy(h, dbg_dev, sizeof(h), cudaMemcpyDeviceToHost);
+    long long t0 = h[0];
+    for (int k = 0; k < 3 * 6 * 8; ++k) if (h[k] && h[k] < t0) t0 = h[k];
+    fprintf(stderr, "TCDBG M=%lld N=%d K=%d stages=%d resident=%d KB=%d\n", g.M, g.N, g.K, stages, P.resident, P.KB);
+    const char* names[3] = {"prod(q)", "mma(it)", "epi(it)"};
+    for (int r = 0; r < 3; ++r) for (int it = 0; it < 6; ++it) {
+      fprintf(stderr, "  %s %d:", names[r], it);
+      for (int e = 0; e < 5; ++e) fprintf(stderr, " %8lld", h[(r * 6 + it) * 8 + e] ? h[(r * 6 + it) * 8 + e] - t0 : -1);
+      fprintf(stderr, "\n");
+    }
+  }
+  return (int)cudaGetLastError();
+}
+#endif
+
+#ifdef SEVENN_EMU
+// the emulation build has no tensor cores: same plan geometry, GEMM through the fp32 loops (tests only)
+extern "C" int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, long long* img_floats) {
+  if (N <= 0 || K <= 0) return SEVENN_ERR_BAD_ARG;
+  *Nt = 16; *n_tiles = (N + 15) / 16; *KB = (K + 31) / 32;
+  *img_floats = (long long)(*n_tiles) * (*KB) * 2 * 16 * 32;
+  return 0;
+}
+extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, void* stream) {
+  (void)Bimg; return sevenn_gemm_f32(args, stream);
+}
+#endif

@@ -11,6 +11,7 @@ convolution input before each layer >= 1 and returns ghost gradients to their ow
 """
 import ctypes
 import math
+import os
 from typing import Dict, Optional
 
 import numpy as np
@@ -33,6 +34,37 @@ class Graph:
 
 def _p(t):
     return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def tc_weight_image(W: np.ndarray, Nt: int, n_tiles: int, KB: int) -> np.ndarray:
+    """[K, N] fp32 -> flat image [n_tiles][KB][2 (hi, lo)][Nt][32] laid out exactly as the UMMA K-major
+    SWIZZLE_128B shared-memory tile (16-byte chunk index XOR row%8), so bulk copies fill the stages.
+    (Nt, n_tiles, KB) come from sevenn_gemm_tc_plan so host and kernel agree on the geometry."""
+    K, N = W.shape
+    Wp = np.zeros((KB * 32, n_tiles * Nt), dtype=np.float32)
+    Wp[:K, :N] = W
+    hi = (Wp.view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32)
+    lo = (Wp - hi).astype(np.float32)
+    lo = (lo.view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32)
+    img = np.zeros((n_tiles, KB, 2, Nt, 32), dtype=np.float32)
+    n_idx = np.arange(Nt)[:, None]
+    k_idx = np.arange(32)[None, :]
+    phys = (((k_idx // 4) ^ (n_idx % 8)) * 4 + k_idx % 4)          # [Nt, 32] physical column of (n, k)
+    for t in range(n_tiles):
+        for kb in range(KB):
+            for h, src in enumerate((hi, lo)):
+                blk = src[kb * 32:(kb + 1) * 32, t * Nt:(t + 1) * Nt].T      # [Nt, 32] (n, k)
+                np.put_along_axis(img[t, kb, h], phys, blk, axis=1)
+    return img.reshape(-1)
+
+
+def tc_image_for(lib, W: np.ndarray) -> np.ndarray:
+    K, N = W.shape
+    nt, tiles, kb, fl = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_longlong()
+    lib.call('sevenn_gemm_tc_plan', N, K, ctypes.byref(nt), ctypes.byref(tiles), ctypes.byref(kb), ctypes.byref(fl))
+    img = tc_weight_image(np.ascontiguousarray(W, dtype=np.float32), nt.value, tiles.value, kb.value)
+    assert img.size == fl.value
+    return img
 
 
 class _Lin:
@@ -115,6 +147,10 @@ class Engine:
         self.act_radial = ACT_ID[spec.act_radial]
         self.cst_radial = ir.normalize2mom_const(spec.act_radial)
         self.n_launch = 0
+        self._tc_cache = {}
+        # dense contractions: 'auto' = tcgen05 3xTF32 arm for big row counts, exact-fp32 SIMT arm otherwise
+        self.gemm_mode = os.environ.get('SEVENN_GEMM', 'auto')
+        self.tc_min_rows = int(os.environ.get('SEVENN_TC_MIN_ROWS', '1024'))
         self.prof = None          # list of (name, cuda event) when profiling is on (bench.py)
 
     # ------------------------------------------------------------------ helpers
@@ -140,12 +176,25 @@ class Engine:
     def _zeros(self, *shape, dtype=torch.float32):
         return torch.zeros(*shape, dtype=dtype, device=self.dev)
 
+    def _tc_image(self, B):
+        """Pre-swizzled (hi, lo) K-major image of a weight matrix for the tcgen05 arm (csrc/gemm_tc.cu)."""
+        key = B.data_ptr()
+        if key not in self._tc_cache:
+            W = B.detach().cpu().numpy().astype(np.float32)
+            self._tc_cache[key] = torch.from_numpy(tc_image_for(self.lib, W)).to(self.dev).contiguous()
+        return self._tc_cache[key]
+
     def _gemm(self, A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi=0, act=0, cst=1.0, C2=None, P=None):
         g = _lib.GemmArgs(A.data_ptr() + 4 * a_off, sAn, sAm, B.data_ptr(), N, C.data_ptr() + 4 * c_off, sCn, sCm,
                           M, R, N, K, epi, act, cst,
                           (C2.data_ptr() + 4 * c_off) if C2 is not None else None,
                           (P.data_ptr() + 4 * c_off) if P is not None else None)
-        self.lib.call('sevenn_gemm_f32', ctypes.byref(g), self._stream())
+        tc = (self.gemm_mode != 'simt' and M >= self.tc_min_rows and (epi < 2 or act == 0) and K % 4 == 0 and sAn % 4 == 0 and sAm % 4 == 0
+              and (A.data_ptr() + 4 * a_off) % 16 == 0)
+        if tc:
+            self.lib.call('sevenn_gemm_tc', ctypes.byref(g), _p(self._tc_image(B)), self._stream())
+        else:
+            self.lib.call('sevenn_gemm_f32', ctypes.byref(g), self._stream())
         self.n_launch += 1
 
     def _linear_fwd(self, lin: _Lin, x, n, y, accumulate=False, types=None):

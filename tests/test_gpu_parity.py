@@ -196,3 +196,59 @@ def test_gemm_against_torch(lib):
         lib.call('sevenn_gemm_f32', ctypes.byref(g), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
         ref = torch.einsum('nrk,kc->nrc', A[:, :R * K].reshape(n, R, K).double(), B.double()).reshape(n, R * N)
         assert (C.double() - ref).abs().max() < 1e-4 * max(1.0, ref.abs().max().item())
+
+
+def test_gemm_tc_3xtf32_against_fp64(lib):
+    """tcgen05 arm: all four epilogues, (node, m)-strided rows, ragged M/N/K; fp32-level accuracy."""
+    import ctypes
+    from sevennet_exp_b200 import _lib as L
+    from sevennet_exp_b200.engine import tc_image_for
+    torch.manual_seed(1)
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    cst = 1.6791767923989418
+    for (n, R, K, N, epi) in [(1000, 1, 8, 64, 2), (4133, 1, 64, 960, 0), (3000, 1, 960, 64, 3), (777, 3, 64, 96, 0),
+                              (513, 5, 352, 32, 1), (2049, 1, 64, 64, 2), (300, 3, 384, 64, 1), (5000, 1, 64, 8, 1),
+                              (1500, 1, 64, 1760, 0)]:
+        ldn = R * K + 8
+        A = torch.randn(n, ldn, device='cuda')
+        B = torch.randn(K, N, device='cuda') / K ** 0.5
+        C = torch.randn(n, R * N, device='cuda')
+        C0 = C.clone()
+        P = torch.randn(n, R * N, device='cuda')
+        C2 = torch.zeros(n, R * N, device='cuda')
+        img = torch.from_numpy(tc_image_for(lib, B.cpu().numpy())).cuda()
+        g = L.GemmArgs(A.data_ptr(), ldn, K, B.data_ptr(), N, C.data_ptr(), R * N, N, n * R, R, N, K, epi, 0, cst,
+                       C2.data_ptr(), P.data_ptr())
+        lib.call('sevenn_gemm_tc', ctypes.byref(g), ctypes.c_void_p(img.data_ptr()), st)
+        torch.cuda.synchronize()
+        acc = torch.einsum('nrk,kc->nrc', A[:, :R * K].reshape(n, R, K).double(), B.double()).reshape(n, R * N)
+        if epi == 0:
+            ref = acc
+        elif epi == 1:
+            ref = C0.double() + acc
+        elif epi == 2:
+            ref = acc
+            assert (C2.double() - cst * torch.nn.functional.silu(acc)).abs().max() < 2e-5
+        else:
+            p = P.double()
+            s = torch.sigmoid(p)
+            ref = acc * cst * s * (1 + p * (1 - s))
+        err = (C.double() - ref).abs().max().item()
+        # tensor-core fp32 accumulation truncates (round-toward-zero) at every K=8 step: the bound grows with K
+        assert err < 2e-5 * max(1.0, K / 128), (n, R, K, N, epi, err)
+
+
+def test_engine_tc_and_simt_arms_agree(lib):
+    """Same SevenNet-0-shaped evaluation through the tcgen05 arm and the exact-fp32 SIMT arm."""
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cfg, model = _random_model('7net-0')
+    numbers, pos, cell = fluorite_hfo2((3, 3, 3), a=4.8)
+    out = {}
+    for mode in ('simt', 'tc'):
+        calc = SevenNetCalculator((cfg, model.state_dict()), file_type='model_instance')
+        calc.engine.gemm_mode, calc.engine.tc_min_rows = mode, 1
+        out[mode] = calc.compute(numbers, pos, cell, [True] * 3)
+    n = len(numbers)
+    assert abs(out['tc']['energy'] - out['simt']['energy']) / n < 5e-6
+    assert np.abs(out['tc']['forces'] - out['simt']['forces']).max() < 5e-5
+    assert np.abs(out['tc']['inferred_stress'] - out['simt']['inferred_stress']).max() * KBAR < 1e-3
