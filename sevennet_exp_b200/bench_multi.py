@@ -1,0 +1,120 @@
+"""bench.py --gpus N (N > 1): weak-scaling domain-decomposed E+F+S (one rank per GPU, NCCL over NVLink).
+
+The 4,096-atom HfO2 workload cell is replicated over the brick grid (2x1x1, 2x2x1, 2x2x2), each rank owns one
+replica (~4,096 atoms) plus its ghost shell; per step every rank rebuilds the neighbour list of its owned +
+ghost atoms, runs the layers with a ghost-feature exchange before each convolution >= 1, the reverse pass
+with the mirror exchange, folds ghost forces back to their owners and all-reduces energy and virial."""
+import json
+import os
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def run(args):
+    import bench as B
+    from .domain import Decomposition, Halo, brick_grid, evaluate_decomposed
+    from .sevennet_calculator import SevenNetCalculator
+    rank, world = int(os.environ.get('RANK', '0')), int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    dev = torch.device(f'cuda:{local}')
+    torch.cuda.set_device(dev)
+    if not dist.is_initialized():
+        dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
+    grid = brick_grid(world)
+    numbers0, pos0, cell0 = B.workload()
+    reps = np.array(grid)
+    shifts = np.stack(np.meshgrid(*[np.arange(r) for r in reps], indexing='ij'), -1).reshape(-1, 3)
+    pos = np.concatenate([pos0 + s @ cell0 for s in shifts])
+    numbers = np.tile(numbers0, len(shifts))
+    cell = cell0 * reps[:, None]
+    n_total = len(numbers)
+
+    cfg = B.model_config()
+    calc = SevenNetCalculator((cfg, B.random_state_dict(cfg)), file_type='model_instance', device=dev)
+    dec = Decomposition(numbers, pos, cell, calc.cutoff, grid, rank)
+    halo = Halo(dec, calc.engine.lib, dev)
+    types_dev = torch.from_numpy(calc._lut[dec.numbers].astype(np.int32)).to(dev)
+    pos_dev = torch.from_numpy(dec.pos).to(dev)
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+
+    def step():
+        return evaluate_decomposed(calc, dec, halo, types_dev=types_dev, pos_dev=pos_dev)
+
+    for _ in range(max(args.warmup, 3)):
+        E, F, vir, g = step()
+    if os.environ.get('SEVENN_CHECK'):
+        # decomposed == single-domain evaluation of the whole cell on one GPU (test_lammps.py:278-316 gate)
+        ref = calc.compute(numbers, pos, cell, [True] * 3)
+        dE = abs(E.item() - ref['energy']) / n_total
+        dF = np.abs(F.cpu().numpy() - ref['forces'][dec.local_ids]).max()
+        dS = np.abs(-(vir.cpu().numpy() / dec.volume) - ref['inferred_stress']).max() * 1602.1766208
+        print(f'[check rank {rank}] |dE|/atom={dE:.2e} max|dF|={dF:.2e} max|dS|={dS:.2e} kbar', flush=True)
+        assert dE < 1e-5 and dF < 1e-4 and dS < 1e-3
+    sampler = B.ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    l0 = calc.engine.n_launch + calc.nl.n_launch
+    torch.cuda.synchronize()
+    dist.barrier()
+    evs = []
+    for _ in range(args.steps):
+        flush.fill_(1.0)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        E, F, vir, g = step()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    dist.barrier()
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = t.item() / args.steps
+    launches = calc.engine.n_launch + calc.nl.n_launch - l0
+
+    # end to end: host positions in, owned forces + energy + virial out, every step
+    pos_host = torch.from_numpy(dec.pos).pin_memory()
+    torch.cuda.synchronize()
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.fill_(1.0)
+        pd = pos_host.to(dev, non_blocking=True)
+        E, F, vir, g = evaluate_decomposed(calc, dec, halo, types_dev=types_dev, pos_dev=pd)
+        host = torch.cat([E.reshape(1), vir, F.reshape(-1).double()]).cpu()
+    torch.cuda.synchronize()
+    dist.barrier()
+    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_t = te.item() / args.steps
+    stats = torch.tensor([dec.n_local, dec.n_ghost, g.n_edges], dtype=torch.float64, device=dev)
+    smax = stats.clone()
+    dist.all_reduce(stats)
+    dist.all_reduce(smax, op=dist.ReduceOp.MAX)
+    if sampler:
+        sampler.stop_flag = True
+        sampler.join(timeout=2)
+    if rank == 0:
+        x_dim = calc.spec.layers[1].conv.lx.dim
+        line = {
+            'metric': B.METRIC, 'value': n_total / (ms_step * 1e-3), 'unit': B.UNIT, 'n_gpus': world,
+            'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_step, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'SevenNet-0 E+F+S, bulk HfO2 cfg2 cell replicated {grid[0]}x{grid[1]}x{grid[2]} '
+                                   f'({n_total} atoms), brick domain decomposition, ghost feature exchange per layer',
+                       'n_atoms': n_total, 'atoms_per_gpu': n_total // world,
+                       'ghosts_per_gpu_max': int(smax[1].item()), 'edges_total': int(stats[2].item()),
+                       'halo_row_bytes': x_dim * 4,
+                       'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)',
+                       'step': 'device neighbour list (owned+ghost) + forward + reverse pass + halo exchanges'},
+            'e2e': {'value': n_total / e2e_t, 'unit': B.UNIT, 'ms_per_step': e2e_t * 1e3,
+                    'h2d_bytes_per_step': int(pos_host.numel() * 8),
+                    'd2h_bytes_per_step': int((7 + 3 * dec.n_local) * 8)},
+            'gpu_launches': int(launches), 'clocks': sampler.summary() if sampler else None,
+            'roofline': None, 'cpu_baseline': None,
+        }
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()

@@ -254,8 +254,8 @@ GKERNEL(gather_rows_kernel)(const float* __restrict__ src, int D, const int* __r
 }
 GKERNEL(scatter_add_rows_kernel)(const float* __restrict__ src, int D, const int* __restrict__ idx, long long n,
                                  float* __restrict__ out) {
-  // idx must not repeat inside one call (one message per peer) -> plain read-modify-write
-  GRID_STRIDE_LOOP(t, n * D) { out[(size_t)idx[t / D] * D + (t % D)] += src[t]; }
+  // an owner row can be wanted by several peers (or as several periodic images): atomic accumulate
+  GRID_STRIDE_LOOP(t, n * D) { ATOMIC_ADD_F32(out + (size_t)idx[t / D] * D + (t % D), src[t]); }
 }
 extern "C" int sevenn_gather_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream) {
   if (n <= 0) return 0;

@@ -23,6 +23,7 @@ static inline int sevenn_grid_for(long long n, int block = 256) {
 #define LAUNCH1D(kern, n, stream) kern<<<sevenn_grid_for(n), 256, 0, (cudaStream_t)(stream)>>>
 #define LAUNCH_STATUS() ((int)cudaGetLastError())
 #define ATOMIC_ADD_I32(p, v) atomicAdd((p), (v))
+#define ATOMIC_ADD_F32(p, v) atomicAdd((p), (v))
 #define LDGF(p) __ldg(p)
 #else
 #define HD static inline
@@ -32,6 +33,7 @@ static inline int sevenn_grid_for(long long n, int block = 256) {
 #define LAUNCH_STATUS() 0
 static inline int sevenn_emu_atomic_add(int* p, int v) { int o = *p; *p += v; return o; }
 #define ATOMIC_ADD_I32(p, v) sevenn_emu_atomic_add((p), (v))
+#define ATOMIC_ADD_F32(p, v) (*(p) += (v))
 #define LDGF(p) (*(p))
 #define __restrict__
 #endif
