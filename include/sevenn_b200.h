@@ -52,7 +52,8 @@ int sevenn_edge_fwd(const float* edge_vec, long long n_edges, int lmax, int norm
 /* analytic d/d(edge_vec): replaces autograd through the same modules (sevenn/nn/force_output.py:173-178) */
 int sevenn_edge_bwd(const float* edge_vec, long long n_edges, int lmax, int normalize, int n_basis,
                     int cutoff_kind, float rc, float p, float r_on, const float* bessel_coeffs,
-                    const float* dY, const float* demb, float* f_edge /* E,3 */, void* stream);
+                    const float* dY /* n_slabs x [E,(lmax+1)^2], summed in slab order */, int n_slabs,
+                    long long slab_stride /* floats */, const float* demb, float* f_edge /* E,3 */, void* stream);
 
 /* ---- dense contractions: replaces e3nn o3.Linear (sevenn/nn/linear.py:49-63,94), the radial MLP
  * e3nn FullyConnectedNet (sevenn/nn/convolution.py:92-101,121) and their input gradients. */

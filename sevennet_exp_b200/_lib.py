@@ -35,7 +35,7 @@ SIGNATURES = {
     'sevenn_nl_fill': ([c_p, c_p, c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p], c_i),
     'sevenn_csc_build': ([c_p, c_ll, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p], c_i),
     'sevenn_edge_fwd': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_p], c_i),
-    'sevenn_edge_bwd': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_p, c_p], c_i),
+    'sevenn_edge_bwd': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_i, c_ll, c_p, c_p, c_p], c_i),
     'sevenn_gemm_f32': ([ctypes.POINTER(GemmArgs), c_p], c_i),
     'sevenn_gemm_tc_plan': ([c_i, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_i), ctypes.POINTER(c_i),
                              ctypes.POINTER(c_ll)], c_i),
@@ -52,7 +52,7 @@ SIGNATURES = {
     'sevenn_scatter_add_rows': ([c_p, c_i, c_p, c_ll, c_p, c_p], c_i),
 }
 CONV_FWD_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p]
-CONV_BWD_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p, c_p, c_i, c_p, c_p]
+CONV_BWD_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p, c_p, c_i, c_p, c_ll, c_p]
 
 
 class SevennError(RuntimeError):

@@ -6,18 +6,23 @@ backward.  One specialised translation unit is emitted per ConvSpec (irreps of
 x, lmax of the filter, path list); CG coefficients become fp32 literals and all
 structural zeros disappear at generation time.
 
-Mapping (both directions): one warp per (destination atom, input-irrep group);
-lanes run over channels u (``cpl = ceil(mul/32)`` channels per lane), the
-destination row's accumulators live in registers, the warp walks the
-dst-sorted CSR row, so the reduction over edges needs no atomics and is
-bit-reproducible.  Per edge and path the warp first forms the edge-only matrix
+Mapping (both directions): one warp per (destination atom, unit) where a unit
+is a 32-channel chunk of one input-irrep group (SevenNet-0: 4 + 2 + 1 = 7 units
+per atom); lanes run over the chunk's channels u, the destination row's
+accumulators live in registers, the warp walks the dst-sorted CSR row, so the
+reduction over edges needs no atomics and is bit-reproducible.  All units run
+in one launch (blockIdx.y = unit).  The edge loop is software pipelined: the
+gathered source row, the radial weights and the spherical harmonics of edge
+e+1 (and the source index of e+2) are in flight while edge e is computed.  Per edge and path the warp first forms the edge-only matrix
 ``M[i,k] = sqrt(2 l3+1) * sum_j C[i,j,k] Y[l2,j]`` (warp-uniform), then
 ``out[u,k] += w[e,p,u] * sum_i M[i,k] x_j[u,i]``.
 
 Backward (same mapping, destination gradient in registers) produces, per edge:
 ``dW[e,p,u]`` (for the radial-MLP backward), the per-edge ``dx_e[e, x_dim]``
 (summed per *source* atom by a separate CSC gather kernel -> no atomics) and
-``dY[e, :]`` (lane partials reduced with warp shuffles).
+``dY[unit, e, :]`` (lane partials reduced with a transposing warp butterfly; one
+slab per unit, so no two warps ever touch the same word; the edge-embedding
+backward sums the slabs).
 
 The same text compiles as CUDA (nvcc, sm_100a) and, with -DSEVENN_EMU, as plain
 C++ where a "warp" is a 32-iteration loop: tests use the latter to check the
@@ -43,15 +48,36 @@ def np_f32(v):
     return np.float32(v)
 
 
+
+
 class _Group:
-    def __init__(self, spec: ConvSpec, g: int):
+    """One input irrep (mul x l1) of x; its channels are cut into 32-wide chunks = units."""
+
+    def __init__(self, spec: ConvSpec, g: int, unit0: int):
         self.g = g
         self.mul, (self.l1, _) = spec.lx.groups[g]
         self.d1 = 2 * self.l1 + 1
-        self.cpl = (self.mul + 31) // 32
+        self.nchunk = (self.mul + 31) // 32
         self.masked = self.mul % 32 != 0
         self.xoff = spec.lx.group_off[g]
         self.paths = [(pi, p) for pi, p in enumerate(spec.paths) if p.gx == g]
+        self.unit0 = unit0
+        self.used_l2 = sorted({p.l2 for _, p in self.paths})
+        self.ys = [jj for l2 in self.used_l2 for jj in range(l2 * l2, (l2 + 1) ** 2)]
+
+
+def make_groups(spec: ConvSpec) -> List[_Group]:
+    out, u = [], 0
+    for g in range(len(spec.lx.groups)):
+        G = _Group(spec, g, u)
+        if G.paths:
+            out.append(G)
+            u += G.nchunk
+    return out
+
+
+def n_units(spec: ConvSpec) -> int:
+    return sum(G.nchunk for G in make_groups(spec))
 
 
 def _m_terms(l1, l2, l3):
@@ -73,140 +99,197 @@ def _emit_M(lines, ent, l2, ind):
         lines.append(f'{ind}const float M_{i}_{k} = {expr};')
 
 
-def _load_common(L, G: _Group, spec: ConvSpec, ind):
+def _on(G, expr, zero='0.f'):
+    return f'(on ? {expr} : {zero})' if G.masked else expr
+
+
+RING_DEPTH = 4      # edges in flight per warp: RING_DEPTH - 1
+
+
+def _stage_floats(G: _Group, spec: ConvSpec) -> int:
     S = (spec.lmax_sh + 1) ** 2
-    L.append(f'{ind}const int j = col[e];')
-    L.append(f'{ind}const float* xr = x + (size_t)j * ldx + {G.xoff};')
-    L.append(f'{ind}const float* wr = w + (size_t)e * {spec.wn};')
-    used = sorted({p.l2 for _, p in G.paths})
-    for l2 in used:
-        for jj in range(l2 * l2, (l2 + 1) ** 2):
-            L.append(f'{ind}const float y{jj} = LDG(Y + (size_t)e * {S} + {jj});')
-    for c in range(G.cpl):
-        for m in range(G.d1):
-            ld = f'LDG(xr + {m * G.mul + c * 32} + lane)'
-            if G.masked:
-                ld = f'(on{c} ? {ld} : 0.f)'
-            L.append(f'{ind}const float x{c}_{m} = {ld};')
+    return (G.d1 + len(G.paths)) * 32 + ((S + 3) // 4) * 4
 
 
-def _ldw(G, p, c):
-    ld = f'LDG(wr + {p.w_off + c * 32} + lane)'
-    return f'(on{c} ? {ld} : 0.f)' if G.masked else ld
+def ring_floats(spec: ConvSpec) -> int:
+    """Shared-memory floats per warp (max over the groups sharing one kernel)."""
+    return RING_DEPTH * max(_stage_floats(G, spec) for G in make_groups(spec))
 
 
-def gen_fwd_group(spec: ConvSpec, G: _Group, sig: str) -> List[str]:
+def _issue_stage(L, G: _Group, spec: ConvSpec, ind, e, j, slot):
+    """cp.async of everything lane ``lane`` consumes for edge ``e`` (source row ``j``) into ring slot ``slot``:
+    its own x_j and w elements (read back by the same lane) and, on lanes < S, one spherical harmonic."""
+    S = (spec.lmax_sh + 1) ** 2
+    np_ = len(G.paths)
+    L.append(f'{ind}{{ float* sd = ring + ({slot}) * {_stage_floats(G, spec)} + lane;')
+    L.append(f'{ind}  const float* xr = x + (size_t)({j}) * ldx + {G.xoff} + c32 + lane;')
+    L.append(f'{ind}  const float* wr = w + (size_t)({e}) * {spec.wn} + c32 + lane;')
+    if G.masked:
+        L.append(f'{ind}  if (on) {{')
+    for m in range(G.d1):
+        L.append(f'{ind}  CP_ASYNC4(sd + {m * 32}, xr + {m * G.mul});')
+    for q, (pi, p) in enumerate(G.paths):
+        L.append(f'{ind}  CP_ASYNC4(sd + {(G.d1 + q) * 32}, wr + {p.w_off});')
+    if G.masked:
+        L.append(f'{ind}  }}')
+    L.append(f'{ind}  if (lane < {S}) CP_ASYNC4(sd + {(G.d1 + np_) * 32}, Y + (size_t)({e}) * {S} + lane);')
+    L.append(f'{ind}}}')
+
+
+def _pipeline_open(L, G: _Group, spec: ConvSpec):
+    """Opens ``if (e0 < e1) { for (e) {`` with x*, w*, y* of edge e defined.  CUDA: a per-warp shared-memory
+    ring fed by cp.async keeps RING_DEPTH-1 edges in flight; emulation build: direct loads."""
+    S = (spec.lmax_sh + 1) ** 2
+    D = RING_DEPTH
+    stg = _stage_floats(G, spec)
+    L.append('    const int e0 = rowptr[row], e1 = rowptr[row + 1];')
+    L.append('    if (e0 < e1) {')
+    L.append('#ifdef SEVENN_EMU')
+    L.append('      for (int e = e0; e < e1; ++e) {')
+    L.append(f'        const float* xr = x + (size_t)col[e] * ldx + {G.xoff} + c32 + lane;')
+    L.append(f'        const float* wr = w + (size_t)e * {spec.wn} + c32 + lane;')
+    for m in range(G.d1):
+        L.append(f'        const float x{m} = {_on(G, f"xr[{m * G.mul}]")};')
+    for pi, p in G.paths:
+        L.append(f'        const float w{pi} = {_on(G, f"wr[{p.w_off}]")};')
+    for jj in G.ys:
+        L.append(f'        const float y{jj} = Y[(size_t)e * {S} + {jj}];')
+    L.append('#else')
+    L.append(f'      for (int d = 0; d < {D - 1}; ++d) {{')
+    L.append('        if (e0 + d < e1) {')
+    _issue_stage(L, G, spec, '          ', 'e0 + d', 'col[e0 + d]', 'd')
+    L.append('        }')
+    L.append('        CP_ASYNC_COMMIT();')
+    L.append('      }')
+    L.append(f'      int jn = col[e0 + {D - 1} < e1 ? e0 + {D - 1} : e1 - 1];')
+    L.append('      int slot = 0;')
+    L.append('      for (int e = e0; e < e1; ++e) {')
+    L.append(f'        CP_ASYNC_WAIT({D - 2});')
+    L.append('        __syncwarp();')
+    L.append(f'        if (e + {D - 1} < e1) {{')
+    _issue_stage(L, G, spec, '          ', f'e + {D - 1}', 'jn', f'(slot + {D - 1}) & {D - 1}')
+    L.append('        }')
+    L.append('        CP_ASYNC_COMMIT();')
+    L.append(f'        jn = col[e + {D} < e1 ? e + {D} : e1 - 1];')
+    L.append(f'        const float* sr = ring + slot * {stg};')
+    L.append(f'        slot = (slot + 1) & {D - 1};')
+    for m in range(G.d1):
+        L.append(f'        const float x{m} = {_on(G, f"sr[{m * 32} + lane]")};')
+    for q, (pi, p) in enumerate(G.paths):
+        L.append(f'        const float w{pi} = {_on(G, f"sr[{(G.d1 + q) * 32} + lane]")};')
+    ybase = (G.d1 + len(G.paths)) * 32
+    for jj in G.ys:
+        L.append(f'        const float y{jj} = sr[{ybase + jj}];')
+    L.append('#endif')
+
+
+def _unit_open(L, G: _Group, first: bool, last: bool):
+    cond = f'unit < {G.unit0 + G.nchunk}'
+    if first and last:
+        L.append('  {')
+    elif first:
+        L.append(f'  if ({cond}) {{')
+    elif last:
+        L.append('  else {')
+    else:
+        L.append(f'  else if ({cond}) {{')
+    L.append(f'    const int c32 = (unit - {G.unit0}) * 32;')
+    if G.masked:
+        L.append(f'    const bool on = (c32 + lane) < {G.mul};')
+
+
+def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
     L = []
-    name = f'conv_fwd_{sig}_g{G.g}'
-    L.append(f'KERNEL_HEAD({name})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
+    L.append(f'KERNEL_HEAD(conv_fwd_{sig})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
     L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
     L.append('    int n_dst, float inv_denom, float* __restrict__ out, int ldo)')
-    L.append('WARP_LOOP_BEGIN(n_dst)')
-    if G.masked:
-        for c in range(G.cpl):
-            L.append(f'  const bool on{c} = ({c * 32} + lane) < {G.mul};')
-    for pi, p in G.paths:
-        for c in range(G.cpl):
+    L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
+    for gi, G in enumerate(groups):
+        _unit_open(L, G, gi == 0, gi == len(groups) - 1)
+        for pi, p in G.paths:
+            L.append('    float ' + ', '.join(f'a{pi}_{k} = 0.f' for k in range(2 * p.l3 + 1)) + ';')
+        _pipeline_open(L, G, spec)
+        for pi, p in G.paths:
+            ent, _ = _m_terms(p.l1, p.l2, p.l3)
+            L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}, mul {p.mul}')
+            _emit_M(L, ent, p.l2, '          ')
             for k in range(2 * p.l3 + 1):
-                L.append(f'  float a{pi}_{c}_{k} = 0.f;')
-    L.append('  const int e0 = rowptr[row], e1 = rowptr[row + 1];')
-    L.append('  for (int e = e0; e < e1; ++e) {')
-    _load_common(L, G, spec, '    ')
-    for pi, p in G.paths:
-        ent, _ = _m_terms(p.l1, p.l2, p.l3)
-        L.append(f'    {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}, mul {p.mul}')
-        _emit_M(L, ent, p.l2, '      ')
-        for c in range(G.cpl):
-            L.append(f'      {{ const float wv = {_ldw(G, p, c)};')
-            for k in range(2 * p.l3 + 1):
-                terms = [f'M_{i}_{k}*x{c}_{i}' for i in range(G.d1) if (i, k) in ent]
+                terms = [f'M_{i}_{k}*x{i}' for i in range(G.d1) if (i, k) in ent]
                 if terms:
-                    L.append(f'        a{pi}_{c}_{k} = fmaf(wv, {" + ".join(terms)}, a{pi}_{c}_{k});')
-            L.append('      }')
-        L.append('    }')
-    L.append('  }')
-    L.append('  float* orow = out + (size_t)row * ldo;')
-    for pi, p in G.paths:
-        Mg = spec.lmid.groups[p.gm][0]
-        base = spec.lmid.group_off[p.gm] + p.u_off
-        for c in range(G.cpl):
+                    L.append(f'          a{pi}_{k} = fmaf(w{pi}, {" + ".join(terms)}, a{pi}_{k});')
+            L.append('        }')
+        L.append('      }')   # for e
+        L.append('    }')     # if e0 < e1
+        L.append('    float* orow = out + (size_t)row * ldo + c32 + lane;')
+        for pi, p in G.paths:
+            Mg = spec.lmid.groups[p.gm][0]
+            base = spec.lmid.group_off[p.gm] + p.u_off
             for k in range(2 * p.l3 + 1):
-                st = f'orow[{base + k * Mg + c * 32} + lane] = a{pi}_{c}_{k} * inv_denom;'
-                L.append(f'  if (on{c}) {st}' if G.masked else f'  {st}')
-    L.append('WARP_LOOP_END')
+                st = f'orow[{base + k * Mg}] = a{pi}_{k} * inv_denom;'
+                L.append(f'    if (on) {st}' if G.masked else f'    {st}')
+        L.append('  }')
+    L.append('UNIT_LOOP_END')
     return L
 
 
-def gen_bwd_group(spec: ConvSpec, G: _Group, sig: str) -> List[str]:
+def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
     S = (spec.lmax_sh + 1) ** 2
+    NP = 1
+    while NP < S:
+        NP *= 2
     L = []
-    name = f'conv_bwd_{sig}_g{G.g}'
-    L.append(f'KERNEL_HEAD({name})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
+    L.append(f'KERNEL_HEAD(conv_bwd_{sig})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
     L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
     L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
-    L.append('    float* __restrict__ dW, float* __restrict__ dxe, int lddx, float* dY)')
-    L.append('WARP_LOOP_BEGIN(n_dst)')
-    if G.masked:
-        for c in range(G.cpl):
-            L.append(f'  const bool on{c} = ({c * 32} + lane) < {G.mul};')
-    L.append('  const float* grow = gout + (size_t)row * ldo;')
-    for pi, p in G.paths:
-        Mg = spec.lmid.groups[p.gm][0]
-        base = spec.lmid.group_off[p.gm] + p.u_off
-        for c in range(G.cpl):
+    L.append('    float* __restrict__ dW, float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
+    L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
+    L.append('  float* dYu = dY + (size_t)unit * (size_t)dy_stride;')
+    for gi, G in enumerate(groups):
+        _unit_open(L, G, gi == 0, gi == len(groups) - 1)
+        L.append('    const float* grow = gout + (size_t)row * ldo + c32 + lane;')
+        for pi, p in G.paths:
+            Mg = spec.lmid.groups[p.gm][0]
+            base = spec.lmid.group_off[p.gm] + p.u_off
             for k in range(2 * p.l3 + 1):
-                ld = f'LDG(grow + {base + k * Mg + c * 32} + lane) * inv_denom'
-                if G.masked:
-                    ld = f'(on{c} ? {ld} : 0.f)'
-                L.append(f'  const float g{pi}_{c}_{k} = {ld};')
-    L.append('  const int e0 = rowptr[row], e1 = rowptr[row + 1];')
-    L.append('  for (int e = e0; e < e1; ++e) {')
-    _load_common(L, G, spec, '    ')
-    used = sorted({p.l2 for _, p in G.paths})
-    for l2 in used:
-        for jj in range(l2 * l2, (l2 + 1) ** 2):
-            L.append(f'    float dy{jj} = 0.f;')
-    for c in range(G.cpl):
-        for m in range(G.d1):
-            L.append(f'    float dx{c}_{m} = 0.f;')
-    L.append(f'    float* dwr = dW + (size_t)e * {spec.wn};')
-    for pi, p in G.paths:
-        ent, nnz = _m_terms(p.l1, p.l2, p.l3)
-        L.append(f'    {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}')
-        _emit_M(L, ent, p.l2, '      ')
-        for (i, k) in ent:
-            L.append(f'      float P_{i}_{k} = 0.f;')
-        for c in range(G.cpl):
-            L.append(f'      {{ const float wv = {_ldw(G, p, c)};')
+                ld = _on(G, f'LDG(grow + {base + k * Mg}) * inv_denom')
+                L.append(f'    const float g{pi}_{k} = {ld};')
+        _pipeline_open(L, G, spec)
+        L.append(f'        float dyv[{NP}] = {{{", ".join(["0.f"] * NP)}}};')
+        L.append('        float ' + ', '.join(f'dx{m} = 0.f' for m in range(G.d1)) + ';')
+        L.append(f'        float* dwr = dW + (size_t)e * {spec.wn} + c32 + lane;')
+        for pi, p in G.paths:
+            ent, nnz = _m_terms(p.l1, p.l2, p.l3)
+            L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}')
+            _emit_M(L, ent, p.l2, '          ')
+            L.append('          float ' + ', '.join(f'P_{i}_{k} = 0.f' for (i, k) in ent) + ';')
             dw_terms = []
             for k in range(2 * p.l3 + 1):
-                terms = [f'M_{i}_{k}*x{c}_{i}' for i in range(G.d1) if (i, k) in ent]
+                terms = [f'M_{i}_{k}*x{i}' for i in range(G.d1) if (i, k) in ent]
                 if terms:
-                    dw_terms.append(f'g{pi}_{c}_{k}*({" + ".join(terms)})')
-            st = f'dwr[{p.w_off + c * 32} + lane] = {" + ".join(dw_terms) if dw_terms else "0.f"};'
-            L.append(f'        if (on{c}) {st}' if G.masked else f'        {st}')
+                    dw_terms.append(f'g{pi}_{k}*({" + ".join(terms)})')
+            st = f'dwr[{p.w_off}] = {" + ".join(dw_terms) if dw_terms else "0.f"};'
+            L.append(f'          if (on) {st}' if G.masked else f'          {st}')
             for k in range(2 * p.l3 + 1):
                 idx = [i for i in range(G.d1) if (i, k) in ent]
                 if not idx:
                     continue
-                L.append(f'        {{ const float wg = wv * g{pi}_{c}_{k};')
+                L.append(f'          {{ const float wg = w{pi} * g{pi}_{k};')
                 for i in idx:
-                    L.append(f'          dx{c}_{i} = fmaf(M_{i}_{k}, wg, dx{c}_{i}); P_{i}_{k} = fmaf(wg, x{c}_{i}, P_{i}_{k});')
-                L.append('        }')
-            L.append('      }')
-        for (i, j, k, cf) in nnz:
-            L.append(f'      dy{p.l2 * p.l2 + j} = fmaf({_f(cf)}, P_{i}_{k}, dy{p.l2 * p.l2 + j});')
-        L.append('    }')
-    L.append(f'    float* dxr = dxe + (size_t)e * lddx + {G.xoff};')
-    for c in range(G.cpl):
+                    L.append(f'            dx{i} = fmaf(M_{i}_{k}, wg, dx{i}); P_{i}_{k} = fmaf(wg, x{i}, P_{i}_{k});')
+                L.append('          }')
+            for (i, j, k, cf) in nnz:
+                q = p.l2 * p.l2 + j
+                L.append(f'          dyv[{q}] = fmaf({_f(cf)}, P_{i}_{k}, dyv[{q}]);')
+            L.append('        }')
+        L.append(f'        float* dxr = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
         for m in range(G.d1):
-            st = f'dxr[{m * G.mul + c * 32} + lane] = dx{c}_{m};'
-            L.append(f'    if (on{c}) {st}' if G.masked else f'    {st}')
-    for l2 in used:
-        for jj in range(l2 * l2, (l2 + 1) ** 2):
-            L.append(f'    WARP_SUM_ADD(dY + (size_t)e * {S} + {jj}, dy{jj});')
-    L.append('  }')
-    L.append('WARP_LOOP_END')
+            st = f'dxr[{m * G.mul}] = dx{m};'
+            L.append(f'        if (on) {st}' if G.masked else f'        {st}')
+        L.append(f'        sevenn_dy_accumulate<{NP}>(dyv, lane, dYu + (size_t)e * {S}, {S});')
+        L.append('      }')
+        L.append('    }')
+        L.append('  }')
+    L.append('UNIT_LOOP_END')
     return L
 
 
@@ -216,31 +299,28 @@ def signature(spec: ConvSpec) -> str:
 
 def generate(spec: ConvSpec) -> str:
     sig = signature(spec)
-    groups = [_Group(spec, g) for g in range(len(spec.lx.groups))]
-    groups = [G for G in groups if G.paths]
+    groups = make_groups(spec)
+    nu = sum(G.nchunk for G in groups)
     out = ['// GENERATED by sevennet_exp_b200/codegen/conv_codegen.py -- do not edit.',
            f'// x: {ir.irreps_str(spec.lx.groups)}  mid: {ir.irreps_str(spec.lmid.groups)}  '
-           f'lmax_sh {spec.lmax_sh}  paths {len(spec.paths)}  wn {spec.wn}',
+           f'lmax_sh {spec.lmax_sh}  paths {len(spec.paths)}  wn {spec.wn}  units {nu}',
            '#include "conv_common.cuh"', '']
-    for G in groups:
-        out += gen_fwd_group(spec, G, sig) + ['']
-        out += gen_bwd_group(spec, G, sig) + ['']
-    # launchers
+    out += gen_fwd(spec, groups, sig) + ['']
+    out += gen_bwd(spec, groups, sig) + ['']
     out.append(f'extern "C" int sevenn_conv_fwd_{sig}(const float* x, int ldx, const float* Y, const float* w,')
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, float* out, int ldo, void* stream) {')
     out.append('  if (n_dst <= 0) return 0;')
-    for G in groups:
-        out.append(f'  LAUNCH(conv_fwd_{sig}_g{G.g}, n_dst, stream)(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo);')
+    out.append(f'  LAUNCH(conv_fwd_{sig}, n_dst, {nu}, stream)(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo);')
     out.append('  return LAUNCH_STATUS();')
     out.append('}')
     out.append(f'extern "C" int sevenn_conv_bwd_{sig}(const float* x, int ldx, const float* Y, const float* w,')
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, const float* gout, int ldo,')
-    out.append('    float* dW, float* dxe, int lddx, float* dY, void* stream) {')
+    out.append('    float* dW, float* dxe, int lddx, float* dY, long long dy_stride, void* stream) {')
     out.append('  if (n_dst <= 0) return 0;')
-    for G in groups:
-        out.append(f'  LAUNCH(conv_bwd_{sig}_g{G.g}, n_dst, stream)(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY);')
+    out.append(f'  LAUNCH(conv_bwd_{sig}, n_dst, {nu}, stream)(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY, dy_stride);')
     out.append('  return LAUNCH_STATUS();')
     out.append('}')
-    out.append(f'extern "C" int sevenn_conv_info_{sig}(int* x_dim, int* mid_dim, int* wn, int* sh_dim) {{')
-    out.append(f'  *x_dim = {spec.lx.dim}; *mid_dim = {spec.lmid.dim}; *wn = {spec.wn}; *sh_dim = {(spec.lmax_sh + 1) ** 2}; return 0; }}')
+    out.append(f'extern "C" int sevenn_conv_info_{sig}(int* x_dim, int* mid_dim, int* wn, int* sh_dim, int* units) {{')
+    out.append(f'  *x_dim = {spec.lx.dim}; *mid_dim = {spec.lmid.dim}; *wn = {spec.wn}; *sh_dim = {(spec.lmax_sh + 1) ** 2};')
+    out.append(f'  *units = {nu}; return 0; }}')
     return '\n'.join(out) + '\n'

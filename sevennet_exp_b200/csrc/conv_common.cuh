@@ -1,5 +1,5 @@
 // Flavor glue for the generated convolution kernels (codegen/conv_codegen.py).
-//   CUDA   : one warp per destination row, 4 warps per CTA.
+//   CUDA   : one warp per (destination row, unit), 4 rows per CTA, blockIdx.y = unit.
 //   -DSEVENN_EMU (tests only, g++): a "warp" is a 32-iteration lane loop.
 #pragma once
 #include <cstddef>
@@ -9,27 +9,55 @@
 #include <cuda_runtime.h>
 #define CONV_WARPS_PER_CTA 4
 #define KERNEL_HEAD(name) __global__ void __launch_bounds__(32 * CONV_WARPS_PER_CTA) name
-#define WARP_LOOP_BEGIN(n) { const int lane = threadIdx.x & 31; \
+#define UNIT_LOOP_BEGIN(n, nunits, ringf) { __shared__ float ring_all[CONV_WARPS_PER_CTA * (ringf)]; \
+    float* ring = ring_all + (threadIdx.x >> 5) * (ringf); (void)ring; \
+    const int lane = threadIdx.x & 31; const int unit = blockIdx.y; \
     const int row = blockIdx.x * CONV_WARPS_PER_CTA + (threadIdx.x >> 5); if (row < (n)) {
-#define WARP_LOOP_END }}
+#define UNIT_LOOP_END }}
 #define LDG(p) __ldg(p)
-__device__ __forceinline__ float sevenn_warp_sum(float v) {
+// per-lane 4-byte asynchronous copy global -> shared (LDGSTS): the gathered source row, the radial weights and
+// the spherical harmonics of the next edges stream into a per-warp ring while the current edge is computed
+#define CP_ASYNC4(sdst, gsrc) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" \
+    :: "r"((unsigned)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory")
+#define CP_ASYNC_COMMIT() asm volatile("cp.async.commit_group;" ::: "memory")
+#define CP_ASYNC_WAIT(n) asm volatile("cp.async.wait_group %0;" :: "n"(n) : "memory")
+// Transposing butterfly: every lane holds NP partial values; after log2(NP) exchange steps (NP-1 shuffles
+// instead of 5*NP) lane L holds one value index (L >> (5 - log2 NP)) summed over a lane subset, the remaining
+// offsets finish the sum.  dst[q] is owned by this warp alone (one slab per unit, one row per edge), so the
+// read-modify-write is race free and the order of additions is fixed.
+template <int NP>
+__device__ __forceinline__ void sevenn_dy_accumulate(float (&v)[NP], int lane, float* dst, int S) {
+  int o = 16;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
+  for (int h = NP / 2; h >= 1; h >>= 1, o >>= 1) {
+    const bool up = (lane & o) != 0;
+#pragma unroll
+    for (int i = 0; i < h; ++i) {
+      const float send = up ? v[i] : v[i + h];
+      const float keep = up ? v[i + h] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+    }
+  }
+  float s = v[0];
+  for (; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  constexpr int SH = (NP == 32) ? 0 : (NP == 16) ? 1 : (NP == 8) ? 2 : (NP == 4) ? 3 : (NP == 2) ? 4 : 5;
+  const int q = lane >> SH;
+  if ((lane & ((1 << SH) - 1)) == 0 && q < S) dst[q] += s;
 }
-// dY[e, j] is owned by exactly one warp at a time (one row owns the edge, groups and layers
-// are stream-ordered launches), so a plain read-modify-write by lane 0 is race free.
-#define WARP_SUM_ADD(ptr, v) { const float s_ = sevenn_warp_sum(v); if (lane == 0) *(ptr) += s_; }
-#define LAUNCH(kern, n, stream) kern<<<((n) + CONV_WARPS_PER_CTA - 1) / CONV_WARPS_PER_CTA, 32 * CONV_WARPS_PER_CTA, 0, (cudaStream_t)(stream)>>>
+#define LAUNCH(kern, n, nunits, stream) kern<<<dim3(((n) + CONV_WARPS_PER_CTA - 1) / CONV_WARPS_PER_CTA, (nunits)), 32 * CONV_WARPS_PER_CTA, 0, (cudaStream_t)(stream)>>>
 #define LAUNCH_STATUS() ((int)cudaGetLastError())
 #else
 #define KERNEL_HEAD(name) static void name
-#define WARP_LOOP_BEGIN(n) { for (int row = 0; row < (n); ++row) for (int lane = 0; lane < 32; ++lane) {
-#define WARP_LOOP_END }}
+#define UNIT_LOOP_BEGIN(n, nunits, ringf) { for (int unit = 0; unit < (nunits); ++unit) for (int row = 0; row < (n); ++row) \
+    for (int lane = 0; lane < 32; ++lane) {
+#define UNIT_LOOP_END }}
 #define LDG(p) (*(p))
-#define WARP_SUM_ADD(ptr, v) { *(ptr) += (v); }
-#define LAUNCH(kern, n, stream) kern
+template <int NP>
+static inline void sevenn_dy_accumulate(float (&v)[NP], int lane, float* dst, int S) {
+  (void)lane;
+  for (int q = 0; q < S; ++q) dst[q] += v[q];
+}
+#define LAUNCH(kern, n, nunits, stream) kern
 #define LAUNCH_STATUS() 0
 #define __restrict__
 #endif

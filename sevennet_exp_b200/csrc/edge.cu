@@ -100,13 +100,16 @@ GKERNEL(edge_fwd_kernel)(const float* __restrict__ vec, long long n, EdgeParams 
 }
 
 GKERNEL(edge_bwd_kernel)(const float* __restrict__ vec, long long n, EdgeParams P, const float* __restrict__ coeffs,
-                         const float* __restrict__ dY, const float* __restrict__ demb, float* __restrict__ fvec) {
+                         const float* __restrict__ dY, int n_slabs, long long slab_stride,
+                         const float* __restrict__ demb, float* __restrict__ fvec) {
   const int S = (P.lmax + 1) * (P.lmax + 1);
   GRID_STRIDE_LOOP(e, n) {
     const float x = vec[3 * e], y = vec[3 * e + 1], z = vec[3 * e + 2];
     const float r = sqrtf(x * x + y * y + z * z), ir = 1.f / r;
     float d[16], g[3];
     for (int k = 0; k < S; ++k) d[k] = dY[e * S + k];
+    for (int sl = 1; sl < n_slabs; ++sl)                     // one slab per convolution unit, fixed order
+      for (int k = 0; k < S; ++k) d[k] += dY[(size_t)sl * slab_stride + e * S + k];
     float fx, fy, fz;
     if (P.normalize) {
       const float ux = x * ir, uy = y * ir, uz = z * ir;
@@ -149,10 +152,11 @@ extern "C" int sevenn_edge_fwd(const float* vec, long long n_edges, int lmax, in
 
 extern "C" int sevenn_edge_bwd(const float* vec, long long n_edges, int lmax, int normalize, int nb,
                                int cutoff_kind, float rc, float p, float r_on, const float* coeffs,
-                               const float* dY, const float* demb, float* fvec, void* stream) {
+                               const float* dY, int n_slabs, long long slab_stride, const float* demb,
+                               float* fvec, void* stream) {
   if (n_edges <= 0) return 0;
-  if (lmax < 0 || lmax > 3 || nb < 1) return SEVENN_ERR_BAD_ARG;
+  if (lmax < 0 || lmax > 3 || nb < 1 || n_slabs < 1) return SEVENN_ERR_BAD_ARG;
   LAUNCH1D(edge_bwd_kernel, n_edges, stream)(vec, n_edges, edge_params(lmax, normalize, nb, cutoff_kind, rc, p, r_on),
-                                             coeffs, dY, demb, fvec);
+                                             coeffs, dY, n_slabs, slab_stride, demb, fvec);
   return LAUNCH_STATUS();
 }

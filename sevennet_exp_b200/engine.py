@@ -20,6 +20,7 @@ import torch
 from . import _lib
 from .spec import ACT_ID, LinearSpec, ModelSpec, nequip_sc_dense
 from . import irreps as ir
+from .codegen import conv_codegen
 
 
 class Graph:
@@ -130,7 +131,7 @@ class Engine:
                 'mlp': [f32(w) for w in Wm],
                 'mlpT': [f32(np.ascontiguousarray(w.T)) for w in Wm],
                 'inv_denom': 1.0 / float(sd[f'{L.conv.name}.denominator'][0]),
-                'sig': L.conv.signature(),
+                'sig': L.conv.signature(), 'units': conv_codegen.n_units(L.conv),
                 'pieces': (_lib.GatePiece * len(L.gate.pieces))(*[
                     _lib.GatePiece(p.kind, p.l, p.mul, p.in_off, p.in_stride, p.gate_off, p.out_off,
                                    p.out_stride, p.act, p.cst) for p in L.gate.pieces]),
@@ -307,7 +308,7 @@ class Engine:
             rc = fwd(_p(h), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(agg), dmid, st)
             if rc:
                 raise _lib.SevennError(f'conv_fwd {lay["sig"]} failed with status {rc}')
-            self.n_launch += len(L.conv.lx.groups)
+            self.n_launch += 1
             self._mark('si2_fwd')
             # self interaction 2 accumulates onto the self connection; then the gate
             self._linear_fwd(lay['si2'], agg, nl, pre, accumulate=True)
@@ -342,7 +343,8 @@ class Engine:
 
         # ---------------- reverse pass: dE/d(edge_vec) --------------------------------------
         self._mark('readout_bwd')
-        dY, demb = self._zeros(max(E, 1), S), self._zeros(max(E, 1), sp.n_basis)
+        n_slab = max(lay['units'] for lay in self.layers)        # one dY slab per convolution unit
+        dY, demb = self._zeros(n_slab * max(E, 1), S), self._zeros(max(E, 1), sp.n_basis)
         dr1 = self._empty(nl, sp.read1.lout.dim)
         self._linear_bwd(self.read2, seed, nl, dr1)
         dx = self._zeros(nl, sp.read1.lin.dim) if self.read1.bwd_needs_zero else self._empty(nl, sp.read1.lin.dim)
@@ -367,10 +369,10 @@ class Engine:
             dxe = self._zeros(max(E, 1), dx_in) if unused else self._empty(max(E, 1), dx_in)
             _, bwd = lib.conv(lay['sig'])
             rc = bwd(_p(sv['h']), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(dagg), dmid,
-                     _p(dW), _p(dxe), dx_in, _p(dY), st)
+                     _p(dW), _p(dxe), dx_in, _p(dY), max(E, 1) * S, st)
             if rc:
                 raise _lib.SevennError(f'conv_bwd {lay["sig"]} failed with status {rc}')
-            self.n_launch += len(L.conv.lx.groups)
+            self.n_launch += 1
             del w
             self._mark('mlp_bwd')
             self._mlp_bwd(lay, dW, sv['pres'], demb, E)
@@ -391,7 +393,7 @@ class Engine:
             dx = dxn
         self._mark('edge_bwd_force')
         fvec = self._empty(max(E, 1), 3)
-        lib.call('sevenn_edge_bwd', _p(g.edge_vec), E, *edge_args, _p(dY), _p(demb), _p(fvec), st)
+        lib.call('sevenn_edge_bwd', _p(g.edge_vec), E, *edge_args, _p(dY), n_slab, max(E, 1) * S, _p(demb), _p(fvec), st)
         F, vir = self._empty(nn, 3), self._empty(nn, 6)
         lib.call('sevenn_force_virial', _p(fvec), _p(g.edge_vec), _p(g.rowptr), nl, _p(g.cptr), _p(g.cedge), nn,
                  _p(F), _p(vir), st)

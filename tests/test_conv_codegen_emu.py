@@ -71,14 +71,15 @@ def test_conv_fwd_bwd_emu(case):
     god = np.ascontiguousarray(conv.lmid.from_e3nn(gout).numpy().astype(np.float32))
     dW = np.zeros((E, conv.wn), np.float32)
     dxe = np.zeros((E, conv.lx.dim), np.float32)
-    dY = np.zeros((E, Ssh), np.float32)
+    nu = cg.n_units(conv)
+    dY = np.zeros((nu, E, Ssh), np.float32)           # one slab per (irrep group, 32-channel chunk)
     b = getattr(lib, f'sevenn_conv_bwd_{sig}')
     b.argtypes = ([ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 4 + [ctypes.c_int, ctypes.c_float,
                   ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
-                  ctypes.c_void_p, ctypes.c_void_p])
+                  ctypes.c_void_p, ctypes.c_longlong, ctypes.c_void_p])
     assert b(fptr(xd), conv.lx.dim, fptr(Yd), fptr(wd), iptr(rowptr), iptr(col), n, 1 / 1.7,
-             fptr(god), conv.lmid.dim, fptr(dW), fptr(dxe), conv.lx.dim, fptr(dY), None) == 0
+             fptr(god), conv.lmid.dim, fptr(dW), fptr(dxe), conv.lx.dim, fptr(dY), E * Ssh, None) == 0
     assert torch.allclose(torch.from_numpy(dW).double(), gw, atol=5e-5, rtol=1e-4)
-    assert torch.allclose(torch.from_numpy(dY).double(), gY, atol=2e-4, rtol=1e-4)
+    assert torch.allclose(torch.from_numpy(dY).double().sum(0), gY, atol=2e-4, rtol=1e-4)
     dx = torch.zeros(n, conv.lx.dim, dtype=torch.float64).index_add_(0, src, torch.from_numpy(dxe).double())
     assert torch.allclose(conv.lx.to_e3nn(dx), gx, atol=2e-4, rtol=1e-4)
