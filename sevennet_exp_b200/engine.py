@@ -93,66 +93,20 @@ class _Lin:
         self.fwd_full = sum(b.N * (2 * b.l + 1) for b in spec.blocks) == spec.lout.dim
 
 
-class Engine:
-    def __init__(self, spec: ModelSpec, state_dict: Dict[str, torch.Tensor], lib: Optional[_lib.Lib] = None,
-                 device='cuda', keep_weights: bool = True):
-        self.spec, self.dev = spec, torch.device(device)
+class Kernels:
+    """Launch plumbing shared by the whole-model Engine and the per-module wrappers in ``nn/``: dense
+    contractions (tcgen05 3xTF32 arm / exact-fp32 SIMT arm), block-wise o3.Linear, the radial MLP."""
+
+    def __init__(self, lib: Optional[_lib.Lib] = None, device='cuda'):
+        self.dev = torch.device(device)
         self.lib = lib if lib is not None else _lib.load()
-        self.keep_w = keep_weights
-        sd = {k: v.detach().cpu().numpy().astype(np.float64) for k, v in state_dict.items()
-              if k in spec.expected_keys()}
-        missing = [k for k in spec.expected_keys() if k not in sd]
-        if missing:
-            raise KeyError(f'state_dict misses {missing}')
-        for k, shp in spec.expected_keys().items():
-            if tuple(sd[k].shape) != shp:
-                raise ValueError(f'{k}: shape {sd[k].shape} != expected {shp}')
-        dev = self.dev
-        f32 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32, device=dev).contiguous()  # noqa: E731
-        self.coeffs = f32(sd['edge_embedding.basis_function.coeffs'])
-        # embedding table [S, d0]
-        emb = spec.embed
-        table = np.zeros((spec.n_species, emb.lout.dim))
-        for b in emb.blocks:
-            assert b.l == 0
-            o = emb.lout.group_off[b.g_out] + b.u_off_out
-            table[:, o:o + b.N] = emb.dense(sd[emb.key], b)
-        self.embed_table = f32(table)
-        self.d0 = emb.lout.dim
-        self.layers = []
-        for L in spec.layers:
-            h = L.conv.hidden
-            Wm = [sd[f'{L.conv.name}.weight_nn.layer{k}.weight'] / math.sqrt(h[k]) for k in range(len(h) - 1)]
-            lay = {
-                'spec': L,
-                'sc': _Lin(L.sc, sd[L.sc.key], dev, spec.n_species if L.sc_type == 'nequip' else 0),
-                'si1': _Lin(L.si1, sd[L.si1.key], dev),
-                'si2': _Lin(L.si2, sd[L.si2.key], dev),
-                'mlp': [f32(w) for w in Wm],
-                'mlpT': [f32(np.ascontiguousarray(w.T)) for w in Wm],
-                'inv_denom': 1.0 / float(sd[f'{L.conv.name}.denominator'][0]),
-                'sig': L.conv.signature(), 'units': conv_codegen.n_units(L.conv),
-                'pieces': (_lib.GatePiece * len(L.gate.pieces))(*[
-                    _lib.GatePiece(p.kind, p.l, p.mul, p.in_off, p.in_stride, p.gate_off, p.out_off,
-                                   p.out_stride, p.act, p.cst) for p in L.gate.pieces]),
-            }
-            if not self.lib.has_conv(lay['sig']):
-                raise _lib.SevennError(
-                    f"no prebuilt conv kernel for signature {lay['sig']} ({ir.irreps_str(L.conv.lx.groups)}); "
-                    'build it with sevennet_exp_b200.build.build(extra_specs=...)')
-            self.layers.append(lay)
-        self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev)
-        self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev)
-        self.scale = f32(sd['rescale_atomic_energy.scale'])
-        self.shift = f32(sd['rescale_atomic_energy.shift'])
-        self.act_radial = ACT_ID[spec.act_radial]
-        self.cst_radial = ir.normalize2mom_const(spec.act_radial)
         self.n_launch = 0
         self._tc_cache = {}
         # dense contractions: 'auto' = tcgen05 3xTF32 arm for big row counts, exact-fp32 SIMT arm otherwise
         self.gemm_mode = os.environ.get('SEVENN_GEMM', 'auto')
         self.tc_min_rows = int(os.environ.get('SEVENN_TC_MIN_ROWS', '1024'))
         self.prof = None          # list of (name, cuda event) when profiling is on (bench.py)
+        self.act_radial, self.cst_radial = ACT_ID['silu'], ir.normalize2mom_const('silu')
 
     # ------------------------------------------------------------------ helpers
     def _mark(self, name):
@@ -239,8 +193,8 @@ class Engine:
             K, N = W.shape
             if k < len(Ws) - 1:
                 pre, act = self._empty(E, N), self._empty(E, N)
-                self._gemm(cur, 0, K, 0, W, pre, 0, N, 0, E, 1, N, K, epi=2, act=self.act_radial,
-                           cst=self.cst_radial, C2=act)
+                self._gemm(cur, 0, K, 0, W, pre, 0, N, 0, E, 1, N, K, epi=2, act=lay.get('act', self.act_radial),
+                           cst=lay.get('cst', self.cst_radial), C2=act)
                 pres.append(pre); acts.append(act); cur = act
             else:
                 w = self._empty(E, N)
@@ -262,11 +216,67 @@ class Engine:
             N, K = WT[k].shape   # WT[k] is [h_out, h_in]
             if k > 0:
                 nxt = self._empty(E, K)
-                self._gemm(cur, 0, N, 0, WT[k], nxt, 0, K, 0, E, 1, K, N, epi=3, act=self.act_radial,
-                           cst=self.cst_radial, P=pres[k - 1])
+                self._gemm(cur, 0, N, 0, WT[k], nxt, 0, K, 0, E, 1, K, N, epi=3, act=lay.get('act', self.act_radial),
+                           cst=lay.get('cst', self.cst_radial), P=pres[k - 1])
                 cur = nxt
             else:
                 self._gemm(cur, 0, N, 0, WT[k], demb, 0, K, 0, E, 1, K, N, epi=1)
+
+
+class Engine(Kernels):
+    def __init__(self, spec: ModelSpec, state_dict: Dict[str, torch.Tensor], lib: Optional[_lib.Lib] = None,
+                 device='cuda', keep_weights: bool = True):
+        super().__init__(lib, device)
+        self.spec = spec
+        self.keep_w = keep_weights
+        sd = {k: v.detach().cpu().numpy().astype(np.float64) for k, v in state_dict.items()
+              if k in spec.expected_keys()}
+        missing = [k for k in spec.expected_keys() if k not in sd]
+        if missing:
+            raise KeyError(f'state_dict misses {missing}')
+        for k, shp in spec.expected_keys().items():
+            if tuple(sd[k].shape) != shp:
+                raise ValueError(f'{k}: shape {sd[k].shape} != expected {shp}')
+        dev = self.dev
+        f32 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32, device=dev).contiguous()  # noqa: E731
+        self.coeffs = f32(sd['edge_embedding.basis_function.coeffs'])
+        # embedding table [S, d0]
+        emb = spec.embed
+        table = np.zeros((spec.n_species, emb.lout.dim))
+        for b in emb.blocks:
+            assert b.l == 0
+            o = emb.lout.group_off[b.g_out] + b.u_off_out
+            table[:, o:o + b.N] = emb.dense(sd[emb.key], b)
+        self.embed_table = f32(table)
+        self.d0 = emb.lout.dim
+        self.layers = []
+        for L in spec.layers:
+            h = L.conv.hidden
+            Wm = [sd[f'{L.conv.name}.weight_nn.layer{k}.weight'] / math.sqrt(h[k]) for k in range(len(h) - 1)]
+            lay = {
+                'spec': L,
+                'sc': _Lin(L.sc, sd[L.sc.key], dev, spec.n_species if L.sc_type == 'nequip' else 0),
+                'si1': _Lin(L.si1, sd[L.si1.key], dev),
+                'si2': _Lin(L.si2, sd[L.si2.key], dev),
+                'mlp': [f32(w) for w in Wm],
+                'mlpT': [f32(np.ascontiguousarray(w.T)) for w in Wm],
+                'inv_denom': 1.0 / float(sd[f'{L.conv.name}.denominator'][0]),
+                'sig': L.conv.signature(), 'units': conv_codegen.n_units(L.conv),
+                'pieces': (_lib.GatePiece * len(L.gate.pieces))(*[
+                    _lib.GatePiece(p.kind, p.l, p.mul, p.in_off, p.in_stride, p.gate_off, p.out_off,
+                                   p.out_stride, p.act, p.cst) for p in L.gate.pieces]),
+            }
+            if not self.lib.has_conv(lay['sig']):
+                raise _lib.SevennError(
+                    f"no prebuilt conv kernel for signature {lay['sig']} ({ir.irreps_str(L.conv.lx.groups)}); "
+                    'build it with sevennet_exp_b200.build.build(extra_specs=...)')
+            self.layers.append(lay)
+        self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev)
+        self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev)
+        self.scale = f32(sd['rescale_atomic_energy.scale'])
+        self.shift = f32(sd['rescale_atomic_energy.shift'])
+        self.act_radial = ACT_ID[spec.act_radial]
+        self.cst_radial = ir.normalize2mom_const(spec.act_radial)
 
     # ------------------------------------------------------------------ evaluation
     def evaluate(self, g: Graph, halo=None, want_forces: bool = True, debug: Optional[dict] = None):

@@ -1,0 +1,7 @@
+"""``sevenn.nn``-compatible modules on the B200 kernels (the reference's module seam)."""
+from .modules import (AtomGraphSequential, AtomReduce, BesselBasis, EdgeEmbedding, EquivariantGate,  # noqa: F401
+                      ForceStressOutputFromEdge, IrrepsConvolution, IrrepsLinear, OnehotEmbedding,
+                      PolynomialCutoff, Rescale, SelfConnectionIntro, SelfConnectionLinearIntro,
+                      SelfConnectionOutro, SpeciesWiseRescale, SphericalEncoding, XPLORCutoff,
+                      build_E3_equivariant_model, init_edge_embedding)
+from ._backend import set_lib  # noqa: F401

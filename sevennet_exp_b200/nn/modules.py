@@ -1,0 +1,496 @@
+"""Drop-in mirrors of the reference's ``sevenn.nn`` modules on the B200 kernels.
+
+Same class names, constructor arguments, ``forward(data) -> data`` contract, data-dict keys
+(sevenn/_keys.py) and parameter names / shapes as the reference, so a reference ``state_dict`` loads with
+``load_state_dict`` unchanged.  Node features cross every module boundary in e3nn's ``[mul][2l+1]``
+layout and are permuted to the library's ``[2l+1][mul]`` layout inside.  Gradients flow to activations
+only (see functional.py)."""
+import math
+from collections import OrderedDict
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from .. import _lib
+from .. import irreps as ir
+from .. import spec as sp
+from ..codegen import conv_codegen
+from ..engine import _Lin
+from . import functional as F
+from ._backend import get_lib, kernels, ptr
+
+# data keys (sevenn/_keys.py:26-86)
+EDGE_VEC, EDGE_IDX, EDGE_LEN = 'edge_vec', 'edge_index', 'edge_length'
+X, X_GHOST, NODE_ATTR, ATOM_TYPE = 'x', 'x_ghost', 'node_attr', 'atom_type'
+EDGE_ATTR, EDGE_EMB = 'edge_attr', 'edge_embedding'
+SC_TMP = 'self_cont_tmp'
+SCALED_AE, AE, E_TOT = 'scaled_atomic_energy', 'atomic_energy', 'inferred_total_energy'
+FORCE, STRESS = 'inferred_force', 'inferred_stress'
+POS, CELL, SHIFT, VOL, NATOMS, BATCH, NLOCAL = (
+    'pos', 'cell_lattice_vectors', 'pbc_shift', 'cell_volume', 'num_atoms', 'batch', 'nlocal')
+Z = 'atomic_numbers'
+GRAPH = '_b200_graph'          # cached CSR/CSC of data[EDGE_IDX] (private key, removed by force_output)
+
+
+def _irreps(x):
+    return ir.parse_irreps(x if isinstance(x, (str, list, tuple)) else str(x))
+
+
+def _perm(layout: ir.Layout, device):
+    p = torch.as_tensor(layout.perm_to_e3nn(), device=device)
+    return p, torch.argsort(p)
+
+
+class _Weight(nn.Module):
+    """Stand-in for the e3nn submodule that owns a flat ``weight`` (o3.Linear / FullyConnectedTensorProduct)."""
+
+    def __init__(self, numel):
+        super().__init__()
+        self.weight = nn.Parameter(torch.randn(numel))
+
+
+class _LinearCore(nn.Module):
+    """Flat e3nn weight -> device blocks (rebuilt when the parameter changes)."""
+
+    def _setup(self, spec: sp.LinearSpec, owner: str, by_type_S: int = 0):
+        self._spec, self._owner, self._S = spec, owner, by_type_S
+        self._cache = None
+
+    def _lin(self, device) -> _Lin:
+        w = getattr(self, self._owner).weight
+        key = (w._version, w.data_ptr(), str(device))
+        if self._cache is None or self._cache[0] != key:
+            flat = w.detach().cpu().numpy().astype(np.float64)
+            self._cache = (key, _Lin(self._spec, flat, device, self._S))
+        return self._cache[1]
+
+    def _apply_linear(self, x, types=None):
+        dev = x.device
+        p_in, inv_in = _perm(self._spec.lin, dev)
+        p_out, _ = _perm(self._spec.lout, dev)
+        y = F.LinearFn.apply(x.float()[:, inv_in], self._lin(dev), types)
+        return y[:, p_out]
+
+
+# ------------------------------------------------------------------ edge --
+class BesselBasis(nn.Module):
+    """sevenn/nn/edge_embedding.py:81-104 (parameter holder; evaluated inside EdgeEmbedding)."""
+
+    def __init__(self, cutoff_length, bessel_basis_num=8, trainable_coeff=True):
+        super().__init__()
+        self.num_basis, self.cutoff_length = bessel_basis_num, float(cutoff_length)
+        c = torch.FloatTensor([n * math.pi / cutoff_length for n in range(1, bessel_basis_num + 1)])
+        self.coeffs = nn.Parameter(c, requires_grad=False) if trainable_coeff else c
+
+
+class PolynomialCutoff(nn.Module):
+    """sevenn/nn/edge_embedding.py:107-133"""
+
+    def __init__(self, cutoff_length, poly_cut_p_value=6):
+        super().__init__()
+        self.cutoff_length, self.p = float(cutoff_length), float(poly_cut_p_value)
+        self.kind, self.r_on = 0, 0.0
+
+
+class XPLORCutoff(nn.Module):
+    """sevenn/nn/edge_embedding.py:136-161"""
+
+    def __init__(self, cutoff_length, cutoff_on):
+        super().__init__()
+        self.cutoff_length, self.r_on = float(cutoff_length), float(cutoff_on)
+        self.kind, self.p = 1, 6.0
+
+
+class SphericalEncoding(nn.Module):
+    """sevenn/nn/edge_embedding.py:165-186"""
+
+    def __init__(self, lmax, parity=-1, normalization='component', normalize=True):
+        super().__init__()
+        assert normalization == 'component' and 0 <= lmax <= 3
+        self.lmax, self.parity, self.normalize = lmax, parity, normalize
+        self.irreps_out = ir.spherical_harmonics_irreps(lmax, parity)
+
+
+class EdgeEmbedding(nn.Module):
+    """sevenn/nn/edge_embedding.py:190-217: one fused kernel for r, Bessel x cutoff and the harmonics."""
+
+    def __init__(self, basis_module, cutoff_module, spherical_module):
+        super().__init__()
+        self.basis_function, self.cutoff_function, self.spherical = basis_module, cutoff_module, spherical_module
+
+    def forward(self, data):
+        rvec = data[EDGE_VEC]
+        b, c, s = self.basis_function, self.cutoff_function, self.spherical
+        args = (s.lmax, bool(s.normalize), b.num_basis, c.kind, c.cutoff_length, c.p, c.r_on)
+        Y, emb = F.EdgeEmbedFn.apply(rvec, b.coeffs.to(rvec.device), args)
+        data[EDGE_LEN] = torch.linalg.norm(rvec.detach(), dim=-1)
+        data[EDGE_EMB], data[EDGE_ATTR] = emb, Y
+        return data
+
+
+# ------------------------------------------------------------------ node --
+class OnehotEmbedding(nn.Module):
+    """sevenn/nn/node_embedding.py:15-53"""
+
+    def __init__(self, num_classes, data_key_x=X, data_key_out=None, data_key_save=None,
+                 data_key_additional=None):
+        super().__init__()
+        self.num_classes, self.key_x = num_classes, data_key_x
+        self.key_output = data_key_out or data_key_x
+        self.key_save, self.key_add = data_key_save, data_key_additional
+
+    def forward(self, data):
+        inp = data[self.key_x]
+        embd = torch.nn.functional.one_hot(inp, self.num_classes).float()
+        data[self.key_output] = embd
+        if self.key_add is not None:
+            data[self.key_add] = embd
+        if self.key_save is not None:
+            data[self.key_save] = inp
+        return data
+
+
+class IrrepsLinear(_LinearCore):
+    """sevenn/nn/linear.py:14-100 (no bias, no modality)."""
+
+    def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, biases=False):
+        super().__init__()
+        if biases:
+            raise NotImplementedError('use_bias_in_linear is outside the B200 hot path')
+        self.key_input, self.key_output = data_key_in, data_key_out or data_key_in
+        self.irreps_in, self.irreps_out = _irreps(irreps_in), _irreps(irreps_out)
+        spec = sp.make_linear('linear.weight', self.irreps_in, self.irreps_out)
+        self.linear = _Weight(spec.numel)
+        self._setup(spec, 'linear')
+
+    def forward(self, data):
+        data[self.key_output] = self._apply_linear(data[self.key_input])
+        return data
+
+
+class SelfConnectionIntro(_LinearCore):
+    """sevenn/nn/self_connection.py:10-64: FullyConnectedTensorProduct(x, one_hot) = species-indexed linear."""
+
+    def __init__(self, irreps_in, irreps_operand, irreps_out):
+        super().__init__()
+        S = ir.irreps_dim(_irreps(irreps_operand))
+        spec = sp.make_linear('fc_tensor_product.weight', _irreps(irreps_in), ir.simplify(_irreps(irreps_out)))
+        spec.numel *= S
+        self.fc_tensor_product = _Weight(spec.numel)
+        self._setup(spec, 'fc_tensor_product', by_type_S=S)
+
+    def forward(self, data):
+        types = data[NODE_ATTR].argmax(dim=1).to(torch.int32).contiguous()
+        data[SC_TMP] = self._apply_linear(data[X], types)
+        return data
+
+
+class SelfConnectionLinearIntro(_LinearCore):
+    """sevenn/nn/self_connection.py:68-108"""
+
+    def __init__(self, irreps_in, irreps_operand, irreps_out):
+        super().__init__()
+        spec = sp.make_linear('linear.weight', _irreps(irreps_in), ir.simplify(_irreps(irreps_out)))
+        self.linear = _Weight(spec.numel)
+        self._setup(spec, 'linear')
+
+    def forward(self, data):
+        data[SC_TMP] = self._apply_linear(data[X])
+        return data
+
+
+class SelfConnectionOutro(nn.Module):
+    """sevenn/nn/self_connection.py:112-128"""
+
+    def forward(self, data):
+        data[X] = data[X] + data[SC_TMP]
+        del data[SC_TMP]
+        return data
+
+
+class EquivariantGate(nn.Module):
+    """sevenn/nn/equivariant_gate.py:13-61 (activations by name: 'silu', 'tanh', ...)."""
+
+    def __init__(self, irreps_x, act_scalar_dict, act_gate_dict):
+        super().__init__()
+        name = lambda a: a if isinstance(a, str) else getattr(a, '__name__', str(a))  # noqa: E731
+        self._gspec, self._irreps_in, self._irreps_out = sp.make_gate(
+            _irreps(irreps_x), {k: name(v) for k, v in act_scalar_dict.items()},
+            {k: name(v) for k, v in act_gate_dict.items()})
+        g = self._gspec
+        self._gate = dict(din=g.lin.dim, dout=g.lout.dim, n_pieces=len(g.pieces),
+                          pieces=(_lib.GatePiece * len(g.pieces))(*[
+                              _lib.GatePiece(p.kind, p.l, p.mul, p.in_off, p.in_stride, p.gate_off, p.out_off,
+                                             p.out_stride, p.act, p.cst) for p in g.pieces]))
+
+    def get_gate_irreps_in(self):
+        return self._irreps_in
+
+    def forward(self, data):
+        x = data[X]
+        _, inv_in = _perm(self._gspec.lin, x.device)
+        p_out, _ = _perm(self._gspec.lout, x.device)
+        data[X] = F.GateFn.apply(x[:, inv_in], self._gate)[:, p_out]
+        return data
+
+
+# ---------------------------------------------------------- convolution --
+class _FCN(nn.Module):
+    """Parameter holder mirroring e3nn.nn.FullyConnectedNet: layer{k}.weight of shape [h_in, h_out]."""
+
+    def __init__(self, hs):
+        super().__init__()
+        for k in range(len(hs) - 1):
+            lay = nn.Module()
+            lay.weight = nn.Parameter(torch.randn(hs[k], hs[k + 1]))
+            self.add_module(f'layer{k}', lay)
+        self.hs = list(hs)
+
+
+class IrrepsConvolution(nn.Module):
+    """sevenn/nn/convolution.py:28-139: radial MLP (tcgen05 GEMMs) + fused gather/TP/segment-sum kernel."""
+
+    def __init__(self, irreps_x, irreps_filter, irreps_out, weight_layer_input_to_hidden,
+                 weight_layer_act='silu', denominator=1.0, train_denominator=False, is_parallel=False):
+        super().__init__()
+        act = weight_layer_act if isinstance(weight_layer_act, str) else getattr(weight_layer_act, '__name__', '')
+        self.denominator = nn.Parameter(torch.FloatTensor([denominator]), requires_grad=False)
+        self.is_parallel = is_parallel
+        hidden = list(weight_layer_input_to_hidden)
+        self._conv = sp.make_conv('convolution', ir.simplify(_irreps(irreps_x)), _irreps(irreps_filter),
+                                  _irreps(irreps_out), hidden)
+        self.weight_numel = self._conv.wn
+        self.irreps_x, self.irreps_filter = _irreps(irreps_x), _irreps(irreps_filter)
+        self.irreps_mid = self._conv.lmid.entries
+        self.weight_nn = _FCN(hidden + [self._conv.wn])
+        self._act, self._cst = sp.ACT_ID[act], ir.normalize2mom_const(act)
+        self._sig = self._conv.signature()
+        self._cache = None
+
+    def _layer(self, device):
+        ws = [getattr(self.weight_nn, f'layer{k}').weight for k in range(len(self.weight_nn.hs) - 1)]
+        key = tuple((w._version, w.data_ptr()) for w in ws) + (str(device),)
+        if self._cache is None or self._cache[0] != key:
+            hs = self.weight_nn.hs
+            Wm = [w.detach().cpu().double().numpy() / math.sqrt(hs[k]) for k, w in enumerate(ws)]
+            f32 = lambda a: torch.tensor(np.ascontiguousarray(a), dtype=torch.float32, device=device)  # noqa: E731
+            self._cache = (key, {'mlp': [f32(w) for w in Wm], 'mlpT': [f32(w.T) for w in Wm],
+                                 'act': self._act, 'cst': self._cst})
+        return self._cache[1]
+
+    def forward(self, data):
+        x = data[X]
+        dev = x.device
+        lib = get_lib()
+        if not lib.has_conv(self._sig):
+            raise _lib.SevennError(f'no prebuilt conv kernel for signature {self._sig}; build it with '
+                                   'sevennet_exp_b200.build.build(extra_specs=...)')
+        if self.is_parallel:
+            x = torch.cat([x, data[X_GHOST]])
+        n_nodes = x.shape[0]
+        n_dst = int(data[NLOCAL]) if self.is_parallel else n_nodes
+        cached = data.get(GRAPH)
+        if cached is None or cached[0]['n_nodes'] != n_nodes or cached[0]['n_dst'] != n_dst:
+            cached = F.build_graph(data[EDGE_IDX], n_nodes, n_dst, dev)
+            data[GRAPH] = cached
+        graph, perm = cached
+        emb, Y = data[EDGE_EMB], data[EDGE_ATTR]
+        if perm is not None:
+            emb, Y = emb[perm], Y[perm]
+        w = F.RadialMLPFn.apply(emb, self._layer(dev))
+        _, inv_x = _perm(self._conv.lx, dev)
+        p_mid, _ = _perm(self._conv.lmid, dev)
+        meta = dict(sig=self._sig, dx=self._conv.lx.dim, dmid=self._conv.lmid.dim, wn=self._conv.wn,
+                    units=conv_codegen.n_units(self._conv), inv_denom=1.0 / float(self.denominator.item()))
+        out = F.ConvFn.apply(x.float()[:, inv_x], Y, w, graph, meta)
+        data[X] = out[:, p_mid]
+        return data
+
+
+# --------------------------------------------------------------- output --
+class Rescale(nn.Module):
+    """sevenn/nn/scale.py:22-56"""
+
+    def __init__(self, shift, scale, train_shift_scale=False):
+        super().__init__()
+        self.shift = nn.Parameter(torch.FloatTensor([shift]), requires_grad=False)
+        self.scale = nn.Parameter(torch.FloatTensor([scale]), requires_grad=False)
+
+    def forward(self, data):
+        data[AE] = data[SCALED_AE] * self.scale + self.shift
+        return data
+
+
+class SpeciesWiseRescale(nn.Module):
+    """sevenn/nn/scale.py:60-161"""
+
+    def __init__(self, shift, scale, train_shift_scale=False):
+        super().__init__()
+        n = len(shift) if isinstance(shift, list) else len(scale)
+        shift = [shift] * n if isinstance(shift, float) else shift
+        scale = [scale] * n if isinstance(scale, float) else scale
+        self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=False)
+        self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=False)
+
+    def forward(self, data):
+        idx = data[ATOM_TYPE]
+        data[AE] = data[SCALED_AE] * self.scale[idx].view(-1, 1) + self.shift[idx].view(-1, 1)
+        return data
+
+
+class AtomReduce(nn.Module):
+    """sevenn/nn/linear.py:104-141 (single graph; fp64 accumulation)."""
+
+    def __init__(self):
+        super().__init__()
+        self._is_batch_data = False
+
+    def forward(self, data):
+        if self._is_batch_data:
+            raise NotImplementedError('batched graphs are SURVEY 8f-1 (training path)')
+        data[E_TOT] = torch.sum(data[AE].double()).to(data[AE].dtype)
+        return data
+
+
+class ForceStressOutputFromEdge(nn.Module):
+    """sevenn/nn/force_output.py:140-224: f_ij = dE/d edge_vec (reverse kernels via autograd), then one
+    kernel for F_i = sum_{centre i} f - sum_{neighbour i} f and the per-atom virial."""
+
+    def __init__(self):
+        super().__init__()
+        self._is_batch_data = False
+
+    def forward(self, data):
+        if self._is_batch_data:
+            raise NotImplementedError('batched graphs are SURVEY 8f-1 (training path)')
+        tot = int(torch.sum(data[NATOMS]))
+        rij = data[EDGE_VEC]
+        fij = torch.autograd.grad([data[E_TOT].sum()], [rij], allow_unused=True)[0]
+        cached = data.pop(GRAPH, None)
+        if fij is None:
+            return data
+        dev = rij.device
+        k = kernels(dev)
+        if cached is None or cached[0]['n_nodes'] != tot or cached[0]['n_dst'] != tot:
+            cached = F.build_graph(data[EDGE_IDX], tot, tot, dev)
+        graph, perm = cached
+        f, r = fij.detach().float(), rij.detach().float()
+        if perm is not None:
+            f, r = f[perm], r[perm]
+        f, r = f.contiguous(), r.contiguous()
+        Fo, vir = k._empty(tot, 3), k._empty(tot, 6)
+        k.lib.call('sevenn_force_virial', ptr(f), ptr(r), ptr(graph['rowptr']), tot, ptr(graph['cptr']),
+                   ptr(graph['cedge']), tot, ptr(Fo), ptr(vir), k._stream())
+        k.n_launch += 1
+        data[FORCE] = Fo
+        vol = data[VOL]
+        data[STRESS] = (torch.neg(vir.double().sum(dim=0)) / vol.double().reshape(-1)[0]).to(f.dtype)
+        return data
+
+
+# ----------------------------------------------------------- sequential --
+class AtomGraphSequential(nn.Sequential):
+    """sevenn/nn/sequential.py:22-205"""
+
+    def __init__(self, modules, cutoff=0.0, type_map=None, eval_type_map=True, data_key_grad=None):
+        super().__init__(OrderedDict(modules))
+        self.cutoff, self.type_map, self.key_grad = cutoff, type_map, data_key_grad
+        self.eval_type_map = eval_type_map and type_map is not None
+        if type_map is not None:
+            lut = -torch.ones(120, dtype=torch.long)
+            for z, i in type_map.items():
+                lut[z] = i
+            self.register_buffer('z_to_onehot_tensor', lut, persistent=False)
+
+    def set_is_batch_data(self, flag):
+        for m in self:
+            if hasattr(m, '_is_batch_data'):
+                m._is_batch_data = flag
+
+    def forward(self, data: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        if self.eval_type_map:
+            data[X] = self.z_to_onehot_tensor.to(data[Z].device)[data[Z]]
+        if self.key_grad is not None:
+            data[self.key_grad].requires_grad_(True)
+        for m in self:
+            data = m(data)
+        return data
+
+
+def init_edge_embedding(cfg):
+    """sevenn/model_build.py:69-116 (single cutoff)."""
+    env = dict(cfg['cutoff_function'])
+    name = env.pop('cutoff_function_name')
+    if name == 'poly_cut':
+        cut = PolynomialCutoff(cfg['cutoff'], **env)
+    elif name == 'XPLOR':
+        cut = XPLORCutoff(cfg['cutoff'], **env)
+    else:
+        raise ValueError(name)
+    lmax_edge = cfg['lmax_edge'] if cfg['lmax_edge'] > 0 else cfg['lmax']
+    sph = SphericalEncoding(lmax_edge, -1 if cfg['is_parity'] else 1, normalize=cfg['_normalize_sph'])
+    rb = dict(cfg['radial_basis'])
+    if rb.pop('radial_basis_name') != 'bessel':
+        raise ValueError('only the bessel radial basis is on the hot path')
+    return EdgeEmbedding(BesselBasis(cfg['cutoff'], **rb), cut, sph)
+
+
+def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGraphSequential:
+    """sevenn/model_build.py:384-576 + nn/interaction_blocks.py:12-88: same layer names, same order."""
+    import copy
+    if parallel:
+        raise NotImplementedError('segment models for LAMMPS e3gnn/parallel: use sevennet_exp_b200.domain')
+    cfg = {**sp.DEFAULTS, **copy.deepcopy(config)}
+    layers = OrderedDict()
+    S, C, L = cfg['_number_of_species'], cfg['channel'], cfg['num_convolution_layer']
+    lmax_node = cfg['lmax_node'] if cfg['lmax_node'] > 0 else cfg['lmax']
+    sc_cls = {'nequip': SelfConnectionIntro, 'linear': SelfConnectionLinearIntro}[cfg['self_connection_type']]
+    manual = None
+    if cfg['irreps_manual'] is not False:
+        manual = [ir.parse_irreps(s) for s in cfg['irreps_manual']]
+    denom = cfg['conv_denominator']
+    denom = list(denom) if isinstance(denom, (list, tuple)) else [denom] * L
+    ee = init_edge_embedding(cfg)
+    irreps_filter = ee.spherical.irreps_out
+    layers['edge_embedding'] = ee
+    one_hot = [(S, (0, 1))]
+    irreps_x = [(C, (0, 1))] if manual is None else manual[0]
+    layers['onehot_idx_to_onehot'] = OnehotEmbedding(S, X, X, ATOM_TYPE, NODE_ATTR)
+    layers['onehot_to_feature_x'] = IrrepsLinear(one_hot, irreps_x, X, biases=cfg['use_bias_in_linear'])
+    wnn = [ee.basis_function.num_basis] + list(cfg['weight_nn_hidden_neurons'])
+    for t in range(L):
+        parity_mode, lm = 'full', lmax_node
+        if t == L - 1:
+            lm, parity_mode = 0, 'even'
+        irreps_out = (ir.infer_irreps_out(irreps_x, irreps_filter, lm, parity_mode, C)
+                      if manual is None else manual[t + 1])
+        out_lmax = max(l for _, (l, _) in irreps_out)
+        irreps_out_tp = ir.infer_irreps_out(irreps_x, irreps_filter, out_lmax, parity_mode, False)
+        gate = EquivariantGate(irreps_out, cfg['act_scalar'], cfg['act_gate'])
+        gate_in = gate.get_gate_irreps_in()
+        layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, one_hot, gate_in)
+        layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X)
+        layers[f'{t}_convolution'] = IrrepsConvolution(irreps_x, irreps_filter, irreps_out_tp, wnn,
+                                                       cfg['act_radial'], denom[t], cfg['train_denominator'])
+        layers[f'{t}_self_interaction_2'] = IrrepsLinear(layers[f'{t}_convolution'].irreps_mid,
+                                                         ir.simplify(gate_in), X)
+        layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()
+        layers[f'{t}_equivariant_gate'] = gate
+        irreps_x = ir.simplify(gate._irreps_out)
+    hidden = [(ir.irreps_dim(irreps_x) // 2, (0, 1))]
+    layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X)
+    layers['reduce_hidden_to_energy'] = IrrepsLinear(hidden, [(1, (0, 1))], X, SCALED_AE)
+    shift, scale = cfg['shift'], cfg['scale']
+    shift = shift.tolist() if hasattr(shift, 'tolist') else shift
+    scale = scale.tolist() if hasattr(scale, 'tolist') else scale
+    if isinstance(shift, float) and isinstance(scale, float):
+        layers['rescale_atomic_energy'] = Rescale(shift, scale, cfg['train_shift_scale'])
+    else:
+        shift = shift * S if isinstance(shift, list) and len(shift) == 1 else shift
+        scale = scale * S if isinstance(scale, list) and len(scale) == 1 else scale
+        layers['rescale_atomic_energy'] = SpeciesWiseRescale(shift, scale, cfg['train_shift_scale'])
+    layers['reduce_total_enegy'] = AtomReduce()
+    layers['force_output'] = ForceStressOutputFromEdge()
+    return AtomGraphSequential(layers, cutoff=cfg['cutoff'], type_map=cfg['_type_map'], data_key_grad=EDGE_VEC)

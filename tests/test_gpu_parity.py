@@ -252,3 +252,37 @@ def test_engine_tc_and_simt_arms_agree(lib):
     assert abs(out['tc']['energy'] - out['simt']['energy']) / n < 5e-6
     assert np.abs(out['tc']['forces'] - out['simt']['forces']).max() < 5e-5
     assert np.abs(out['tc']['inferred_stress'] - out['simt']['inferred_stress']).max() * KBAR < 1e-3
+
+
+@pytest.mark.parametrize('name,n_atoms', [('test-so3-l2', 48), ('7net-0', 64)])
+def test_nn_module_seam_on_gpu(lib, name, n_atoms):
+    """sevennet_exp_b200.nn.AtomGraphSequential (reference module names, reference state_dict, shuffled
+    edge order, forces through torch.autograd.grad over our reverse kernels) vs the fp64 oracle."""
+    import copy
+    from sevennet_exp_b200 import nn as bnn
+    cfg, om = _random_model(name)
+    if name == '7net-0':
+        numbers, pos, cell = diamond_si((2, 2, 2))
+    else:
+        numbers, pos, cell = random_cell(n_atoms, list(cfg['_type_map']), density=0.05, seed=3)
+    model = bnn.build_E3_equivariant_model(cfg).eval()
+    missing, _ = model.load_state_dict(om.state_dict(), strict=False)
+    assert not missing
+    model = model.cuda()
+    torch.set_default_dtype(torch.float64)
+    try:
+        g64 = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'], dtype=torch.float64)
+        ref = copy.deepcopy(om).double()(dict(g64))
+    finally:
+        torch.set_default_dtype(torch.float32)
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+    p = torch.from_numpy(np.random.default_rng(0).permutation(g[S.EDGE_IDX].shape[1]))
+    g[S.EDGE_IDX], g[S.EDGE_VEC] = g[S.EDGE_IDX][:, p].contiguous(), g[S.EDGE_VEC].detach()[p].contiguous()
+    data = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in g.items()}
+    out = model(data)
+    n = len(numbers)
+    dE = abs(out[S.E_TOT].item() - ref[S.E_TOT].item()) / n
+    dF = (out[S.FORCE].cpu().double() - ref[S.FORCE].detach()).abs().max().item()
+    dS = (out[S.STRESS].cpu().double() - ref[S.STRESS].detach()).abs().max().item() * KBAR
+    assert dE < 1e-5 and dF < 1e-4, (dE, dF)
+    assert dS < 1e-3 * max(1.0, ref[S.STRESS].abs().max().item() * KBAR * 1e-3), dS

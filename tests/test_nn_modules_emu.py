@@ -1,0 +1,120 @@
+"""sevennet_exp_b200.nn (the reference's module seam) against the oracle modules of the same name:
+same state_dict, same data dict, arbitrary edge order.  Kernels run through the emulation build."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import sevenn_ref as S
+from sevennet_exp_b200 import nn as bnn
+from sevennet_exp_b200 import presets, spec as sp
+from sevennet_exp_b200.checkpoint import patch_state_dict
+from tests.emu_util import build_full_emu
+from tests.structures import random_cell
+
+KBAR = 1602.1766208
+
+
+@pytest.fixture(autouse=True)
+def _reset_lib():
+    yield
+    bnn.set_lib(None)
+
+
+def _shuffled(g, seed=0):
+    """The reference accepts edges in any order; so must the drop-in."""
+    E = g[S.EDGE_IDX].shape[1]
+    p = torch.from_numpy(np.random.default_rng(seed).permutation(E))
+    g = dict(g)
+    g[S.EDGE_IDX] = g[S.EDGE_IDX][:, p].contiguous()
+    g[S.EDGE_VEC] = g[S.EDGE_VEC].detach()[p].contiguous()
+    return g
+
+
+def _run_pair(cfg, sd, oracle_model, numbers, pos, cell, shuffle=True):
+    spec = sp.build_spec(cfg)
+    bnn.set_lib(build_full_emu([L.conv for L in spec.layers]))
+    model = bnn.build_E3_equivariant_model(cfg).eval()
+    missing, unexpected = model.load_state_dict(sd, strict=False)
+    assert not missing, missing                    # sevenn/checkpoint.py:306-310 contract
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+    if shuffle:
+        g = _shuffled(g)
+    ref = oracle_model({k: (v.clone() if torch.is_tensor(v) else v) for k, v in g.items()})
+    out = model({k: (v.clone() if torch.is_tensor(v) else v) for k, v in g.items()})
+    n = len(numbers)
+    dE = abs(out[S.E_TOT].item() - ref[S.E_TOT].item()) / n
+    dF = (out[S.FORCE] - ref[S.FORCE].detach()).abs().max().item()
+    dS = (out[S.STRESS] - ref[S.STRESS].detach()).abs().max().item() * KBAR
+    dA = (out[S.AE] - ref[S.AE].detach()).abs().max().item()
+    assert dE < 1e-5 and dF < 1e-4 and dA < 1e-4, (dE, dF, dA)
+    assert dS < 1e-3 * max(1.0, ref[S.STRESS].abs().max().item() * KBAR * 1e-3), dS
+    assert '_b200_graph' not in out
+    return model
+
+
+@pytest.mark.parametrize('name', ['test-so3-l2'])
+def test_sequential_matches_oracle_random_weights(name):
+    cfg = dict(presets.PRESETS[name])
+    torch.manual_seed(777)
+    om = S.build_model(cfg).eval()
+    numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=5)
+    model = _run_pair(cfg, om.state_dict(), om, numbers, pos, cell)
+    # module names and order are the reference's (state_dict prefixes)
+    assert [n for n, _ in model.named_children()] == [n for n, _ in om.named_children()]
+
+
+def test_sequential_cp0_checkpoint_o3_nequip_sc(golden_dir):
+    om, cfg = S.load_checkpoint(os.path.join(golden_dir, 'cp0_model.pt'))
+    om.eval()
+    cp = torch.load(os.path.join(golden_dir, 'cp0_model.pt'))
+    sd = patch_state_dict(sp.build_spec(cfg), cp['model_state_dict'], cfg.get('version', '0.0.0'))
+    fr = np.load(os.path.join(golden_dir, 'hfo2_frames.npz'))
+    num, pos, cell = (fr[f'f0_{n}'] for n in ('numbers', 'pos', 'cell'))
+    _run_pair(cfg, sd, om, num, pos, cell)
+
+
+def test_single_modules_match_oracle():
+    """Module by module (forward value and gradient w.r.t. the input) on e3nn-layout tensors."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    spec = sp.build_spec(cfg)
+    bnn.set_lib(build_full_emu([L.conv for L in spec.layers]))
+    torch.manual_seed(3)
+    om = S.build_model(cfg).eval()
+    bm = bnn.build_E3_equivariant_model(cfg).eval()
+    bm.load_state_dict(om.state_dict(), strict=False)
+    numbers, pos, cell = random_cell(12, list(cfg['_type_map']), density=0.05, seed=1)
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+
+    def both(name, data_o, data_b, key_in, key_out):
+        xo = data_o[key_in].detach().clone().requires_grad_(True)
+        xb = data_b[key_in].detach().clone().requires_grad_(True)
+        data_o, data_b = dict(data_o), dict(data_b)
+        data_o[key_in], data_b[key_in] = xo, xb
+        yo = getattr(om, name)(data_o)[key_out]
+        yb = getattr(bm, name)(data_b)[key_out]
+        assert torch.allclose(yo, yb, atol=2e-5, rtol=1e-4), (name, (yo - yb).abs().max())
+        seed = torch.randn_like(yo)
+        go, = torch.autograd.grad((yo * seed).sum(), xo)
+        gb, = torch.autograd.grad((yb * seed).sum(), xb)
+        assert torch.allclose(go, gb, atol=5e-5, rtol=1e-4), (name, (go - gb).abs().max())
+        return data_o, data_b
+
+    do = {k: v for k, v in g.items()}
+    do[S.X] = om.z_to_onehot_tensor[do[S.Z]]
+    db = dict(do)
+    # edge embedding: value + d/d(edge_vec)
+    for key in (S.EDGE_ATTR, S.EDGE_EMB):
+        both('edge_embedding', do, db, S.EDGE_VEC, key)
+    do, db = om.edge_embedding(do), bm.edge_embedding(db)
+    do, db = om.onehot_idx_to_onehot(do), bm.onehot_idx_to_onehot(db)
+    do, db = om.onehot_to_feature_x(do), bm.onehot_to_feature_x(db)
+    for t in range(2):
+        do, db = both(f'{t}_self_connection_intro', do, db, S.X, S.SC_TMP)
+        do, db = both(f'{t}_self_interaction_1', do, db, S.X, S.X)
+        do, db = both(f'{t}_convolution', do, db, S.X, S.X)
+        do, db = both(f'{t}_self_interaction_2', do, db, S.X, S.X)
+        do = getattr(om, f'{t}_self_connection_outro')(do)
+        db = getattr(bm, f'{t}_self_connection_outro')(db)
+        do, db = both(f'{t}_equivariant_gate', do, db, S.X, S.X)
