@@ -93,8 +93,10 @@ __device__ __forceinline__ void sts128(uint32_t a, float4 v) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(a), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 // the tcgen05 arm fuses SiLU only (act_radial default, sevenn/_const.py:102); other activations use the SIMT arm
-__device__ __forceinline__ float silu_f(float x) { return x / (1.f + expf(-x)); }
-__device__ __forceinline__ float dsilu_f(float x) { const float s = 1.f / (1.f + expf(-x)); return s * (1.f + x * (1.f - s)); }
+// MUFU-based (ex2.approx / rcp.approx): ~3e-7 relative error for |x| < 5.  The libm forms cost ~40 instructions per
+// element, which made the 128 x 64 SiLU epilogue (8,192 evaluations per tile) the bottleneck of the K <= 64 layers.
+__device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.f + __expf(-x)); }
+__device__ __forceinline__ float dsilu_f(float x) { const float s = __fdividef(1.f, 1.f + __expf(-x)); return s * (1.f + x * (1.f - s)); }
 __device__ __forceinline__ float tc_act_unused(int id, float x) {
   switch (id) {
     case 0: return x / (1.f + expf(-x));
@@ -113,6 +115,104 @@ __device__ __forceinline__ float tc_dact_unused(int id, float x) {
     case 3: return x > 0.f ? 1.f : 0.f;
     case 4: { const float s = 1.f / (1.f + expf(-x)); return s * (1.f - s); }
     default: return 1.f / (1.f + expf(-x));
+  }
+}
+
+// Epilogue of one 128-row tile for one warp (TMEM lanes 32*ew ..): tcgen05.ld 32 columns at a time, transpose through
+// XOR-swizzled smem, full-line coalesced 16 B accesses with the fused epilogue.
+template <int EPI>
+__device__ __forceinline__ void tc_epilogue_tile(const sevenn_gemm_args& g, uint32_t d_taddr, uint8_t* tb, int ew, int lane,
+                                                 const long long (&roff)[8], int n0, int ncols, int vec4, int mode,
+                                                 int part2_cols = 0) {
+  const int sub = lane >> 3, ch = lane & 7; (void)sub;
+  for (int cc = 0; cc < ncols; cc += 32) {
+    uint32_t v[32];
+    const uint32_t taddr = d_taddr + ((uint32_t)(ew * 32) << 16) + (uint32_t)cc;
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    if (part2_cols) {                                  // accumulator split over two issuing warps: D = D_x + D_y
+      uint32_t u[32];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+          : "=r"(u[0]), "=r"(u[1]), "=r"(u[2]), "=r"(u[3]), "=r"(u[4]), "=r"(u[5]), "=r"(u[6]), "=r"(u[7]),
+            "=r"(u[8]), "=r"(u[9]), "=r"(u[10]), "=r"(u[11]), "=r"(u[12]), "=r"(u[13]), "=r"(u[14]), "=r"(u[15]),
+            "=r"(u[16]), "=r"(u[17]), "=r"(u[18]), "=r"(u[19]), "=r"(u[20]), "=r"(u[21]), "=r"(u[22]), "=r"(u[23]),
+            "=r"(u[24]), "=r"(u[25]), "=r"(u[26]), "=r"(u[27]), "=r"(u[28]), "=r"(u[29]), "=r"(u[30]), "=r"(u[31])
+          : "r"(taddr + (uint32_t)part2_cols) : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int q = 0; q < 32; ++q) v[q] = __float_as_uint(__uint_as_float(v[q]) + __uint_as_float(u[q]));
+    }
+    if (mode & 2) continue;
+    // transpose through smem: thread = row writes 8 chunks, XOR-swizzled (conflict free both ways)
+    const uint32_t tbs = smem_u32(tb);
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      sts128(tbs + lane * 128 + ((q ^ (lane & 7)) << 4),
+             make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                         __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])));
+    __syncwarp();
+    const int col = cc + ch * 4;                     // first of this lane's 4 columns (tile-relative)
+    const int nvalid = ncols - col;                  // >= 4 -> whole float4 valid
+    float4 x[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int row = 4 * i + sub;
+      x[i] = lds128(tbs + row * 128 + ((ch ^ (row & 7)) << 4));
+    }
+    if (vec4 && nvalid >= 4) {
+      float4 aux[8];
+      if (EPI == 1 || EPI == 3) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (roff[i] >= 0)
+            aux[i] = *reinterpret_cast<const float4*>((EPI == 1 ? g.C : g.P) + roff[i] + n0 + col);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (roff[i] < 0) continue;
+        float4* c4 = reinterpret_cast<float4*>(g.C + roff[i] + n0 + col);
+        const float4 xv = x[i];
+        if (EPI == 0) {
+          *c4 = xv;
+        } else if (EPI == 1) {
+          *c4 = make_float4(aux[i].x + xv.x, aux[i].y + xv.y, aux[i].z + xv.z, aux[i].w + xv.w);
+        } else if (EPI == 2) {
+          *c4 = xv;
+          *reinterpret_cast<float4*>(g.C2 + roff[i] + n0 + col) =
+              make_float4(g.cst * silu_f(xv.x), g.cst * silu_f(xv.y), g.cst * silu_f(xv.z), g.cst * silu_f(xv.w));
+        } else {
+          *c4 = make_float4(xv.x * g.cst * dsilu_f(aux[i].x), xv.y * g.cst * dsilu_f(aux[i].y),
+                            xv.z * g.cst * dsilu_f(aux[i].z), xv.w * g.cst * dsilu_f(aux[i].w));
+        }
+      }
+    } else if (nvalid > 0) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        if (roff[i] < 0) continue;
+        const float xs[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          if (e >= nvalid) break;
+          float* cp = g.C + roff[i] + n0 + col + e;
+          if (EPI == 0) *cp = xs[e];
+          else if (EPI == 1) *cp += xs[e];
+          else if (EPI == 2) { *cp = xs[e]; g.C2[roff[i] + n0 + col + e] = g.cst * silu_f(xs[e]); }
+          else *cp = xs[e] * g.cst * dsilu_f(g.P[roff[i] + n0 + col + e]);
+        }
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -306,82 +406,232 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcParams P
       mbar_wait(tfull_bar(ab), aphase);
       if (ew == 0) DBG(2, it, 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      for (int cc = 0; cc < ncols; cc += 32) {
-        uint32_t v[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(ab * 256 + cc);
-        asm volatile(
-            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-            : "r"(taddr) : "memory");
-        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        if (ew == 0 && cc == 0) DBG(2, it, 2);
-        if (P.mode & 2) continue;
-        // transpose through smem: thread = row writes 8 chunks, XOR-swizzled (conflict free both ways)
-        const uint32_t tbs = smem_u32(tb);
+      tc_epilogue_tile<EPI>(g, tmem_base + (uint32_t)(ab * 256), tb, ew, lane, roff, n0, ncols, P.vec4, P.mode);
+      if (ew == 0) DBG(2, it, 3);
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      mbar_arrive(tempty_bar(ab));
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == TC_MMA_WARP) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Large-K variant (streaming B, Nt <= 64): the A operand is fed to the tensor core from TENSOR MEMORY.
+// Shared memory is the scarce resource of the 3xTF32 scheme when A goes through it: per 32-wide k-block the
+// smem-A kernel above moves 16 KB in (cp.async) + 16 KB out/32 KB in (hi/lo split) + 3 x 16 KB of MMA operand
+// reads = 112 KB, i.e. ~900 clk at 128 B/clk against a tensor-pipe floor of 12 MMAs x 32 clk = 384 clk (N = 64).
+// Here the producers read their own row from a plain fp32 staging ring, split it in registers and write
+// (hi | lo) straight into TMEM with tcgen05.st (row r = lane r, k = column); the MMAs take A from TMEM
+// ([d], [a] form) and only B (2 x 8 KB per k-block, TMA bulk) still crosses shared memory.
+//   warps 0-3 / 4-7 : two producer groups, alternating k-blocks, cp.async staging ring (3 slots per group)
+//   warps 12, 13    : MMA issuers.  One thread sustains one tcgen05.mma per ~50 clk and stalls ~270 clk per
+//                     tcgen05.commit (tools/mma_rate.cu), more than the tensor pipe needs for N = 64 (32 clk), so the
+//                     k-steps of every k-block are split between two issuing warps with private accumulators
+//                     (D_x: k-steps 0,1; D_y: k-steps 2,3); the epilogue adds the two.
+//   warps 8-11      : epilogue (D: TMEM columns 128*buffer + 64*part ..), same code as above
+#define TCA_THREADS 448
+#define TCA_NS 4                       // TMEM-A / smem-B stages
+#define TCA_ACOL0 256                  // D: 2 buffers x 2 parts x 64 columns = [0, 256)
+#define TCA_SLOTS 3                    // fp32 staging slots per producer group
+
+__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+        "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+        "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+        "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+      : "memory");
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(TCA_THREADS, 1) gemm_tca_kernel(const TcParams P) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const sevenn_gemm_args& g = P.g;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t a_bytes = TC_BM * 128, b_bytes = (uint32_t)P.Nt * 128;
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* bring = smem;                                           // TCA_NS x (B_hi | B_lo)
+  uint8_t* aring = bring + (size_t)TCA_NS * 2 * b_bytes;           // 2 groups x TCA_SLOTS x 16 KB fp32 staging
+  uint8_t* epi_buf = aring + (size_t)2 * TCA_SLOTS * a_bytes;
+  uint64_t* bars = (uint64_t*)(epi_buf + TC_EPI_BYTES);
+  const uint32_t bar0 = smem_u32(bars);
+  auto full_bar = [&](int s) { return bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (TCA_NS + s); };
+  auto tfull_bar = [&](int b) { return bar0 + 8u * (2 * TCA_NS + b); };
+  auto tempty_bar = [&](int b) { return bar0 + 8u * (2 * TCA_NS + 2 + b); };
+  uint32_t* tmem_slot = (uint32_t*)(bars + 2 * TCA_NS + 4);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < TCA_NS; ++s) { mbar_init(full_bar(s), 128); mbar_init(empty_bar(s), 2); }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 2); mbar_init(tempty_bar(b), 128); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == TC_MMA_WARP) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  const long long my_items = (P.m_tiles > blockIdx.x) ? (P.m_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  const long long total_q = my_items * P.KB;
+  const float* bimg = P.Bimg;                                       // n_tiles == 1
+
+  if (warp < 8) {
+    // ================= producers =================
+    const int grp = warp >> 2, gt = threadIdx.x & 127;             // gt = row of the tile this thread owns in TMEM
+    const int c = gt & 7;
+    const long long n_my = total_q > grp ? (total_q - grp + 1) / 2 : 0;
+    uint8_t* my_ring = aring + (size_t)grp * TCA_SLOTS * a_bytes;
+    long long rows_it = -1;
+    const float* rowp[8];
+    auto issue_copy = [&](long long j) {
+      if (j < n_my && !(P.mode & 64)) {                              // (mode 64: diagnostic, no A traffic at all)
+        const long long q = 2 * j + grp;
+        const long long it = q / P.KB;
+        const int kb = (int)(q - it * P.KB);
+        if (it != rows_it) {
+          rows_it = it;
+          const long long mt = blockIdx.x + it * gridDim.x;
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          sts128(tbs + lane * 128 + ((q ^ (lane & 7)) << 4),
-                 make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
-                             __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3])));
-        __syncwarp();
-        const int col = cc + ch * 4;                     // first of this lane's 4 columns (tile-relative)
-        const int nvalid = ncols - col;                  // >= 4 -> whole float4 valid
-        float4 x[8];
+          for (int i = 0; i < 8; ++i) {
+            const long long r = mt * TC_BM + i * 16 + (gt >> 3);
+            rowp[i] = (r < g.M) ? g.A + row_offset(r, g.R, g.sAn, g.sAm) : nullptr;
+          }
+        }
+        const uint32_t sbase = smem_u32(my_ring + (size_t)(j % TCA_SLOTS) * a_bytes);
+        const int k = kb * TC_BK + c * 4;
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const int row = 4 * i + sub;
-          x[i] = lds128(tbs + row * 128 + ((ch ^ (row & 7)) << 4));
+          const int row = i * 16 + (gt >> 3);
+          const uint32_t dst = sbase + row * 128 + ((c ^ (row & 7)) << 4);
+          const bool ok = rowp[i] != nullptr && k < g.K;
+          const float* src = ok ? rowp[i] + k : g.A;
+          const uint32_t nbytes = ok ? 16u : 0u;                    // zero fill: rows >= M and the K tail
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
         }
-        if (P.vec4 && nvalid >= 4) {
-          float4 aux[8];
-          if (EPI == 1 || EPI == 3) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-              if (roff[i] >= 0)
-                aux[i] = *reinterpret_cast<const float4*>((EPI == 1 ? g.C : g.P) + roff[i] + n0 + col);
-          }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            if (roff[i] < 0) continue;
-            float4* c4 = reinterpret_cast<float4*>(g.C + roff[i] + n0 + col);
-            const float4 xv = x[i];
-            if (EPI == 0) {
-              *c4 = xv;
-            } else if (EPI == 1) {
-              *c4 = make_float4(aux[i].x + xv.x, aux[i].y + xv.y, aux[i].z + xv.z, aux[i].w + xv.w);
-            } else if (EPI == 2) {
-              *c4 = xv;
-              *reinterpret_cast<float4*>(g.C2 + roff[i] + n0 + col) =
-                  make_float4(g.cst * silu_f(xv.x), g.cst * silu_f(xv.y), g.cst * silu_f(xv.z), g.cst * silu_f(xv.w));
-            } else {
-              *c4 = make_float4(xv.x * g.cst * dsilu_f(aux[i].x), xv.y * g.cst * dsilu_f(aux[i].y),
-                                xv.z * g.cst * dsilu_f(aux[i].z), xv.w * g.cst * dsilu_f(aux[i].w));
-            }
-          }
-        } else if (nvalid > 0) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            if (roff[i] < 0) continue;
-            const float xs[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              if (e >= nvalid) break;
-              float* cp = g.C + roff[i] + n0 + col + e;
-              if (EPI == 0) *cp = xs[e];
-              else if (EPI == 1) *cp += xs[e];
-              else if (EPI == 2) { *cp = xs[e]; g.C2[roff[i] + n0 + col + e] = g.cst * silu_f(xs[e]); }
-              else *cp = xs[e] * g.cst * dsilu_f(g.P[roff[i] + n0 + col + e]);
-            }
-          }
-        }
-        __syncwarp();
       }
-      if (ew == 0) DBG(2, it, 3);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    issue_copy(0);
+    issue_copy(1);
+    const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    for (long long j = 0; j < n_my; ++j) {
+      const long long qd = 2 * j + grp - 12;                        // trace window: k-blocks 12..17 of the first tile
+      if ((warp & 3) == 0 && qd >= 0) DBG(grp * 2, qd, 0);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");          // my copies of k-block j have landed
+      if ((warp & 3) == 0 && qd >= 0) DBG(grp * 2, qd, 1);
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory"); // ... and everybody else's; slot (j-1)%3 is drained
+      issue_copy(j + 2);
+      const uint32_t srow = smem_u32(my_ring + (size_t)(j % TCA_SLOTS) * a_bytes) + gt * 128;
+      uint32_t hi[32], lo[32];
+#pragma unroll
+      for (int cc = 0; cc < 8; ++cc) {
+        const float4 v = (P.mode & 64) ? make_float4(1.f, 2.f, 3.f, 4.f) : lds128(srow + ((cc ^ (gt & 7)) << 4));
+        hi[4 * cc + 0] = __float_as_uint(v.x) & 0xFFFFE000u; lo[4 * cc + 0] = __float_as_uint(v.x - __uint_as_float(hi[4 * cc + 0]));
+        hi[4 * cc + 1] = __float_as_uint(v.y) & 0xFFFFE000u; lo[4 * cc + 1] = __float_as_uint(v.y - __uint_as_float(hi[4 * cc + 1]));
+        hi[4 * cc + 2] = __float_as_uint(v.z) & 0xFFFFE000u; lo[4 * cc + 2] = __float_as_uint(v.z - __uint_as_float(hi[4 * cc + 2]));
+        hi[4 * cc + 3] = __float_as_uint(v.w) & 0xFFFFE000u; lo[4 * cc + 3] = __float_as_uint(v.w - __uint_as_float(hi[4 * cc + 3]));
+      }
+      const long long q = 2 * j + grp;
+      const int ts = (int)(q % TCA_NS);
+      if ((warp & 3) == 0 && qd >= 0) DBG(grp * 2, qd, 2);
+      // stages are released in pairs (one tcgen05.commit per two k-blocks: a commit stalls its issuing thread
+      // for several hundred cycles, tools/mma_rate.cu), so wait on the pair's barrier
+      mbar_wait(empty_bar((int)((q >> 1) & 1)), (uint32_t)(((q >> 2) & 1) ^ 1));
+      if ((warp & 3) == 0 && qd >= 0) DBG(grp * 2, qd, 3);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      if (gt == 0 && (!(P.mode & 128) || q < TCA_NS)) {              // (mode 128: diagnostic, B loaded once per stage)
+        const int kb = (int)(q % P.KB);
+        mbar_expect_tx(full_bar(ts), 2 * b_bytes);
+        bulk_g2s(smem_u32(bring + (size_t)ts * 2 * b_bytes),
+                 bimg + (size_t)((P.mode & 32) ? 0 : kb) * (size_t)(2 * P.Nt * 32), 2 * b_bytes, full_bar(ts));
+      }
+      const uint32_t ta = t_lane + (uint32_t)(TCA_ACOL0 + ts * 64);
+      if (!(P.mode & 16)) {                                          // diagnostic: skip the TMEM stores
+        tmem_st32(ta, hi);
+        tmem_st32(ta + 32, lo);
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      mbar_arrive(full_bar(ts));
+      if ((warp & 3) == 0 && qd >= 0) DBG(grp * 2, qd, 4);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+  } else if (warp >= TC_MMA_WARP) {
+    // ================= MMA issuers (part = warp - 12 owns k-steps 2*part, 2*part+1 and accumulator D_part) ======
+    const int part = warp - TC_MMA_WARP;
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(P.Nt >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
+    long long q = 0;
+    // a single thread runs the whole issue loop (no per-k-block warp reconvergence)
+    if (lane == 0)
+    for (long long it = 0; it < my_items; ++it) {
+      const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
+      mbar_wait(tempty_bar(ab), aphase ^ 1);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t d_tmem = tmem_base + (uint32_t)(ab * 128 + part * 64);
+      for (int kb = 0; kb < P.KB; ++kb, ++q) {
+        const int ts = (int)(q % TCA_NS);
+        if (part == 0 && q >= 12) DBG(1, q - 12, 0);
+        mbar_wait(full_bar(ts), (uint32_t)((q / TCA_NS) & 1));
+        if (part == 0 && q >= 12) DBG(1, q - 12, 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        {
+          const uint32_t sb = smem_u32(bring + (size_t)ts * 2 * b_bytes);
+          const uint64_t b_hi = make_desc(sb), b_lo = make_desc(sb + b_bytes);
+          const uint32_t a_hi = tmem_base + (uint32_t)(TCA_ACOL0 + ts * 64), a_lo = a_hi + 32;
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {
+            const int j = 2 * part + jj;
+            const uint64_t adv = (uint64_t)(j * 2);
+            if (P.mode & 4) continue;                                  // diagnostic: no tensor work
+            umma_tf32_ts(d_tmem, a_lo + j * 8, b_hi + adv, idesc, (kb | jj) != 0);
+            if (P.dbg && part == 0 && q >= 12 && q < 18 && blockIdx.x == 0) P.dbg[((1) * 6 + (q - 12)) * 8 + 2 + jj * 3] = clock64();
+            if (P.mode & 1) continue;                                  // diagnostic: 1 MMA per k-step
+            umma_tf32_ts(d_tmem, a_hi + j * 8, b_lo + adv, idesc, 1);
+            if (P.dbg && part == 0 && q >= 12 && q < 18 && blockIdx.x == 0) P.dbg[((1) * 6 + (q - 12)) * 8 + 3 + jj * 3] = clock64();
+            umma_tf32_ts(d_tmem, a_hi + j * 8, b_hi + adv, idesc, 1);
+            if (P.dbg && part == 0 && q >= 12 && q < 18 && blockIdx.x == 0) P.dbg[((1) * 6 + (q - 12)) * 8 + 4 + jj * 3] = clock64();
+          }
+          if ((q & 1) || q == total_q - 1) umma_commit(empty_bar((int)((q >> 1) & 1)));
+          if (kb == P.KB - 1) umma_commit(tfull_bar(ab));
+        }
+      }
+    }
+  } else {
+    // ================= epilogue =================
+    const int ew = warp - TC_EPI_WARP0;
+    uint8_t* tb = epi_buf + ew * (32 * 128);
+    const int ncols = min(P.Nt, g.N);
+    const int sub = lane >> 3;
+    for (long long it = 0; it < my_items; ++it) {
+      const long long mt = blockIdx.x + it * gridDim.x;
+      const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
+      long long roff[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const long long r = mt * TC_BM + ew * 32 + 4 * i + sub;
+        roff[i] = (r < g.M) ? row_offset(r, g.R, g.sCn, g.sCm) : -1;
+      }
+      mbar_wait(tfull_bar(ab), aphase);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      tc_epilogue_tile<EPI>(g, tmem_base + (uint32_t)(ab * 128), tb, ew, lane, roff, 0, ncols, P.vec4, P.mode, 64);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       mbar_arrive(tempty_bar(ab));
     }
@@ -439,14 +689,23 @@ extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, v
   { const char* e = getenv("SEVENN_TC_DSLACK"); P.dslack = e ? atoi(e) : 1; }
   P.vec4 = !((g.sCn & 3) || (g.sCm & 3) || ((uintptr_t)g.C & 15) || (g.C2 && ((uintptr_t)g.C2 & 15)) ||
              (g.P && ((uintptr_t)g.P & 15)));
-  const size_t smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * stages + 5) + 16;
+  // large K with a narrow column tile: A through tensor memory (see gemm_tca_kernel)
+  static int tmema_ok = -1;
+  if (tmema_ok < 0) { const char* e = getenv("SEVENN_TC_TMEMA"); tmema_ok = e ? atoi(e) : 1; }
+  const bool tca = tmema_ok && !P.resident && P.n_tiles == 1 && P.Nt <= 64 && P.KB >= 4;
+  size_t smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * stages + 5) + 16;
   void (*kern)(const TcParams) = g.epi == 0 ? gemm_tc_kernel<0> : g.epi == 1 ? gemm_tc_kernel<1>
                                : g.epi == 2 ? gemm_tc_kernel<2> : gemm_tc_kernel<3>;
-  static bool attr_set[4] = {false, false, false, false};
-  if (!attr_set[g.epi]) {
+  if (tca) {
+    kern = g.epi == 0 ? gemm_tca_kernel<0> : g.epi == 1 ? gemm_tca_kernel<1>
+         : g.epi == 2 ? gemm_tca_kernel<2> : gemm_tca_kernel<3>;
+    smem = 1024 + (size_t)TCA_NS * 2 * b_bytes + (size_t)2 * TCA_SLOTS * TC_BM * 128 + TC_EPI_BYTES + 8 * (2 * TCA_NS + 5) + 16;
+  }
+  static bool attr_set[8] = {false, false, false, false, false, false, false, false};
+  if (!attr_set[g.epi + (tca ? 4 : 0)]) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
-    attr_set[g.epi] = true;
+    attr_set[g.epi + (tca ? 4 : 0)] = true;
   }
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
@@ -460,7 +719,7 @@ extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, v
   if (dbg && !dbg_dev) cudaMalloc(&dbg_dev, 3 * 6 * 8 * sizeof(long long));
   if (dbg) cudaMemset(dbg_dev, 0, 3 * 6 * 8 * sizeof(long long));
   P.dbg = dbg ? dbg_dev : nullptr;
-  kern<<<grid, TC_THREADS, smem, (cudaStream_t)stream>>>(P);
+  kern<<<grid, tca ? TCA_THREADS : TC_THREADS, smem, (cudaStream_t)stream>>>(P);
   if (dbg) {
     long long h[3 * 6 * 8];
     cudaDeviceSynchronize();
@@ -468,10 +727,10 @@ extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, v
     long long t0 = h[0];
     for (int k = 0; k < 3 * 6 * 8; ++k) if (h[k] && h[k] < t0) t0 = h[k];
     fprintf(stderr, "TCDBG M=%lld N=%d K=%d stages=%d resident=%d KB=%d\n", g.M, g.N, g.K, stages, P.resident, P.KB);
-    const char* names[3] = {"prod(q)", "mma(it)", "epi(it)"};
+    const char* names[3] = {"prod/grp0", "mma", "epi/grp1"};
     for (int r = 0; r < 3; ++r) for (int it = 0; it < 6; ++it) {
       fprintf(stderr, "  %s %d:", names[r], it);
-      for (int e = 0; e < 5; ++e) fprintf(stderr, " %8lld", h[(r * 6 + it) * 8 + e] ? h[(r * 6 + it) * 8 + e] - t0 : -1);
+      for (int e = 0; e < 8; ++e) fprintf(stderr, " %8lld", h[(r * 6 + it) * 8 + e] ? h[(r * 6 + it) * 8 + e] - t0 : -1);
       fprintf(stderr, "\n");
     }
   }

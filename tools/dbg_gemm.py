@@ -3,7 +3,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from sevennet_exp_b200 import _lib as L
 from sevennet_exp_b200.engine import tc_image_for
 lib = L.load(); st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-for (n, R, K, N, epi) in [(198356, 1, 960, 64, 3)]:
+import os as _os
+shape = eval(_os.environ.get("DBG_SHAPE", "(198356, 1, 960, 64, 3)"))
+for (n, R, K, N, epi) in [shape]:
     A = torch.randn(n, R * K, device='cuda'); B = torch.randn(K, N, device='cuda')
     C = torch.zeros(n, R * N, device='cuda'); C2 = torch.zeros(n, R * N, device='cuda'); P = torch.randn(n, R * N, device='cuda')
     img = torch.from_numpy(tc_image_for(lib, B.cpu().numpy())).cuda()
