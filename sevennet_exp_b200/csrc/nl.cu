@@ -107,7 +107,71 @@ GKERNEL(nl_walk_kernel)(const double* __restrict__ pw, const int* __restrict__ w
   }
 }
 
-// in-place insertion sort of each CSR segment (segments are ~10-100 long)
+#ifndef SEVENN_EMU
+// CUDA flavour of the walk: one warp per centre atom, lanes over the atoms of each stencil bin, ballot compaction
+// (the order inside a row is irrelevant: rows are sorted by key afterwards).  4x fewer dependent global loads per
+// thread than the thread-per-atom loop above, which is what a 4,096-atom cell needs to fill 148 SMs.
+template <bool FILL>
+__global__ void __launch_bounds__(128) nl_walk_warp_kernel(const double* __restrict__ pw, const int* __restrict__ wrap,
+                                                           const int* __restrict__ atom_bin,
+                                                           const int* __restrict__ bin_start,
+                                                           const int* __restrict__ bin_atoms, int n, NlParams P,
+                                                           int* __restrict__ count, const int* __restrict__ rowptr,
+                                                           unsigned long long* __restrict__ keys) {
+  const int lane = threadIdx.x & 31;
+  for (long long i = blockIdx.x * 4ll + (threadIdx.x >> 5); i < n; i += gridDim.x * 4ll) {
+    const double xi = pw[3 * i], yi = pw[3 * i + 1], zi = pw[3 * i + 2];
+    const int bin = atom_bin[i];
+    const int b2 = bin % P.nb[2], b1 = (bin / P.nb[2]) % P.nb[1], b0 = bin / (P.nb[2] * P.nb[1]);
+    const int wi0 = wrap[3 * i], wi1 = wrap[3 * i + 1], wi2 = wrap[3 * i + 2];
+    int cnt = 0;
+    const long long base = FILL ? rowptr[i] : 0;
+    for (int d0 = -P.R[0]; d0 <= P.R[0]; ++d0) {
+      int c0 = b0 + d0, s0 = 0;
+      if (P.pbc[0]) { s0 = floordiv(c0, P.nb[0]); c0 -= s0 * P.nb[0]; } else if (c0 < 0 || c0 >= P.nb[0]) continue;
+      for (int d1 = -P.R[1]; d1 <= P.R[1]; ++d1) {
+        int c1 = b1 + d1, s1 = 0;
+        if (P.pbc[1]) { s1 = floordiv(c1, P.nb[1]); c1 -= s1 * P.nb[1]; } else if (c1 < 0 || c1 >= P.nb[1]) continue;
+        for (int d2 = -P.R[2]; d2 <= P.R[2]; ++d2) {
+          int c2 = b2 + d2, s2 = 0;
+          if (P.pbc[2]) { s2 = floordiv(c2, P.nb[2]); c2 -= s2 * P.nb[2]; } else if (c2 < 0 || c2 >= P.nb[2]) continue;
+          const double ox = s0 * P.cell[0] + s1 * P.cell[3] + s2 * P.cell[6] - xi;
+          const double oy = s0 * P.cell[1] + s1 * P.cell[4] + s2 * P.cell[7] - yi;
+          const double oz = s0 * P.cell[2] + s1 * P.cell[5] + s2 * P.cell[8] - zi;
+          const int nbin = (c0 * P.nb[1] + c1) * P.nb[2] + c2;
+          const int a0 = bin_start[nbin], a1 = bin_start[nbin + 1];
+          const bool home = (s0 == 0 && s1 == 0 && s2 == 0);
+          for (int ab = a0; ab < a1; ab += 32) {
+            const int a = ab + lane;
+            bool ok = false;
+            int j = 0;
+            if (a < a1) {
+              j = bin_atoms[a];
+              const double dx = pw[3 * j] + ox, dy = pw[3 * j + 1] + oy, dz = pw[3 * j + 2] + oz;
+              ok = (dx * dx + dy * dy + dz * dz) < P.rc2 && !(home && j == (int)i);
+            }
+            const unsigned mask = __ballot_sync(0xffffffffu, ok);
+            if (FILL && ok) {
+              const int S0 = s0 - wrap[3 * j] + wi0, S1 = s1 - wrap[3 * j + 1] + wi1, S2 = s2 - wrap[3 * j + 2] + wi2;
+              keys[base + cnt + __popc(mask & ((1u << lane) - 1u))] =
+                  ((unsigned long long)j << 24) | ((unsigned long long)(S0 + 128) << 16) |
+                  ((unsigned long long)(S1 + 128) << 8) | (unsigned long long)(S2 + 128);
+            }
+            cnt += __popc(mask);
+          }
+        }
+      }
+    }
+    if (!FILL && lane == 0) count[i] = cnt;
+  }
+}
+#define LAUNCH_WALK(FILL, n, stream) nl_walk_warp_kernel<FILL><<<(unsigned)(((n) + 3) / 4 < 65535 * 16 ? ((n) + 3) / 4 : 65535 * 16), 128, 0, (cudaStream_t)(stream)>>>
+#else
+#define LAUNCH_WALK(FILL, n, stream) nl_walk_kernel<FILL>
+#endif
+
+// in-place sort of each CSR segment (segments are ~10-100 long)
+#ifdef SEVENN_EMU
 GKERNEL(segment_sort_u64_kernel)(unsigned long long* __restrict__ keys, const int* __restrict__ ptr, int n) {
   GRID_STRIDE_LOOP(i, n) {
     const int a = ptr[i], b = ptr[i + 1];
@@ -119,6 +183,51 @@ GKERNEL(segment_sort_u64_kernel)(unsigned long long* __restrict__ keys, const in
     }
   }
 }
+#define LAUNCH_SEGSORT(n, stream) segment_sort_u64_kernel
+#else
+// one warp per segment: bitonic network in shared memory for segments up to 256 keys (coalesced load / store,
+// 32 compare-exchanges per step); longer segments fall back to a lane-0 insertion sort (keys are unique, so the
+// result does not depend on the algorithm)
+#define SEGSORT_MAX 256
+__global__ void __launch_bounds__(128) segment_sort_u64_kernel(unsigned long long* __restrict__ keys,
+                                                               const int* __restrict__ ptr, int n) {
+  __shared__ unsigned long long buf_all[4][SEGSORT_MAX];
+  unsigned long long* buf = buf_all[threadIdx.x >> 5];
+  const int lane = threadIdx.x & 31;
+  for (long long seg = blockIdx.x * 4ll + (threadIdx.x >> 5); seg < n; seg += gridDim.x * 4ll) {
+    const int a = ptr[seg], len = ptr[seg + 1] - a;
+    if (len <= 1) continue;
+    if (len > SEGSORT_MAX) {
+      if (lane == 0) {
+        for (int p = a + 1; p < a + len; ++p) {
+          const unsigned long long k = keys[p];
+          int q = p - 1;
+          while (q >= a && keys[q] > k) { keys[q + 1] = keys[q]; --q; }
+          keys[q + 1] = k;
+        }
+      }
+      continue;
+    }
+    int m = 2;
+    while (m < len) m <<= 1;
+    for (int t = lane; t < m; t += 32) buf[t] = t < len ? keys[a + t] : ~0ull;
+    __syncwarp();
+    for (int k = 2; k <= m; k <<= 1)
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = lane; t < (m >> 1); t += 32) {
+          const int lo = ((t & ~(j - 1)) << 1) | (t & (j - 1)), hi = lo | j;   // pair (lo, lo + j)
+          const bool up = (lo & k) == 0;
+          const unsigned long long x = buf[lo], y = buf[hi];
+          if ((x > y) == up) { buf[lo] = y; buf[hi] = x; }
+        }
+        __syncwarp();
+      }
+    for (int t = lane; t < len; t += 32) keys[a + t] = buf[t];
+    __syncwarp();
+  }
+}
+#define LAUNCH_SEGSORT(n, stream) segment_sort_u64_kernel<<<(unsigned)(((n) + 3) / 4 < 65535 * 16 ? ((n) + 3) / 4 : 65535 * 16), 128, 0, (cudaStream_t)(stream)>>>
+#endif
 
 GKERNEL(nl_decode_kernel)(const unsigned long long* __restrict__ keys, const int* __restrict__ rowptr, int n,
                           const double* __restrict__ pos, NlParams P, int* __restrict__ center,
@@ -253,7 +362,7 @@ extern "C" int sevenn_nl_count(const double* pw, const int* wrap, const int* ato
                                const int* bin_atoms, int n, const double* dpar, const int* ipar, int* count,
                                void* stream) {
   if (n <= 0) return 0;
-  LAUNCH1D(nl_walk_kernel<false>, n, stream)(pw, wrap, atom_bin, bin_start, bin_atoms, n, make_params(dpar, ipar),
+  LAUNCH_WALK(false, n, stream)(pw, wrap, atom_bin, bin_start, bin_atoms, n, make_params(dpar, ipar),
                                              count, nullptr, nullptr);
   return LAUNCH_STATUS();
 }
@@ -263,8 +372,8 @@ extern "C" int sevenn_nl_fill(const double* pw, const int* wrap, const int* atom
                               float* vec, void* stream) {
   if (n <= 0) return 0;
   NlParams P = make_params(dpar, ipar);
-  LAUNCH1D(nl_walk_kernel<true>, n, stream)(pw, wrap, atom_bin, bin_start, bin_atoms, n, P, nullptr, rowptr, keys);
-  LAUNCH1D(segment_sort_u64_kernel, n, stream)(keys, rowptr, n);
+  LAUNCH_WALK(true, n, stream)(pw, wrap, atom_bin, bin_start, bin_atoms, n, P, nullptr, rowptr, keys);
+  LAUNCH_SEGSORT(n, stream)(keys, rowptr, n);
   LAUNCH1D(nl_decode_kernel, n, stream)(keys, rowptr, n, pos, P, center, col, shift, vec);
   return LAUNCH_STATUS();
 }
@@ -276,7 +385,7 @@ extern "C" int sevenn_csc_build(const int* col, long long n_edges, int n_nodes, 
   if (rc) return rc;
   if (n_edges > 0) {
     LAUNCH1D(csc_scatter_kernel, n_edges, stream)(col, n_edges, cptr, fill, keys);
-    LAUNCH1D(segment_sort_u64_kernel, n_nodes, stream)(keys, cptr, n_nodes);
+    LAUNCH_SEGSORT(n_nodes, stream)(keys, cptr, n_nodes);
     LAUNCH1D(u64_to_i32_kernel, n_edges, stream)(keys, n_edges, cedge);
   }
   return LAUNCH_STATUS();
