@@ -72,6 +72,9 @@ int sevenn_gemm_f32(const sevenn_gemm_args* args /* host */, void* stream);   /*
  * Needs K % 4 == 0 and 16-byte aligned A rows; returns SEVENN_ERR_BAD_ARG otherwise. */
 int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, long long* img_floats);
 int sevenn_gemm_tc(const sevenn_gemm_args* args /* host */, const float* Bimg, void* stream);
+/* up to 4 independent problems with the same epilogue in one launch (the per-l blocks of one o3.Linear) */
+int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args /* host array */, const float* const* Bimgs /* host array */,
+                           void* stream);
 
 /* species-indexed linear = FullyConnectedTensorProduct(x, one_hot): sevenn/nn/self_connection.py:10-64 */
 int sevenn_linear_by_type(const float* A, long long sAn, int sAm, const float* W /* S,K,N */, const int* types,

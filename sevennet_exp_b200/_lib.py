@@ -40,6 +40,7 @@ SIGNATURES = {
     'sevenn_gemm_tc_plan': ([c_i, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_i), ctypes.POINTER(c_i),
                              ctypes.POINTER(c_ll)], c_i),
     'sevenn_gemm_tc': ([ctypes.POINTER(GemmArgs), c_p, c_p], c_i),
+    'sevenn_gemm_tc_grouped': ([c_i, ctypes.POINTER(GemmArgs), ctypes.POINTER(c_p), c_p], c_i),
     'sevenn_linear_by_type': ([c_p, c_ll, c_i, c_p, c_p, c_p, c_ll, c_i, c_ll, c_i, c_i, c_i, c_i, c_p], c_i),
     'sevenn_embed': ([c_p, c_ll, c_i, c_p, c_p, c_p], c_i),
     'sevenn_gate_fwd': ([c_p, c_i, c_p, c_i, c_ll, ctypes.POINTER(GatePiece), c_i, c_p], c_i),

@@ -41,6 +41,12 @@ struct TcParams {
   long long m_tiles;
   long long* dbg;       // optional clock64 trace of CTA (0,0) (SEVENN_TC_DBG=1)
 };
+#define TC_MAX_GROUP 4
+struct TcGroup {
+  int n;
+  int cta_start[TC_MAX_GROUP + 1];
+  TcParams p[TC_MAX_GROUP];
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -216,12 +222,20 @@ __device__ __forceinline__ void tc_epilogue_tile(const sevenn_gemm_args& g, uint
   }
 }
 
-#define DBG(role, it, ev) do { if (P.dbg && blockIdx.x == 0 && blockIdx.y == 0 && (it) < 6 && (threadIdx.x & 31) == 0) \
+#define DBG(role, it, ev) do { if (P.dbg && blockIdx.x == 0 && (it) < 6 && (threadIdx.x & 31) == 0) \
   P.dbg[((role) * 6 + (it)) * 8 + (ev)] = clock64(); } while (0)
 
+// Up to TC_MAX_GROUP independent problems per launch (the per-l blocks of one o3.Linear): each CTA serves one of
+// them, so the launch / TMEM-allocation / pipeline-fill latencies of the small node GEMMs overlap.
 template <int EPI>
-__global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcParams P) {
+__global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
+  int pi = 0;
+  while (pi + 1 < G.n && (int)blockIdx.x >= G.cta_start[pi + 1]) ++pi;
+  const TcParams P = G.p[pi];          // by value: fields live in registers, not behind indexed constant loads
+  const int local = (int)blockIdx.x - G.cta_start[pi];
+  const int gx = (G.cta_start[pi + 1] - G.cta_start[pi]) / P.n_tiles;      // CTAs per column tile
+  const int bx = local % gx;
   const sevenn_gemm_args& g = P.g;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t a_bytes = TC_BM * 128, b_bytes = (uint32_t)P.Nt * 128;
@@ -255,9 +269,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcParams P
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const uint32_t tmem_base = *tmem_slot;
 
-  // this CTA owns column tile nt and the row tiles mt = blockIdx.x, blockIdx.x + gridDim.x, ...
-  const int nt = blockIdx.y;
-  const long long my_items = (P.m_tiles > blockIdx.x) ? (P.m_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  // this CTA owns column tile nt and the row tiles mt = bx, bx + gx, ...
+  const int nt = local / gx;
+  const long long my_items = (P.m_tiles > bx) ? (P.m_tiles - bx + gx - 1) / gx : 0;
   const float* bimg_nt = P.Bimg + (size_t)nt * P.KB * (size_t)(2 * P.Nt * 32);
 
   if (warp < TC_PRODUCERS / 32) {
@@ -279,7 +293,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcParams P
     long long q_i = 0, it_i = 0; int kb_i = 0;
     const float* rowp[4];
     auto set_rows = [&](long long it) {
-      const long long mt = blockIdx.x + it * gridDim.x;
+      const long long mt = bx + it * (long long)gx;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const long long r = mt * TC_BM + i * 32 + (tid >> 3);
@@ -394,7 +408,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcParams P
     const int ncols = min(P.Nt, g.N - n0);
     const int sub = lane >> 3, ch = lane & 7;            // read phase: row 4*i + sub, 16 B chunk ch
     for (long long it = 0; it < my_items; ++it) {
-      const long long mt = blockIdx.x + it * gridDim.x;
+      const long long mt = bx + it * (long long)gx;
       const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
       long long roff[8];
 #pragma unroll
@@ -666,11 +680,10 @@ extern "C" int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB,
   return 0;
 }
 
-extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, void* stream) {
-  TcParams P;
+// fills P (geometry, stages, modes) and the dynamic shared memory it needs; tca = large-K variant eligible
+static int tc_prepare(const sevenn_gemm_args* args, const float* Bimg, TcParams& P, size_t* smem, bool* tca) {
   P.g = *args;
   const sevenn_gemm_args& g = P.g;
-  if (g.M <= 0 || g.N <= 0) return 0;
   if (g.K <= 0 || g.R <= 0 || g.epi < 0 || g.epi > 3 || (g.K & 3) || (g.sAn & 3) || (g.sAm & 3) ||
       ((uintptr_t)g.A & 15) || (g.epi >= 2 && g.act != 0))
     return SEVENN_ERR_BAD_ARG;
@@ -689,44 +702,120 @@ extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, v
   { const char* e = getenv("SEVENN_TC_DSLACK"); P.dslack = e ? atoi(e) : 1; }
   P.vec4 = !((g.sCn & 3) || (g.sCm & 3) || ((uintptr_t)g.C & 15) || (g.C2 && ((uintptr_t)g.C2 & 15)) ||
              (g.P && ((uintptr_t)g.P & 15)));
-  // large K with a narrow column tile: A through tensor memory (see gemm_tca_kernel)
+  P.dbg = nullptr;
   static int tmema_ok = -1;
   if (tmema_ok < 0) { const char* e = getenv("SEVENN_TC_TMEMA"); tmema_ok = e ? atoi(e) : 1; }
-  const bool tca = tmema_ok && !P.resident && P.n_tiles == 1 && P.Nt <= 64 && P.KB >= 4;
-  size_t smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * stages + 5) + 16;
-  void (*kern)(const TcParams) = g.epi == 0 ? gemm_tc_kernel<0> : g.epi == 1 ? gemm_tc_kernel<1>
-                               : g.epi == 2 ? gemm_tc_kernel<2> : gemm_tc_kernel<3>;
-  if (tca) {
-    kern = g.epi == 0 ? gemm_tca_kernel<0> : g.epi == 1 ? gemm_tca_kernel<1>
-         : g.epi == 2 ? gemm_tca_kernel<2> : gemm_tca_kernel<3>;
-    smem = 1024 + (size_t)TCA_NS * 2 * b_bytes + (size_t)2 * TCA_SLOTS * TC_BM * 128 + TC_EPI_BYTES + 8 * (2 * TCA_NS + 5) + 16;
-  }
-  static bool attr_set[8] = {false, false, false, false, false, false, false, false};
-  if (!attr_set[g.epi + (tca ? 4 : 0)]) {
+  *tca = tmema_ok && !P.resident && P.n_tiles == 1 && P.Nt <= 64 && P.KB >= 4;
+  *smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * stages + 5) + 16;
+  if (*tca)
+    *smem = 1024 + (size_t)TCA_NS * 2 * b_bytes + (size_t)2 * TCA_SLOTS * TC_BM * 128 + TC_EPI_BYTES + 8 * (2 * TCA_NS + 5) + 16;
+  return 0;
+}
+
+static int tc_sm_count() {
+  static int sms = 0;
+  if (!sms) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev); }
+  return sms;
+}
+
+template <typename K>
+static int tc_set_smem_attr(K kern, bool* done) {
+  if (!*done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return (int)e;
-    attr_set[g.epi + (tca ? 4 : 0)] = true;
+    *done = true;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  long long gx = sms / P.n_tiles;
-  if (gx < 1) gx = 1;
-  if (gx > P.m_tiles) gx = P.m_tiles;
-  dim3 grid((unsigned)gx, (unsigned)P.n_tiles);
-  static long long* dbg_dev = nullptr;
+  return 0;
+}
+
+extern "C" int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args, const float* const* Bimgs, void* stream) {
+  if (n <= 0) return 0;
+  if (n > TC_MAX_GROUP) return SEVENN_ERR_BAD_ARG;
+  TcGroup G;
+  G.n = 0;
+  size_t smem = 0;
+  long long tiles[TC_MAX_GROUP], total = 0;
+  const int epi = args[0].epi;
+  for (int i = 0; i < n; ++i) {
+    if (args[i].M <= 0 || args[i].N <= 0) continue;
+    if (args[i].epi != epi) return SEVENN_ERR_BAD_ARG;
+    size_t sm; bool tca;
+    int rc = tc_prepare(&args[i], Bimgs[i], G.p[G.n], &sm, &tca);
+    if (rc) return rc;
+    // members of a group always run the shared-memory-A kernel
+    const size_t b_bytes = (size_t)G.p[G.n].Nt * 128;
+    const size_t stage_bytes = 2 * TC_BM * 128 + (G.p[G.n].resident ? 0 : 2 * b_bytes);
+    const size_t fixed = G.p[G.n].resident ? (size_t)G.p[G.n].KB * 2 * b_bytes : 0;
+    sm = 1024 + (size_t)G.p[G.n].stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * G.p[G.n].stages + 5) + 16;
+    if (sm > smem) smem = sm;
+    tiles[G.n] = G.p[G.n].m_tiles * G.p[G.n].n_tiles;
+    total += tiles[G.n];
+    ++G.n;
+  }
+  if (G.n == 0) return 0;
+  const int sms = tc_sm_count();
+  int start = 0;
+  for (int i = 0; i < G.n; ++i) {
+    const TcParams& P = G.p[i];
+    long long gx = total <= sms ? P.m_tiles : (long long)((double)sms * (double)tiles[i] / (double)total) / P.n_tiles;
+    if (gx < 1) gx = 1;
+    if (gx > P.m_tiles) gx = P.m_tiles;
+    G.cta_start[i] = start;
+    start += (int)gx * P.n_tiles;
+  }
+  G.cta_start[G.n] = start;
+  void (*kern)(const TcGroup) = epi == 0 ? gemm_tc_kernel<0> : epi == 1 ? gemm_tc_kernel<1>
+                              : epi == 2 ? gemm_tc_kernel<2> : gemm_tc_kernel<3>;
+  static bool attr_set[4] = {false, false, false, false};
+  int rc = tc_set_smem_attr(kern, &attr_set[epi]);
+  if (rc) return rc;
+  kern<<<(unsigned)start, TC_THREADS, smem, (cudaStream_t)stream>>>(G);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, void* stream) {
+  if (args->M <= 0 || args->N <= 0) return 0;
+  TcParams P;
+  size_t smem; bool tca;
+  int rc = tc_prepare(args, Bimg, P, &smem, &tca);
+  if (rc) return rc;
   const bool dbg = getenv("SEVENN_TC_DBG") != nullptr;
+  if (!tca && !dbg) return sevenn_gemm_tc_grouped(1, args, &Bimg, stream);
+  const sevenn_gemm_args& g = P.g;
+  static long long* dbg_dev = nullptr;
   if (dbg && !dbg_dev) cudaMalloc(&dbg_dev, 3 * 6 * 8 * sizeof(long long));
   if (dbg) cudaMemset(dbg_dev, 0, 3 * 6 * 8 * sizeof(long long));
   P.dbg = dbg ? dbg_dev : nullptr;
-  kern<<<grid, tca ? TCA_THREADS : TC_THREADS, smem, (cudaStream_t)stream>>>(P);
+  if (tca) {
+    void (*kern)(const TcParams) = g.epi == 0 ? gemm_tca_kernel<0> : g.epi == 1 ? gemm_tca_kernel<1>
+                                 : g.epi == 2 ? gemm_tca_kernel<2> : gemm_tca_kernel<3>;
+    static bool attr_set[4] = {false, false, false, false};
+    rc = tc_set_smem_attr(kern, &attr_set[g.epi]);
+    if (rc) return rc;
+    long long gx = tc_sm_count();
+    if (gx > P.m_tiles) gx = P.m_tiles;
+    kern<<<(unsigned)gx, TCA_THREADS, smem, (cudaStream_t)stream>>>(P);
+  } else {
+    TcGroup G;
+    G.n = 1; G.p[0] = P;
+    long long gx = tc_sm_count() / P.n_tiles;
+    if (gx < 1) gx = 1;
+    if (gx > P.m_tiles) gx = P.m_tiles;
+    G.cta_start[0] = 0; G.cta_start[1] = (int)gx * P.n_tiles;
+    void (*kern)(const TcGroup) = g.epi == 0 ? gemm_tc_kernel<0> : g.epi == 1 ? gemm_tc_kernel<1>
+                                : g.epi == 2 ? gemm_tc_kernel<2> : gemm_tc_kernel<3>;
+    static bool attr_set2[4] = {false, false, false, false};
+    rc = tc_set_smem_attr(kern, &attr_set2[g.epi]);
+    if (rc) return rc;
+    kern<<<(unsigned)G.cta_start[1], TC_THREADS, smem, (cudaStream_t)stream>>>(G);
+  }
   if (dbg) {
     long long h[3 * 6 * 8];
     cudaDeviceSynchronize();
     cudaMemcpy(h, dbg_dev, sizeof(h), cudaMemcpyDeviceToHost);
     long long t0 = h[0];
     for (int k = 0; k < 3 * 6 * 8; ++k) if (h[k] && h[k] < t0) t0 = h[k];
-    fprintf(stderr, "TCDBG M=%lld N=%d K=%d stages=%d resident=%d KB=%d\n", g.M, g.N, g.K, stages, P.resident, P.KB);
+    fprintf(stderr, "TCDBG M=%lld N=%d K=%d stages=%d resident=%d KB=%d tca=%d\n", g.M, g.N, g.K, P.stages, P.resident, P.KB, (int)tca);
     const char* names[3] = {"prod/grp0", "mma", "epi/grp1"};
     for (int r = 0; r < 3; ++r) for (int it = 0; it < 6; ++it) {
       fprintf(stderr, "  %s %d:", names[r], it);
@@ -748,5 +837,10 @@ extern "C" int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB,
 }
 extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, void* stream) {
   (void)Bimg; return sevenn_gemm_f32(args, stream);
+}
+extern "C" int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args, const float* const* Bimgs, void* stream) {
+  (void)Bimgs;
+  for (int i = 0; i < n; ++i) { int rc = sevenn_gemm_f32(&args[i], stream); if (rc) return rc; }
+  return 0;
 }
 #endif

@@ -87,6 +87,7 @@ class _Lin:
         for b in spec.blocks:
             cover[b.g_in] += 1
         self.bwd_needs_zero = any(c != 1 for c in cover)
+        self.bwd_overlap = any(c > 1 for c in cover)     # two blocks accumulate into one input group
         cover_o = {}
         for b in spec.blocks:
             cover_o[(b.g_out, b.u_off_out)] = 1
@@ -139,21 +140,44 @@ class Kernels:
             self._tc_cache[key] = torch.from_numpy(tc_image_for(self.lib, W)).to(self.dev).contiguous()
         return self._tc_cache[key]
 
-    def _gemm(self, A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi=0, act=0, cst=1.0, C2=None, P=None):
+    def _gemm_args(self, A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi=0, act=0, cst=1.0, C2=None, P=None):
         g = _lib.GemmArgs(A.data_ptr() + 4 * a_off, sAn, sAm, B.data_ptr(), N, C.data_ptr() + 4 * c_off, sCn, sCm,
                           M, R, N, K, epi, act, cst,
                           (C2.data_ptr() + 4 * c_off) if C2 is not None else None,
                           (P.data_ptr() + 4 * c_off) if P is not None else None)
-        tc = (self.gemm_mode != 'simt' and M >= self.tc_min_rows and (epi < 2 or act == 0) and K % 4 == 0 and sAn % 4 == 0 and sAm % 4 == 0
-              and (A.data_ptr() + 4 * a_off) % 16 == 0)
+        tc = (self.gemm_mode != 'simt' and M >= self.tc_min_rows and (epi < 2 or act == 0) and K % 4 == 0
+              and sAn % 4 == 0 and sAm % 4 == 0 and (A.data_ptr() + 4 * a_off) % 16 == 0)
+        return g, tc
+
+    def _gemm(self, A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi=0, act=0, cst=1.0, C2=None, P=None):
+        g, tc = self._gemm_args(A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi, act, cst, C2, P)
         if tc:
             self.lib.call('sevenn_gemm_tc', ctypes.byref(g), _p(self._tc_image(B)), self._stream())
         else:
             self.lib.call('sevenn_gemm_f32', ctypes.byref(g), self._stream())
         self.n_launch += 1
 
+    def _gemm_group(self, items):
+        """items: list of _gemm argument tuples with one epilogue; the tcgen05-eligible ones share launches of up
+        to 4 problems (sevenn_gemm_tc_grouped), the rest go to the SIMT arm one by one."""
+        group = []
+        for it in items:
+            g, tc = self._gemm_args(*it)
+            if tc:
+                group.append((g, self._tc_image(it[4])))
+            else:
+                self.lib.call('sevenn_gemm_f32', ctypes.byref(g), self._stream())
+                self.n_launch += 1
+        for k in range(0, len(group), 4):
+            part = group[k:k + 4]
+            arr = (_lib.GemmArgs * len(part))(*[g for g, _ in part])
+            imgs = (ctypes.c_void_p * len(part))(*[im.data_ptr() for _, im in part])
+            self.lib.call('sevenn_gemm_tc_grouped', len(part), arr, imgs, self._stream())
+            self.n_launch += 1
+
     def _linear_fwd(self, lin: _Lin, x, n, y, accumulate=False, types=None):
         sp = lin.spec
+        items = []
         for b, W in zip(sp.blocks, lin.W):
             a_off = sp.lin.group_off[b.g_in]
             c_off = sp.lout.group_off[b.g_out] + b.u_off_out
@@ -164,13 +188,16 @@ class Kernels:
                               sp.lout.groups[b.g_out][0], n, R, b.K, b.N, int(accumulate), self._stream())
                 self.n_launch += 1
             else:
-                self._gemm(x, a_off, sp.lin.dim, b.K, W, y, c_off, sp.lout.dim, sp.lout.groups[b.g_out][0],
-                           n * R, R, b.N, b.K, epi=1 if accumulate else 0)
+                items.append((x, a_off, sp.lin.dim, b.K, W, y, c_off, sp.lout.dim, sp.lout.groups[b.g_out][0],
+                              n * R, R, b.N, b.K, 1 if accumulate else 0))
+        if items:
+            self._gemm_group(items)
 
     def _linear_bwd(self, lin: _Lin, dy, n, dx, accumulate=False, types=None):
         """dx (+)= dy @ W^T ; dx must be zero-initialised by the caller when lin.bwd_needs_zero."""
         sp = lin.spec
         acc = accumulate or lin.bwd_needs_zero
+        items = []
         for b, WT in zip(sp.blocks, lin.WT):
             a_off = sp.lout.group_off[b.g_out] + b.u_off_out
             c_off = sp.lin.group_off[b.g_in]
@@ -182,8 +209,13 @@ class Kernels:
                               int(acc), self._stream())
                 self.n_launch += 1
             else:
-                self._gemm(dy, a_off, sp.lout.dim, sp.lout.groups[b.g_out][0], WT, dx, c_off, sp.lin.dim, b.K,
-                           n * R, R, b.K, b.N, epi=1 if acc else 0)
+                items.append((dy, a_off, sp.lout.dim, sp.lout.groups[b.g_out][0], WT, dx, c_off, sp.lin.dim, b.K,
+                              n * R, R, b.K, b.N, 1 if acc else 0))
+        if items and lin.bwd_overlap:
+            for it in items:          # read-modify-write of shared columns: keep the launches ordered
+                self._gemm(*it)
+        elif items:
+            self._gemm_group(items)
 
     def _mlp_fwd(self, lay, emb, E):
         """radial MLP (e3nn FullyConnectedNet): returns (pre-activations, activations, w)."""
