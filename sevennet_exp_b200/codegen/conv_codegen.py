@@ -105,6 +105,14 @@ def _on(G, expr, zero='0.f'):
 
 RING_DEPTH = 4      # edges in flight per warp: RING_DEPTH - 1
 
+# Occupancy targets (CTAs of 4 warps per SM) for (forward, backward), by signature.  ptxas caps registers at
+# 65536 / (128 * target); the values below were checked to compile without spills (cuobjdump --dump-resource-usage).
+MIN_CTAS = {
+    'c377d4386a8': (8, 6),      # SevenNet-0 inner layers: 64 / 80 registers
+    'c703e622066': (4, 3),      # SevenNet-l3i5 inner layers: 127 / 168 registers
+}
+MIN_CTAS_DEFAULT = (1, 1)
+
 
 def _stage_floats(G: _Group, spec: ConvSpec) -> int:
     S = (spec.lmax_sh + 1) ** 2
@@ -200,7 +208,7 @@ def _unit_open(L, G: _Group, first: bool, last: bool):
 
 def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
     L = []
-    L.append(f'KERNEL_HEAD(conv_fwd_{sig})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
+    L.append(f'KERNEL_HEAD(conv_fwd_{sig}, {MIN_CTAS.get(sig, MIN_CTAS_DEFAULT)[0]})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
     L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
     L.append('    int n_dst, float inv_denom, float* __restrict__ out, int ldo)')
     L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
@@ -238,7 +246,7 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
     while NP < S:
         NP *= 2
     L = []
-    L.append(f'KERNEL_HEAD(conv_bwd_{sig})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
+    L.append(f'KERNEL_HEAD(conv_bwd_{sig}, {MIN_CTAS.get(sig, MIN_CTAS_DEFAULT)[1]})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
     L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
     L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
     L.append('    float* __restrict__ dW, float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')

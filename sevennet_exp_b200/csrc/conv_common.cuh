@@ -8,7 +8,8 @@
 #ifndef SEVENN_EMU
 #include <cuda_runtime.h>
 #define CONV_WARPS_PER_CTA 4
-#define KERNEL_HEAD(name) __global__ void __launch_bounds__(32 * CONV_WARPS_PER_CTA) name
+// minctas: occupancy target handed to ptxas (register cap = 65536 / (128 * minctas)); chosen per kernel by the generator
+#define KERNEL_HEAD(name, minctas) __global__ void __launch_bounds__(32 * CONV_WARPS_PER_CTA, minctas) name
 #define UNIT_LOOP_BEGIN(n, nunits, ringf) { __shared__ float ring_all[CONV_WARPS_PER_CTA * (ringf)]; \
     float* ring = ring_all + (threadIdx.x >> 5) * (ringf); (void)ring; \
     const int lane = threadIdx.x & 31; const int unit = blockIdx.y; \
@@ -47,7 +48,7 @@ __device__ __forceinline__ void sevenn_dy_accumulate(float (&v)[NP], int lane, f
 #define LAUNCH(kern, n, nunits, stream) kern<<<dim3(((n) + CONV_WARPS_PER_CTA - 1) / CONV_WARPS_PER_CTA, (nunits)), 32 * CONV_WARPS_PER_CTA, 0, (cudaStream_t)(stream)>>>
 #define LAUNCH_STATUS() ((int)cudaGetLastError())
 #else
-#define KERNEL_HEAD(name) static void name
+#define KERNEL_HEAD(name, minctas) static void name
 #define UNIT_LOOP_BEGIN(n, nunits, ringf) { for (int unit = 0; unit < (nunits); ++unit) for (int row = 0; row < (n); ++row) \
     for (int lane = 0; lane < 32; ++lane) {
 #define UNIT_LOOP_END }}
