@@ -76,6 +76,18 @@ class Lib:
         if rc != 0:
             raise SevennError(f'{name} failed with status {rc}')
 
+    def fused_fwd(self, sig):
+        """Fused radial-MLP-last-layer + convolution forward of this signature, or None."""
+        key = ('fused', sig)
+        if key not in self._conv:
+            f = getattr(self.cdll, f'sevenn_conv_fwd_fused_{sig}', None) if hasattr(
+                self.cdll, f'sevenn_conv_fwd_fused_{sig}') else None
+            if f is not None:
+                f.argtypes = [c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_i, c_i, c_f, c_p, c_i, c_p, c_p]
+                f.restype = c_i
+            self._conv[key] = f
+        return self._conv[key]
+
     def has_conv(self, sig):
         return hasattr(self.cdll, f'sevenn_conv_fwd_{sig}')
 

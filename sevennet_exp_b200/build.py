@@ -46,22 +46,28 @@ def _compile(src, obj):
     if os.path.exists(obj) and os.path.getmtime(obj) >= max(
             os.path.getmtime(src), os.path.getmtime(os.path.join(CSRC, 'sevenn_common.cuh')),
             os.path.getmtime(os.path.join(CSRC, 'conv_common.cuh')),
+            os.path.getmtime(os.path.join(CSRC, 'fused_common.cuh')),
             os.path.getmtime(os.path.join(HERE, '..', 'include', 'sevenn_b200.h'))):
         return
     subprocess.check_call([nvcc()] + NVCC_FLAGS + ['-I', CSRC, '-c', src, '-o', obj])
 
 
 def write_generated(specs):
-    from .codegen import conv_codegen
+    from .codegen import conv_codegen, fused_codegen
     os.makedirs(GEN, exist_ok=True)
     paths = []
     for sig, spec in specs.items():
-        p = os.path.join(GEN, f'conv_{sig}.cu')
-        text = conv_codegen.generate(spec)
-        if not os.path.exists(p) or open(p).read() != text:
-            with open(p, 'w') as f:
-                f.write(text)
-        paths.append(p)
+        units = [(f'conv_{sig}.cu', conv_codegen.generate(spec))]
+        # experimental fused radial-MLP + convolution forward (correct, but slower than GEMM + conv on B200: see
+        # DESIGN.md 6.3); built only on request, nothing in the product path calls it
+        if os.environ.get('SEVENN_BUILD_FUSED') == '1' and fused_codegen.supported(spec):
+            units.append((f'fused_{sig}.cu', fused_codegen.generate(spec)))
+        for name, text in units:
+            p = os.path.join(GEN, name)
+            if not os.path.exists(p) or open(p).read() != text:
+                with open(p, 'w') as f:
+                    f.write(text)
+            paths.append(p)
     return paths
 
 
