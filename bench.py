@@ -250,6 +250,9 @@ def main():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours')
+    ap.add_argument('--workload', default='cfg2', help="N>1 only: 'cfg2' (weak scaling, default) or 'si1m' = BASELINE "
+                    "config 4, strong scaling: one 1M-atom bulk-Si cell (50^3 diamond cells) cut over the N GPUs")
+    ap.add_argument('--si-cells', type=int, default=50)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != 'reference' else args.warmup
     if args.impl == 'reference':

@@ -24,16 +24,26 @@ def run(args):
     if not dist.is_initialized():
         dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
     grid = brick_grid(world)
-    numbers0, pos0, cell0 = B.workload()
-    reps = np.array(grid)
-    shifts = np.stack(np.meshgrid(*[np.arange(r) for r in reps], indexing='ij'), -1).reshape(-1, 3)
-    pos = np.concatenate([pos0 + s @ cell0 for s in shifts])
-    numbers = np.tile(numbers0, len(shifts))
-    cell = cell0 * reps[:, None]
+    strong = getattr(args, 'workload', 'cfg2') == 'si1m'
+    if strong:
+        # BASELINE config 4: one bulk-Si cell (50^3 conventional cells = 1,000,000 atoms, rattle 0.05 A, seed 2),
+        # strong scaling: the same cell is cut into `world` bricks
+        from tests.structures import diamond_si
+        nc = int(args.si_cells)
+        numbers, pos, cell = diamond_si((nc, nc, nc))
+        pos = pos + np.random.default_rng(2).normal(0.0, 0.05, pos.shape)
+    else:
+        numbers0, pos0, cell0 = B.workload()
+        reps = np.array(grid)
+        shifts = np.stack(np.meshgrid(*[np.arange(r) for r in reps], indexing='ij'), -1).reshape(-1, 3)
+        pos = np.concatenate([pos0 + s @ cell0 for s in shifts])
+        numbers = np.tile(numbers0, len(shifts))
+        cell = cell0 * reps[:, None]
     n_total = len(numbers)
 
     cfg = B.model_config()
-    calc = SevenNetCalculator((cfg, B.random_state_dict(cfg)), file_type='model_instance', device=dev)
+    calc = SevenNetCalculator((cfg, B.random_state_dict(cfg)), file_type='model_instance', device=dev,
+                              keep_weights=not strong)
     dec = Decomposition(numbers, pos, cell, calc.cutoff, grid, rank)
     halo = Halo(dec, calc.engine.lib, dev)
     types_dev = torch.from_numpy(calc._lut[dec.numbers].astype(np.int32)).to(dev)
@@ -45,7 +55,7 @@ def run(args):
 
     for _ in range(max(args.warmup, 3)):
         E, F, vir, g = step()
-    if os.environ.get('SEVENN_CHECK'):
+    if os.environ.get('SEVENN_CHECK') and not strong:
         # decomposed == single-domain evaluation of the whole cell on one GPU (test_lammps.py:278-316 gate)
         ref = calc.compute(numbers, pos, cell, [True] * 3)
         dE = abs(E.item() - ref['energy']) / n_total
@@ -101,10 +111,13 @@ def run(args):
         line = {
             'metric': B.METRIC, 'value': n_total / (ms_step * 1e-3), 'unit': B.UNIT, 'n_gpus': world,
             'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_step, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': f'SevenNet-0 E+F+S, bulk HfO2 cfg2 cell replicated {grid[0]}x{grid[1]}x{grid[2]} '
-                                   f'({n_total} atoms), brick domain decomposition, ghost feature exchange per layer',
-                       'n_atoms': n_total, 'atoms_per_gpu': n_total // world,
+            'scaling': 'strong' if strong else 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': (f'SevenNet-0 E+F+S, bulk Si {args.si_cells}^3 diamond cells ({n_total} atoms) cut into '
+                                    f'{grid[0]}x{grid[1]}x{grid[2]} bricks, ghost feature exchange per layer'
+                                    if strong else
+                                    f'SevenNet-0 E+F+S, bulk HfO2 cfg2 cell replicated {grid[0]}x{grid[1]}x{grid[2]} '
+                                    f'({n_total} atoms), brick domain decomposition, ghost feature exchange per layer'),
+                       'n_atoms': n_total, 'atoms_per_gpu': n_total // world, 'energy_per_atom_eV': float(E.item()) / n_total,
                        'ghosts_per_gpu_max': int(smax[1].item()), 'edges_total': int(stats[2].item()),
                        'halo_row_bytes': x_dim * 4,
                        'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)',

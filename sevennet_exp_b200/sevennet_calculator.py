@@ -50,7 +50,10 @@ class SevenNetCalculator(_AseCalculator):
 
     def __init__(self, model: Union[str, tuple] = '7net-0', file_type: str = 'checkpoint',
                  device: Union[torch.device, str] = 'auto', modal: Optional[str] = None,
-                 enable_cueq: bool = False, sevennet_config: Optional[Dict] = None, **kwargs):
+                 enable_cueq: bool = False, sevennet_config: Optional[Dict] = None, keep_weights: bool = True,
+                 **kwargs):
+        # keep_weights=False: the per-edge tensor-product weights (the largest activation, 3.84 KB per edge and layer
+        # for SevenNet-0) are recomputed in the reverse pass instead of being kept: ~3x more atoms per GPU
         super().__init__(**kwargs)
         if enable_cueq:
             raise ValueError('enable_cueq: the B200 backend replaces cuEquivariance, not combines with it')
@@ -83,7 +86,7 @@ class SevenNetCalculator(_AseCalculator):
         self.sevennet_config = sevennet_config or cfg
         self.spec, self.cutoff = spec, spec.cutoff
         self.type_map = spec.type_map
-        self.engine = Engine(spec, sd, device=self.device)
+        self.engine = Engine(spec, sd, device=self.device, keep_weights=keep_weights)
         self.nl = NeighborList(device=self.device)
         lut = -np.ones(120, dtype=np.int64)
         for z, i in self.type_map.items():
