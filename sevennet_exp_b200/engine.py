@@ -303,12 +303,66 @@ class Engine(Kernels):
                     f"no prebuilt conv kernel for signature {lay['sig']} ({ir.irreps_str(L.conv.lx.groups)}); "
                     'build it with sevennet_exp_b200.build.build(extra_specs=...)')
             self.layers.append(lay)
+        # The radial MLPs depend on the edge embedding only, so the first hidden layer of all convolution layers is one
+        # GEMM [E, nb] x [nb, L*h1] (and one [E, L*h1] x [L*h1, nb] in the reverse pass) instead of L latency-bound ones.
+        hs = [tuple(L.conv.hidden[:-1]) for L in spec.layers]
+        self.mlp_batched = (len(set(hs)) == 1 and len(hs[0]) >= 2 and os.environ.get('SEVENN_MLP_BATCH', '1') == '1')
+        if self.mlp_batched:
+            W1 = np.concatenate([lay['mlp'][0].cpu().numpy() for lay in self.layers], axis=1)   # [nb, L*h1]
+            self.mlp_w1cat = f32(W1)
+            self.mlp_w1catT = f32(np.ascontiguousarray(W1.T))
+            self.mlp_h1 = hs[0][1]
         self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev)
         self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev)
         self.scale = f32(sd['rescale_atomic_energy.scale'])
         self.shift = f32(sd['rescale_atomic_energy.shift'])
         self.act_radial = ACT_ID[spec.act_radial]
         self.cst_radial = ir.normalize2mom_const(spec.act_radial)
+
+    def _mlp_fwd_rest(self, lay, t, pre1_all, act1_all, E):
+        """Layers >= 1 of the radial MLP of convolution layer t; layer 0 comes from the batched GEMM (column block t)."""
+        Ws = lay['mlp']
+        h1, ld = self.mlp_h1, act1_all.shape[1]
+        pres, acts = [], []
+        cur, c_off, c_ld = act1_all, t * h1, ld
+        for k in range(1, len(Ws)):
+            K, N = Ws[k].shape
+            if k < len(Ws) - 1:
+                pre, act = self._empty(E, N), self._empty(E, N)
+                self._gemm(cur, c_off, c_ld, 0, Ws[k], pre, 0, N, 0, E, 1, N, K, epi=2, act=lay.get('act', self.act_radial),
+                           cst=lay.get('cst', self.cst_radial), C2=act)
+                pres.append(pre); acts.append(act)
+                cur, c_off, c_ld = act, 0, N
+            else:
+                w = self._empty(E, N)
+                self._gemm(cur, c_off, c_ld, 0, Ws[k], w, 0, N, 0, E, 1, N, K)
+        return pres, acts, w, (cur, c_off, c_ld)
+
+    def _mlp_last_from(self, lay, h_last, E):
+        cur, c_off, c_ld = h_last
+        W = lay['mlp'][-1]
+        K, N = W.shape
+        w = self._empty(E, N)
+        self._gemm(cur, c_off, c_ld, 0, W, w, 0, N, 0, E, 1, N, K)
+        return w
+
+    def _mlp_bwd_rest(self, lay, t, dW, pres, pre1_all, dact1_all, E):
+        """Reverse of layers >= 1; the gradient w.r.t. the first hidden activation lands in column block t of
+        dact1_all (already multiplied by act'(pre1)), the batched GEMM to d(emb) follows after the layer loop."""
+        WT = lay['mlpT']
+        h1, ld = self.mlp_h1, dact1_all.shape[1]
+        cur = dW
+        for k in range(len(WT) - 1, 0, -1):
+            N, K = WT[k].shape   # WT[k] is [h_out, h_in]
+            if k > 1:
+                nxt = self._empty(E, K)
+                self._gemm(cur, 0, N, 0, WT[k], nxt, 0, K, 0, E, 1, K, N, epi=3, act=lay.get('act', self.act_radial),
+                           cst=lay.get('cst', self.cst_radial), P=pres[k - 2])
+                cur = nxt
+            else:
+                # C and P share offset / row stride: both are column block t of [E, L*h1] buffers
+                self._gemm(cur, 0, N, 0, WT[k], dact1_all, t * h1, ld, 0, E, 1, K, N, epi=3,
+                           act=lay.get('act', self.act_radial), cst=lay.get('cst', self.cst_radial), P=pre1_all)
 
     # ------------------------------------------------------------------ evaluation
     def evaluate(self, g: Graph, halo=None, want_forces: bool = True, debug: Optional[dict] = None):
@@ -329,6 +383,13 @@ class Engine(Kernels):
         self.n_launch += 2
         saved = []
         n_x = nn                      # rows of x that are valid (all nodes for layer 0, owned afterwards)
+        pre1_all = act1_all = None
+        if self.mlp_batched and E > 0:
+            self._mark('mlp_fwd')
+            nL1 = self.mlp_w1cat.shape[1]
+            pre1_all, act1_all = self._empty(E, nL1), self._empty(E, nL1)
+            self._gemm(emb, 0, sp.n_basis, 0, self.mlp_w1cat, pre1_all, 0, nL1, 0, E, 1, nL1, sp.n_basis, epi=2,
+                       act=self.act_radial, cst=self.cst_radial, C2=act1_all)
         for t, lay in enumerate(self.layers):
             L = lay['spec']
             dx_in, dmid, dgi, dout = L.conv.lx.dim, L.conv.lmid.dim, L.gate.lin.dim, L.gate.lout.dim
@@ -343,7 +404,11 @@ class Engine(Kernels):
             if n_x < nn:
                 halo.forward(t, h)    # fills rows [n_local, n_nodes)
             self._mark('mlp_fwd')
-            pres, acts, w = self._mlp_fwd(lay, emb, E)
+            if pre1_all is not None:
+                pres, acts, w, h_last = self._mlp_fwd_rest(lay, t, pre1_all, act1_all, E)
+            else:
+                pres, acts, w = self._mlp_fwd(lay, emb, E)
+                h_last = (acts[-1], 0, acts[-1].shape[1]) if acts else (emb, 0, emb.shape[1])
             self._mark(f'conv_fwd_{lay["sig"]}')
             agg = self._empty(nl, dmid)
             fwd, _ = lib.conv(lay['sig'])
@@ -359,7 +424,7 @@ class Engine(Kernels):
             lib.call('sevenn_gate_fwd', _p(pre), dgi, _p(xo), dout, nl, lay['pieces'], len(L.gate.pieces), st)
             self.n_launch += 1
             saved.append({'pre': pre, 'h': h, 'w': w if self.keep_w else None, 'pres': pres,
-                          'h_last': acts[-1] if acts else emb})
+                          'h_last': h_last})
             if debug is not None:
                 debug[f'{t}_x'] = xo
                 debug[f'{t}_agg'] = agg
@@ -391,6 +456,7 @@ class Engine(Kernels):
         self._linear_bwd(self.read2, seed, nl, dr1)
         dx = self._zeros(nl, sp.read1.lin.dim) if self.read1.bwd_needs_zero else self._empty(nl, sp.read1.lin.dim)
         self._linear_bwd(self.read1, dr1, nl, dx)
+        dact1_all = None
         for t in range(len(self.layers) - 1, -1, -1):
             lay, sv = self.layers[t], saved[t]
             L = lay['spec']
@@ -404,7 +470,7 @@ class Engine(Kernels):
             dagg = self._zeros(nl, dmid) if lay['si2'].bwd_needs_zero else self._empty(nl, dmid)
             self._linear_bwd(lay['si2'], dpre, nl, dagg)
             self._mark('mlp_recompute')
-            w = sv['w'] if sv['w'] is not None else self._mlp_last(lay, sv['h_last'], E)
+            w = sv['w'] if sv['w'] is not None else self._mlp_last_from(lay, sv['h_last'], E)
             self._mark(f'conv_bwd_{lay["sig"]}')
             dW = self._empty(max(E, 1), L.conv.wn)
             unused = any(not any(p.gx == gi for p in L.conv.paths) for gi in range(len(L.conv.lx.groups)))
@@ -417,7 +483,12 @@ class Engine(Kernels):
             self.n_launch += 1
             del w
             self._mark('mlp_bwd')
-            self._mlp_bwd(lay, dW, sv['pres'], demb, E)
+            if pre1_all is not None:
+                if dact1_all is None:
+                    dact1_all = self._empty(E, pre1_all.shape[1])
+                self._mlp_bwd_rest(lay, t, dW, sv['pres'], pre1_all, dact1_all, E)
+            else:
+                self._mlp_bwd(lay, dW, sv['pres'], demb, E)
             del dW
             if t == 0:
                 break                 # layer-0 inputs do not depend on positions
@@ -433,6 +504,10 @@ class Engine(Kernels):
             self._linear_bwd(lay['si1'], dh, nl, dxn)
             self._linear_bwd(lay['sc'], dpre, nl, dxn, accumulate=True, types=g.types)
             dx = dxn
+        if dact1_all is not None:
+            self._mark('mlp_bwd')
+            nL1 = dact1_all.shape[1]
+            self._gemm(dact1_all, 0, nL1, 0, self.mlp_w1catT, demb, 0, sp.n_basis, 0, E, 1, sp.n_basis, nL1, epi=1)
         self._mark('edge_bwd_force')
         fvec = self._empty(max(E, 1), 3)
         lib.call('sevenn_edge_bwd', _p(g.edge_vec), E, *edge_args, _p(dY), n_slab, max(E, 1) * S, _p(demb), _p(fvec), st)
