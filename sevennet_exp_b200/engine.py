@@ -306,6 +306,8 @@ class Engine(Kernels):
         # The radial MLPs depend on the edge embedding only, so the first hidden layer of all convolution layers is one
         # GEMM [E, nb] x [nb, L*h1] (and one [E, L*h1] x [L*h1, nb] in the reverse pass) instead of L latency-bound ones.
         hs = [tuple(L.conv.hidden[:-1]) for L in spec.layers]
+        self.overlap = os.environ.get('SEVENN_OVERLAP', '1') == '1'
+        self._side = None
         self.mlp_batched = (len(set(hs)) == 1 and len(hs[0]) >= 2 and os.environ.get('SEVENN_MLP_BATCH', '1') == '1')
         if self.mlp_batched:
             W1 = np.concatenate([lay['mlp'][0].cpu().numpy() for lay in self.layers], axis=1)   # [nb, L*h1]
@@ -384,12 +386,36 @@ class Engine(Kernels):
         saved = []
         n_x = nn                      # rows of x that are valid (all nodes for layer 0, owned afterwards)
         pre1_all = act1_all = None
+        # The radial MLPs need the edge embedding only: with `overlap` they run for all layers on a side stream and
+        # fill the SMs that the small, latency-bound node kernels (self connection, self interactions, gate) leave idle.
+        w_bytes = 4 * E * sum(lay['spec'].conv.wn for lay in self.layers)
+        overlap = (self.overlap and self.mlp_batched and self.keep_w and self.prof is None and E > 0
+                   and self.dev.type == 'cuda' and w_bytes < (16 << 30))
+        main = torch.cuda.current_stream() if self.dev.type == 'cuda' else None
+        mlp_out, mlp_ev = [], []
         if self.mlp_batched and E > 0:
             self._mark('mlp_fwd')
             nL1 = self.mlp_w1cat.shape[1]
-            pre1_all, act1_all = self._empty(E, nL1), self._empty(E, nL1)
-            self._gemm(emb, 0, sp.n_basis, 0, self.mlp_w1cat, pre1_all, 0, nL1, 0, E, 1, nL1, sp.n_basis, epi=2,
-                       act=self.act_radial, cst=self.cst_radial, C2=act1_all)
+            if overlap:
+                if self._side is None:
+                    self._side = torch.cuda.Stream(device=self.dev)
+                side = self._side
+                ev0 = main.record_event()
+                emb.record_stream(side)
+                with torch.cuda.stream(side):
+                    side.wait_event(ev0)
+                    pre1_all, act1_all = self._empty(E, nL1), self._empty(E, nL1)
+                    self._gemm(emb, 0, sp.n_basis, 0, self.mlp_w1cat, pre1_all, 0, nL1, 0, E, 1, nL1, sp.n_basis, epi=2,
+                               act=self.act_radial, cst=self.cst_radial, C2=act1_all)
+                    for t, lay in enumerate(self.layers):
+                        res = self._mlp_fwd_rest(lay, t, pre1_all, act1_all, E)
+                        res[2].record_stream(main)                  # w: consumed by the convolutions on the main stream
+                        mlp_out.append(res)
+                        mlp_ev.append(side.record_event())
+            else:
+                pre1_all, act1_all = self._empty(E, nL1), self._empty(E, nL1)
+                self._gemm(emb, 0, sp.n_basis, 0, self.mlp_w1cat, pre1_all, 0, nL1, 0, E, 1, nL1, sp.n_basis, epi=2,
+                           act=self.act_radial, cst=self.cst_radial, C2=act1_all)
         for t, lay in enumerate(self.layers):
             L = lay['spec']
             dx_in, dmid, dgi, dout = L.conv.lx.dim, L.conv.lmid.dim, L.gate.lin.dim, L.gate.lout.dim
@@ -404,7 +430,10 @@ class Engine(Kernels):
             if n_x < nn:
                 halo.forward(t, h)    # fills rows [n_local, n_nodes)
             self._mark('mlp_fwd')
-            if pre1_all is not None:
+            if overlap:
+                main.wait_event(mlp_ev[t])
+                pres, acts, w, h_last = mlp_out[t]
+            elif pre1_all is not None:
                 pres, acts, w, h_last = self._mlp_fwd_rest(lay, t, pre1_all, act1_all, E)
             else:
                 pres, acts, w = self._mlp_fwd(lay, emb, E)
@@ -486,7 +515,16 @@ class Engine(Kernels):
             if pre1_all is not None:
                 if dact1_all is None:
                     dact1_all = self._empty(E, pre1_all.shape[1])
-                self._mlp_bwd_rest(lay, t, dW, sv['pres'], pre1_all, dact1_all, E)
+                    if overlap:
+                        dact1_all.record_stream(self._side)
+                if overlap:
+                    ev = main.record_event()
+                    dW.record_stream(self._side)
+                    with torch.cuda.stream(self._side):
+                        self._side.wait_event(ev)
+                        self._mlp_bwd_rest(lay, t, dW, sv['pres'], pre1_all, dact1_all, E)
+                else:
+                    self._mlp_bwd_rest(lay, t, dW, sv['pres'], pre1_all, dact1_all, E)
             else:
                 self._mlp_bwd(lay, dW, sv['pres'], demb, E)
             del dW
@@ -506,6 +544,8 @@ class Engine(Kernels):
             dx = dxn
         if dact1_all is not None:
             self._mark('mlp_bwd')
+            if overlap:
+                main.wait_event(self._side.record_event())
             nL1 = dact1_all.shape[1]
             self._gemm(dact1_all, 0, nL1, 0, self.mlp_w1catT, demb, 0, sp.n_basis, 0, E, 1, sp.n_basis, nL1, epi=1)
         self._mark('edge_bwd_force')
