@@ -558,5 +558,5 @@ class Engine(Kernels):
         lib.call('sevenn_colsum_f64', _p(vir), nn, 6, _p(part), _p(v6), st)
         self.n_launch += 4
         self._mark('end')
-        out.update({'forces': F, 'virial6': v6, 'f_edge': fvec})
+        out.update({'forces': F, 'virial6': v6, 'f_edge': fvec, 'virial_per_atom': vir})
         return out

@@ -115,6 +115,54 @@ class SevenNetCalculator(_AseCalculator):
         return {'energy': energy, 'free_energy': energy, 'forces': forces, 'stress': stress,
                 'energies': energies, 'inferred_stress': stress_model, 'n_edges': g.n_edges}
 
+    def compute_batch(self, structures):
+        """Several structures in one evaluation (the reference batches graphs with torch_geometric's Collater,
+        sevenn/train/dataload.py + nn/force_output.py:210-219 per-graph stress): the graphs are concatenated
+        block-diagonally (node indices offset per graph), the kernels run once over the merged edge list, and
+        energy / virial are reduced per graph.  ``structures`` = iterable of (numbers, positions, cell, pbc)."""
+        from .engine import Graph
+        from .neighbor import csc_build
+        parts, types_all, n_off, e_off = [], [], [0], [0]
+        for numbers, positions, cell, pbc in structures:
+            numbers = np.asarray(numbers)
+            types = self._lut[numbers]
+            if (types < 0).any():
+                bad = sorted({int(z) for z in numbers[types < 0]})
+                raise ValueError(f'Unknown atomic numbers {bad} for this model')
+            pos = np.ascontiguousarray(np.asarray(positions, dtype=np.float64))
+            r = self.nl.build(pos, cell, pbc, self.cutoff)
+            parts.append(r)
+            types_all.append(types.astype(np.int32))
+            n_off.append(n_off[-1] + len(numbers))
+            e_off.append(e_off[-1] + r['n_edges'])
+        nB, n_tot = len(parts), n_off[-1]
+        if nB == 0:
+            return []
+        dev = self.device
+        types_dev = torch.from_numpy(np.concatenate(types_all)).to(dev)
+        col = torch.cat([r['col'] + n_off[b] for b, r in enumerate(parts)]).to(torch.int32).contiguous()
+        rowptr = torch.cat([parts[0]['rowptr'][:1]] + [r['rowptr'][1:] + e_off[b] for b, r in enumerate(parts)]
+                           ).to(torch.int32).contiguous()
+        edge_vec = torch.cat([r['edge_vec'] for r in parts]).contiguous()
+        cptr, cedge = csc_build(self.nl.lib, col, n_tot, dev, self.nl._stream())
+        g = Graph(types_dev, edge_vec, rowptr, col, cptr, cedge, n_tot, 1.0)
+        out = self.engine.evaluate(g)
+        seg = torch.repeat_interleave(torch.arange(nB, device=dev),
+                                      torch.tensor(np.diff(n_off), device=dev))
+        e_g = torch.zeros(nB, dtype=torch.float64, device=dev).index_add_(0, seg, out['atomic_energy'].double())
+        v_g = torch.zeros(nB, 6, dtype=torch.float64, device=dev).index_add_(0, seg, out['virial_per_atom'].double())
+        host_e, host_v = e_g.cpu().numpy(), v_g.cpu().numpy()
+        F = out['forces'].double().cpu().numpy()
+        ae = out['atomic_energy'].double().cpu().numpy()
+        res = []
+        for b, r in enumerate(parts):
+            stress_model = -host_v[b] / r['volume']
+            res.append({'energy': float(host_e[b]), 'free_energy': float(host_e[b]),
+                        'forces': F[n_off[b]:n_off[b + 1]], 'stress': -stress_model[[0, 1, 2, 4, 5, 3]],
+                        'energies': ae[n_off[b]:n_off[b + 1]], 'inferred_stress': stress_model,
+                        'n_edges': r['n_edges']})
+        return res
+
     def calculate(self, atoms=None, properties=None, system_changes=all_changes):
         super().calculate(atoms, properties, system_changes)
         if atoms is None:

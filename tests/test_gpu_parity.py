@@ -286,3 +286,28 @@ def test_nn_module_seam_on_gpu(lib, name, n_atoms):
     dS = (out[S.STRESS].cpu().double() - ref[S.STRESS].detach()).abs().max().item() * KBAR
     assert dE < 1e-5 and dF < 1e-4, (dE, dF)
     assert dS < 1e-3 * max(1.0, ref[S.STRESS].abs().max().item() * KBAR * 1e-3), dS
+
+
+def test_batched_structures_match_single(lib):
+    """compute_batch (block-diagonal graph, per-graph energy / stress reduction; reference: PyG batching +
+    force_output.py:210-219) == one compute() per structure, incl. a non-periodic and an empty-neighbour structure."""
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cfg, model = _random_model('test-so3-l2')
+    calc = SevenNetCalculator((cfg, model.state_dict()), file_type='model_instance')
+    zs = list(cfg['_type_map'])
+    structs = []
+    for k, n in enumerate((17, 64, 5, 40)):
+        numbers, pos, cell = random_cell(n, zs, density=0.05, seed=10 + k)
+        structs.append((numbers, pos, cell, [True] * 3 if k != 2 else [False] * 3))
+    structs.append((np.array([zs[0]]), np.zeros((1, 3)), np.eye(3) * 20.0, [True] * 3))      # no neighbours at all
+    batch = calc.compute_batch(structs)
+    assert len(batch) == len(structs)
+    for s, b in zip(structs, batch):
+        one = calc.compute(*s)
+        assert b['n_edges'] == one['n_edges']
+        # the merged graph is large enough for the tcgen05 (3xTF32) GEMM arm, the single small structures run the
+        # exact-fp32 SIMT arm: agreement is at the level test_engine_tc_and_simt_arms_agree allows
+        assert abs(b['energy'] - one['energy']) < 5e-6 * max(1, len(s[0]))
+        assert np.abs(b['forces'] - one['forces']).max() < 5e-5
+        assert np.abs(b['stress'] - one['stress']).max() * KBAR < 1e-3
+        assert np.abs(b['energies'] - one['energies']).max() < 5e-5
