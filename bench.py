@@ -232,9 +232,13 @@ def run_single(args):
                 'h2d_bytes_per_step': int(pos.nbytes + n * 4), 'd2h_bytes_per_step': int((1 + 6 + 3 * n + n) * 8)},
         'gpu_launches': int(launches),
         'clocks': sampler.summary(),
-        'roofline': {'bound': 'hbm', 'kernel': f'conv_bwd (inner layer, {len(inner.lx.groups)} group launches)',
+        'roofline': {'bound': 'hbm', 'kernel': f'conv_bwd_{inner.signature()} (inner layers, one launch per layer)',
                      'achieved': achieved, 'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': achieved / peak,
-                     'algorithmic_bytes': alg, 'ms': dom_ms, 'traffic': None,
+                     'algorithmic_bytes': alg, 'ms': dom_ms,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel on this workload
+                     # (ncu --set full, profiles/r01c_conv_fwd_bwd_raw.csv: 937 MB + 1,141 MB); below the algorithmic
+                     # bytes because the gathered source rows (7.9 MB of node features) are served by L2
+                     'traffic': 2078e6 if (n, inner.signature()) == (4096, 'c377d4386a8') else None,
                      'conv_fwd_achieved': fwd_ach, 'conv_fwd_frac': fwd_ach / peak},
         'stage_ms': stage_sorted,
         'cpu_baseline': {'value': cpu_v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
