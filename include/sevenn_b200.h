@@ -55,6 +55,17 @@ int sevenn_edge_bwd(const float* edge_vec, long long n_edges, int lmax, int norm
                     const float* dY /* n_slabs x [E,(lmax+1)^2], summed in slab order */, int n_slabs,
                     long long slab_stride /* floats */, const float* demb, float* f_edge /* E,3 */, void* stream);
 
+/* Tabulated-radial variants.  The radial MLP (sevenn/nn/convolution.py:92-101,121) maps the edge length alone to the
+ * tensor-product weights; for fixed model weights that map is tabulated on n_int intervals of width h = rc / n_int
+ * (cubic Hermite nodes, sevennet_exp_b200/radial_table.py) and the convolutions interpolate it per edge.
+ * Yt row: (Y_0 .. Y_{S-1}, t, bits(i)), S = (lmax+1)^2, edge length = (i + t) h. */
+int sevenn_edge_fwd_tab(const float* edge_vec, long long n_edges, int lmax, int normalize, float inv_h, int n_int,
+                        float* Yt /* E,S+2 */, void* stream);
+/* dY rows: (dE/dY_0 .. dE/dY_{S-1}, sum_c dE/dw_c * h dw_c/dr), one slab per convolution unit */
+int sevenn_edge_bwd_tab(const float* edge_vec, long long n_edges, int lmax, int normalize, float inv_h,
+                        const float* dY /* n_slabs x [E,S+1] */, int n_slabs, long long slab_stride /* floats */,
+                        float* f_edge /* E,3 */, void* stream);
+
 /* ---- dense contractions: replaces e3nn o3.Linear (sevenn/nn/linear.py:49-63,94), the radial MLP
  * e3nn FullyConnectedNet (sevenn/nn/convolution.py:92-101,121) and their input gradients. */
 typedef struct {
@@ -113,8 +124,11 @@ int sevenn_scatter_add_rows(const float* src, int D, const int* idx, long long n
 
 /* ---- fused gather + uvu CG tensor product + segment sum (generated per irreps signature <sig>):
  *   int sevenn_conv_fwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo, stream)
- *   int sevenn_conv_bwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY, stream)
- *   int sevenn_conv_info_<sig>(&x_dim, &mid_dim, &wn, &sh_dim)
+ *   int sevenn_conv_bwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY, dy_stride, stream)
+ *   int sevenn_conv_info_<sig>(&x_dim, &mid_dim, &wn, &sh_dim, &units)
+ * tabulated-radial variants (w interpolated from tab[n_int][wn] float4 nodes; Yt / dY rows as for sevenn_edge_*_tab):
+ *   int sevenn_conv_fwd_tab_<sig>(x, ldx, Yt, tab, rowptr, col, n_dst, inv_denom, out, ldo, stream)
+ *   int sevenn_conv_bwd_tab_<sig>(x, ldx, Yt, tab, rowptr, col, n_dst, inv_denom, gout, ldo, dxe, lddx, dY, dy_stride, stream)
  * replaces IrrepsConvolution.forward's TensorProduct + message_gather (sevenn/nn/convolution.py:16-25,118-137). */
 
 #ifdef __cplusplus

@@ -36,6 +36,8 @@ SIGNATURES = {
     'sevenn_csc_build': ([c_p, c_ll, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p], c_i),
     'sevenn_edge_fwd': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_p], c_i),
     'sevenn_edge_bwd': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_i, c_ll, c_p, c_p, c_p], c_i),
+    'sevenn_edge_fwd_tab': ([c_p, c_ll, c_i, c_i, c_f, c_i, c_p, c_p], c_i),
+    'sevenn_edge_bwd_tab': ([c_p, c_ll, c_i, c_i, c_f, c_p, c_i, c_ll, c_p, c_p], c_i),
     'sevenn_gemm_f32': ([ctypes.POINTER(GemmArgs), c_p], c_i),
     'sevenn_gemm_tc_plan': ([c_i, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_i), ctypes.POINTER(c_i),
                              ctypes.POINTER(c_ll)], c_i),
@@ -54,6 +56,7 @@ SIGNATURES = {
 }
 CONV_FWD_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p]
 CONV_BWD_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p, c_p, c_i, c_p, c_ll, c_p]
+CONV_BWD_TAB_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p, c_i, c_p, c_ll, c_p]
 
 
 class SevennError(RuntimeError):
@@ -86,6 +89,17 @@ class Lib:
                 f.argtypes = [c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_i, c_i, c_f, c_p, c_i, c_p, c_p]
                 f.restype = c_i
             self._conv[key] = f
+        return self._conv[key]
+
+    def conv_tab(self, sig):
+        """Tabulated-radial forward / backward of this signature (same translation unit as conv())."""
+        key = ('tab', sig)
+        if key not in self._conv:
+            f = getattr(self.cdll, f'sevenn_conv_fwd_tab_{sig}')
+            b = getattr(self.cdll, f'sevenn_conv_bwd_tab_{sig}')
+            f.argtypes, f.restype = CONV_FWD_ARGS, c_i
+            b.argtypes, b.restype = CONV_BWD_TAB_ARGS, c_i
+            self._conv[key] = (f, b)
         return self._conv[key]
 
     def has_conv(self, sig):

@@ -112,6 +112,10 @@ MIN_CTAS = {
     'c703e622066': (4, 3),      # SevenNet-l3i5 inner layers: 127 / 168 registers
 }
 MIN_CTAS_DEFAULT = (1, 1)
+MIN_CTAS_TAB = {
+    'c377d4386a8': (6, 5),
+    'c703e622066': (3, 2),
+}
 
 
 def _stage_floats(G: _Group, spec: ConvSpec) -> int:
@@ -206,17 +210,27 @@ def _unit_open(L, G: _Group, first: bool, last: bool):
         L.append(f'    const bool on = (c32 + lane) < {G.mul};')
 
 
-def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
+def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -> List[str]:
     L = []
-    L.append(f'KERNEL_HEAD(conv_fwd_{sig}, {MIN_CTAS.get(sig, MIN_CTAS_DEFAULT)[0]})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
-    L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
-    L.append('    int n_dst, float inv_denom, float* __restrict__ out, int ldo)')
-    L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
+    mc = (MIN_CTAS_TAB if tab else MIN_CTAS).get(sig, MIN_CTAS_DEFAULT)[0]
+    if tab:
+        L.append(f'KERNEL_HEAD(conv_fwd_tab_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Yt,')
+        L.append('    const float4* __restrict__ tab, const int* __restrict__ rowptr, const int* __restrict__ col,')
+        L.append('    int n_dst, float inv_denom, float* __restrict__ out, int ldo)')
+        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec)})')
+    else:
+        L.append(f'KERNEL_HEAD(conv_fwd_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
+        L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
+        L.append('    int n_dst, float inv_denom, float* __restrict__ out, int ldo)')
+        L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
     for gi, G in enumerate(groups):
         _unit_open(L, G, gi == 0, gi == len(groups) - 1)
         for pi, p in G.paths:
             L.append('    float ' + ', '.join(f'a{pi}_{k} = 0.f' for k in range(2 * p.l3 + 1)) + ';')
-        _pipeline_open(L, G, spec)
+        if tab:
+            _tab_pipeline_open(L, G, spec, False)
+        else:
+            _pipeline_open(L, G, spec)
         for pi, p in G.paths:
             ent, _ = _m_terms(p.l1, p.l2, p.l3)
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}, mul {p.mul}')
@@ -240,17 +254,27 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
     return L
 
 
-def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
+def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -> List[str]:
     S = (spec.lmax_sh + 1) ** 2
+    SD = S + 1 if tab else S          # dY row width: the tabulated kernels append the radial term
     NP = 1
     while NP < S:
         NP *= 2
+    gr_in_butterfly = tab and NP > S
     L = []
-    L.append(f'KERNEL_HEAD(conv_bwd_{sig}, {MIN_CTAS.get(sig, MIN_CTAS_DEFAULT)[1]})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
-    L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
-    L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
-    L.append('    float* __restrict__ dW, float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
-    L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
+    mc = (MIN_CTAS_TAB if tab else MIN_CTAS).get(sig, MIN_CTAS_DEFAULT)[1]
+    if tab:
+        L.append(f'KERNEL_HEAD(conv_bwd_tab_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Yt,')
+        L.append('    const float4* __restrict__ tab, const int* __restrict__ rowptr, const int* __restrict__ col,')
+        L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
+        L.append('    float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
+        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec)})')
+    else:
+        L.append(f'KERNEL_HEAD(conv_bwd_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
+        L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
+        L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
+        L.append('    float* __restrict__ dW, float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
+        L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
     L.append('  float* dYu = dY + (size_t)unit * (size_t)dy_stride;')
     for gi, G in enumerate(groups):
         _unit_open(L, G, gi == 0, gi == len(groups) - 1)
@@ -261,10 +285,16 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
             for k in range(2 * p.l3 + 1):
                 ld = _on(G, f'LDG(grow + {base + k * Mg}) * inv_denom')
                 L.append(f'    const float g{pi}_{k} = {ld};')
-        _pipeline_open(L, G, spec)
+        if tab:
+            _tab_pipeline_open(L, G, spec, True)
+        else:
+            _pipeline_open(L, G, spec)
         L.append(f'        float dyv[{NP}] = {{{", ".join(["0.f"] * NP)}}};')
         L.append('        float ' + ', '.join(f'dx{m} = 0.f' for m in range(G.d1)) + ';')
-        L.append(f'        float* dwr = dW + (size_t)e * {spec.wn} + c32 + lane;')
+        if tab:
+            L.append('        float gr = 0.f;')
+        else:
+            L.append(f'        float* dwr = dW + (size_t)e * {spec.wn} + c32 + lane;')
         for pi, p in G.paths:
             ent, nnz = _m_terms(p.l1, p.l2, p.l3)
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}')
@@ -275,8 +305,12 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
                 terms = [f'M_{i}_{k}*x{i}' for i in range(G.d1) if (i, k) in ent]
                 if terms:
                     dw_terms.append(f'g{pi}_{k}*({" + ".join(terms)})')
-            st = f'dwr[{p.w_off}] = {" + ".join(dw_terms) if dw_terms else "0.f"};'
-            L.append(f'          if (on) {st}' if G.masked else f'          {st}')
+            if tab:
+                if dw_terms:
+                    L.append(f'          gr = fmaf({" + ".join(dw_terms)}, wd{pi}, gr);')
+            else:
+                st = f'dwr[{p.w_off}] = {" + ".join(dw_terms) if dw_terms else "0.f"};'
+                L.append(f'          if (on) {st}' if G.masked else f'          {st}')
             for k in range(2 * p.l3 + 1):
                 idx = [i for i in range(G.d1) if (i, k) in ent]
                 if not idx:
@@ -293,12 +327,149 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
         for m in range(G.d1):
             st = f'dxr[{m * G.mul}] = dx{m};'
             L.append(f'        if (on) {st}' if G.masked else f'        {st}')
-        L.append(f'        sevenn_dy_accumulate<{NP}>(dyv, lane, dYu + (size_t)e * {S}, {S});')
+        if gr_in_butterfly:
+            L.append(f'        dyv[{S}] = gr;')
+        L.append(f'        sevenn_dy_accumulate<{NP}>(dyv, lane, dYu + (size_t)e * {SD}, {SD if gr_in_butterfly else S});')
+        if tab and not gr_in_butterfly:
+            L.append(f'        sevenn_gr_accumulate(gr, lane, dYu + (size_t)e * {SD} + {S});')
         L.append('      }')
         L.append('    }')
         L.append('  }')
     L.append('UNIT_LOOP_END')
     return L
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Tabulated radial weights.  The radial MLP output w[e, :] is a smooth function of the edge length alone, so
+# for fixed model weights it is tabulated once (radial_table.py: fp64, cubic Hermite nodes every h = rc / n_int)
+# and the convolution interpolates it per edge from an L2-resident table instead of reading a [E, wn] array
+# from HBM.  Table layout: tab[i][c] = float4(f_i, h f'_i, f_{i+1}, h f'_{i+1}) for interval i, column c.
+# Per edge the kernels read Yt[e] = (Y_0 .. Y_{S-1}, t, bits(i)) (edge.cu: sevenn_edge_fwd_tab).  The backward
+# contracts dE/dw with dw/dr in registers and emits one scalar per (unit, edge) next to dY -- no dW array, no
+# reverse radial MLP.
+TAB_XY_DEPTH = 4     # ring slots for x_j / Y (3 edges in flight)
+TAB_W_DEPTH = 2      # ring slots for the table rows (1 edge in flight: they come from L2)
+
+
+def _tab_ypad(spec: ConvSpec) -> int:
+    S = (spec.lmax_sh + 1) ** 2
+    return ((S + 1 + 3) // 4) * 4
+
+
+def _tab_xy_floats(G: _Group, spec: ConvSpec) -> int:
+    return G.d1 * 32 + _tab_ypad(spec)
+
+
+def _tab_w_floats(G: _Group) -> int:
+    return len(G.paths) * 128
+
+
+def tab_ring_floats(spec: ConvSpec) -> int:
+    return max(TAB_XY_DEPTH * _tab_xy_floats(G, spec) + TAB_W_DEPTH * _tab_w_floats(G) for G in make_groups(spec))
+
+
+def _tab_issue_xy(L, G: _Group, spec: ConvSpec, ind, e, j, slot):
+    S = (spec.lmax_sh + 1) ** 2
+    L.append(f'{ind}{{ float* sd = ring + ({slot}) * {_tab_xy_floats(G, spec)} + lane;')
+    L.append(f'{ind}  const float* xr = x + (size_t)({j}) * ldx + {G.xoff} + c32 + lane;')
+    if G.masked:
+        L.append(f'{ind}  if (on) {{')
+    for m in range(G.d1):
+        L.append(f'{ind}  CP_ASYNC4(sd + {m * 32}, xr + {m * G.mul});')
+    if G.masked:
+        L.append(f'{ind}  }}')
+    L.append(f'{ind}  if (lane < {S + 1}) CP_ASYNC4(sd + {G.d1 * 32}, Yt + (size_t)({e}) * {S + 2} + lane);')
+    L.append(f'{ind}}}')
+
+
+def _tab_issue_w(L, G: _Group, spec: ConvSpec, ind, idx, slot):
+    base = TAB_XY_DEPTH * _tab_xy_floats(G, spec)
+    L.append(f'{ind}{{ float* sd = ring + {base} + ({slot}) * {_tab_w_floats(G)} + lane * 4;')
+    L.append(f'{ind}  const float4* tr = tab + (size_t)({idx}) * {spec.wn} + c32 + lane;')
+    if G.masked:
+        L.append(f'{ind}  if (on) {{')
+    for q, (pi, p) in enumerate(G.paths):
+        L.append(f'{ind}  CP_ASYNC16(sd + {q * 128}, tr + {p.w_off});')
+    if G.masked:
+        L.append(f'{ind}  }}')
+    L.append(f'{ind}}}')
+
+
+def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
+    """Opens ``if (e0 < e1) { for (e) {`` with x*, y*, w* (and wd* = h dw/dr when ``bwd``) of edge e defined.
+    cp.async groups alternate  ... X(e+2) | T(e+1) | X(e+3) | T(e+2) ...  so that ``wait_group 1`` at the top of
+    iteration e leaves only the newest x/Y stage in flight."""
+    S = (spec.lmax_sh + 1) ** 2
+    S2 = S + 2
+    DX = TAB_XY_DEPTH
+    xyf, wf = _tab_xy_floats(G, spec), _tab_w_floats(G)
+    wbase = DX * xyf
+    idx_of = lambda e: f'F2I(LDG(Yt + (size_t)({e}) * {S2} + {S + 1}))'   # noqa: E731
+    L.append('    const int e0 = rowptr[row], e1 = rowptr[row + 1];')
+    L.append('    if (e0 < e1) {')
+    L.append('#ifdef SEVENN_EMU')
+    L.append('      for (int e = e0; e < e1; ++e) {')
+    L.append(f'        const float* xr = x + (size_t)col[e] * ldx + {G.xoff} + c32 + lane;')
+    L.append(f'        const float4* tr = tab + (size_t){idx_of("e")} * {spec.wn} + c32 + lane;')
+    L.append(f'        const float t = Yt[(size_t)e * {S2} + {S}];')
+    for m in range(G.d1):
+        L.append(f'        const float x{m} = {_on(G, f"xr[{m * G.mul}]")};')
+    for pi, p in G.paths:
+        z = 'float4{0.f, 0.f, 0.f, 0.f}'
+        L.append(f'        const float4 T{pi} = {_on(G, f"tr[{p.w_off}]", z)};')
+    for jj in G.ys:
+        L.append(f'        const float y{jj} = Yt[(size_t)e * {S2} + {jj}];')
+    L.append('#else')
+    # prologue: X(e0), X(e0+1), T(e0), X(e0+2)
+    for d in (0, 1):
+        L.append(f'      if (e0 + {d} < e1) {{')
+        _tab_issue_xy(L, G, spec, '        ', f'e0 + {d}', f'col[e0 + {d}]', str(d))
+        L.append('      }')
+        L.append('      CP_ASYNC_COMMIT();')
+    _tab_issue_w(L, G, spec, '      ', idx_of('e0'), '0')
+    L.append('      CP_ASYNC_COMMIT();')
+    L.append('      if (e0 + 2 < e1) {')
+    _tab_issue_xy(L, G, spec, '        ', 'e0 + 2', 'col[e0 + 2]', '2')
+    L.append('      }')
+    L.append('      CP_ASYNC_COMMIT();')
+    L.append(f'      int jn = col[e0 + {DX - 1} < e1 ? e0 + {DX - 1} : e1 - 1];')
+    L.append(f'      int in = {idx_of("(e0 + 1 < e1 ? e0 + 1 : e1 - 1)")};')
+    L.append('      int slot = 0;')
+    L.append('      for (int e = e0; e < e1; ++e) {')
+    L.append('        CP_ASYNC_WAIT(1);')
+    L.append('        __syncwarp();')
+    L.append('        if (e + 1 < e1) {')
+    _tab_issue_w(L, G, spec, '          ', 'in', '(e + 1 - e0) & 1')
+    L.append('        }')
+    L.append('        CP_ASYNC_COMMIT();')
+    L.append(f'        if (e + {DX - 1} < e1) {{')
+    _tab_issue_xy(L, G, spec, '          ', f'e + {DX - 1}', 'jn', f'(slot + {DX - 1}) & {DX - 1}')
+    L.append('        }')
+    L.append('        CP_ASYNC_COMMIT();')
+    L.append(f'        jn = col[e + {DX} < e1 ? e + {DX} : e1 - 1];')
+    L.append(f'        in = {idx_of("(e + 2 < e1 ? e + 2 : e1 - 1)")};')
+    L.append(f'        const float* sr = ring + slot * {xyf};')
+    L.append(f'        const float* tw = ring + {wbase} + ((e - e0) & 1) * {wf} + lane * 4;')
+    L.append(f'        slot = (slot + 1) & {DX - 1};')
+    for m in range(G.d1):
+        L.append(f'        const float x{m} = {_on(G, f"sr[{m * 32} + lane]")};')
+    for q, (pi, p) in enumerate(G.paths):
+        z = 'make_float4(0.f, 0.f, 0.f, 0.f)'
+        L.append(f'        const float4 T{pi} = {_on(G, f"*reinterpret_cast<const float4*>(tw + {q * 128})", z)};')
+    ybase = G.d1 * 32
+    for jj in G.ys:
+        L.append(f'        const float y{jj} = sr[{ybase + jj}];')
+    L.append(f'        const float t = sr[{ybase + S}];')
+    L.append('#endif')
+    # cubic Hermite basis (and its derivative) at t
+    L.append('        const float u = 1.f - t, tt = t * t, uu = u * u;')
+    L.append('        const float h00 = (1.f + 2.f * t) * uu, h10 = t * uu, h01 = tt * (3.f - 2.f * t), h11 = -tt * u;')
+    for pi, p in G.paths:
+        L.append(f'        const float w{pi} = fmaf(T{pi}.x, h00, fmaf(T{pi}.y, h10, fmaf(T{pi}.z, h01, T{pi}.w * h11)));')
+    if bwd:
+        L.append('        const float d00 = -6.f * t * u, d10 = u * (1.f - 3.f * t), d11 = t * (3.f * t - 2.f);')
+        for pi, p in G.paths:
+            L.append(f'        const float wd{pi} = fmaf(d00, T{pi}.x - T{pi}.z, fmaf(d10, T{pi}.y, d11 * T{pi}.w));')
 
 
 def signature(spec: ConvSpec) -> str:
@@ -315,6 +486,22 @@ def generate(spec: ConvSpec) -> str:
            '#include "conv_common.cuh"', '']
     out += gen_fwd(spec, groups, sig) + ['']
     out += gen_bwd(spec, groups, sig) + ['']
+    out += gen_fwd(spec, groups, sig, tab=True) + ['']
+    out += gen_bwd(spec, groups, sig, tab=True) + ['']
+    rf = tab_ring_floats(spec)
+    out.append(f'extern "C" int sevenn_conv_fwd_tab_{sig}(const float* x, int ldx, const float* Yt, const float* tab,')
+    out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, float* out, int ldo, void* stream) {')
+    out.append('  if (n_dst <= 0) return 0;')
+    out.append(f'  LAUNCH_DYN(conv_fwd_tab_{sig}, n_dst, {nu}, {rf}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, out, ldo);')
+    out.append('  return LAUNCH_STATUS();')
+    out.append('}')
+    out.append(f'extern "C" int sevenn_conv_bwd_tab_{sig}(const float* x, int ldx, const float* Yt, const float* tab,')
+    out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, const float* gout, int ldo,')
+    out.append('    float* dxe, int lddx, float* dY, long long dy_stride, void* stream) {')
+    out.append('  if (n_dst <= 0) return 0;')
+    out.append(f'  LAUNCH_DYN(conv_bwd_tab_{sig}, n_dst, {nu}, {rf}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, gout, ldo, dxe, lddx, dY, dy_stride);')
+    out.append('  return LAUNCH_STATUS();')
+    out.append('}')
     out.append(f'extern "C" int sevenn_conv_fwd_{sig}(const float* x, int ldx, const float* Y, const float* w,')
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, float* out, int ldo, void* stream) {')
     out.append('  if (n_dst <= 0) return 0;')

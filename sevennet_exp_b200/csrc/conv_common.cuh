@@ -16,9 +16,12 @@
     const int row = blockIdx.x * CONV_WARPS_PER_CTA + (threadIdx.x >> 5); if (row < (n)) {
 #define UNIT_LOOP_END }}
 #define LDG(p) __ldg(p)
+#define F2I(v) __float_as_int(v)
 // per-lane 4-byte asynchronous copy global -> shared (LDGSTS): the gathered source row, the radial weights and
 // the spherical harmonics of the next edges stream into a per-warp ring while the current edge is computed
 #define CP_ASYNC4(sdst, gsrc) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" \
+    :: "r"((unsigned)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory")
+#define CP_ASYNC16(sdst, gsrc) asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" \
     :: "r"((unsigned)__cvta_generic_to_shared(sdst)), "l"(gsrc) : "memory")
 #define CP_ASYNC_COMMIT() asm volatile("cp.async.commit_group;" ::: "memory")
 #define CP_ASYNC_WAIT(n) asm volatile("cp.async.wait_group %0;" :: "n"(n) : "memory")
@@ -45,6 +48,23 @@ __device__ __forceinline__ void sevenn_dy_accumulate(float (&v)[NP], int lane, f
   const int q = lane >> SH;
   if ((lane & ((1 << SH) - 1)) == 0 && q < S) dst[q] += s;
 }
+// radial term of the tabulated kernels: warp sum of the lane partials, added to one word owned by this warp
+__device__ __forceinline__ void sevenn_gr_accumulate(float v, int lane, float* dst) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if (lane == 0) *dst += v;
+}
+// tabulated-radial kernels: the ring lives in dynamic shared memory (it can exceed the 48 KB static limit)
+#define UNIT_LOOP_BEGIN_DYN(n, nunits, ringf) { extern __shared__ __align__(16) float ring_all[]; \
+    float* ring = ring_all + (threadIdx.x >> 5) * (ringf); (void)ring; \
+    const int lane = threadIdx.x & 31; const int unit = blockIdx.y; \
+    const int row = blockIdx.x * CONV_WARPS_PER_CTA + (threadIdx.x >> 5); if (row < (n)) {
+#define LAUNCH_DYN(kern, n, nunits, ringf, stream) \
+    { static bool attr_done = false; const int smem_bytes = CONV_WARPS_PER_CTA * (ringf) * 4; \
+      if (!attr_done && smem_bytes > 48 * 1024) { \
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes); attr_done = true; } } \
+    kern<<<dim3(((n) + CONV_WARPS_PER_CTA - 1) / CONV_WARPS_PER_CTA, (nunits)), 32 * CONV_WARPS_PER_CTA, \
+           CONV_WARPS_PER_CTA * (ringf) * 4, (cudaStream_t)(stream)>>>
 #define LAUNCH(kern, n, nunits, stream) kern<<<dim3(((n) + CONV_WARPS_PER_CTA - 1) / CONV_WARPS_PER_CTA, (nunits)), 32 * CONV_WARPS_PER_CTA, 0, (cudaStream_t)(stream)>>>
 #define LAUNCH_STATUS() ((int)cudaGetLastError())
 #else
@@ -53,11 +73,17 @@ __device__ __forceinline__ void sevenn_dy_accumulate(float (&v)[NP], int lane, f
     for (int lane = 0; lane < 32; ++lane) {
 #define UNIT_LOOP_END }}
 #define LDG(p) (*(p))
+#include <cstring>
+static inline int F2I(float v) { int i; std::memcpy(&i, &v, 4); return i; }
 template <int NP>
 static inline void sevenn_dy_accumulate(float (&v)[NP], int lane, float* dst, int S) {
   (void)lane;
   for (int q = 0; q < S; ++q) dst[q] += v[q];
 }
+static inline void sevenn_gr_accumulate(float v, int lane, float* dst) { (void)lane; *dst += v; }
+struct float4 { float x, y, z, w; };
+#define UNIT_LOOP_BEGIN_DYN(n, nunits, ringf) UNIT_LOOP_BEGIN(n, nunits, ringf)
+#define LAUNCH_DYN(kern, n, nunits, ringf, stream) kern
 #define LAUNCH(kern, n, nunits, stream) kern
 #define LAUNCH_STATUS() 0
 #define __restrict__

@@ -135,6 +135,55 @@ GKERNEL(edge_bwd_kernel)(const float* __restrict__ vec, long long n, EdgeParams 
   }
 }
 
+// Tabulated-radial variant (codegen/conv_codegen.py "Tabulated radial weights"): per edge
+// Yt[e] = (Y_0 .. Y_{S-1}, t, bits(i)) with r = (i + t) h the position of the edge length in the table.
+GKERNEL(edge_fwd_tab_kernel)(const float* __restrict__ vec, long long n, int lmax, int normalize, float inv_h,
+                             int n_int, float* __restrict__ Yt) {
+  const int S = (lmax + 1) * (lmax + 1);
+  GRID_STRIDE_LOOP(e, n) {
+    const float x = vec[3 * e], y = vec[3 * e + 1], z = vec[3 * e + 2];
+    const float r = sqrtf(x * x + y * y + z * z);
+    float yv[16];
+    if (normalize) { const float ir = 1.f / r; sh_eval(lmax, x * ir, y * ir, z * ir, yv); }
+    else sh_eval(lmax, x, y, z, yv);
+    float* row = Yt + e * (S + 2);
+    for (int k = 0; k < S; ++k) row[k] = yv[k];
+    const float s = r * inv_h;
+    int i = (int)s;
+    if (i > n_int - 1) i = n_int - 1;
+    if (i < 0) i = 0;
+    row[S] = s - (float)i;
+    reinterpret_cast<int*>(row)[S + 1] = i;
+  }
+}
+
+// dY rows carry S + 1 values: d/dY and the radial term sum_c dE/dw_c * h dw_c/dr (one slab per convolution unit).
+GKERNEL(edge_bwd_tab_kernel)(const float* __restrict__ vec, long long n, int lmax, int normalize, float inv_h,
+                             const float* __restrict__ dY, int n_slabs, long long slab_stride,
+                             float* __restrict__ fvec) {
+  const int S = (lmax + 1) * (lmax + 1), S1 = S + 1;
+  GRID_STRIDE_LOOP(e, n) {
+    const float x = vec[3 * e], y = vec[3 * e + 1], z = vec[3 * e + 2];
+    const float r = sqrtf(x * x + y * y + z * z), ir = 1.f / r;
+    float d[17], g[3];
+    for (int k = 0; k < S1; ++k) d[k] = dY[e * S1 + k];
+    for (int sl = 1; sl < n_slabs; ++sl)
+      for (int k = 0; k < S1; ++k) d[k] += dY[(size_t)sl * slab_stride + e * S1 + k];
+    float fx, fy, fz;
+    if (normalize) {
+      const float ux = x * ir, uy = y * ir, uz = z * ir;
+      sh_grad_contract(lmax, ux, uy, uz, d, g);
+      const float dot = ux * g[0] + uy * g[1] + uz * g[2];
+      fx = (g[0] - ux * dot) * ir; fy = (g[1] - uy * dot) * ir; fz = (g[2] - uz * dot) * ir;
+    } else {
+      sh_grad_contract(lmax, x, y, z, d, g);
+      fx = g[0]; fy = g[1]; fz = g[2];
+    }
+    const float dr = d[S] * inv_h;
+    fvec[3 * e] = fx + dr * x * ir; fvec[3 * e + 1] = fy + dr * y * ir; fvec[3 * e + 2] = fz + dr * z * ir;
+  }
+}
+
 static EdgeParams edge_params(int lmax, int normalize, int nb, int cutoff_kind, float rc, float p, float r_on) {
   EdgeParams P; P.lmax = lmax; P.normalize = normalize; P.nb = nb; P.cutoff_kind = cutoff_kind;
   P.rc = rc; P.p = p; P.r_on = r_on; return P;
@@ -158,5 +207,21 @@ extern "C" int sevenn_edge_bwd(const float* vec, long long n_edges, int lmax, in
   if (lmax < 0 || lmax > 3 || nb < 1 || n_slabs < 1) return SEVENN_ERR_BAD_ARG;
   LAUNCH1D(edge_bwd_kernel, n_edges, stream)(vec, n_edges, edge_params(lmax, normalize, nb, cutoff_kind, rc, p, r_on),
                                              coeffs, dY, n_slabs, slab_stride, demb, fvec);
+  return LAUNCH_STATUS();
+}
+
+extern "C" int sevenn_edge_fwd_tab(const float* vec, long long n_edges, int lmax, int normalize, float inv_h,
+                                   int n_int, float* Yt, void* stream) {
+  if (n_edges <= 0) return 0;
+  if (lmax < 0 || lmax > 3 || n_int < 1 || !(inv_h > 0.f)) return SEVENN_ERR_BAD_ARG;
+  LAUNCH1D(edge_fwd_tab_kernel, n_edges, stream)(vec, n_edges, lmax, normalize, inv_h, n_int, Yt);
+  return LAUNCH_STATUS();
+}
+
+extern "C" int sevenn_edge_bwd_tab(const float* vec, long long n_edges, int lmax, int normalize, float inv_h,
+                                   const float* dY, int n_slabs, long long slab_stride, float* fvec, void* stream) {
+  if (n_edges <= 0) return 0;
+  if (lmax < 0 || lmax > 3 || n_slabs < 1) return SEVENN_ERR_BAD_ARG;
+  LAUNCH1D(edge_bwd_tab_kernel, n_edges, stream)(vec, n_edges, lmax, normalize, inv_h, dY, n_slabs, slab_stride, fvec);
   return LAUNCH_STATUS();
 }

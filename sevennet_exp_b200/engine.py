@@ -20,6 +20,7 @@ import torch
 from . import _lib
 from .spec import ACT_ID, LinearSpec, ModelSpec, nequip_sc_dense
 from . import irreps as ir
+from . import radial_table
 from .codegen import conv_codegen
 
 
@@ -257,10 +258,19 @@ class Kernels:
 
 class Engine(Kernels):
     def __init__(self, spec: ModelSpec, state_dict: Dict[str, torch.Tensor], lib: Optional[_lib.Lib] = None,
-                 device='cuda', keep_weights: bool = True):
+                 device='cuda', keep_weights: bool = True, radial: Optional[str] = None):
+        """radial: 'table' (default) interpolates the radial weight function from per-layer tables built here
+        (radial_table.py); 'mlp' evaluates the radial MLP per edge with the GEMM kernels, as the nn modules do.
+        Non-smooth radial activations (abs, relu) always take 'mlp'."""
         super().__init__(lib, device)
         self.spec = spec
         self.keep_w = keep_weights
+        radial = radial or os.environ.get('SEVENN_RADIAL', 'table')
+        if radial not in ('table', 'mlp'):
+            raise ValueError(f"radial must be 'table' or 'mlp', got {radial!r}")
+        if spec.act_radial not in radial_table.SMOOTH_ACTS:
+            radial = 'mlp'
+        self.radial = radial
         sd = {k: v.detach().cpu().numpy().astype(np.float64) for k, v in state_dict.items()
               if k in spec.expected_keys()}
         missing = [k for k in spec.expected_keys() if k not in sd]
@@ -282,6 +292,7 @@ class Engine(Kernels):
         self.embed_table = f32(table)
         self.d0 = emb.lout.dim
         self.layers = []
+        t_first = True
         for L in spec.layers:
             h = L.conv.hidden
             Wm = [sd[f'{L.conv.name}.weight_nn.layer{k}.weight'] / math.sqrt(h[k]) for k in range(len(h) - 1)]
@@ -298,6 +309,14 @@ class Engine(Kernels):
                     _lib.GatePiece(p.kind, p.l, p.mul, p.in_off, p.in_stride, p.gate_off, p.out_off,
                                    p.out_stride, p.act, p.cst) for p in L.gate.pieces]),
             }
+            if self.radial == 'table':
+                if t_first:
+                    self.tab_n = radial_table.choose_intervals(spec.cutoff, spec.cutoff_fn, spec.cutoff_on)
+                    self.tab_inv_h = self.tab_n / spec.cutoff
+                    t_first = False
+                lay['tab'] = f32(radial_table.build_table(
+                    sd['edge_embedding.basis_function.coeffs'], spec.cutoff_fn, spec.cutoff, spec.cutoff_p,
+                    spec.cutoff_on, Wm, spec.act_radial, ir.normalize2mom_const(spec.act_radial), self.tab_n))
             if not self.lib.has_conv(lay['sig']):
                 raise _lib.SevennError(
                     f"no prebuilt conv kernel for signature {lay['sig']} ({ir.irreps_str(L.conv.lx.groups)}); "
@@ -308,7 +327,8 @@ class Engine(Kernels):
         hs = [tuple(L.conv.hidden[:-1]) for L in spec.layers]
         self.overlap = os.environ.get('SEVENN_OVERLAP', '1') == '1'
         self._side = None
-        self.mlp_batched = (len(set(hs)) == 1 and len(hs[0]) >= 2 and os.environ.get('SEVENN_MLP_BATCH', '1') == '1')
+        self.mlp_batched = (len(set(hs)) == 1 and len(hs[0]) >= 2 and os.environ.get('SEVENN_MLP_BATCH', '1') == '1'
+                            and self.radial == 'mlp')
         if self.mlp_batched:
             W1 = np.concatenate([lay['mlp'][0].cpu().numpy() for lay in self.layers], axis=1)   # [nb, L*h1]
             self.mlp_w1cat = f32(W1)
@@ -378,8 +398,15 @@ class Engine(Kernels):
         edge_args = (sp.lmax_sh, int(sp.normalize_sph), sp.n_basis, ckind, sp.cutoff, sp.cutoff_p, sp.cutoff_on,
                      _p(self.coeffs))
         self._mark('edge_fwd')
-        Y, emb = self._empty(max(E, 1), S), self._empty(max(E, 1), sp.n_basis)
-        lib.call('sevenn_edge_fwd', _p(g.edge_vec), E, *edge_args, _p(Y), _p(emb), st)
+        table = self.radial == 'table'
+        if table:
+            # Y rows carry (Y, t, i): the position of the edge length in the radial tables
+            Y, emb = self._empty(max(E, 1), S + 2), None
+            lib.call('sevenn_edge_fwd_tab', _p(g.edge_vec), E, sp.lmax_sh, int(sp.normalize_sph), self.tab_inv_h,
+                     self.tab_n, _p(Y), st)
+        else:
+            Y, emb = self._empty(max(E, 1), S), self._empty(max(E, 1), sp.n_basis)
+            lib.call('sevenn_edge_fwd', _p(g.edge_vec), E, *edge_args, _p(Y), _p(emb), st)
         x = self._empty(nn, self.d0)
         lib.call('sevenn_embed', _p(g.types), nn, self.d0, _p(self.embed_table), _p(x), st)
         self.n_launch += 2
@@ -389,7 +416,7 @@ class Engine(Kernels):
         # The radial MLPs need the edge embedding only: with `overlap` they run for all layers on a side stream and
         # fill the SMs that the small, latency-bound node kernels (self connection, self interactions, gate) leave idle.
         w_bytes = 4 * E * sum(lay['spec'].conv.wn for lay in self.layers)
-        overlap = (self.overlap and self.mlp_batched and self.keep_w and self.prof is None and E > 0
+        overlap = (self.overlap and self.mlp_batched and not table and self.keep_w and self.prof is None and E > 0
                    and self.dev.type == 'cuda' and w_bytes < (16 << 30))
         main = torch.cuda.current_stream() if self.dev.type == 'cuda' else None
         mlp_out, mlp_ev = [], []
@@ -430,7 +457,9 @@ class Engine(Kernels):
             if n_x < nn:
                 halo.forward(t, h)    # fills rows [n_local, n_nodes)
             self._mark('mlp_fwd')
-            if overlap:
+            if table:
+                pres = acts = w = h_last = None
+            elif overlap:
                 main.wait_event(mlp_ev[t])
                 pres, acts, w, h_last = mlp_out[t]
             elif pre1_all is not None:
@@ -440,8 +469,8 @@ class Engine(Kernels):
                 h_last = (acts[-1], 0, acts[-1].shape[1]) if acts else (emb, 0, emb.shape[1])
             self._mark(f'conv_fwd_{lay["sig"]}')
             agg = self._empty(nl, dmid)
-            fwd, _ = lib.conv(lay['sig'])
-            rc = fwd(_p(h), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(agg), dmid, st)
+            fwd, _ = lib.conv_tab(lay['sig']) if table else lib.conv(lay['sig'])
+            rc = fwd(_p(h), dx_in, _p(Y), _p(lay['tab'] if table else w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(agg), dmid, st)
             if rc:
                 raise _lib.SevennError(f'conv_fwd {lay["sig"]} failed with status {rc}')
             self.n_launch += 1
@@ -480,7 +509,9 @@ class Engine(Kernels):
         # ---------------- reverse pass: dE/d(edge_vec) --------------------------------------
         self._mark('readout_bwd')
         n_slab = max(lay['units'] for lay in self.layers)        # one dY slab per convolution unit
-        dY, demb = self._zeros(n_slab * max(E, 1), S), self._zeros(max(E, 1), sp.n_basis)
+        SD = S + 1 if table else S      # tabulated kernels: the radial term rides in the last column of dY
+        dY = self._zeros(n_slab * max(E, 1), SD)
+        demb = None if table else self._zeros(max(E, 1), sp.n_basis)
         dr1 = self._empty(nl, sp.read1.lout.dim)
         self._linear_bwd(self.read2, seed, nl, dr1)
         dx = self._zeros(nl, sp.read1.lin.dim) if self.read1.bwd_needs_zero else self._empty(nl, sp.read1.lin.dim)
@@ -499,20 +530,29 @@ class Engine(Kernels):
             dagg = self._zeros(nl, dmid) if lay['si2'].bwd_needs_zero else self._empty(nl, dmid)
             self._linear_bwd(lay['si2'], dpre, nl, dagg)
             self._mark('mlp_recompute')
-            w = sv['w'] if sv['w'] is not None else self._mlp_last_from(lay, sv['h_last'], E)
+            if not table:
+                w = sv['w'] if sv['w'] is not None else self._mlp_last_from(lay, sv['h_last'], E)
             self._mark(f'conv_bwd_{lay["sig"]}')
-            dW = self._empty(max(E, 1), L.conv.wn)
             unused = any(not any(p.gx == gi for p in L.conv.paths) for gi in range(len(L.conv.lx.groups)))
             dxe = self._zeros(max(E, 1), dx_in) if unused else self._empty(max(E, 1), dx_in)
-            _, bwd = lib.conv(lay['sig'])
-            rc = bwd(_p(sv['h']), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(dagg), dmid,
-                     _p(dW), _p(dxe), dx_in, _p(dY), max(E, 1) * S, st)
+            if table:
+                dW = w = None
+                _, bwd = lib.conv_tab(lay['sig'])
+                rc = bwd(_p(sv['h']), dx_in, _p(Y), _p(lay['tab']), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'],
+                         _p(dagg), dmid, _p(dxe), dx_in, _p(dY), max(E, 1) * SD, st)
+            else:
+                dW = self._empty(max(E, 1), L.conv.wn)
+                _, bwd = lib.conv(lay['sig'])
+                rc = bwd(_p(sv['h']), dx_in, _p(Y), _p(w), _p(g.rowptr), _p(g.col), nl, lay['inv_denom'], _p(dagg),
+                         dmid, _p(dW), _p(dxe), dx_in, _p(dY), max(E, 1) * S, st)
             if rc:
                 raise _lib.SevennError(f'conv_bwd {lay["sig"]} failed with status {rc}')
             self.n_launch += 1
             del w
             self._mark('mlp_bwd')
-            if pre1_all is not None:
+            if table:
+                pass
+            elif pre1_all is not None:
                 if dact1_all is None:
                     dact1_all = self._empty(E, pre1_all.shape[1])
                     if overlap:
@@ -550,7 +590,12 @@ class Engine(Kernels):
             self._gemm(dact1_all, 0, nL1, 0, self.mlp_w1catT, demb, 0, sp.n_basis, 0, E, 1, sp.n_basis, nL1, epi=1)
         self._mark('edge_bwd_force')
         fvec = self._empty(max(E, 1), 3)
-        lib.call('sevenn_edge_bwd', _p(g.edge_vec), E, *edge_args, _p(dY), n_slab, max(E, 1) * S, _p(demb), _p(fvec), st)
+        if table:
+            lib.call('sevenn_edge_bwd_tab', _p(g.edge_vec), E, sp.lmax_sh, int(sp.normalize_sph), self.tab_inv_h,
+                     _p(dY), n_slab, max(E, 1) * SD, _p(fvec), st)
+        else:
+            lib.call('sevenn_edge_bwd', _p(g.edge_vec), E, *edge_args, _p(dY), n_slab, max(E, 1) * S, _p(demb),
+                     _p(fvec), st)
         F, vir = self._empty(nn, 3), self._empty(nn, 6)
         lib.call('sevenn_force_virial', _p(fvec), _p(g.edge_vec), _p(g.rowptr), nl, _p(g.cptr), _p(g.cedge), nn,
                  _p(F), _p(vir), st)

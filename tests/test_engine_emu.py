@@ -19,23 +19,27 @@ KBAR = 1602.1766208
 def _compare(cfg, sd, numbers, pos, cell, pbc, oracle_model, tol_e=1e-5, tol_f=1e-4, tol_s=1e-3):
     spec = sp.build_spec(cfg)
     lib = build_full_emu([L.conv for L in spec.layers])
-    eng = Engine(spec, sd, lib=lib, device='cpu')
     g = S.atoms_to_graph(numbers, pos, cell, pbc, cfg['cutoff'])
     ref = oracle_model(dict(g))
     tmap = cfg['_type_map']
     types = np.array([tmap[int(z)] for z in numbers])
     vol = float(g[S.VOL])
     gr = graph_from_edges(types, g[S.EDGE_IDX].numpy(), g[S.EDGE_VEC].detach().numpy(), len(numbers), vol)
-    out = eng.evaluate(gr)
     n = len(numbers)
-    dE = abs(out['energy'].item() - ref[S.E_TOT].item()) / n
-    dF = (out['forces'] - ref[S.FORCE].detach()).abs().max().item()
-    stress = -(out['virial6'] / vol).float()
-    dS = (stress - ref[S.STRESS].detach()).abs().max().item() * KBAR
-    assert dE < tol_e, dE
-    assert dF < tol_f, dF
-    assert dS < tol_s * max(1.0, ref[S.STRESS].abs().max().item() * KBAR * 1e-3), dS
-    return dE, dF, dS
+    res = {}
+    for radial in ('mlp', 'table'):     # per-edge radial MLP (GEMM kernels) and the tabulated radial function
+        eng = Engine(spec, sd, lib=lib, device='cpu', radial=radial)
+        assert eng.radial == radial
+        out = eng.evaluate(gr)
+        dE = abs(out['energy'].item() - ref[S.E_TOT].item()) / n
+        dF = (out['forces'] - ref[S.FORCE].detach()).abs().max().item()
+        stress = -(out['virial6'] / vol).float()
+        dS = (stress - ref[S.STRESS].detach()).abs().max().item() * KBAR
+        assert dE < tol_e, (radial, dE)
+        assert dF < tol_f, (radial, dF)
+        assert dS < tol_s * max(1.0, ref[S.STRESS].abs().max().item() * KBAR * 1e-3), (radial, dS)
+        res[radial] = (dE, dF, dS)
+    return res
 
 
 def test_engine_emu_cp0_hfo2(golden_dir):
