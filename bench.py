@@ -220,6 +220,18 @@ def run_single(args):
     stage_sorted = dict(sorted(((k, round(v, 4)) for k, v in stage.items()), key=lambda kv: -kv[1]))
 
     cpu_v, cpu_t, cores, cn, ce = cpu_oracle_sample((3, 3, 3), 1, 0)
+    tab = calc.engine.radial == 'table'
+    S_sh = (inner.lmax_sh + 1) ** 2
+    # bytes the launch really has to move through HBM: the tabulated kernels neither read w nor write dW
+    # ("say which tensors were elided"); `achieved` keeps SURVEY 8d's figure so rounds stay comparable
+    touched = alg - (E * 8 * inner.wn if tab else 0)
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this workload (ncu --set full):
+    # table mode profiles/r01d_conv_tab_fwd_bwd_raw.csv (155 MB + 379 MB), mlp mode r01c_conv_fwd_bwd_raw.csv
+    # (937 MB + 1,141 MB); below the algorithmic bytes because the gathered source rows are served by L2
+    traffic = None
+    if (n, inner.signature()) == (4096, 'c377d4386a8'):
+        traffic = 534.6e6 if tab else 2078e6
+    path_bytes_per_atom = 5.39e6          # forward + reverse, 5 layers, ~50 neighbours/atom
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': 1, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
@@ -227,19 +239,25 @@ def run_single(args):
         'config': {'workload': f'SevenNet-0 (lmax2, 5 layers, 128x0e+64x1e+32x2e, rc=5A, random-init weights) E+F+S, '
                                f'{n}-atom bulk HfO2 (fluorite 7x7x7, a={A_LAT}A, 20 vacancies), {E / n:.1f} neighbours/atom',
                    'n_atoms': n, 'n_edges': E, 'step': 'device neighbour list + forward + analytic reverse pass',
+                   'radial': calc.engine.radial,
                    'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)'},
         'e2e': {'value': n / e2e_t, 'unit': UNIT, 'ms_per_step': e2e_t * 1e3,
                 'h2d_bytes_per_step': int(pos.nbytes + n * 4), 'd2h_bytes_per_step': int((1 + 6 + 3 * n + n) * 8)},
         'gpu_launches': int(launches),
         'clocks': sampler.summary(),
-        'roofline': {'bound': 'hbm', 'kernel': f'conv_bwd_{inner.signature()} (inner layers, one launch per layer)',
+        'roofline': {'bound': 'hbm',
+                     'kernel': f'conv_bwd_{"tab_" if tab else ""}{inner.signature()} (inner layers, one launch per layer)',
                      'achieved': achieved, 'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': achieved / peak,
-                     'algorithmic_bytes': alg, 'ms': dom_ms,
-                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel on this workload
-                     # (ncu --set full, profiles/r01c_conv_fwd_bwd_raw.csv: 937 MB + 1,141 MB); below the algorithmic
-                     # bytes because the gathered source rows (7.9 MB of node features) are served by L2
-                     'traffic': 2078e6 if (n, inner.signature()) == (4096, 'c377d4386a8') else None,
-                     'conv_fwd_achieved': fwd_ach, 'conv_fwd_frac': fwd_ach / peak},
+                     'algorithmic_bytes': alg, 'ms': dom_ms, 'traffic': traffic,
+                     'elided': ('w and dW [E, wn] (radial weights interpolated from an L2-resident table inside the '
+                                'kernel)' if tab else None),
+                     'touched_bytes': touched, 'touched_frac': touched / (dom_ms * 1e-3) / 1e9 / peak,
+                     'limiter': ('ncu r01d: issue slots 75 %, fp32 pipe 47 %, L1 data pipe 63 %, DRAM 10 % -> '
+                                 'instruction bound, not HBM bound' if tab else
+                                 'ncu r01c: DRAM 42 %, issue slots 63 %'),
+                     'conv_fwd_achieved': fwd_ach, 'conv_fwd_frac': fwd_ach / peak,
+                     'path': {'bytes_per_atom': path_bytes_per_atom, 'ceiling_atom_steps_s': peak * 1e9 / path_bytes_per_atom,
+                              'frac': value / (peak * 1e9 / path_bytes_per_atom)}},
         'stage_ms': stage_sorted,
         'cpu_baseline': {'value': cpu_v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
                          'sample': f'oracle (CPU restatement of the reference path) on a {cn}-atom HfO2 3x3x3 cell, '
