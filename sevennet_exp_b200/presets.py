@@ -44,6 +44,16 @@ CP0_LIKE = {
     '_type_map': {72: 0, 8: 1}, 'shift': 0.0, 'scale': 1.0, 'irreps_manual': False,
 }
 
+# example_inputs/md_serial_example/deployed_serial.pt (sevenn 0.8.6 artefact: Hf/O, lmax 1, O3 parity, 4 layers,
+# unnormalised SH); weights transplanted by tests/golden/make_deployed_transplant.py
+DEPLOYED_SERIAL_LIKE = {
+    'cutoff': 4.0, 'channel': 4, 'lmax': 1, 'is_parity': True, 'num_convolution_layer': 4,
+    'weight_nn_hidden_neurons': [64, 64], 'radial_basis': {'radial_basis_name': 'bessel', 'bessel_basis_num': 8},
+    'cutoff_function': {'cutoff_function_name': 'poly_cut', 'poly_cut_p_value': 6},
+    'conv_denominator': 4.793977737426758, 'self_connection_type': 'nequip', '_normalize_sph': False,
+    '_number_of_species': 2, '_type_map': {72: 0, 8: 1}, 'shift': 0.0, 'scale': 1.0, 'irreps_manual': False,
+}
+
 # small SO3 models used by the GPU parity tests (same structure as SevenNet-0 / l3i5, 32 channels)
 TEST_SO3_L2 = {
     **_common(), 'channel': 32, 'lmax': 2, 'num_convolution_layer': 3,
@@ -61,4 +71,5 @@ TEST_SO3_L3 = {
 }
 
 PRESETS = {'7net-0': SEVENNET_0, '7net-l3i5': SEVENNET_L3I5, 'cp0': CP0_LIKE,
+           'deployed-serial': DEPLOYED_SERIAL_LIKE,
            'test-so3-l2': TEST_SO3_L2, 'test-so3-l3': TEST_SO3_L3}

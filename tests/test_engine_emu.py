@@ -64,3 +64,26 @@ def test_engine_emu_so3_random_weights(name):
         model.edge_embedding.basis_function.coeffs.mul_(1.03)
     numbers, pos, cell = random_cell(24, list(cfg['_type_map']), density=0.05, seed=3)
     print(_compare(cfg, model.state_dict(), numbers, pos, cell, [True] * 3, model))
+
+
+def test_engine_emu_reference_deployed_torchscript(golden_dir):
+    """The reference's frozen TorchScript artefact (deployed_serial.pt): its weights, its frame -> our engine
+    (emulation build) must give ITS outputs (tests/golden/deployed_serial_hfo2.npz), no oracle in between."""
+    from sevennet_exp_b200.checkpoint import patch_old_config, patch_state_dict
+    from tests.test_oracle import deployed_serial_case
+    cfg, sd, numbers, pos, cell, gold = deployed_serial_case(golden_dir)
+    cfg = patch_old_config(dict(cfg))
+    spec = sp.build_spec(cfg)
+    sd = patch_state_dict(spec, sd, cfg['version'])
+    lib = build_full_emu([L.conv for L in spec.layers])
+    ei = gold['edge_index']
+    ev = pos[ei[1]] - pos[ei[0]] + gold['pbc_shift'] @ cell
+    types = np.array([cfg['_type_map'][int(z)] for z in numbers])
+    vol = abs(np.linalg.det(cell))
+    gr = graph_from_edges(types, ei, ev.astype(np.float32), len(numbers), vol)
+    for radial in ('mlp', 'table'):
+        out = Engine(spec, sd, lib=lib, device='cpu', radial=radial).evaluate(gr)
+        assert abs(out['energy'].item() - float(gold['energy'])) / len(numbers) < 1e-5, radial
+        assert np.abs(out['forces'].numpy() - gold['force']).max() < 1e-4, radial
+        stress = -(out['virial6'].numpy() / vol)
+        assert np.abs(stress - gold['stress']).max() * KBAR < 1e-2, radial

@@ -125,6 +125,29 @@ def test_cp0_checkpoint_hfo2_known_answer(lib, golden_dir):
     assert abs(np.sqrt(np.mean((np.array(dS) ** 2).sum(1))) * KBAR - 190.014237) < 1e-3
 
 
+def test_reference_deployed_torchscript_outputs_on_gpu(lib, golden_dir):
+    """example_inputs/md_serial_example/deployed_serial.pt (the reference's frozen e3nn code path, sevenn 0.8.6):
+    its weights (tests/golden/make_deployed_transplant.py) + its input frame through SevenNetCalculator on the GPU
+    must reproduce ITS energy / atomic energies / forces / stress (tests/golden/deployed_serial_hfo2.npz) --
+    the CUDA path against the real reference, no oracle in between.  Both radial modes."""
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    from tests.test_oracle import deployed_serial_case
+    cfg, sd, numbers, pos, cell, gold = deployed_serial_case(golden_dir)
+    for radial in ('table', 'mlp'):
+        os.environ['SEVENN_RADIAL'] = radial
+        try:
+            calc = SevenNetCalculator((dict(cfg), sd), file_type='model_instance')
+        finally:
+            os.environ.pop('SEVENN_RADIAL')
+        assert calc.engine.radial == radial
+        res = calc.compute(numbers, pos, cell, [True] * 3)
+        assert res['n_edges'] == gold['edge_index'].shape[1]
+        assert abs(res['energy'] - float(gold['energy'])) / len(numbers) < 1e-5, radial
+        assert np.abs(res['energies'] - gold['atomic_energy'].reshape(-1)).max() < 1e-5, radial
+        assert np.abs(res['forces'] - gold['force']).max() < 1e-4, radial
+        assert np.abs(res['inferred_stress'] - gold['stress']).max() * KBAR < 1e-2, radial   # reference ran in fp32
+
+
 def test_cp0_vs_oracle(lib, golden_dir):
     model, cfg = S.load_checkpoint(os.path.join(golden_dir, 'cp0_model.pt'))
     cp = torch.load(os.path.join(golden_dir, 'cp0_model.pt'))

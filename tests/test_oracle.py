@@ -4,6 +4,8 @@
   * test_train.py:284-316 metric goldens of cp_0.pth on hfo2.extxyz
   * edge counts of test_data.py:48
   * SH / w3j self-consistency (SURVEY Appendix A rules 2-3)
+  * per-atom E/F/S of the reference's deployed TorchScript artefact (its real e3nn code path, frozen) with
+    its weights transplanted into the oracle (tests/golden/make_deployed_transplant.py)
 """
 import math
 import os
@@ -109,3 +111,41 @@ def test_oracle_forces_are_energy_gradient_fp64(golden_dir):
             assert abs(-(es[0] - es[1]) / (2 * h) - F[a, d]) < 1e-6
     finally:
         torch.set_default_dtype(torch.float32)
+
+
+def deployed_serial_case(golden_dir):
+    """(config, old-format state_dict, numbers, pos, cell, golden outputs of the reference artefact)."""
+    cp = torch.load(os.path.join(golden_dir, 'deployed_serial_transplant.pt'), weights_only=False)
+    gold = np.load(os.path.join(golden_dir, 'deployed_serial_hfo2.npz'))
+    fr = np.load(os.path.join(golden_dir, 'hfo2_frames.npz'))
+    return cp['config'], cp['model_state_dict'], fr['f0_numbers'], fr['f0_pos'], fr['f0_cell'], gold
+
+
+def test_oracle_reproduces_reference_deployed_torchscript(golden_dir):
+    """example_inputs/md_serial_example/deployed_serial.pt is the reference's own code (EdgePreprocess,
+    e3nn-generated TP / Linear / Gate, ForceStressOutput by autograd over pos and strain) frozen by
+    scripts/deploy.py:20-70.  Same inputs + its weights through the restatement must give its outputs:
+    lmax 1, O3 parity (1o, 1e, 0o with tanh gates), nequip self-connection, unnormalised SH, pre-0.11
+    instruction order (sort_old_convolution)."""
+    cfg, sd, numbers, pos, cell, gold = deployed_serial_case(golden_dir)
+    torch.set_default_dtype(torch.float64)
+    try:
+        model = S.build_model(cfg)
+        sd = S.sort_old_convolution(model, sd)
+        own = model.state_dict()
+        assert not [k for k in own if k not in sd and own[k].numel() > 0]
+        model.load_state_dict({k: v for k, v in sd.items() if k in own}, strict=False)
+        model = model.double().eval()
+        ei = torch.tensor(gold['edge_index'])
+        post, cellt = torch.tensor(pos), torch.tensor(cell)
+        ev = post[ei[1]] - post[ei[0]] + torch.tensor(gold['pbc_shift'], dtype=torch.float64) @ cellt
+        out = model({S.Z: torch.tensor(numbers), S.EDGE_IDX: ei, S.EDGE_VEC: ev,
+                     S.NATOMS: torch.tensor([len(numbers)]), S.VOL: torch.tensor(abs(np.linalg.det(cell)))})
+    finally:
+        torch.set_default_dtype(torch.float32)
+    n = len(numbers)
+    assert abs(out[S.E_TOT].item() - float(gold['energy'])) / n < 1e-5            # eV/atom (reference ran fp32)
+    assert np.abs(out[S.AE].detach().numpy().reshape(-1) - gold['atomic_energy'].reshape(-1)).max() < 1e-5
+    assert np.abs(out[S.FORCE].detach().numpy() - gold['force']).max() < 2e-5      # eV/A
+    # the artefact's stress comes from dE/d(strain): same (xx,yy,zz,xy,yz,zx) order as the edge virial
+    assert np.abs(out[S.STRESS].detach().numpy() - gold['stress']).max() * 1602.1766208 < 1e-3 * 10   # kbar, fp32 ref
