@@ -130,6 +130,28 @@ class EdgeEmbedding(nn.Module):
         return data
 
 
+class EdgePreprocess(nn.Module):
+    """sevenn/nn/edge_embedding.py:13-78, the first module of a serial deployed model: edge vectors from
+    ``pos``, ``pbc_shift`` and the cell.  The reference also threads a zero strain tensor through ``pos`` and the
+    cell so that autograd can return the stress; here the stress is the analytic edge virial (ForceStressOutput
+    below), so no strain tensor is needed -- ``is_stress`` is kept for signature compatibility."""
+
+    def __init__(self, is_stress: bool = True):
+        super().__init__()
+        self.is_stress = is_stress
+        self._is_batch_data = False
+
+    def forward(self, data):
+        if self._is_batch_data:
+            raise NotImplementedError('batched graphs are SURVEY 8f-1 (training path)')
+        pos, ei = data[POS], data[EDGE_IDX]
+        cell = data[CELL].reshape(3, 3).to(pos.dtype)
+        ev = pos.detach()[ei[1]] - pos.detach()[ei[0]] + data[SHIFT].to(pos.dtype) @ cell
+        data[EDGE_VEC] = ev.float().requires_grad_(True)
+        data[EDGE_LEN] = torch.linalg.norm(ev, dim=-1)
+        return data
+
+
 # ------------------------------------------------------------------ node --
 class OnehotEmbedding(nn.Module):
     """sevenn/nn/node_embedding.py:15-53"""
@@ -262,6 +284,7 @@ class IrrepsConvolution(nn.Module):
         self._conv = sp.make_conv('convolution', ir.simplify(_irreps(irreps_x)), _irreps(irreps_filter),
                                   _irreps(irreps_out), hidden)
         self.weight_numel = self._conv.wn
+        self._comm_size = self._conv.lx.dim        # ghost row width, convolution.py:55 / deploy.py:121-126
         self.irreps_x, self.irreps_filter = _irreps(irreps_x), _irreps(irreps_filter)
         self.irreps_mid = self._conv.lmid.entries
         self.weight_nn = _FCN(hidden + [self._conv.wn])
@@ -390,6 +413,34 @@ class ForceStressOutputFromEdge(nn.Module):
         return data
 
 
+class ForceStressOutput(ForceStressOutputFromEdge):
+    """sevenn/nn/force_output.py:55-136 (serial deployed models).  The reference differentiates E w.r.t. ``pos`` and
+    the strain of EdgePreprocess; since edge_vec = pos_j - pos_i + shift.cell, dE/dpos_k is the same signed sum of
+    dE/d edge_vec that ForceStressOutputFromEdge forms and -dE/d(strain)/V is the edge virial, so both classes run
+    the same force/virial kernel (checked against the reference's own TorchScript outputs, tests/golden)."""
+
+    def __init__(self, data_key_pos=POS, data_key_energy=E_TOT, data_key_force=FORCE, data_key_stress=STRESS,
+                 data_key_cell_volume=VOL):
+        super().__init__()
+
+
+class ForceOutput(ForceStressOutputFromEdge):
+    """sevenn/nn/force_output.py:12-51: forces only."""
+
+    def __init__(self, data_key_pos=POS, data_key_energy=E_TOT, data_key_force=FORCE):
+        super().__init__()
+
+    def forward(self, data):
+        had_vol = VOL in data
+        if not had_vol:
+            data[VOL] = torch.ones((), device=data[EDGE_VEC].device)
+        data = super().forward(data)
+        data.pop(STRESS, None)
+        if not had_vol:
+            data.pop(VOL)
+        return data
+
+
 # ----------------------------------------------------------- sequential --
 class AtomGraphSequential(nn.Sequential):
     """sevenn/nn/sequential.py:22-205"""
@@ -440,8 +491,6 @@ def init_edge_embedding(cfg):
 def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGraphSequential:
     """sevenn/model_build.py:384-576 + nn/interaction_blocks.py:12-88: same layer names, same order."""
     import copy
-    if parallel:
-        raise NotImplementedError('segment models for LAMMPS e3gnn/parallel: use sevennet_exp_b200.domain')
     cfg = {**sp.DEFAULTS, **copy.deepcopy(config)}
     layers = OrderedDict()
     S, C, L = cfg['_number_of_species'], cfg['channel'], cfg['num_convolution_layer']
@@ -473,7 +522,8 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
         layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, one_hot, gate_in)
         layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X)
         layers[f'{t}_convolution'] = IrrepsConvolution(irreps_x, irreps_filter, irreps_out_tp, wnn,
-                                                       cfg['act_radial'], denom[t], cfg['train_denominator'])
+                                                       cfg['act_radial'], denom[t], cfg['train_denominator'],
+                                                       is_parallel=parallel)
         layers[f'{t}_self_interaction_2'] = IrrepsLinear(layers[f'{t}_convolution'].irreps_mid,
                                                          ir.simplify(gate_in), X)
         layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()
@@ -493,4 +543,39 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
         layers['rescale_atomic_energy'] = SpeciesWiseRescale(shift, scale, cfg['train_shift_scale'])
     layers['reduce_total_enegy'] = AtomReduce()
     layers['force_output'] = ForceStressOutputFromEdge()
-    return AtomGraphSequential(layers, cutoff=cfg['cutoff'], type_map=cfg['_type_map'], data_key_grad=EDGE_VEC)
+    common = dict(cutoff=cfg['cutoff'], type_map=cfg['_type_map'], data_key_grad=EDGE_VEC)
+    if not parallel:
+        return AtomGraphSequential(layers, **common)
+    return [AtomGraphSequential(seg, eval_type_map=False, **common) for seg in _parallel_segments(layers, cfg, S, L)]
+
+
+def _parallel_segments(layers, cfg, n_species, n_layers):
+    """sevenn/model_build.py:299-367 (`_to_parallel_model`): what LAMMPS `pair_style e3gnn/parallel` loads, one
+    module list per interaction layer.  Ghost atoms get their own embedding + first self-interaction (their types
+    are known locally, so layer 0 needs no communication); the chain is cut after every `{t}_self_interaction_1`
+    with t >= 1, because that is the tensor the next convolution gathers from ghosts (`x_ghost`, refreshed by the
+    caller between segments); each later segment starts with its own edge embedding (edge_vec is a fresh autograd
+    leaf per segment on the LAMMPS side); forces are assembled by the caller, so `force_output` is dropped.
+    Ghost modules share the parameters of their local twins through the state_dict keys the reference uses
+    (`ghost_onehot_to_feature_x`, `ghost_0_self_interaction_1`)."""
+    emb_irreps = layers['onehot_to_feature_x'].irreps_out
+    seq = []
+    for name, mod in layers.items():
+        if name == 'force_output':
+            continue
+        seq.append((name, mod))
+        if name == 'onehot_to_feature_x':
+            seq.append(('one_hot_ghost', OnehotEmbedding(n_species, X_GHOST)))
+            seq.append(('ghost_onehot_to_feature_x', IrrepsLinear([(n_species, (0, 1))], emb_irreps, X_GHOST)))
+        elif name == '0_self_interaction_1':
+            seq.append(('ghost_0_self_interaction_1', IrrepsLinear(emb_irreps, emb_irreps, X_GHOST)))
+    cuts = [k for k, (name, _) in enumerate(seq)
+            if name.endswith('_self_interaction_1') and name[0].isdigit() and int(name.split('_')[0]) >= 1]
+    segments, start = [], 0
+    for c in cuts + [len(seq) - 1]:
+        part = seq[start:c + 1]
+        if start > 0:
+            part = [('edge_embedding', init_edge_embedding(cfg))] + part
+        segments.append(OrderedDict(part))
+        start = c + 1
+    return segments

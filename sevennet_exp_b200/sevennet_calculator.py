@@ -63,7 +63,14 @@ class SevenNetCalculator(_AseCalculator):
         if file_type not in ('checkpoint', 'model_instance', 'torchscript'):
             raise ValueError('file_type should be checkpoint, model_instance or torchscript')
         if file_type == 'torchscript':
-            raise NotImplementedError('deployed TorchScript files freeze the e3nn graph; load the checkpoint')
+            # the reference loads a deployed serial model here (sevennet_calculator.py:103-125); ours is the bundle
+            # written by sevennet_exp_b200.deploy.deploy() (a file frozen by the reference raises ValueError)
+            from .deploy import SERIAL_FORMAT
+            b = torch.load(model, weights_only=False, map_location='cpu') if os.path.isfile(str(model)) else None
+            if not (isinstance(b, dict) and b.get('format') == SERIAL_FORMAT):
+                raise ValueError(f'{model}: not a serial model deployed by sevennet_exp_b200.deploy.deploy(); a '
+                                 'TorchScript file written by the reference freezes the e3nn graph')
+            model, file_type = (b['config'], b['model_state_dict']), 'model_instance'
         if device == 'auto':
             device = 'cuda'
         self.device = torch.device(device)

@@ -334,3 +334,45 @@ def test_batched_structures_match_single(lib):
         assert np.abs(b['forces'] - one['forces']).max() < 5e-5
         assert np.abs(b['stress'] - one['stress']).max() * KBAR < 1e-3
         assert np.abs(b['energies'] - one['energies']).max() < 5e-5
+
+
+def test_deployed_entry_points_on_gpu(lib, golden_dir, tmp_path):
+    """deploy.py on the real library: serial bundle through the deployed-model dict contract and through
+    SevenNetCalculator(file_type='torchscript'); parallel segments + comm loop; all against the reference
+    artefact's outputs / the serial evaluation."""
+    from sevennet_exp_b200 import deploy as D
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    from tests.test_deploy_emu import _periodic_ghost_graph
+    from tests.test_oracle import deployed_serial_case
+    cfg, sd, numbers, pos, cell, gold = deployed_serial_case(golden_dir)
+    path = D.deploy((cfg, sd), str(tmp_path / 'serial.pt'))
+    model, extra = D.load_deployed(path)
+    n = len(numbers)
+    data = {'x': torch.tensor([cfg['_type_map'][int(z)] for z in numbers]),
+            'pos': torch.tensor(pos, dtype=torch.float32), 'edge_index': torch.tensor(gold['edge_index']),
+            'num_atoms': torch.tensor([n]), 'cell_lattice_vectors': torch.tensor(cell, dtype=torch.float32),
+            'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32),
+            'pbc_shift': torch.tensor(gold['pbc_shift'], dtype=torch.float32)}
+    out = model(data)
+    assert out['inferred_force'].is_cuda
+    assert abs(out['inferred_total_energy'].item() - float(gold['energy'])) / n < 1e-5
+    assert np.abs(out['inferred_force'].cpu().numpy() - gold['force']).max() < 1e-4
+    assert np.abs(out['inferred_stress'].cpu().numpy() - gold['stress']).max() * KBAR < 1e-2
+    calc = SevenNetCalculator(path, file_type='torchscript')
+    res = calc.compute(numbers, pos, cell, [True] * 3)
+    assert abs(res['energy'] - float(gold['energy'])) / n < 1e-5
+    assert np.abs(res['forces'] - gold['force']).max() < 1e-4
+    with pytest.raises(ValueError):
+        SevenNetCalculator(os.path.join(golden_dir, 'cp0_model.pt'), file_type='torchscript')
+
+    par, extra = D.load_deployed(D.deploy_parallel((cfg, sd), str(tmp_path / 'par')))
+    ei, ev, owner = _periodic_ghost_graph(numbers, pos, cell, float(extra['cutoff']))
+    own_t = torch.tensor(owner, device='cuda')
+    types = data['x'].cuda()
+    E, dE_dr, ae = par.compute(types, types[own_t], torch.tensor(ei), torch.tensor(ev),
+                               lambda x: x[own_t], lambda dx, dg: dx.clone().index_add_(0, own_t, dg))
+    assert abs(E.item() - float(gold['energy'])) / n < 1e-5
+    eit = torch.tensor(ei, device='cuda')
+    F = torch.zeros(n + len(owner), 3, device='cuda').index_add_(0, eit[0], dE_dr).index_add_(0, eit[1], -dE_dr)
+    F = F[:n].index_add_(0, own_t, F[n:])
+    assert np.abs(F.cpu().numpy() - gold['force']).max() < 1e-4
