@@ -165,47 +165,58 @@ class DeployedParallel:
     def __getitem__(self, i):
         return self.segments[i]
 
-    def compute(self, x: torch.Tensor, x_ghost: torch.Tensor, edge_index: torch.Tensor, edge_vec: torch.Tensor,
-                forward_comm: Callable[[torch.Tensor], torch.Tensor],
-                reverse_comm: Callable[[torch.Tensor, torch.Tensor], torch.Tensor]
-                ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-        """pair_e3gnn_parallel.cpp:331-437.  x / x_ghost: type indices of the owned / ghost atoms; edge_index rows
-        index [owned | ghost]; `forward_comm(x_local) -> x_ghost` fills ghost rows from their owners;
-        `reverse_comm(dx_local, dx_ghost) -> dx_local` adds ghost gradients to their owners.
-        Returns (energy of the owned atoms, dE/d edge_vec [E,3], atomic energies [nlocal,1])."""
-        dev = self.device
-        nlocal = int(x.shape[0])
-        ev0 = edge_vec.detach().to(dev).float().requires_grad_(True)
-        data = {'x': x.to(dev), 'x_ghost': x_ghost.to(dev), 'edge_index': edge_index.to(dev), 'edge_vec': ev0,
-                'num_atoms': torch.tensor([nlocal]), 'nlocal': torch.tensor(nlocal)}
-        wrt: List[List[torch.Tensor]] = [[ev0]]
-        out = self.segments[0](data)
-        for seg in self.segments[1:]:
-            xg = forward_comm(out['x'].detach()).detach().requires_grad_(True)
-            out['x_ghost'] = xg
-            out['edge_vec'] = out['edge_vec'].detach().clone().requires_grad_(True)
-            wrt.append([out['edge_vec'], out['x'], out['self_cont_tmp'], xg])
-            out = seg(out)
-        energy = out['inferred_total_energy'].squeeze()
-        dE_dr = torch.zeros_like(ev0)
-        of: List[torch.Tensor] = []
-        gouts: Optional[List[torch.Tensor]] = None
-        for k in range(len(wrt) - 1, -1, -1):
-            w = wrt[k]
-            if gouts is None:
-                grads = torch.autograd.grad([energy], w, allow_unused=True)
-            else:
-                grads = torch.autograd.grad(of, w, gouts, allow_unused=True)
-            if grads[0] is not None:
-                dE_dr = dE_dr + grads[0]
-            if k == 0:
-                break
-            of = [w[1], w[2]]
-            dx_ghost = grads[3] if grads[3] is not None else torch.zeros_like(w[3])
-            dx_local = reverse_comm(grads[1].detach(), dx_ghost.detach())
-            dsc = grads[2] if grads[2] is not None else torch.zeros_like(w[2])
-            gouts = [dx_local, dsc]
-        return energy.detach(), dE_dr.detach(), out['atomic_energy'].detach()
+    def compute(self, x, x_ghost, edge_index, edge_vec, forward_comm, reverse_comm, record: Optional[dict] = None):
+        """The pair style's evaluation of one rank; see `run_parallel_segments`."""
+        return run_parallel_segments(self.segments, x, x_ghost, edge_index, edge_vec, forward_comm, reverse_comm,
+                                     device=self.device, record=record)
+
+
+def run_parallel_segments(segments, x: torch.Tensor, x_ghost: torch.Tensor, edge_index: torch.Tensor,
+                          edge_vec: torch.Tensor, forward_comm: Callable[[torch.Tensor], torch.Tensor],
+                          reverse_comm: Callable[[torch.Tensor, torch.Tensor], torch.Tensor], device='cuda',
+                          record: Optional[dict] = None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """pair_e3gnn_parallel.cpp:331-437 for any list of segment callables with the deployed-parallel dict contract
+    (ours, or the reference's own `deployed_parallel_{i}.pt` loaded with torch.jit -- tests/golden uses that).
+    x / x_ghost: type indices of the owned / ghost atoms; edge_index rows index [owned | ghost];
+    `forward_comm(x_local) -> x_ghost` fills ghost rows from their owners; `reverse_comm(dx_local, dx_ghost) ->
+    dx_local` adds ghost gradients to their owners.  Returns (energy of the owned atoms, dE/d edge_vec [E,3],
+    atomic energies [nlocal,1]); `record` (optional) receives the ghost payload `x` sent before each segment."""
+    dev = torch.device(device)
+    nlocal = int(x.shape[0])
+    ev0 = edge_vec.detach().to(dev).float().requires_grad_(True)
+    data = {'x': x.to(dev), 'x_ghost': x_ghost.to(dev), 'edge_index': edge_index.to(dev), 'edge_vec': ev0,
+            'num_atoms': torch.tensor([nlocal]).to(dev), 'nlocal': torch.tensor([nlocal])}    # 1-D CPU tensor, as pair_e3gnn_parallel.cpp:337 sends it
+    wrt: List[List[torch.Tensor]] = [[ev0]]
+    out = dict(segments[0](data))
+    for k, seg in enumerate(segments[1:], start=1):
+        if record is not None:
+            record[f'x_{k}'] = out['x'].detach().cpu().clone()
+        xg = forward_comm(out['x'].detach()).detach().requires_grad_(True)
+        out['x_ghost'] = xg
+        out['edge_vec'] = out['edge_vec'].detach().clone().requires_grad_(True)
+        wrt.append([out['edge_vec'], out['x'], out['self_cont_tmp'], xg])
+        out = dict(seg(out))
+    energy = out['inferred_total_energy'].squeeze()
+    dE_dr = torch.zeros_like(ev0)
+    of: List[torch.Tensor] = []
+    gouts: Optional[List[torch.Tensor]] = None
+    for k in range(len(wrt) - 1, -1, -1):
+        w = wrt[k]
+        if gouts is None:
+            grads = torch.autograd.grad([energy], w, allow_unused=True)
+        else:
+            grads = torch.autograd.grad(of, w, gouts, allow_unused=True)
+        if grads[0] is not None:
+            dE_dr = dE_dr + grads[0]
+        if k == 0:
+            break
+        of = [w[1], w[2]]
+        dx_ghost = grads[3] if grads[3] is not None else torch.zeros_like(w[3])
+        dx_own = grads[1] if grads[1] is not None else torch.zeros_like(w[1])
+        dx_local = reverse_comm(dx_own.detach(), dx_ghost.detach())
+        dsc = grads[2] if grads[2] is not None else torch.zeros_like(w[2])
+        gouts = [dx_local, dsc]
+    return energy.detach(), dE_dr.detach(), out['atomic_energy'].detach()
 
 
 def load_deployed(path: str, device='cuda', lib=None):

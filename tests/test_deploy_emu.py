@@ -135,3 +135,26 @@ def test_deployed_parallel_segments_and_comm_loop(name, golden_dir, tmp_path):
         0, torch.tensor(ei[1]), -dE_dr)
     F = F[:n].index_add_(0, own_t, F[n:])
     assert (F - ref[S.FORCE].detach()).abs().max() < 1e-4
+
+
+def test_deployed_parallel_against_reference_parallel_artefacts(golden_dir):
+    """tests/golden/deployed_parallel_hfo2.npz holds what the reference's own deployed_parallel_{0..3}.pt produced
+    under the pair style's loop (make_deployed_parallel_golden.py): the ghost payload before every segment, the
+    energy, dE/d edge_vec and the atomic energies.  Same weights (transplant), same graph -> same numbers."""
+    cfg, sd, numbers, pos, cell, _ = deployed_serial_case(golden_dir)
+    gold = np.load(os.path.join(golden_dir, 'deployed_parallel_hfo2.npz'))
+    _emu_for(cfg)
+    _, sd_now, cfg_now = D._resolve((cfg, sd))       # 0.8.6 column order -> sorted instruction order
+    par = D.DeployedParallel(cfg_now, sd_now, device='cpu')
+    assert int(par.extra_files['comm_size']) == 32                 # the artefact's own `comm_size` extra file
+    own = torch.tensor(gold['owner'])
+    types = torch.tensor([cfg['_type_map'][int(z)] for z in numbers], dtype=torch.int64)
+    rec = {}
+    E, dE_dr, ae = par.compute(types, types[own], torch.tensor(gold['edge_index']), torch.tensor(gold['edge_vec']),
+                               lambda x: x[own], lambda dx, dg: dx.clone().index_add_(0, own, dg), record=rec)
+    for k in (1, 2, 3):
+        assert rec[f'x_{k}'].shape == gold[f'x_{k}'].shape
+        assert np.abs(rec[f'x_{k}'].numpy() - gold[f'x_{k}']).max() < 2e-5, k
+    assert abs(E.item() - float(gold['energy'])) / len(numbers) < 1e-5
+    assert np.abs(ae.numpy() - gold['atomic_energy']).max() < 1e-5
+    assert np.abs(dE_dr.numpy() - gold['dE_dr']).max() < 1e-4
