@@ -46,7 +46,7 @@ class BesselBasis(nn.Module):
 
     def __init__(self, cutoff_length, bessel_basis_num=8, trainable_coeff=True):
         super().__init__()
-        self.num_basis = bessel_basis_num
+        self.num_basis, self.cutoff_length = bessel_basis_num, cutoff_length
         self.prefactor = 2.0 / cutoff_length
         c = torch.FloatTensor([n * math.pi / cutoff_length for n in range(1, bessel_basis_num + 1)])
         self.coeffs = nn.Parameter(c) if trainable_coeff else c
@@ -110,6 +110,32 @@ class EdgeEmbedding(nn.Module):
         data[EDGE_LEN] = r
         data[EDGE_EMB] = self.basis_function(r) * self.cutoff_function(r).unsqueeze(-1)
         data[EDGE_ATTR] = self.spherical(rvec)
+        return data
+
+
+class MultiCutoffEdgeEmbedding(nn.Module):
+    """sevenn/nn/edge_embedding.py:220-257 (the fork's per-layer cutoffs): for every distinct cutoff c the edges
+    with r <= c, their Bessel(c) x envelope(c) embedding and harmonics are stored under keys suffixed str(c)."""
+
+    def __init__(self, basis_module, cutoff_module, spherical_module):
+        super().__init__()
+        self.basis_functions = nn.ModuleList(basis_module)
+        self.cutoff_function, self.spherical = cutoff_module, spherical_module
+
+    def forward(self, data):
+        rvec = data[EDGE_VEC]
+        r = torch.linalg.norm(rvec, dim=-1)
+        data[EDGE_LEN] = r
+        for basis in self.basis_functions:
+            c = basis.cutoff_length
+            self.cutoff_function.r_cut = c
+            if isinstance(self.cutoff_function, XPLORCutoff):
+                self.cutoff_function.r_on = c - 1
+            keep = r <= c
+            rr = r[keep]
+            data[EDGE_EMB + str(c)] = basis(rr) * self.cutoff_function(rr).unsqueeze(-1)
+            data[EDGE_ATTR + str(c)] = self.spherical(rvec[keep])
+            data[EDGE_IDX + str(c)] = data[EDGE_IDX][:, keep]
         return data
 
 
@@ -232,8 +258,11 @@ class IrrepsConvolution(nn.Module):
     """sevenn/nn/convolution.py:29-137"""
 
     def __init__(self, irreps_x, irreps_filter, irreps_out, weight_layer_input_to_hidden,
-                 weight_layer_act, denominator=1.0, train_denominator=False, is_parallel=False):
+                 weight_layer_act, denominator=1.0, train_denominator=False, is_parallel=False,
+                 data_key_filter=EDGE_ATTR, data_key_weight_input=EDGE_EMB, data_key_edge_idx=EDGE_IDX):
         super().__init__()
+        self.key_filter, self.key_weight_input, self.key_edge_idx = (
+            data_key_filter, data_key_weight_input, data_key_edge_idx)
         irreps_x, irreps_filter, irreps_out = Irreps(irreps_x), Irreps(irreps_filter), Irreps(irreps_out)
         self.denominator = nn.Parameter(torch.FloatTensor([denominator]),
                                         requires_grad=train_denominator)
@@ -259,12 +288,12 @@ class IrrepsConvolution(nn.Module):
                                               weight_layer_act)
 
     def forward(self, data):
-        weight = self.weight_nn(data[EDGE_EMB])
+        weight = self.weight_nn(data[self.key_weight_input])
         x = data[X]
         if self.is_parallel:
             x = torch.cat([x, data[X_GHOST]])
-        edge_src, edge_dst = data[EDGE_IDX][1], data[EDGE_IDX][0]
-        message = self.convolution(x[edge_src], data[EDGE_ATTR], weight)
+        edge_src, edge_dst = data[self.key_edge_idx][1], data[self.key_edge_idx][0]
+        message = self.convolution(x[edge_src], data[self.key_filter], weight)
         out = torch.zeros(len(x), message.shape[1], dtype=x.dtype)
         out.index_add_(0, edge_dst, message)
         out = out.div(self.denominator)
@@ -442,6 +471,9 @@ def init_edge_embedding(cfg):
     sph = SphericalEncoding(lmax_edge, -1 if cfg['is_parity'] else 1, normalize=cfg['_normalize_sph'])
     rb = dict(cfg['radial_basis'])
     assert rb.pop('radial_basis_name') == 'bessel'
+    if cfg.get('multi_cutoff'):
+        # model_build.py:87-103; the reference iterates list(set(...)), i.e. ascending for small numbers
+        return MultiCutoffEdgeEmbedding([BesselBasis(c, **rb) for c in sorted(set(cfg['multi_cutoff']))], cut, sph)
     return EdgeEmbedding(BesselBasis(cfg['cutoff'], **rb), cut, sph)
 
 
@@ -469,7 +501,9 @@ def build_model(config, parallel=False):
     layers['onehot_idx_to_onehot'] = OnehotEmbedding(S, X, X, ATOM_TYPE, NODE_ATTR)
     layers['onehot_to_feature_x'] = IrrepsLinear(Irreps(f'{S}x0e'), irreps_x, X,
                                                  biases=cfg['use_bias_in_linear'])
-    wnn = [ee.basis_function.num_basis] + list(cfg['weight_nn_hidden_neurons'])
+    multi = cfg.get('multi_cutoff') or None
+    basis0 = ee.basis_functions[0] if multi else ee.basis_function
+    wnn = [basis0.num_basis] + list(cfg['weight_nn_hidden_neurons'])
     act_s = {k: ACT[v] for k, v in cfg['act_scalar'].items()}
     act_g = {k: ACT[v] for k, v in cfg['act_gate'].items()}
     for t in range(L):
@@ -484,9 +518,13 @@ def build_model(config, parallel=False):
         layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, Irreps(f'{S}x0e'), gate_in)
         layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X,
                                                          biases=cfg['use_bias_in_linear'])
+        ckeys = {}
+        if multi:                                        # interaction_blocks.py:54-60
+            ckeys = dict(data_key_filter=f'{EDGE_ATTR}{multi[t]}', data_key_weight_input=f'{EDGE_EMB}{multi[t]}',
+                         data_key_edge_idx=f'{EDGE_IDX}{multi[t]}')
         layers[f'{t}_convolution'] = IrrepsConvolution(
             irreps_x, irreps_filter, irreps_out_tp, wnn, act_radial, denom[t],
-            cfg['train_denominator'], is_parallel=parallel)
+            cfg['train_denominator'], is_parallel=parallel, **ckeys)
         layers[f'{t}_self_interaction_2'] = IrrepsLinear(
             layers[f'{t}_convolution'].irreps_mid, gate_in, X, biases=cfg['use_bias_in_linear'])
         layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()

@@ -80,7 +80,7 @@ class BesselBasis(nn.Module):
 
     def __init__(self, cutoff_length, bessel_basis_num=8, trainable_coeff=True):
         super().__init__()
-        self.num_basis, self.cutoff_length = bessel_basis_num, float(cutoff_length)
+        self.num_basis, self.cutoff_length = bessel_basis_num, cutoff_length
         c = torch.FloatTensor([n * math.pi / cutoff_length for n in range(1, bessel_basis_num + 1)])
         self.coeffs = nn.Parameter(c, requires_grad=False) if trainable_coeff else c
 
@@ -130,6 +130,32 @@ class EdgeEmbedding(nn.Module):
         return data
 
 
+class MultiCutoffEdgeEmbedding(nn.Module):
+    """sevenn/nn/edge_embedding.py:220-257, the fork's per-layer cutoffs: one fused edge kernel launch per distinct
+    cutoff c over the edges with r <= c (Bessel and envelope at cutoff c; XPLOR switches on at c - 1), stored
+    under `edge_embedding{c}` / `edge_attr{c}` / `edge_index{c}` for the convolutions that use that cutoff."""
+
+    def __init__(self, basis_module, cutoff_module, spherical_module):
+        super().__init__()
+        self.basis_functions = nn.ModuleList(basis_module)
+        self.cutoff_function, self.spherical = cutoff_module, spherical_module
+
+    def forward(self, data):
+        rvec = data[EDGE_VEC]
+        r = torch.linalg.norm(rvec.detach(), dim=-1)
+        data[EDGE_LEN] = r
+        c, s = self.cutoff_function, self.spherical
+        for b in self.basis_functions:
+            rc = b.cutoff_length
+            keep = r <= rc
+            r_on = rc - 1 if isinstance(c, XPLORCutoff) else c.r_on
+            args = (s.lmax, bool(s.normalize), b.num_basis, c.kind, float(rc), c.p, float(r_on))
+            Y, emb = F.EdgeEmbedFn.apply(rvec[keep], b.coeffs.to(rvec.device), args)
+            data[EDGE_EMB + str(rc)], data[EDGE_ATTR + str(rc)] = emb, Y
+            data[EDGE_IDX + str(rc)] = data[EDGE_IDX][:, keep]
+        return data
+
+
 class EdgePreprocess(nn.Module):
     """sevenn/nn/edge_embedding.py:13-78, the first module of a serial deployed model: edge vectors from
     ``pos``, ``pbc_shift`` and the cell.  The reference also threads a zero strain tensor through ``pos`` and the
@@ -175,19 +201,39 @@ class OnehotEmbedding(nn.Module):
 
 
 class IrrepsLinear(_LinearCore):
-    """sevenn/nn/linear.py:14-100 (no bias, no modality)."""
+    """sevenn/nn/linear.py:14-100.  Same constructor and lazy-layer seam (`linear_cls`, `linear_kwargs`,
+    `instantiate()`): `linear_cls(irreps_in, irreps_out, **linear_kwargs)` must return a module owning a flat e3nn
+    `weight`; the default is the B200 parameter holder.  Bias and modality variants are outside this hot path."""
 
-    def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, biases=False):
+    def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, data_key_modal_attr='modal_attr',
+                 num_modalities=0, lazy_layer_instantiate=False, **linear_kwargs):
         super().__init__()
-        if biases:
+        if linear_kwargs.get('biases', False):
             raise NotImplementedError('use_bias_in_linear is outside the B200 hot path')
+        if num_modalities > 1:
+            raise NotImplementedError('multi-modal checkpoints are outside the B200 hot path')
         self.key_input, self.key_output = data_key_in, data_key_out or data_key_in
+        self.key_modal_attr, self.num_modalities = data_key_modal_attr, num_modalities
         self.irreps_in, self.irreps_out = _irreps(irreps_in), _irreps(irreps_out)
-        spec = sp.make_linear('linear.weight', self.irreps_in, self.irreps_out)
-        self.linear = _Weight(spec.numel)
-        self._setup(spec, 'linear')
+        self.linear_kwargs, self.linear_cls = linear_kwargs, None
+        self.linear, self.layer_instantiated = None, False
+        self._is_batch_data = True
+        self._lspec = sp.make_linear('linear.weight', self.irreps_in, self.irreps_out)
+        if not lazy_layer_instantiate:
+            self.instantiate()
+
+    def instantiate(self):
+        if self.linear is not None:
+            raise ValueError('Linear layer already exists')
+        if self.linear_cls is not None:
+            self.linear = self.linear_cls(self.irreps_in, self.irreps_out, **self.linear_kwargs)
+        else:
+            self.linear = _Weight(self._lspec.numel)
+        self._setup(self._lspec, 'linear')
+        self.layer_instantiated = True
 
     def forward(self, data):
+        assert self.linear is not None, 'Layer is not instantiated'
         data[self.key_output] = self._apply_linear(data[self.key_input])
         return data
 
@@ -195,39 +241,70 @@ class IrrepsLinear(_LinearCore):
 class SelfConnectionIntro(_LinearCore):
     """sevenn/nn/self_connection.py:10-64: FullyConnectedTensorProduct(x, one_hot) = species-indexed linear."""
 
-    def __init__(self, irreps_in, irreps_operand, irreps_out):
+    def __init__(self, irreps_in, irreps_operand, irreps_out, data_key_x=X, data_key_operand=NODE_ATTR,
+                 lazy_layer_instantiate=False, **kwargs):
         super().__init__()
-        S = ir.irreps_dim(_irreps(irreps_operand))
-        spec = sp.make_linear('fc_tensor_product.weight', _irreps(irreps_in), ir.simplify(_irreps(irreps_out)))
-        spec.numel *= S
-        self.fc_tensor_product = _Weight(spec.numel)
-        self._setup(spec, 'fc_tensor_product', by_type_S=S)
+        self.key_x, self.key_operand = data_key_x, data_key_operand
+        self.irreps_in1, self.irreps_in2, self.irreps_out = _irreps(irreps_in), _irreps(irreps_operand), _irreps(irreps_out)
+        self._S = ir.irreps_dim(self.irreps_in2)
+        self._lspec = sp.make_linear('fc_tensor_product.weight', self.irreps_in1, ir.simplify(self.irreps_out))
+        self._lspec.numel *= self._S
+        self.fc_tensor_product, self.layer_instantiated = None, False
+        self.fc_tensor_product_cls, self.fc_tensor_product_kwargs = None, kwargs
+        if not lazy_layer_instantiate:
+            self.instantiate()
+
+    def instantiate(self):
+        if self.fc_tensor_product is not None:
+            raise ValueError('fc_tensor_product layer already exists')
+        self.fc_tensor_product = _Weight(self._lspec.numel)
+        self._setup(self._lspec, 'fc_tensor_product', by_type_S=self._S)
+        self.layer_instantiated = True
 
     def forward(self, data):
-        types = data[NODE_ATTR].argmax(dim=1).to(torch.int32).contiguous()
-        data[SC_TMP] = self._apply_linear(data[X], types)
+        assert self.fc_tensor_product is not None, 'Layer is not instantiated'
+        types = data[self.key_operand].argmax(dim=1).to(torch.int32).contiguous()
+        data[SC_TMP] = self._apply_linear(data[self.key_x], types)
         return data
 
 
 class SelfConnectionLinearIntro(_LinearCore):
-    """sevenn/nn/self_connection.py:68-108"""
+    """sevenn/nn/self_connection.py:68-108 (`irreps_operand` arrives as a keyword from the interaction block and is
+    dropped, as in the reference)."""
 
-    def __init__(self, irreps_in, irreps_operand, irreps_out):
+    def __init__(self, irreps_in, irreps_out=None, data_key_x=X, lazy_layer_instantiate=False, **kwargs):
         super().__init__()
-        spec = sp.make_linear('linear.weight', _irreps(irreps_in), ir.simplify(_irreps(irreps_out)))
-        self.linear = _Weight(spec.numel)
-        self._setup(spec, 'linear')
+        kwargs.pop('irreps_operand', None)
+        self.key_x = data_key_x
+        self.irreps_in, self.irreps_out = _irreps(irreps_in), _irreps(irreps_out)
+        self._lspec = sp.make_linear('linear.weight', self.irreps_in, ir.simplify(self.irreps_out))
+        self.linear, self.layer_instantiated = None, False
+        self.linear_cls, self.linear_kwargs = None, kwargs
+        if not lazy_layer_instantiate:
+            self.instantiate()
+
+    def instantiate(self):
+        if self.linear is not None:
+            raise ValueError('Linear layer already exists')
+        self.linear = _Weight(self._lspec.numel)
+        self._setup(self._lspec, 'linear')
+        self.layer_instantiated = True
 
     def forward(self, data):
-        data[SC_TMP] = self._apply_linear(data[X])
+        assert self.linear is not None, 'Layer is not instantiated'
+        data[SC_TMP] = self._apply_linear(data[self.key_x])
         return data
 
 
 class SelfConnectionOutro(nn.Module):
     """sevenn/nn/self_connection.py:112-128"""
 
+    def __init__(self, data_key_x=X):
+        super().__init__()
+        self.key_x = data_key_x
+
     def forward(self, data):
-        data[X] = data[X] + data[SC_TMP]
+        data[self.key_x] = data[self.key_x] + data[SC_TMP]
         del data[SC_TMP]
         return data
 
@@ -235,8 +312,9 @@ class SelfConnectionOutro(nn.Module):
 class EquivariantGate(nn.Module):
     """sevenn/nn/equivariant_gate.py:13-61 (activations by name: 'silu', 'tanh', ...)."""
 
-    def __init__(self, irreps_x, act_scalar_dict, act_gate_dict):
+    def __init__(self, irreps_x, act_scalar_dict, act_gate_dict, data_key_x=X):
         super().__init__()
+        self.key_x = data_key_x
         name = lambda a: a if isinstance(a, str) else getattr(a, '__name__', str(a))  # noqa: E731
         self._gspec, self._irreps_in, self._irreps_out = sp.make_gate(
             _irreps(irreps_x), {k: name(v) for k, v in act_scalar_dict.items()},
@@ -251,10 +329,10 @@ class EquivariantGate(nn.Module):
         return self._irreps_in
 
     def forward(self, data):
-        x = data[X]
+        x = data[self.key_x]
         _, inv_in = _perm(self._gspec.lin, x.device)
         p_out, _ = _perm(self._gspec.lout, x.device)
-        data[X] = F.GateFn.apply(x[:, inv_in], self._gate)[:, p_out]
+        data[self.key_x] = F.GateFn.apply(x[:, inv_in], self._gate)[:, p_out]
         return data
 
 
@@ -275,8 +353,13 @@ class IrrepsConvolution(nn.Module):
     """sevenn/nn/convolution.py:28-139: radial MLP (tcgen05 GEMMs) + fused gather/TP/segment-sum kernel."""
 
     def __init__(self, irreps_x, irreps_filter, irreps_out, weight_layer_input_to_hidden,
-                 weight_layer_act='silu', denominator=1.0, train_denominator=False, is_parallel=False):
+                 weight_layer_act='silu', denominator=1.0, train_denominator=False, data_key_x=X,
+                 data_key_filter=EDGE_ATTR, data_key_weight_input=EDGE_EMB, data_key_edge_idx=EDGE_IDX,
+                 lazy_layer_instantiate=False, is_parallel=False):
         super().__init__()
+        self.key_x, self.key_filter = data_key_x, data_key_filter
+        self.key_weight_input, self.key_edge_idx = data_key_weight_input, data_key_edge_idx
+        self.layer_instantiated = True       # the fused kernel has no separate e3nn TensorProduct to build lazily
         act = weight_layer_act if isinstance(weight_layer_act, str) else getattr(weight_layer_act, '__name__', '')
         self.denominator = nn.Parameter(torch.FloatTensor([denominator]), requires_grad=False)
         self.is_parallel = is_parallel
@@ -303,8 +386,12 @@ class IrrepsConvolution(nn.Module):
                                  'act': self._act, 'cst': self._cst})
         return self._cache[1]
 
+    def instantiate(self):
+        """convolution.py:103-116: nothing to build lazily here (kept for the reference's builder loop)."""
+        self.layer_instantiated = True
+
     def forward(self, data):
-        x = data[X]
+        x = data[self.key_x]
         dev = x.device
         lib = get_lib()
         if not lib.has_conv(self._sig):
@@ -314,12 +401,13 @@ class IrrepsConvolution(nn.Module):
             x = torch.cat([x, data[X_GHOST]])
         n_nodes = x.shape[0]
         n_dst = int(data[NLOCAL]) if self.is_parallel else n_nodes
-        cached = data.get(GRAPH)
+        gkey = GRAPH + ('' if self.key_edge_idx == EDGE_IDX else self.key_edge_idx)
+        cached = data.get(gkey)
         if cached is None or cached[0]['n_nodes'] != n_nodes or cached[0]['n_dst'] != n_dst:
-            cached = F.build_graph(data[EDGE_IDX], n_nodes, n_dst, dev)
-            data[GRAPH] = cached
+            cached = F.build_graph(data[self.key_edge_idx], n_nodes, n_dst, dev)
+            data[gkey] = cached
         graph, perm = cached
-        emb, Y = data[EDGE_EMB], data[EDGE_ATTR]
+        emb, Y = data[self.key_weight_input], data[self.key_filter]
         if perm is not None:
             emb, Y = emb[perm], Y[perm]
         w = F.RadialMLPFn.apply(emb, self._layer(dev))
@@ -328,7 +416,7 @@ class IrrepsConvolution(nn.Module):
         meta = dict(sig=self._sig, dx=self._conv.lx.dim, dmid=self._conv.lmid.dim, wn=self._conv.wn,
                     units=conv_codegen.n_units(self._conv), inv_denom=1.0 / float(self.denominator.item()))
         out = F.ConvFn.apply(x.float()[:, inv_x], Y, w, graph, meta)
-        data[X] = out[:, p_mid]
+        data[self.key_x] = out[:, p_mid]
         return data
 
 
@@ -336,44 +424,79 @@ class IrrepsConvolution(nn.Module):
 class Rescale(nn.Module):
     """sevenn/nn/scale.py:22-56"""
 
-    def __init__(self, shift, scale, train_shift_scale=False):
+    def __init__(self, shift, scale, data_key_in=SCALED_AE, data_key_out=AE, train_shift_scale=False):
         super().__init__()
         self.shift = nn.Parameter(torch.FloatTensor([shift]), requires_grad=False)
         self.scale = nn.Parameter(torch.FloatTensor([scale]), requires_grad=False)
+        self.key_input, self.key_output = data_key_in, data_key_out
+
+    def get_shift(self):
+        return self.shift.detach().cpu().tolist()[0]
+
+    def get_scale(self):
+        return self.scale.detach().cpu().tolist()[0]
 
     def forward(self, data):
-        data[AE] = data[SCALED_AE] * self.scale + self.shift
+        data[self.key_output] = data[self.key_input] * self.scale + self.shift
         return data
 
 
 class SpeciesWiseRescale(nn.Module):
     """sevenn/nn/scale.py:60-161"""
 
-    def __init__(self, shift, scale, train_shift_scale=False):
+    def __init__(self, shift, scale, data_key_in=SCALED_AE, data_key_out=AE, data_key_indices=ATOM_TYPE,
+                 train_shift_scale=False):
         super().__init__()
+        self.key_input, self.key_output, self.key_indices = data_key_in, data_key_out, data_key_indices
         n = len(shift) if isinstance(shift, list) else len(scale)
         shift = [shift] * n if isinstance(shift, float) else shift
         scale = [scale] * n if isinstance(scale, float) else scale
         self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=False)
         self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=False)
 
+    def get_shift(self, type_map=None):
+        v = self.shift.detach().cpu().tolist()
+        return v if type_map is None else {z: v[i] for z, i in type_map.items()}
+
+    def get_scale(self, type_map=None):
+        v = self.scale.detach().cpu().tolist()
+        return v if type_map is None else {z: v[i] for z, i in type_map.items()}
+
+    @staticmethod
+    def from_mappers(shift, scale, type_map, **kwargs):
+        """scale.py:112-147: per-species lists from floats, lists in type order, or {atomic number: value} dicts."""
+        def as_list(v):
+            if isinstance(v, dict):
+                return [float(v[z]) for z, _ in sorted(type_map.items(), key=lambda kv: kv[1])]
+            if isinstance(v, (list, tuple)):
+                return [float(t) for t in v] if len(v) != 1 else [float(v[0])] * len(type_map)
+            return [float(v)] * len(type_map)
+        return SpeciesWiseRescale(as_list(shift), as_list(scale), **kwargs)
+
     def forward(self, data):
-        idx = data[ATOM_TYPE]
-        data[AE] = data[SCALED_AE] * self.scale[idx].view(-1, 1) + self.shift[idx].view(-1, 1)
+        idx = data[self.key_indices]
+        data[self.key_output] = (data[self.key_input] * self.scale[idx].view(-1, 1)
+                                 + self.shift[idx].view(-1, 1))
         return data
 
 
 class AtomReduce(nn.Module):
     """sevenn/nn/linear.py:104-141 (single graph; fp64 accumulation)."""
 
-    def __init__(self):
+    def __init__(self, data_key_in=AE, data_key_out=E_TOT, reduce='sum', constant=1.0):
         super().__init__()
+        self.key_input, self.key_output, self.reduce, self.constant = data_key_in, data_key_out, reduce, constant
         self._is_batch_data = False
 
     def forward(self, data):
+        src = data[self.key_input]
         if self._is_batch_data:
-            raise NotImplementedError('batched graphs are SURVEY 8f-1 (training path)')
-        data[E_TOT] = torch.sum(data[AE].double()).to(data[AE].dtype)
+            b = data[BATCH]
+            out = torch.zeros(int(b.max()) + 1, dtype=torch.float64, device=src.device)
+            out.index_add_(0, b, src.reshape(-1).double())
+            data[self.key_output] = out.to(src.dtype) * self.constant
+        else:
+            data[self.key_output] = torch.sum(src.double()).to(src.dtype) * self.constant
         return data
 
 
@@ -381,9 +504,13 @@ class ForceStressOutputFromEdge(nn.Module):
     """sevenn/nn/force_output.py:140-224: f_ij = dE/d edge_vec (reverse kernels via autograd), then one
     kernel for F_i = sum_{centre i} f - sum_{neighbour i} f and the per-atom virial."""
 
-    def __init__(self):
+    def __init__(self, data_key_edge=EDGE_VEC, data_key_edge_idx=EDGE_IDX, data_key_energy=E_TOT,
+                 data_key_force=FORCE, data_key_stress=STRESS, data_key_cell_volume=VOL):
         super().__init__()
         self._is_batch_data = False
+
+    def get_grad_key(self):
+        return EDGE_VEC
 
     def forward(self, data):
         if self._is_batch_data:
@@ -392,6 +519,8 @@ class ForceStressOutputFromEdge(nn.Module):
         rij = data[EDGE_VEC]
         fij = torch.autograd.grad([data[E_TOT].sum()], [rij], allow_unused=True)[0]
         cached = data.pop(GRAPH, None)
+        for k in [k for k in data if isinstance(k, str) and k.startswith(GRAPH)]:
+            del data[k]                     # per-cutoff graphs of MultiCutoffEdgeEmbedding models
         if fij is None:
             return data
         dev = rij.device
@@ -443,12 +572,21 @@ class ForceOutput(ForceStressOutputFromEdge):
 
 # ----------------------------------------------------------- sequential --
 class AtomGraphSequential(nn.Sequential):
-    """sevenn/nn/sequential.py:22-205"""
+    """sevenn/nn/sequential.py:41-205: the model container (same constructor, same helper methods)."""
 
-    def __init__(self, modules, cutoff=0.0, type_map=None, eval_type_map=True, data_key_grad=None):
-        super().__init__(OrderedDict(modules))
-        self.cutoff, self.type_map, self.key_grad = cutoff, type_map, data_key_grad
+    def __init__(self, modules, cutoff=0.0, type_map=None, modal_map=None, eval_type_map=True,
+                 eval_modal_map=False, data_key_atomic_numbers=Z, data_key_node_feature=X, data_key_grad=None):
+        modules = modules if isinstance(modules, OrderedDict) else OrderedDict(modules)
+        if eval_modal_map or modal_map is not None:
+            raise NotImplementedError('multi-modal models are outside the B200 hot path')
+        for m in modules.values():                        # sequential.py:_instantiate_modules (lazy-layer seam)
+            if not getattr(m, 'layer_instantiated', True):
+                m.instantiate()
+        super().__init__(modules)
+        self.cutoff, self.type_map, self.modal_map, self.key_grad = cutoff, type_map, None, data_key_grad
+        self.key_atomic_numbers, self.key_node_feature = data_key_atomic_numbers, data_key_node_feature
         self.eval_type_map = eval_type_map and type_map is not None
+        self.eval_modal_map, self.is_batch_data = False, False
         if type_map is not None:
             lut = -torch.ones(120, dtype=torch.long)
             for z, i in type_map.items():
@@ -459,12 +597,36 @@ class AtomGraphSequential(nn.Sequential):
         for m in self:
             if hasattr(m, '_is_batch_data'):
                 m._is_batch_data = flag
+        self.is_batch_data = flag
 
-    def forward(self, data: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    def get_irreps_in(self, modlue_name, attr_key='irreps_in'):
+        for m in self._modules[modlue_name].modules():
+            if hasattr(m, attr_key):
+                return ir.irreps_str(getattr(m, attr_key))
+        return None
+
+    def prepand_module(self, key, module):
+        self._modules[key] = module
+        self._modules.move_to_end(key, last=False)
+
+    def replace_module(self, key, module):
+        self._modules[key] = module
+
+    def delete_module_by_key(self, key):
+        self._modules.pop(key, None)
+
+    def _atomic_numbers_to_onehot(self, atomic_numbers):
+        return self.z_to_onehot_tensor.to(atomic_numbers.device)[atomic_numbers]
+
+    def _preprocess(self, data):
         if self.eval_type_map:
-            data[X] = self.z_to_onehot_tensor.to(data[Z].device)[data[Z]]
+            data[self.key_node_feature] = self._atomic_numbers_to_onehot(data[self.key_atomic_numbers])
         if self.key_grad is not None:
             data[self.key_grad].requires_grad_(True)
+        return data
+
+    def forward(self, data: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        data = self._preprocess(data)
         for m in self:
             data = m(data)
         return data
@@ -485,6 +647,8 @@ def init_edge_embedding(cfg):
     rb = dict(cfg['radial_basis'])
     if rb.pop('radial_basis_name') != 'bessel':
         raise ValueError('only the bessel radial basis is on the hot path')
+    if cfg.get('multi_cutoff'):
+        return MultiCutoffEdgeEmbedding([BesselBasis(c, **rb) for c in sorted(set(cfg['multi_cutoff']))], cut, sph)
     return EdgeEmbedding(BesselBasis(cfg['cutoff'], **rb), cut, sph)
 
 
@@ -508,7 +672,8 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
     irreps_x = [(C, (0, 1))] if manual is None else manual[0]
     layers['onehot_idx_to_onehot'] = OnehotEmbedding(S, X, X, ATOM_TYPE, NODE_ATTR)
     layers['onehot_to_feature_x'] = IrrepsLinear(one_hot, irreps_x, X, biases=cfg['use_bias_in_linear'])
-    wnn = [ee.basis_function.num_basis] + list(cfg['weight_nn_hidden_neurons'])
+    multi = cfg.get('multi_cutoff') or None
+    wnn = [(ee.basis_functions[0] if multi else ee.basis_function).num_basis] + list(cfg['weight_nn_hidden_neurons'])
     for t in range(L):
         parity_mode, lm = 'full', lmax_node
         if t == L - 1:
@@ -519,11 +684,15 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
         irreps_out_tp = ir.infer_irreps_out(irreps_x, irreps_filter, out_lmax, parity_mode, False)
         gate = EquivariantGate(irreps_out, cfg['act_scalar'], cfg['act_gate'])
         gate_in = gate.get_gate_irreps_in()
-        layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, one_hot, gate_in)
+        layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, irreps_operand=one_hot, irreps_out=gate_in)
         layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X)
         layers[f'{t}_convolution'] = IrrepsConvolution(irreps_x, irreps_filter, irreps_out_tp, wnn,
                                                        cfg['act_radial'], denom[t], cfg['train_denominator'],
-                                                       is_parallel=parallel)
+                                                       is_parallel=parallel,
+                                                       **({} if not multi else dict(
+                                                           data_key_filter=f'{EDGE_ATTR}{multi[t]}',
+                                                           data_key_weight_input=f'{EDGE_EMB}{multi[t]}',
+                                                           data_key_edge_idx=f'{EDGE_IDX}{multi[t]}')))
         layers[f'{t}_self_interaction_2'] = IrrepsLinear(layers[f'{t}_convolution'].irreps_mid,
                                                          ir.simplify(gate_in), X)
         layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()
@@ -536,11 +705,11 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale
     if isinstance(shift, float) and isinstance(scale, float):
-        layers['rescale_atomic_energy'] = Rescale(shift, scale, cfg['train_shift_scale'])
+        layers['rescale_atomic_energy'] = Rescale(shift, scale, train_shift_scale=cfg['train_shift_scale'])
     else:
         shift = shift * S if isinstance(shift, list) and len(shift) == 1 else shift
         scale = scale * S if isinstance(scale, list) and len(scale) == 1 else scale
-        layers['rescale_atomic_energy'] = SpeciesWiseRescale(shift, scale, cfg['train_shift_scale'])
+        layers['rescale_atomic_energy'] = SpeciesWiseRescale(shift, scale, train_shift_scale=cfg['train_shift_scale'])
     layers['reduce_total_enegy'] = AtomReduce()
     layers['force_output'] = ForceStressOutputFromEdge()
     common = dict(cutoff=cfg['cutoff'], type_map=cfg['_type_map'], data_key_grad=EDGE_VEC)

@@ -170,6 +170,12 @@ class SevenNetCalculator(_AseCalculator):
                         'n_edges': r['n_edges']})
         return res
 
+    def set_atoms(self, atoms):
+        """sevennet_calculator.py:153-161: ASE calls this on `atoms.calc = calc`; unknown species fail early."""
+        for z in sorted(set(int(z) for z in atoms.get_atomic_numbers())):
+            if z not in self.type_map:
+                raise ValueError(f'Model do not know atomic number: {z}, (knows: {list(self.type_map.keys())})')
+
     def calculate(self, atoms=None, properties=None, system_changes=all_changes):
         super().calculate(atoms, properties, system_changes)
         if atoms is None:

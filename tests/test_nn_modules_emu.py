@@ -118,3 +118,20 @@ def test_single_modules_match_oracle():
         do = getattr(om, f'{t}_self_connection_outro')(do)
         db = getattr(bm, f'{t}_self_connection_outro')(db)
         do, db = both(f'{t}_equivariant_gate', do, db, S.X, S.X)
+
+
+@pytest.mark.parametrize('cutoff_fn', [{'cutoff_function_name': 'XPLOR', 'cutoff_on': 4.5},
+                                       {'cutoff_function_name': 'poly_cut', 'poly_cut_p_value': 6}])
+def test_multi_cutoff_edge_embedding_matches_oracle(cutoff_fn):
+    """The fork's per-layer cutoffs (edge_embedding.py:220-257, interaction_blocks.py:54-60): every convolution
+    runs over the sub-graph of its own cutoff."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg['cutoff_function'] = cutoff_fn
+    cfg['multi_cutoff'] = [5.0, 3.5, 5.0]
+    torch.manual_seed(21)
+    om = S.build_model(cfg).eval()
+    assert [k for k in om.state_dict() if 'basis_functions' in k] == [
+        'edge_embedding.basis_functions.0.coeffs', 'edge_embedding.basis_functions.1.coeffs']
+    numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=7)
+    model = _run_pair(cfg, om.state_dict(), om, numbers, pos, cell)
+    assert isinstance(model.edge_embedding, bnn.MultiCutoffEdgeEmbedding)
