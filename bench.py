@@ -149,10 +149,17 @@ def run_single(args):
     from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
     dev = torch.device('cuda:0')
     torch.cuda.set_device(dev)
-    cfg = model_config()
+    cfg3 = args.workload == 'cfg3'
+    if cfg3:
+        # BASELINE config 3: SevenNet-l3i5 (lmax 3) on a 32,768-atom disordered Li-P-S cell (not the default line)
+        from tests.structures import jittered_lips
+        cfg = dict(presets.PRESETS['7net-l3i5'])
+        numbers, pos, cell = jittered_lips()
+    else:
+        cfg = model_config()
+        numbers, pos, cell = workload()
     sd = random_state_dict(cfg)
     calc = SevenNetCalculator((cfg, sd), file_type='model_instance', device=dev)
-    numbers, pos, cell = workload()
     n = len(numbers)
     pbc = [True] * 3
     types_dev = torch.from_numpy(calc._lut[numbers].astype(np.int32)).to(dev)
@@ -219,7 +226,10 @@ def run_single(args):
     fwd_ach = conv_fwd_algorithmic_bytes(inner, n, E) / (stage[key_f] / n_inner * 1e-3) / 1e9
     stage_sorted = dict(sorted(((k, round(v, 4)) for k, v in stage.items()), key=lambda kv: -kv[1]))
 
-    cpu_v, cpu_t, cores, cn, ce = cpu_oracle_sample((3, 3, 3), 1, 0)
+    if cfg3:
+        cpu_v = None
+    else:
+        cpu_v, cpu_t, cores, cn, ce = cpu_oracle_sample((3, 3, 3), 1, 0)
     tab = calc.engine.radial == 'table'
     S_sh = (inner.lmax_sh + 1) ** 2
     # bytes the launch really has to move through HBM: the tabulated kernels neither read w nor write dW
@@ -236,8 +246,11 @@ def run_single(args):
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': 1, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
         'data': 'synthetic',
-        'config': {'workload': f'SevenNet-0 (lmax2, 5 layers, 128x0e+64x1e+32x2e, rc=5A, random-init weights) E+F+S, '
-                               f'{n}-atom bulk HfO2 (fluorite 7x7x7, a={A_LAT}A, 20 vacancies), {E / n:.1f} neighbours/atom',
+        'config': {'workload': (f'SevenNet-l3i5 (lmax3, 5 layers, 128x0e+64x1e+32x2e+32x3e, rc=5A, random-init weights) '
+                                f'E+F+S, {n}-atom disordered Li-P-S cell (3:1:4, 0.048 atoms/A^3, hard core 1.95 A), '
+                                f'{E / n:.1f} neighbours/atom' if cfg3 else
+                                f'SevenNet-0 (lmax2, 5 layers, 128x0e+64x1e+32x2e, rc=5A, random-init weights) E+F+S, '
+                                f'{n}-atom bulk HfO2 (fluorite 7x7x7, a={A_LAT}A, 20 vacancies), {E / n:.1f} neighbours/atom'),
                    'n_atoms': n, 'n_edges': E, 'step': 'device neighbour list + forward + analytic reverse pass',
                    'radial': calc.engine.radial,
                    'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)'},
@@ -259,10 +272,14 @@ def run_single(args):
                      'path': {'bytes_per_atom': path_bytes_per_atom, 'ceiling_atom_steps_s': peak * 1e9 / path_bytes_per_atom,
                               'frac': value / (peak * 1e9 / path_bytes_per_atom)}},
         'stage_ms': stage_sorted,
-        'cpu_baseline': {'value': cpu_v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-                         'sample': f'oracle (CPU restatement of the reference path) on a {cn}-atom HfO2 3x3x3 cell, '
-                                   f'{ce / cn:.1f} neighbours/atom, 1 evaluation = {cpu_t:.1f} s'},
+        'cpu_baseline': None if cpu_v is None else {
+            'value': cpu_v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+            'sample': f'oracle (CPU restatement of the reference path) on a {cn}-atom HfO2 3x3x3 cell, '
+                      f'{ce / cn:.1f} neighbours/atom, 1 evaluation = {cpu_t:.1f} s'},
     }
+    if cfg3:
+        line['metric'] = 'atom-steps/s (E+F+S) SevenNet-l3i5'
+        line['roofline']['path'] = None
     print(json.dumps(line), flush=True)
 
 
@@ -272,8 +289,9 @@ def main():
     ap.add_argument('--steps', type=int, default=20)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours')
-    ap.add_argument('--workload', default='cfg2', help="N>1 only: 'cfg2' (weak scaling, default) or 'si1m' = BASELINE "
-                    "config 4, strong scaling: one 1M-atom bulk-Si cell (50^3 diamond cells) cut over the N GPUs")
+    ap.add_argument('--workload', default='cfg2', help="'cfg2' (default: BASELINE config 2; weak scaling for N>1); "
+                    "'cfg3' (N=1: BASELINE config 3, SevenNet-l3i5 on 32,768 Li-P-S atoms); 'si1m' (N>1: BASELINE "
+                    "config 4, strong scaling: one 1M-atom bulk-Si cell (50^3 diamond cells) cut over the N GPUs)")
     ap.add_argument('--si-cells', type=int, default=50)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl != 'reference' else args.warmup

@@ -75,24 +75,28 @@ class NeighborList:
             n = len(pos)
             cell_eff, dpar, ipar = nl_params(pos, cell, pbc, cutoff, max_bins=max(8 * n, 64))
         nbins = int(ipar[3] * ipar[4] * ipar[5])
-        i32 = lambda *s: torch.zeros(*s, dtype=torch.int32, device=dev)  # noqa: E731
         if pos_dev is None:
             pos_dev = torch.from_numpy(pos).to(dev, non_blocking=True)
         pw = torch.empty(n, 3, dtype=torch.float64, device=dev)
-        wrap, atom_bin = i32(n, 3), i32(n)
-        bin_count, bin_start, bin_fill, bin_atoms = i32(nbins + 1), i32(nbins + 1), i32(nbins), i32(n)
-        tmp = i32(int(lib.cdll.sevenn_scan_tmp_ints(max(nbins, n) + 1)) + 1)
+        # every per-atom / per-bin int32 array out of ONE zero-filled workspace (one fill launch instead of ten)
+        n_tmp = int(lib.cdll.sevenn_scan_tmp_ints(max(nbins, n) + 1)) + 1
+        sizes = [3 * n, n, nbins + 1, nbins + 1, nbins, n, n_tmp, n + 1, n + 1]
+        offs = np.concatenate([[0], np.cumsum([(s_ + 3) // 4 * 4 for s_ in sizes])])
+        ws = torch.zeros(int(offs[-1]), dtype=torch.int32, device=dev)
+        wrap, atom_bin, bin_count, bin_start, bin_fill, bin_atoms, tmp, count, rowptr = (
+            ws[int(o):int(o) + s_] for o, s_ in zip(offs[:-1], sizes))
+        wrap = wrap.view(n, 3)
         dp, ip = dpar.ctypes.data_as(ctypes.c_void_p), ipar.ctypes.data_as(ctypes.c_void_p)
         lib.call('sevenn_nl_bin', _p(pos_dev), n, dp, ip, _p(pw), _p(wrap), _p(atom_bin), _p(bin_count), st)
         lib.call('sevenn_scan_i32', _p(bin_count), _p(bin_start), nbins, _p(tmp), st)
         lib.call('sevenn_nl_scatter', _p(atom_bin), n, _p(bin_start), _p(bin_fill), _p(bin_atoms), st)
-        count, rowptr = i32(n + 1), i32(n + 1)
         lib.call('sevenn_nl_count', _p(pw), _p(wrap), _p(atom_bin), _p(bin_start), _p(bin_atoms), n, dp, ip,
                  _p(count), st)
         lib.call('sevenn_scan_i32', _p(count), _p(rowptr), n, _p(tmp), st)
         E = int(rowptr[n].item())               # the one host sync of the build
         keys = torch.empty(max(E, 1), dtype=torch.int64, device=dev)
-        center, col, shift = i32(max(E, 1)), i32(max(E, 1)), i32(max(E, 1), 3)
+        ebuf = torch.empty(5 * max(E, 1), dtype=torch.int32, device=dev)       # written in full by the decode kernel
+        center, col, shift = ebuf[:max(E, 1)], ebuf[max(E, 1):2 * max(E, 1)], ebuf[2 * max(E, 1):].view(max(E, 1), 3)
         vec = torch.empty(max(E, 1), 3, dtype=torch.float32, device=dev)
         lib.call('sevenn_nl_fill', _p(pw), _p(wrap), _p(atom_bin), _p(bin_start), _p(bin_atoms), n, dp, ip,
                  _p(rowptr), _p(keys), _p(pos_dev), _p(center), _p(col), _p(shift), _p(vec), st)
@@ -112,12 +116,13 @@ class NeighborList:
 
 def csc_build(lib, col, n_nodes, dev, st):
     E = int(col.shape[0])
-    cnt = torch.zeros(n_nodes + 1, dtype=torch.int32, device=dev)
-    fill = torch.zeros(max(n_nodes, 1), dtype=torch.int32, device=dev)
-    cptr = torch.zeros(n_nodes + 1, dtype=torch.int32, device=dev)
+    n_tmp = int(lib.cdll.sevenn_scan_tmp_ints(n_nodes + 1)) + 1
+    sizes = [n_nodes + 1, max(n_nodes, 1), n_nodes + 1, n_tmp]
+    offs = np.concatenate([[0], np.cumsum([(s_ + 3) // 4 * 4 for s_ in sizes])])
+    ws = torch.zeros(int(offs[-1]), dtype=torch.int32, device=dev)            # one fill launch
+    cnt, fill, cptr, tmp = (ws[int(o):int(o) + s_] for o, s_ in zip(offs[:-1], sizes))
     keys = torch.empty(max(E, 1), dtype=torch.int64, device=dev)
-    cedge = torch.zeros(max(E, 1), dtype=torch.int32, device=dev)
-    tmp = torch.zeros(int(lib.cdll.sevenn_scan_tmp_ints(n_nodes + 1)) + 1, dtype=torch.int32, device=dev)
+    cedge = torch.empty(max(E, 1), dtype=torch.int32, device=dev)             # written in full by the build
     lib.call('sevenn_csc_build', _p(col) if E else None, E, n_nodes, _p(cnt), _p(fill), _p(cptr), _p(keys),
              _p(cedge), _p(tmp), st)
     return cptr, cedge[:E]

@@ -52,3 +52,15 @@ def fluorite_hfo2(reps, a=4.85, sigma=0.05, seed=0, n_remove=0):
     pos = frac * a + rng.normal(0, sigma, frac.shape)
     cell = np.diag(np.array(reps) * a)
     return numbers, pos, cell
+
+
+def jittered_lips(n_side=32, density=0.048, jitter=0.4, seed=1):
+    """BASELINE config 3 stand-in: n_side^3 atoms, Li:P:S = 3:1:4, disordered positions at `density` atoms/A^3 with
+    a hard core (simple-cubic sites of spacing density^(-1/3) = 2.75 A, each coordinate displaced uniformly by up to
+    +-`jitter` A, so no pair is closer than spacing - 2 jitter = 1.95 A).  O(n), unlike random_cell()."""
+    rng = np.random.default_rng(seed)
+    a = density ** (-1.0 / 3.0)
+    g = np.stack(np.meshgrid(*[np.arange(n_side)] * 3, indexing='ij'), -1).reshape(-1, 3).astype(np.float64)
+    pos = g * a + rng.uniform(-jitter, jitter, g.shape)
+    numbers = rng.choice(np.array([3, 15, 16]), len(pos), p=[3 / 8, 1 / 8, 4 / 8])
+    return numbers, pos, np.eye(3) * (n_side * a)
