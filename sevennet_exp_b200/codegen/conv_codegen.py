@@ -118,6 +118,18 @@ MIN_CTAS_TAB = {
 }
 
 
+def _env_overrides():
+    """Tuning runs only (tools/tune_occupancy.sh): SEVENN_MIN_CTAS / SEVENN_MIN_CTAS_TAB = 'sig:fwd,bwd;sig:fwd,bwd'."""
+    import os
+    for var, table in (('SEVENN_MIN_CTAS', MIN_CTAS), ('SEVENN_MIN_CTAS_TAB', MIN_CTAS_TAB)):
+        for item in filter(None, os.environ.get(var, '').split(';')):
+            sig, v = item.split(':')
+            table[sig] = tuple(int(t) for t in v.split(','))
+
+
+_env_overrides()
+
+
 def _stage_floats(G: _Group, spec: ConvSpec) -> int:
     S = (spec.lmax_sh + 1) ** 2
     return (G.d1 + len(G.paths)) * 32 + ((S + 3) // 4) * 4

@@ -281,7 +281,12 @@ class Engine(Kernels):
                 raise ValueError(f'{k}: shape {sd[k].shape} != expected {shp}')
         dev = self.dev
         f32 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32, device=dev).contiguous()  # noqa: E731
-        self.coeffs = f32(sd['edge_embedding.basis_function.coeffs'])
+        if spec.multi_cutoff:
+            if self.radial != 'table':
+                raise NotImplementedError("multi_cutoff models run with radial='table' (per-layer tables on one grid)")
+            if len(spec.multi_cutoff) != len(spec.layers) or max(spec.multi_cutoff) > spec.cutoff * (1 + 1e-12):
+                raise ValueError('multi_cutoff needs one cutoff per convolution layer, none above `cutoff`')
+        self.coeffs = f32(sd[spec.coeff_key(0)])
         # embedding table [S, d0]
         emb = spec.embed
         table = np.zeros((spec.n_species, emb.lout.dim))
@@ -310,13 +315,20 @@ class Engine(Kernels):
                                    p.out_stride, p.act, p.cst) for p in L.gate.pieces]),
             }
             if self.radial == 'table':
+                xplor = spec.cutoff_fn != 'poly_cut'
                 if t_first:
-                    self.tab_n = radial_table.choose_intervals(spec.cutoff, spec.cutoff_fn, spec.cutoff_on)
+                    extra = []
+                    for c in (spec.multi_cutoff or []):              # every layer cutoff (and XPLOR switch-on) a node
+                        extra += [c, c - 1.0] if xplor else [c]
+                    self.tab_n = radial_table.choose_intervals(spec.cutoff, spec.cutoff_fn, spec.cutoff_on,
+                                                               extra_nodes=extra)
                     self.tab_inv_h = self.tab_n / spec.cutoff
                     t_first = False
+                rc_t = spec.multi_cutoff[L.t] if spec.multi_cutoff else spec.cutoff
+                r_on_t = (rc_t - 1.0) if (spec.multi_cutoff and xplor) else spec.cutoff_on   # edge_embedding.py:244-246
                 lay['tab'] = f32(radial_table.build_table(
-                    sd['edge_embedding.basis_function.coeffs'], spec.cutoff_fn, spec.cutoff, spec.cutoff_p,
-                    spec.cutoff_on, Wm, spec.act_radial, ir.normalize2mom_const(spec.act_radial), self.tab_n))
+                    sd[spec.coeff_key(L.t)], spec.cutoff_fn, rc_t, spec.cutoff_p, r_on_t, Wm, spec.act_radial,
+                    ir.normalize2mom_const(spec.act_radial), self.tab_n, grid_rc=spec.cutoff))
             if not self.lib.has_conv(lay['sig']):
                 raise _lib.SevennError(
                     f"no prebuilt conv kernel for signature {lay['sig']} ({ir.irreps_str(L.conv.lx.groups)}); "

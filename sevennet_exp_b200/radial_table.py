@@ -78,14 +78,18 @@ def radial_function(r: np.ndarray, coeffs: np.ndarray, kind: str, rc: float, p: 
     return cur, dcur
 
 
-def choose_intervals(rc: float, kind: str, r_on: float, n_min: int = 1000, n_max: int = 2048) -> int:
-    """Number of grid intervals: the smallest n >= n_min for which ``cutoff_on`` is (numerically) a node."""
-    if kind == 'poly_cut' or not (0.0 < r_on < rc):
+def choose_intervals(rc: float, kind: str, r_on: float, n_min: int = 1000, n_max: int = 2048,
+                     extra_nodes: Sequence[float] = ()) -> int:
+    """Number of grid intervals over [0, rc]: the smallest n >= n_min for which ``cutoff_on`` and every radius in
+    ``extra_nodes`` (per-layer cutoffs of multi-cutoff models) is (numerically) a node."""
+    special = [float(x) for x in extra_nodes if 0.0 < float(x) < rc]
+    if kind != 'poly_cut' and 0.0 < r_on < rc:
+        special.append(float(r_on))
+    if not special:
         return n_min
     best, best_err = n_min, 1.0
     for n in range(n_min, n_max + 1):
-        s = r_on * n / rc
-        err = abs(s - round(s))
+        err = max(abs(x * n / rc - round(x * n / rc)) for x in special)
         if err < 1e-9:
             return n
         if err < best_err:
@@ -94,11 +98,17 @@ def choose_intervals(rc: float, kind: str, r_on: float, n_min: int = 1000, n_max
 
 
 def build_table(coeffs, kind: str, rc: float, p: float, r_on: float, weights: Sequence[np.ndarray], act: str,
-                act_cst: float, n_int: int) -> np.ndarray:
-    """fp32 [n_int, wn, 4]: (f_i, h f'_i, f_{i+1}, h f'_{i+1}) per interval and column."""
-    h = rc / n_int
+                act_cst: float, n_int: int, grid_rc: float = None) -> np.ndarray:
+    """fp32 [n_int, wn, 4]: (f_i, h f'_i, f_{i+1}, h f'_{i+1}) per interval and column.  ``grid_rc`` (>= rc, default
+    rc) is the extent of the grid: a layer whose own cutoff ``rc`` is shorter than the neighbour-list cutoff sees no
+    edge beyond ``rc`` (MultiCutoffEdgeEmbedding keeps r <= rc), i.e. its radial function is identically zero
+    there; value and slope vanish at ``rc`` for both envelopes, so the zero continuation is C1."""
+    grid_rc = rc if grid_rc is None else grid_rc
+    h = grid_rc / n_int
     r = np.arange(n_int + 1, dtype=np.float64) * h
-    f, df = radial_function(r, coeffs, kind, rc, p, r_on, weights, act, act_cst)
+    inside = r <= rc * (1 + 1e-12)
+    f, df = radial_function(np.where(inside, r, rc), coeffs, kind, rc, p, r_on, weights, act, act_cst)
+    f, df = f * inside[:, None], df * inside[:, None]
     g = h * df
     tab = np.stack([f[:-1], g[:-1], f[1:], g[1:]], axis=-1)
     return np.ascontiguousarray(tab.astype(np.float32))

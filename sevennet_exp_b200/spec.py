@@ -247,10 +247,18 @@ class ModelSpec:
     read1: LinearSpec
     read2: LinearSpec
     rescale_species_wise: bool
+    multi_cutoff: Optional[List[float]] = None     # per-layer cutoffs (MultiCutoffEdgeEmbedding), else None
+
+    def coeff_key(self, t: int) -> str:
+        """state_dict key of the Bessel coefficients convolution layer ``t`` uses (model_build.py:87-103: one
+        BesselBasis per distinct cutoff, ascending)."""
+        if not self.multi_cutoff:
+            return 'edge_embedding.basis_function.coeffs'
+        return f'edge_embedding.basis_functions.{sorted(set(self.multi_cutoff)).index(self.multi_cutoff[t])}.coeffs'
 
     def expected_keys(self) -> Dict[str, Tuple[int, ...]]:
-        out = {'edge_embedding.basis_function.coeffs': (self.n_basis,),
-               self.embed.key: (self.embed.numel,)}
+        out = {self.coeff_key(t): (self.n_basis,) for t in range(len(self.layers))}
+        out[self.embed.key] = (self.embed.numel,)
         for L in self.layers:
             out[L.sc.key] = (L.sc.numel,)
             out[L.si1.key] = (L.si1.numel,)
@@ -327,7 +335,8 @@ def build_spec(config: dict) -> ModelSpec:
         lmax_sh=lmax_edge, sh_parity=sh_p, normalize_sph=bool(cfg['_normalize_sph']), n_basis=nb,
         cutoff_fn=name, cutoff_p=float(cf.get('poly_cut_p_value', 6)),
         cutoff_on=float(cf.get('cutoff_on', 0.0)), act_radial=cfg['act_radial'], embed=embed,
-        layers=layers, read1=read1, read2=read2, rescale_species_wise=species_wise)
+        layers=layers, read1=read1, read2=read2, rescale_species_wise=species_wise,
+        multi_cutoff=[float(c) for c in cfg['multi_cutoff']] if cfg.get('multi_cutoff') else None)
 
 
 def nequip_sc_dense(spec: LinearSpec, flat: np.ndarray, block: LinearBlock, S: int) -> np.ndarray:

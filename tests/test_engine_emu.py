@@ -87,3 +87,30 @@ def test_engine_emu_reference_deployed_torchscript(golden_dir):
         assert np.abs(out['forces'].numpy() - gold['force']).max() < 1e-4, radial
         stress = -(out['virial6'].numpy() / vol)
         assert np.abs(stress - gold['stress']).max() * KBAR < 1e-2, radial
+
+
+@pytest.mark.parametrize('cutoff_fn', [{'cutoff_function_name': 'XPLOR', 'cutoff_on': 4.5},
+                                       {'cutoff_function_name': 'poly_cut', 'poly_cut_p_value': 6}])
+def test_engine_emu_multi_cutoff(cutoff_fn):
+    """The fork's MultiCutoffEdgeEmbedding through the whole-model engine: per-layer radial tables on one grid
+    (zero beyond the layer's cutoff) against the oracle's per-cutoff sub-graphs."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg['cutoff_function'] = cutoff_fn
+    cfg['multi_cutoff'] = [5.0, 3.5, 5.0]
+    torch.manual_seed(31)
+    model = S.build_model(cfg).eval()
+    numbers, pos, cell = random_cell(24, list(cfg['_type_map']), density=0.05, seed=9)
+    spec = sp.build_spec(cfg)
+    assert spec.coeff_key(1) == 'edge_embedding.basis_functions.0.coeffs'
+    lib = build_full_emu([L.conv for L in spec.layers])
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+    ref = model(dict(g))
+    types = np.array([cfg['_type_map'][int(z)] for z in numbers])
+    vol = float(g[S.VOL])
+    gr = graph_from_edges(types, g[S.EDGE_IDX].numpy(), g[S.EDGE_VEC].detach().numpy(), len(numbers), vol)
+    with pytest.raises(NotImplementedError):
+        Engine(spec, model.state_dict(), lib=lib, device='cpu', radial='mlp')
+    out = Engine(spec, model.state_dict(), lib=lib, device='cpu', radial='table').evaluate(gr)
+    assert abs(out['energy'].item() - ref[S.E_TOT].item()) / len(numbers) < 1e-5
+    assert (out['forces'] - ref[S.FORCE].detach()).abs().max().item() < 1e-4
+    assert ((-(out['virial6'] / vol)).float() - ref[S.STRESS].detach()).abs().max().item() * KBAR < 1e-2
