@@ -62,31 +62,57 @@ def random_state_dict(cfg):
 
 
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons DURING the timed region, every 20 ms through NVML (no process spawn, so the
+    launching thread is not disturbed); falls back to polling `nvidia-smi` when pynvml is unusable."""
+
+    NAMES = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+
     def __init__(self, index=0):
         super().__init__(daemon=True)
         self.rows, self.stop_flag, self.index = [], False, index
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get('CUDA_VISIBLE_DEVICES')
+            phys = int(vis.split(',')[index]) if vis and vis.split(',')[index].strip().isdigit() else index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.masks = [pynvml.nvmlClocksEventReasonHwSlowdown, pynvml.nvmlClocksEventReasonHwThermalSlowdown,
+                          pynvml.nvmlClocksEventReasonSwThermalSlowdown, pynvml.nvmlClocksEventReasonSwPowerCap]
+            self.nvml = pynvml
+        except Exception:  # noqa: BLE001
+            self.nvml = None
 
-    def run(self):
+    def _sample_smi(self):
         q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+        o = subprocess.run(['nvidia-smi', f'--query-gpu={q}', '--format=csv,noheader,nounits', '-i',
+                            str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+        t = [x.strip() for x in o.split(',')]
+        self.max_mhz = float(t[1])
+        return float(t[0]), [n for k, n in enumerate(self.NAMES) if t[2 + k] == 'Active']
+
+    def run(self):
         while not self.stop_flag:
             try:
-                o = subprocess.run(['nvidia-smi', f'--query-gpu={q}', '--format=csv,noheader,nounits', '-i',
-                                    str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if o:
-                    self.rows.append([t.strip() for t in o.split(',')])
+                if self.nvml is not None:
+                    mhz = float(self.nvml.nvmlDeviceGetClockInfo(self.handle, self.nvml.NVML_CLOCK_SM))
+                    bits = int(self.nvml.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+                    self.rows.append((mhz, [n for n, m in zip(self.NAMES, self.masks) if bits & m]))
+                else:
+                    self.rows.append(self._sample_smi())
             except Exception:  # noqa: BLE001
                 pass
-            time.sleep(0.1)
+            time.sleep(0.02 if self.nvml is not None else 0.1)
 
     def summary(self):
         if not self.rows:
-            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
-        sm = sorted(float(r[0]) for r in self.rows if r[0].replace('.', '').isdigit())
-        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
-        reasons = [n for k, n in enumerate(names) if any(len(r) > 2 + k and r[2 + k] == 'Active' for r in self.rows)]
-        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': float(self.rows[0][1]),
-                'reasons': reasons, 'samples': len(self.rows)}
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['clock sampling unavailable']}
+        sm = sorted(r[0] for r in self.rows)
+        reasons = sorted({n for r in self.rows for n in r[1]})
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': self.max_mhz, 'reasons': reasons, 'samples': len(self.rows),
+                'source': 'nvml' if self.nvml is not None else 'nvidia-smi'}
 
 
 def measured_peak():

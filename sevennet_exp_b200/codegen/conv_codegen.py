@@ -112,9 +112,12 @@ MIN_CTAS = {
     'c703e622066': (4, 3),      # SevenNet-l3i5 inner layers: 127 / 168 registers
 }
 MIN_CTAS_DEFAULT = (1, 1)
+# tabulated kernels: measured with tools/tune_occupancy.sh on B200 (profiles/r01e_occupancy_sweep.log): SevenNet-0
+# forward 1.090 -> 1.045 ms at 5 instead of 6; l3i5 backward 22.5 -> 18.6 ms at 4 instead of 2 (128 registers,
+# 64 B of spill; 4 CTAs is also what the 56.6 KB ring per CTA allows)
 MIN_CTAS_TAB = {
-    'c377d4386a8': (6, 5),
-    'c703e622066': (3, 2),
+    'c377d4386a8': (5, 5),
+    'c703e622066': (3, 4),
 }
 
 
