@@ -323,7 +323,7 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl != 'reference' else args.warmup
     if args.impl == 'reference':
         return run_reference(args)
-    if args.gpus > 1 or int(os.environ.get('WORLD_SIZE', '1')) > 1:
+    if args.gpus > 1 or int(os.environ.get('WORLD_SIZE', '1')) > 1 or args.workload == 'si1m':
         from sevennet_exp_b200 import bench_multi
         return bench_multi.run(args)
     run_single(args)

@@ -22,6 +22,8 @@ def run(args):
     dev = torch.device(f'cuda:{local}')
     torch.cuda.set_device(dev)
     if not dist.is_initialized():
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')          # plain `python bench.py --workload si1m` (N = 1)
+        os.environ.setdefault('MASTER_PORT', '29555')
         dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
     grid = brick_grid(world)
     strong = getattr(args, 'workload', 'cfg2') == 'si1m'
@@ -106,7 +108,33 @@ def run(args):
     if sampler:
         sampler.stop_flag = True
         sampler.join(timeout=2)
+    # per-stage device times of this rank (separate pass, every stage alone on its launch stream) -> roofline of the
+    # dominant kernel on rank 0's sub-domain, same conventions as the single-GPU line
+    stage, reps_prof = {}, 2
+    for _ in range(reps_prof):
+        flush.fill_(1.0)
+        calc.engine.prof = []
+        E, F, vir, g = step()
+        torch.cuda.synchronize()
+        for k, v in calc.engine.profile_summary().items():
+            stage[k] = stage.get(k, 0.0) + v / reps_prof
+    calc.engine.prof = None
+    dist.barrier()
     if rank == 0:
+        inner = calc.spec.layers[1].conv
+        n_inner = sum(1 for L in calc.spec.layers if L.conv.signature() == inner.signature())
+        tab = calc.engine.radial == 'table'
+        dom_ms = stage[f'conv_bwd_{inner.signature()}'] / n_inner
+        alg = B.conv_bwd_algorithmic_bytes(inner, dec.n_local, g.n_edges)
+        peak, how = B.measured_peak()
+        touched = alg - (g.n_edges * 8 * inner.wn if tab else 0)
+        roofline = {'bound': 'hbm', 'kernel': f'conv_bwd_{"tab_" if tab else ""}{inner.signature()} on rank 0 '
+                                              f'({dec.n_local} owned atoms, {g.n_edges} edges)',
+                    'achieved': alg / (dom_ms * 1e-3) / 1e9, 'peak': peak, 'peak_source': how, 'unit': 'GB/s',
+                    'frac': alg / (dom_ms * 1e-3) / 1e9 / peak, 'algorithmic_bytes': alg, 'ms': dom_ms, 'traffic': None,
+                    'elided': 'w and dW [E, wn] (tabulated radial weights)' if tab else None,
+                    'touched_bytes': touched, 'touched_frac': touched / (dom_ms * 1e-3) / 1e9 / peak}
+        stage_sorted = dict(sorted(((k, round(v, 4)) for k, v in stage.items()), key=lambda kv: -kv[1])[:12])
         x_dim = calc.spec.layers[1].conv.lx.dim
         line = {
             'metric': B.METRIC, 'value': n_total / (ms_step * 1e-3), 'unit': B.UNIT, 'n_gpus': world,
@@ -126,7 +154,7 @@ def run(args):
                     'h2d_bytes_per_step': int(pos_host.numel() * 8),
                     'd2h_bytes_per_step': int((7 + 3 * dec.n_local) * 8)},
             'gpu_launches': int(launches), 'clocks': sampler.summary() if sampler else None,
-            'roofline': None, 'cpu_baseline': None,
+            'roofline': roofline, 'stage_ms_rank0': stage_sorted, 'cpu_baseline': None,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
