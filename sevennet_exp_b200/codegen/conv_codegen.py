@@ -232,7 +232,7 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
         L.append(f'KERNEL_HEAD(conv_fwd_tab_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Yt,')
         L.append('    const float4* __restrict__ tab, const int* __restrict__ rowptr, const int* __restrict__ col,')
         L.append('    int n_dst, float inv_denom, float* __restrict__ out, int ldo)')
-        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec)})')
+        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec, False)})')
     else:
         L.append(f'KERNEL_HEAD(conv_fwd_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
         L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
@@ -283,7 +283,7 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
         L.append('    const float4* __restrict__ tab, const int* __restrict__ rowptr, const int* __restrict__ col,')
         L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
         L.append('    float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
-        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec)})')
+        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec, True)})')
     else:
         L.append(f'KERNEL_HEAD(conv_bwd_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
         L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
@@ -379,8 +379,19 @@ def _tab_w_floats(G: _Group) -> int:
     return len(G.paths) * 128
 
 
-def tab_ring_floats(spec: ConvSpec) -> int:
-    return max(TAB_XY_DEPTH * _tab_xy_floats(G, spec) + TAB_W_DEPTH * _tab_w_floats(G) for G in make_groups(spec))
+# Where the table rows of the next edge wait: 'smem' = cp.async into the ring (rows cross the L1 data pipe twice:
+# LDGSTS write + LDS read), 'regs' = 16-byte __ldg straight into registers one edge ahead (once).  (forward, backward)
+import os as _os
+TAB_T_MODE = tuple((_os.environ.get('SEVENN_TAB_T', 'smem,smem') + ',smem').split(',')[:2])
+
+
+def tab_t_regs(bwd: bool) -> bool:
+    return TAB_T_MODE[1 if bwd else 0] == 'regs'
+
+
+def tab_ring_floats(spec: ConvSpec, bwd: bool = False) -> int:
+    wd = 0 if tab_t_regs(bwd) else TAB_W_DEPTH
+    return max(TAB_XY_DEPTH * _tab_xy_floats(G, spec) + wd * _tab_w_floats(G) for G in make_groups(spec))
 
 
 def _tab_issue_xy(L, G: _Group, spec: ConvSpec, ind, e, j, slot):
@@ -410,31 +421,8 @@ def _tab_issue_w(L, G: _Group, spec: ConvSpec, ind, idx, slot):
     L.append(f'{ind}}}')
 
 
-def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
-    """Opens ``if (e0 < e1) { for (e) {`` with x*, y*, w* (and wd* = h dw/dr when ``bwd``) of edge e defined.
-    cp.async groups alternate  ... X(e+2) | T(e+1) | X(e+3) | T(e+2) ...  so that ``wait_group 1`` at the top of
-    iteration e leaves only the newest x/Y stage in flight."""
-    S = (spec.lmax_sh + 1) ** 2
-    S2 = S + 2
+def _tab_pipeline_smem(L, G: _Group, spec: ConvSpec, idx_of, xyf, wf, wbase):
     DX = TAB_XY_DEPTH
-    xyf, wf = _tab_xy_floats(G, spec), _tab_w_floats(G)
-    wbase = DX * xyf
-    idx_of = lambda e: f'F2I(LDG(Yt + (size_t)({e}) * {S2} + {S + 1}))'   # noqa: E731
-    L.append('    const int e0 = rowptr[row], e1 = rowptr[row + 1];')
-    L.append('    if (e0 < e1) {')
-    L.append('#ifdef SEVENN_EMU')
-    L.append('      for (int e = e0; e < e1; ++e) {')
-    L.append(f'        const float* xr = x + (size_t)col[e] * ldx + {G.xoff} + c32 + lane;')
-    L.append(f'        const float4* tr = tab + (size_t){idx_of("e")} * {spec.wn} + c32 + lane;')
-    L.append(f'        const float t = Yt[(size_t)e * {S2} + {S}];')
-    for m in range(G.d1):
-        L.append(f'        const float x{m} = {_on(G, f"xr[{m * G.mul}]")};')
-    for pi, p in G.paths:
-        z = 'float4{0.f, 0.f, 0.f, 0.f}'
-        L.append(f'        const float4 T{pi} = {_on(G, f"tr[{p.w_off}]", z)};')
-    for jj in G.ys:
-        L.append(f'        const float y{jj} = Yt[(size_t)e * {S2} + {jj}];')
-    L.append('#else')
     # prologue: X(e0), X(e0+1), T(e0), X(e0+2)
     for d in (0, 1):
         L.append(f'      if (e0 + {d} < e1) {{')
@@ -471,6 +459,74 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
     for q, (pi, p) in enumerate(G.paths):
         z = 'make_float4(0.f, 0.f, 0.f, 0.f)'
         L.append(f'        const float4 T{pi} = {_on(G, f"*reinterpret_cast<const float4*>(tw + {q * 128})", z)};')
+
+
+def _tab_pipeline_regs(L, G: _Group, spec: ConvSpec, idx_of, xyf):
+    """x_j / Y through the cp.async ring (3 edges ahead); the table rows of edge e+1 are fetched with 16-byte
+    read-only loads into registers while edge e is being processed (they come from L2, one edge of latency cover)."""
+    DX = TAB_XY_DEPTH
+    z = 'make_float4(0.f, 0.f, 0.f, 0.f)'
+    for d in range(DX - 1):
+        L.append(f'      if (e0 + {d} < e1) {{')
+        _tab_issue_xy(L, G, spec, '        ', f'e0 + {d}', f'col[e0 + {d}]', str(d))
+        L.append('      }')
+        L.append('      CP_ASYNC_COMMIT();')
+    L.append(f'      const float4* tr0 = tab + (size_t)({idx_of("e0")}) * {spec.wn} + c32 + lane;')
+    for pi, p in G.paths:
+        L.append(f'      float4 Tn{pi} = {_on(G, f"__ldg(tr0 + {p.w_off})", z)};')
+    L.append(f'      int jn = col[e0 + {DX - 1} < e1 ? e0 + {DX - 1} : e1 - 1];')
+    L.append(f'      int in = {idx_of("(e0 + 1 < e1 ? e0 + 1 : e1 - 1)")};')
+    L.append('      int slot = 0;')
+    L.append('      for (int e = e0; e < e1; ++e) {')
+    for pi, p in G.paths:
+        L.append(f'        const float4 T{pi} = Tn{pi};')
+    L.append(f'        {{ const float4* tr = tab + (size_t)(in) * {spec.wn} + c32 + lane;')
+    for pi, p in G.paths:
+        L.append(f'          Tn{pi} = {_on(G, f"__ldg(tr + {p.w_off})", z)};')
+    L.append('        }')
+    L.append(f'        CP_ASYNC_WAIT({DX - 2});')
+    L.append('        __syncwarp();')
+    L.append(f'        if (e + {DX - 1} < e1) {{')
+    _tab_issue_xy(L, G, spec, '          ', f'e + {DX - 1}', 'jn', f'(slot + {DX - 1}) & {DX - 1}')
+    L.append('        }')
+    L.append('        CP_ASYNC_COMMIT();')
+    L.append(f'        jn = col[e + {DX} < e1 ? e + {DX} : e1 - 1];')
+    L.append(f'        in = {idx_of("(e + 2 < e1 ? e + 2 : e1 - 1)")};')
+    L.append(f'        const float* sr = ring + slot * {xyf};')
+    L.append(f'        slot = (slot + 1) & {DX - 1};')
+    for m in range(G.d1):
+        L.append(f'        const float x{m} = {_on(G, f"sr[{m * 32} + lane]")};')
+
+
+def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
+    """Opens ``if (e0 < e1) { for (e) {`` with x*, y*, w* (and wd* = h dw/dr when ``bwd``) of edge e defined.
+    cp.async groups alternate  ... X(e+2) | T(e+1) | X(e+3) | T(e+2) ...  so that ``wait_group 1`` at the top of
+    iteration e leaves only the newest x/Y stage in flight."""
+    S = (spec.lmax_sh + 1) ** 2
+    S2 = S + 2
+    DX = TAB_XY_DEPTH
+    xyf, wf = _tab_xy_floats(G, spec), _tab_w_floats(G)
+    wbase = DX * xyf
+    idx_of = lambda e: f'F2I(LDG(Yt + (size_t)({e}) * {S2} + {S + 1}))'   # noqa: E731
+    L.append('    const int e0 = rowptr[row], e1 = rowptr[row + 1];')
+    L.append('    if (e0 < e1) {')
+    L.append('#ifdef SEVENN_EMU')
+    L.append('      for (int e = e0; e < e1; ++e) {')
+    L.append(f'        const float* xr = x + (size_t)col[e] * ldx + {G.xoff} + c32 + lane;')
+    L.append(f'        const float4* tr = tab + (size_t){idx_of("e")} * {spec.wn} + c32 + lane;')
+    L.append(f'        const float t = Yt[(size_t)e * {S2} + {S}];')
+    for m in range(G.d1):
+        L.append(f'        const float x{m} = {_on(G, f"xr[{m * G.mul}]")};')
+    for pi, p in G.paths:
+        z = 'float4{0.f, 0.f, 0.f, 0.f}'
+        L.append(f'        const float4 T{pi} = {_on(G, f"tr[{p.w_off}]", z)};')
+    for jj in G.ys:
+        L.append(f'        const float y{jj} = Yt[(size_t)e * {S2} + {jj}];')
+    L.append('#else')
+    if tab_t_regs(bwd):
+        _tab_pipeline_regs(L, G, spec, idx_of, xyf)
+    else:
+        _tab_pipeline_smem(L, G, spec, idx_of, xyf, wf, wbase)
     ybase = G.d1 * 32
     for jj in G.ys:
         L.append(f'        const float y{jj} = sr[{ybase + jj}];')
@@ -503,7 +559,7 @@ def generate(spec: ConvSpec) -> str:
     out += gen_bwd(spec, groups, sig) + ['']
     out += gen_fwd(spec, groups, sig, tab=True) + ['']
     out += gen_bwd(spec, groups, sig, tab=True) + ['']
-    rf = tab_ring_floats(spec)
+    rf, rb = tab_ring_floats(spec, False), tab_ring_floats(spec, True)
     out.append(f'extern "C" int sevenn_conv_fwd_tab_{sig}(const float* x, int ldx, const float* Yt, const float* tab,')
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, float* out, int ldo, void* stream) {')
     out.append('  if (n_dst <= 0) return 0;')
@@ -514,7 +570,7 @@ def generate(spec: ConvSpec) -> str:
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, const float* gout, int ldo,')
     out.append('    float* dxe, int lddx, float* dY, long long dy_stride, void* stream) {')
     out.append('  if (n_dst <= 0) return 0;')
-    out.append(f'  LAUNCH_DYN(conv_bwd_tab_{sig}, n_dst, {nu}, {rf}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, gout, ldo, dxe, lddx, dY, dy_stride);')
+    out.append(f'  LAUNCH_DYN(conv_bwd_tab_{sig}, n_dst, {nu}, {rb}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, gout, ldo, dxe, lddx, dY, dy_stride);')
     out.append('  return LAUNCH_STATUS();')
     out.append('}')
     out.append(f'extern "C" int sevenn_conv_fwd_{sig}(const float* x, int ldx, const float* Y, const float* w,')
