@@ -116,7 +116,7 @@ MIN_CTAS_DEFAULT = (1, 1)
 # forward 1.090 -> 1.045 ms at 5 instead of 6; l3i5 backward 22.5 -> 18.6 ms at 4 instead of 2 (128 registers,
 # 64 B of spill; 4 CTAs is also what the 56.6 KB ring per CTA allows)
 MIN_CTAS_TAB = {
-    'c377d4386a8': (5, 5),
+    'c377d4386a8': (5, 4),      # with the table rows prefetched into registers (TAB_T_MODE below)
     'c703e622066': (3, 4),
 }
 
@@ -381,12 +381,21 @@ def _tab_w_floats(G: _Group) -> int:
 
 # Where the table rows of the next edge wait: 'smem' = cp.async into the ring (rows cross the L1 data pipe twice:
 # LDGSTS write + LDS read), 'regs' = 16-byte __ldg straight into registers one edge ahead (once).  (forward, backward)
+# by signature; measured with tools/tune_tabmode.sh on B200 (profiles/r01e_table_staging_sweep.log): SevenNet-0 inner
+# forward 1.042 -> 0.804 ms, backward 1.914 -> 1.864 ms; l3i5 inner forward 8.22 -> 7.97 ms, backward slower in
+# registers (18.6 -> 19.2 ms: 128 registers are already spilling there), first / last layers 5-25 % faster both ways.
 import os as _os
-TAB_T_MODE = tuple((_os.environ.get('SEVENN_TAB_T', 'smem,smem') + ',smem').split(',')[:2])
+TAB_T_DEFAULT = ('regs', 'regs')
+TAB_T_MODE = {
+    'c703e622066': ('regs', 'smem'),
+}
+_TAB_T_ENV = _os.environ.get('SEVENN_TAB_T')          # tuning runs: 'fwd,bwd' for every signature
+_cur_sig = [None]
 
 
 def tab_t_regs(bwd: bool) -> bool:
-    return TAB_T_MODE[1 if bwd else 0] == 'regs'
+    mode = tuple(_TAB_T_ENV.split(',')) if _TAB_T_ENV else TAB_T_MODE.get(_cur_sig[0], TAB_T_DEFAULT)
+    return mode[1 if bwd else 0] == 'regs'
 
 
 def tab_ring_floats(spec: ConvSpec, bwd: bool = False) -> int:
@@ -549,6 +558,7 @@ def signature(spec: ConvSpec) -> str:
 
 def generate(spec: ConvSpec) -> str:
     sig = signature(spec)
+    _cur_sig[0] = sig
     groups = make_groups(spec)
     nu = sum(G.nchunk for G in groups)
     out = ['// GENERATED by sevennet_exp_b200/codegen/conv_codegen.py -- do not edit.',
