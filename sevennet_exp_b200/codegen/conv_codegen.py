@@ -310,33 +310,39 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append('        float gr = 0.f;')
         else:
             L.append(f'        float* dwr = dW + (size_t)e * {spec.wn} + c32 + lane;')
+        touched = set()
         for pi, p in G.paths:
+            # With m_k = sum_i M_ik x_i (the forward message / w) and g_k the output gradient:
+            #   q_i   = sum_k M_ik g_k          dx_i += w q_i          dE/dw = sum_i x_i q_i  (= sum_k g_k m_k)
+            #   dE/dY_j += sum_{ik} c_ijk (w x_i) g_k
+            # i.e. 2 nnz(M) + 3 d1 + nnz(C) operations per path instead of 3 nnz(M) + 2 (2 l3 + 1) + nnz(C).
             ent, nnz = _m_terms(p.l1, p.l2, p.l3)
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}')
             _emit_M(L, ent, p.l2, '          ')
-            L.append('          float ' + ', '.join(f'P_{i}_{k} = 0.f' for (i, k) in ent) + ';')
-            dw_terms = []
-            for k in range(2 * p.l3 + 1):
-                terms = [f'M_{i}_{k}*x{i}' for i in range(G.d1) if (i, k) in ent]
-                if terms:
-                    dw_terms.append(f'g{pi}_{k}*({" + ".join(terms)})')
+            rows = [i for i in range(G.d1) if any((i, k) in ent for k in range(2 * p.l3 + 1))]
+            for i in rows:
+                terms = [f'M_{i}_{k}*g{pi}_{k}' for k in range(2 * p.l3 + 1) if (i, k) in ent]
+                L.append(f'          const float q{i} = {" + ".join(terms)};')
+                L.append(f'          dx{i} = fmaf(w{pi}, q{i}, dx{i});')
+            dw = ' + '.join(f'x{i}*q{i}' for i in rows) if rows else '0.f'
             if tab:
-                if dw_terms:
-                    L.append(f'          gr = fmaf({" + ".join(dw_terms)}, wd{pi}, gr);')
+                if rows:
+                    L.append(f'          gr = fmaf({dw}, wd{pi}, gr);')
             else:
-                st = f'dwr[{p.w_off}] = {" + ".join(dw_terms) if dw_terms else "0.f"};'
+                st = f'dwr[{p.w_off}] = {dw};'
                 L.append(f'          if (on) {st}' if G.masked else f'          {st}')
-            for k in range(2 * p.l3 + 1):
-                idx = [i for i in range(G.d1) if (i, k) in ent]
-                if not idx:
-                    continue
-                L.append(f'          {{ const float wg = w{pi} * g{pi}_{k};')
-                for i in idx:
-                    L.append(f'            dx{i} = fmaf(M_{i}_{k}, wg, dx{i}); P_{i}_{k} = fmaf(wg, x{i}, P_{i}_{k});')
-                L.append('          }')
+            for i in rows:
+                L.append(f'          const float X{i} = w{pi} * x{i};')
+            for (i, k) in ent:
+                L.append(f'          const float P_{i}_{k} = X{i} * g{pi}_{k};')
             for (i, j, k, cf) in nnz:
                 q = p.l2 * p.l2 + j
-                L.append(f'          dyv[{q}] = fmaf({_f(cf)}, P_{i}_{k}, dyv[{q}]);')
+                if q not in touched:
+                    touched.add(q)
+                    L.append(f'          dyv[{q}] = P_{i}_{k};' if abs(cf - 1.0) < 1e-12 else
+                             f'          dyv[{q}] = {_f(cf)} * P_{i}_{k};')
+                else:
+                    L.append(f'          dyv[{q}] = fmaf({_f(cf)}, P_{i}_{k}, dyv[{q}]);')
             L.append('        }')
         L.append(f'        float* dxr = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
         for m in range(G.d1):
