@@ -250,10 +250,21 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             ent, _ = _m_terms(p.l1, p.l2, p.l3)
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}, mul {p.mul}')
             _emit_M(L, ent, p.l2, '          ')
-            for k in range(2 * p.l3 + 1):
-                terms = [f'M_{i}_{k}*x{i}' for i in range(G.d1) if (i, k) in ent]
-                if terms:
-                    L.append(f'          a{pi}_{k} = fmaf(w{pi}, {" + ".join(terms)}, a{pi}_{k});')
+            rows = [i for i in range(G.d1) if any((i, k) in ent for k in range(2 * p.l3 + 1))]
+            if 2 * p.l3 + 1 > len(rows):
+                # fewer input than output components: scale the inputs once (nnz(M) + d1 operations) ...
+                for i in rows:
+                    L.append(f'          const float X{i} = w{pi} * x{i};')
+                for k in range(2 * p.l3 + 1):
+                    for i in range(G.d1):
+                        if (i, k) in ent:
+                            L.append(f'          a{pi}_{k} = fmaf(M_{i}_{k}, X{i}, a{pi}_{k});')
+            else:
+                # ... otherwise scale the outputs (nnz(M) + 2 l3 + 1 operations)
+                for k in range(2 * p.l3 + 1):
+                    terms = [f'M_{i}_{k}*x{i}' for i in range(G.d1) if (i, k) in ent]
+                    if terms:
+                        L.append(f'          a{pi}_{k} = fmaf(w{pi}, {" + ".join(terms)}, a{pi}_{k});')
             L.append('        }')
         L.append('      }')   # for e
         L.append('    }')     # if e0 < e1
