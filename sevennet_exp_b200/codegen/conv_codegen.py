@@ -287,6 +287,9 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
     while NP < S:
         NP *= 2
     gr_in_butterfly = tab and NP > S
+    nv_smem = dy_smem_values(spec) if tab else 0
+    if nv_smem:
+        gr_in_butterfly = nv_smem > S          # here: "the radial term goes through the same reduction"
     L = []
     mc = (MIN_CTAS_TAB if tab else MIN_CTAS).get(sig, MIN_CTAS_DEFAULT)[1]
     if tab:
@@ -302,6 +305,8 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
         L.append('    float* __restrict__ dW, float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
         L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
     L.append('  float* dYu = dY + (size_t)unit * (size_t)dy_stride;')
+    if nv_smem:
+        L.append(f'  sevenn_dy_scratch_init<{nv_smem}>(ring + {tab_data_floats(spec, True)}, lane);')
     for gi, G in enumerate(groups):
         _unit_open(L, G, gi == 0, gi == len(groups) - 1)
         L.append('    const float* grow = gout + (size_t)row * ldo + c32 + lane;')
@@ -315,7 +320,8 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             _tab_pipeline_open(L, G, spec, True)
         else:
             _pipeline_open(L, G, spec)
-        L.append(f'        float dyv[{NP}] = {{{", ".join(["0.f"] * NP)}}};')
+        ndy = max(NP, nv_smem)
+        L.append(f'        float dyv[{ndy}] = {{{", ".join(["0.f"] * ndy)}}};')
         L.append('        float ' + ', '.join(f'dx{m} = 0.f' for m in range(G.d1)) + ';')
         if tab:
             L.append('        float gr = 0.f;')
@@ -361,7 +367,10 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append(f'        if (on) {st}' if G.masked else f'        {st}')
         if gr_in_butterfly:
             L.append(f'        dyv[{S}] = gr;')
-        L.append(f'        sevenn_dy_accumulate<{NP}>(dyv, lane, dYu + (size_t)e * {SD}, {SD if gr_in_butterfly else S});')
+        if nv_smem:
+            L.append(f'        sevenn_dy_accumulate_smem<{nv_smem}>(dyv, lane, ring + {tab_data_floats(spec, True)}, dYu + (size_t)e * {SD});')
+        else:
+            L.append(f'        sevenn_dy_accumulate<{NP}>(dyv, lane, dYu + (size_t)e * {SD}, {SD if gr_in_butterfly else S});')
         if tab and not gr_in_butterfly:
             L.append(f'        sevenn_gr_accumulate(gr, lane, dYu + (size_t)e * {SD} + {S});')
         L.append('      }')
@@ -415,9 +424,24 @@ def tab_t_regs(bwd: bool) -> bool:
     return mode[1 if bwd else 0] == 'regs'
 
 
-def tab_ring_floats(spec: ConvSpec, bwd: bool = False) -> int:
+DY_SMEM = _os.environ.get('SEVENN_DY_SMEM', '1') == '1'     # dY lane reduction through shared memory (tab backward)
+
+
+def dy_smem_values(spec: ConvSpec) -> int:
+    """Values per edge that go through the shared-memory reduction of the tabulated backward (0 = butterfly)."""
+    S = (spec.lmax_sh + 1) ** 2
+    nv = S + 1 if 32 // (S + 1) >= 2 else S      # the radial term rides along when it fits
+    return nv if DY_SMEM and 32 // nv >= 2 else 0
+
+
+def tab_data_floats(spec: ConvSpec, bwd: bool) -> int:
     wd = 0 if tab_t_regs(bwd) else TAB_W_DEPTH
     return max(TAB_XY_DEPTH * _tab_xy_floats(G, spec) + wd * _tab_w_floats(G) for G in make_groups(spec))
+
+
+def tab_ring_floats(spec: ConvSpec, bwd: bool = False) -> int:
+    scratch = (dy_smem_values(spec) * 33 + 3) // 4 * 4 if bwd else 0
+    return tab_data_floats(spec, bwd) + scratch
 
 
 def _tab_issue_xy(L, G: _Group, spec: ConvSpec, ind, e, j, slot):

@@ -48,6 +48,39 @@ __device__ __forceinline__ void sevenn_dy_accumulate(float (&v)[NP], int lane, f
   const int q = lane >> SH;
   if ((lane & ((1 << SH) - 1)) == 0 && q < S) dst[q] += s;
 }
+// Same reduction through shared memory (fewer issue slots than the butterfly: NV stores + 32 / PARTS loads and adds +
+// PARTS - 1 shuffles instead of 4 (NP - 1) select / shuffle / add instructions).  Every lane stores its NV partials into
+// a [NV][33] scratch (lane-major rows: conflict free); PARTS = min(32 / NV, 4) adjacent lanes share one value index and add up
+// PER consecutive lanes' entries each (bank = q + part * PER + t: conflict free for PARTS in {2, 3, 4}); column 32 of
+// every row is zero (sevenn_dy_scratch_init) so the last part may read one slot past lane 31.  Fixed order of
+// additions; the caller's __syncwarp() at the top of the edge loop orders these reads before the next edge's stores.
+template <int NV>
+__device__ __forceinline__ void sevenn_dy_scratch_init(float* scratch, int lane) {
+  if (lane < NV) scratch[lane * 33 + 32] = 0.f;
+  __syncwarp();
+}
+template <int NV>
+__device__ __forceinline__ void sevenn_dy_accumulate_smem(const float* v, int lane, float* scratch, float* dst) {
+  constexpr int PARTS = (32 / NV) < 4 ? (32 / NV) : 4;
+  constexpr int PER = (32 + PARTS - 1) / PARTS;
+  static_assert(PARTS >= 2 && PARTS * PER <= 33, "value count not supported by the shared-memory reduction");
+#pragma unroll
+  for (int q = 0; q < NV; ++q) scratch[q * 33 + lane] = v[q];
+  __syncwarp();
+  const int q = lane / PARTS, part = lane - q * PARTS;
+  float s = 0.f;
+  if (q < NV) {
+    const float* colp = scratch + q * 33 + part * PER;
+#pragma unroll
+    for (int t = 0; t < PER; ++t) s += colp[t];
+  }
+#pragma unroll
+  for (int o = 1; o < PARTS; ++o) {
+    const float other = __shfl_down_sync(0xffffffffu, s, o);
+    s += other;                 // only part 0 keeps a meaningful sum: s0 + s1 (+ s2 (+ s3)), always in this order
+  }
+  if (part == 0 && q < NV) dst[q] += s;
+}
 // radial term of the tabulated kernels: warp sum of the lane partials, added to one word owned by this warp
 __device__ __forceinline__ void sevenn_gr_accumulate(float v, int lane, float* dst) {
 #pragma unroll
@@ -70,7 +103,7 @@ __device__ __forceinline__ void sevenn_gr_accumulate(float v, int lane, float* d
 #else
 #define KERNEL_HEAD(name, minctas) static void name
 #define UNIT_LOOP_BEGIN(n, nunits, ringf) { for (int unit = 0; unit < (nunits); ++unit) for (int row = 0; row < (n); ++row) \
-    for (int lane = 0; lane < 32; ++lane) {
+    for (int lane = 0; lane < 32; ++lane) { float* ring = nullptr; (void)ring;
 #define UNIT_LOOP_END }}
 #define LDG(p) (*(p))
 #include <cstring>
@@ -81,6 +114,12 @@ static inline void sevenn_dy_accumulate(float (&v)[NP], int lane, float* dst, in
   for (int q = 0; q < S; ++q) dst[q] += v[q];
 }
 static inline void sevenn_gr_accumulate(float v, int lane, float* dst) { (void)lane; *dst += v; }
+template <int NV> static inline void sevenn_dy_scratch_init(float*, int) {}
+template <int NV>
+static inline void sevenn_dy_accumulate_smem(const float* v, int lane, float*, float* dst) {
+  (void)lane;
+  for (int q = 0; q < NV; ++q) dst[q] += v[q];
+}
 struct float4 { float x, y, z, w; };
 #define UNIT_LOOP_BEGIN_DYN(n, nunits, ringf) UNIT_LOOP_BEGIN(n, nunits, ringf)
 #define LAUNCH_DYN(kern, n, nunits, ringf, stream) kern

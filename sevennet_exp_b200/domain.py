@@ -119,6 +119,14 @@ class Halo:
     def _exchange(self, send_buf, send_counts, send_off, recv_buf, recv_counts, recv_off):
         """rows send_buf[send_off[p] : +send_counts[p]] -> peer p ; recv_buf[recv_off[p] : ...] <- peer p."""
         me = self.rank
+        if self.world > 1 and send_buf.is_cuda:
+            # NCCL: ONE all-to-all-v per exchange (rows are already grouped by peer on both sides), instead of a
+            # batch of 2 (world - 1) point-to-point operations: the host cost per exchange drops several-fold, and at
+            # ~5 ms per step with nine exchanges the host, not the link, is what the small-brick case waits for
+            ns, nr = int(send_off[-1]), int(recv_off[-1])
+            dist.all_to_all_single(recv_buf[:nr], send_buf[:ns], [int(c) for c in recv_counts],
+                                   [int(c) for c in send_counts], group=self.group)
+            return
         if send_counts[me]:
             recv_buf[recv_off[me]:recv_off[me] + recv_counts[me]].copy_(
                 send_buf[send_off[me]:send_off[me] + send_counts[me]])
