@@ -424,7 +424,10 @@ def tab_t_regs(bwd: bool) -> bool:
     return mode[1 if bwd else 0] == 'regs'
 
 
-DY_SMEM = _os.environ.get('SEVENN_DY_SMEM', '1') == '1'     # dY lane reduction through shared memory (tab backward)
+# dY lane reduction through shared memory instead of the shuffle butterfly (tabulated backward).  Fewer instructions
+# on paper (37 against 68 per edge and unit) but measured SLOWER on B200 (SevenNet-0 inner backward 1.68 -> 1.78 ms:
+# the store -> __syncwarp -> load round trip sits on the critical path of every edge); kept as an option, off.
+DY_SMEM = _os.environ.get('SEVENN_DY_SMEM', '0') == '1'
 
 
 def dy_smem_values(spec: ConvSpec) -> int:

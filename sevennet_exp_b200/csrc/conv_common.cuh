@@ -74,12 +74,10 @@ __device__ __forceinline__ void sevenn_dy_accumulate_smem(const float* v, int la
 #pragma unroll
     for (int t = 0; t < PER; ++t) s += colp[t];
   }
+  float tot = s;
 #pragma unroll
-  for (int o = 1; o < PARTS; ++o) {
-    const float other = __shfl_down_sync(0xffffffffu, s, o);
-    s += other;                 // only part 0 keeps a meaningful sum: s0 + s1 (+ s2 (+ s3)), always in this order
-  }
-  if (part == 0 && q < NV) dst[q] += s;
+  for (int o = 1; o < PARTS; ++o) tot += __shfl_down_sync(0xffffffffu, s, o);   // s0 + s1 (+ s2 (+ s3)) on part 0
+  if (part == 0 && q < NV) dst[q] += tot;
 }
 // radial term of the tabulated kernels: warp sum of the lane partials, added to one word owned by this warp
 __device__ __forceinline__ void sevenn_gr_accumulate(float v, int lane, float* dst) {
