@@ -252,7 +252,7 @@ def run_single(args):
     fwd_ach = conv_fwd_algorithmic_bytes(inner, n, E) / (stage[key_f] / n_inner * 1e-3) / 1e9
     stage_sorted = dict(sorted(((k, round(v, 4)) for k, v in stage.items()), key=lambda kv: -kv[1]))
 
-    if cfg3:
+    if cfg3 or os.environ.get('SEVENN_BENCH_NO_CPU'):      # tuning runs (tools/gpu_ab.sh) skip the CPU oracle leg
         cpu_v = None
     else:
         cpu_v, cpu_t, cores, cn, ce = cpu_oracle_sample((3, 3, 3), 1, 0)

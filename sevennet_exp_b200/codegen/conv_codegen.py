@@ -62,22 +62,38 @@ class _Group:
         self.xoff = spec.lx.group_off[g]
         self.paths = [(pi, p) for pi, p in enumerate(spec.paths) if p.gx == g]
         self.unit0 = unit0
+        self.cpw = 1                      # 32-channel chunks handled by one warp (tabulated kernels: see make_groups)
         self.used_l2 = sorted({p.l2 for _, p in self.paths})
         self.ys = [jj for l2 in self.used_l2 for jj in range(l2 * l2, (l2 + 1) ** 2)]
 
 
-def make_groups(spec: ConvSpec) -> List[_Group]:
+# Tabulated kernels: a warp of a scalar (l1 = 0) group takes TWO 32-channel chunks.  Those units are light (one input
+# component, 2 l + 1 trivial M entries per path) and the kernel's register budget is set by the heavy l1 >= 1 units, so
+# the second chunk is free in registers, while everything that does not depend on the channel -- Hermite basis, Y loads,
+# source-index / table-index loads, loop control and above all the per-edge dY lane reduction -- is paid once per pair.
+import os as _os0
+TAB_CPW = int(_os0.environ.get('SEVENN_TAB_CPW', '2'))
+
+
+def make_groups(spec: ConvSpec, tab: bool = False) -> List[_Group]:
     out, u = [], 0
     for g in range(len(spec.lx.groups)):
         G = _Group(spec, g, u)
         if G.paths:
+            if tab and TAB_CPW == 2 and G.l1 == 0 and not G.masked and G.nchunk % 2 == 0:
+                G.cpw = 2
             out.append(G)
-            u += G.nchunk
+            u += G.nchunk // G.cpw
     return out
 
 
-def n_units(spec: ConvSpec) -> int:
-    return sum(G.nchunk for G in make_groups(spec))
+def n_units(spec: ConvSpec, tab: bool = False) -> int:
+    return sum(G.nchunk // G.cpw for G in make_groups(spec, tab))
+
+
+def _sx(G: _Group, c: int) -> str:
+    """Suffix of the per-channel variables of chunk c of a warp."""
+    return '' if G.cpw == 1 else '_' + 'ab'[c]
 
 
 def _m_terms(l1, l2, l3):
@@ -211,7 +227,7 @@ def _pipeline_open(L, G: _Group, spec: ConvSpec):
 
 
 def _unit_open(L, G: _Group, first: bool, last: bool):
-    cond = f'unit < {G.unit0 + G.nchunk}'
+    cond = f'unit < {G.unit0 + G.nchunk // G.cpw}'
     if first and last:
         L.append('  {')
     elif first:
@@ -220,7 +236,7 @@ def _unit_open(L, G: _Group, first: bool, last: bool):
         L.append('  else {')
     else:
         L.append(f'  else if ({cond}) {{')
-    L.append(f'    const int c32 = (unit - {G.unit0}) * 32;')
+    L.append(f'    const int c32 = (unit - {G.unit0}) * {32 * G.cpw};')
     if G.masked:
         L.append(f'    const bool on = (c32 + lane) < {G.mul};')
 
@@ -232,7 +248,7 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
         L.append(f'KERNEL_HEAD(conv_fwd_tab_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Yt,')
         L.append('    const float4* __restrict__ tab, const int* __restrict__ rowptr, const int* __restrict__ col,')
         L.append('    int n_dst, float inv_denom, float* __restrict__ out, int ldo)')
-        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec, False)})')
+        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk // G.cpw for G in groups)}, {tab_ring_floats(spec, False)})')
     else:
         L.append(f'KERNEL_HEAD(conv_fwd_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
         L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
@@ -241,7 +257,8 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
     for gi, G in enumerate(groups):
         _unit_open(L, G, gi == 0, gi == len(groups) - 1)
         for pi, p in G.paths:
-            L.append('    float ' + ', '.join(f'a{pi}_{k} = 0.f' for k in range(2 * p.l3 + 1)) + ';')
+            for c in range(G.cpw):
+                L.append('    float ' + ', '.join(f'a{pi}_{k}{_sx(G, c)} = 0.f' for k in range(2 * p.l3 + 1)) + ';')
         if tab:
             _tab_pipeline_open(L, G, spec, False)
         else:
@@ -251,20 +268,22 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}, mul {p.mul}')
             _emit_M(L, ent, p.l2, '          ')
             rows = [i for i in range(G.d1) if any((i, k) in ent for k in range(2 * p.l3 + 1))]
-            if 2 * p.l3 + 1 > len(rows):
-                # fewer input than output components: scale the inputs once (nnz(M) + d1 operations) ...
-                for i in rows:
-                    L.append(f'          const float X{i} = w{pi} * x{i};')
-                for k in range(2 * p.l3 + 1):
-                    for i in range(G.d1):
-                        if (i, k) in ent:
-                            L.append(f'          a{pi}_{k} = fmaf(M_{i}_{k}, X{i}, a{pi}_{k});')
-            else:
-                # ... otherwise scale the outputs (nnz(M) + 2 l3 + 1 operations)
-                for k in range(2 * p.l3 + 1):
-                    terms = [f'M_{i}_{k}*x{i}' for i in range(G.d1) if (i, k) in ent]
-                    if terms:
-                        L.append(f'          a{pi}_{k} = fmaf(w{pi}, {" + ".join(terms)}, a{pi}_{k});')
+            for c in range(G.cpw):
+                sx = _sx(G, c)
+                if 2 * p.l3 + 1 > len(rows):
+                    # fewer input than output components: scale the inputs once (nnz(M) + d1 operations) ...
+                    for i in rows:
+                        L.append(f'          const float X{i}{sx} = w{pi}{sx} * x{i}{sx};')
+                    for k in range(2 * p.l3 + 1):
+                        for i in range(G.d1):
+                            if (i, k) in ent:
+                                L.append(f'          a{pi}_{k}{sx} = fmaf(M_{i}_{k}, X{i}{sx}, a{pi}_{k}{sx});')
+                else:
+                    # ... otherwise scale the outputs (nnz(M) + 2 l3 + 1 operations)
+                    for k in range(2 * p.l3 + 1):
+                        terms = [f'M_{i}_{k}*x{i}{sx}' for i in range(G.d1) if (i, k) in ent]
+                        if terms:
+                            L.append(f'          a{pi}_{k}{sx} = fmaf(w{pi}{sx}, {" + ".join(terms)}, a{pi}_{k}{sx});')
             L.append('        }')
         L.append('      }')   # for e
         L.append('    }')     # if e0 < e1
@@ -273,8 +292,9 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             Mg = spec.lmid.groups[p.gm][0]
             base = spec.lmid.group_off[p.gm] + p.u_off
             for k in range(2 * p.l3 + 1):
-                st = f'orow[{base + k * Mg}] = a{pi}_{k} * inv_denom;'
-                L.append(f'    if (on) {st}' if G.masked else f'    {st}')
+                for c in range(G.cpw):
+                    st = f'orow[{base + k * Mg + c * 32}] = a{pi}_{k}{_sx(G, c)} * inv_denom;'
+                    L.append(f'    if (on) {st}' if G.masked else f'    {st}')
         L.append('  }')
     L.append('UNIT_LOOP_END')
     return L
@@ -297,7 +317,7 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
         L.append('    const float4* __restrict__ tab, const int* __restrict__ rowptr, const int* __restrict__ col,')
         L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
         L.append('    float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
-        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk for G in groups)}, {tab_ring_floats(spec, True)})')
+        L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk // G.cpw for G in groups)}, {tab_ring_floats(spec, True)})')
     else:
         L.append(f'KERNEL_HEAD(conv_bwd_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Y,')
         L.append('    const float* __restrict__ w, const int* __restrict__ rowptr, const int* __restrict__ col,')
@@ -314,15 +334,16 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             Mg = spec.lmid.groups[p.gm][0]
             base = spec.lmid.group_off[p.gm] + p.u_off
             for k in range(2 * p.l3 + 1):
-                ld = _on(G, f'LDG(grow + {base + k * Mg}) * inv_denom')
-                L.append(f'    const float g{pi}_{k} = {ld};')
+                for c in range(G.cpw):
+                    ld = _on(G, f'LDG(grow + {base + k * Mg + c * 32}) * inv_denom')
+                    L.append(f'    const float g{pi}_{k}{_sx(G, c)} = {ld};')
         if tab:
             _tab_pipeline_open(L, G, spec, True)
         else:
             _pipeline_open(L, G, spec)
         ndy = max(NP, nv_smem)
         L.append(f'        float dyv[{ndy}] = {{{", ".join(["0.f"] * ndy)}}};')
-        L.append('        float ' + ', '.join(f'dx{m} = 0.f' for m in range(G.d1)) + ';')
+        L.append('        float ' + ', '.join(f'dx{m}{_sx(G, c)} = 0.f' for m in range(G.d1) for c in range(G.cpw)) + ';')
         if tab:
             L.append('        float gr = 0.f;')
         else:
@@ -337,21 +358,25 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}')
             _emit_M(L, ent, p.l2, '          ')
             rows = [i for i in range(G.d1) if any((i, k) in ent for k in range(2 * p.l3 + 1))]
-            for i in rows:
-                terms = [f'M_{i}_{k}*g{pi}_{k}' for k in range(2 * p.l3 + 1) if (i, k) in ent]
-                L.append(f'          const float q{i} = {" + ".join(terms)};')
-                L.append(f'          dx{i} = fmaf(w{pi}, q{i}, dx{i});')
-            dw = ' + '.join(f'x{i}*q{i}' for i in rows) if rows else '0.f'
-            if tab:
-                if rows:
-                    L.append(f'          gr = fmaf({dw}, wd{pi}, gr);')
-            else:
-                st = f'dwr[{p.w_off}] = {dw};'
-                L.append(f'          if (on) {st}' if G.masked else f'          {st}')
-            for i in rows:
-                L.append(f'          const float X{i} = w{pi} * x{i};')
+            for c in range(G.cpw):
+                sx = _sx(G, c)
+                for i in rows:
+                    terms = [f'M_{i}_{k}*g{pi}_{k}{sx}' for k in range(2 * p.l3 + 1) if (i, k) in ent]
+                    L.append(f'          const float q{i}{sx} = {" + ".join(terms)};')
+                    L.append(f'          dx{i}{sx} = fmaf(w{pi}{sx}, q{i}{sx}, dx{i}{sx});')
+                dw = ' + '.join(f'x{i}{sx}*q{i}{sx}' for i in rows) if rows else '0.f'
+                if tab:
+                    if rows:
+                        L.append(f'          gr = fmaf({dw}, wd{pi}{sx}, gr);')
+                else:
+                    st = f'dwr[{p.w_off}] = {dw};'
+                    L.append(f'          if (on) {st}' if G.masked else f'          {st}')
+                for i in rows:
+                    L.append(f'          const float X{i}{sx} = w{pi}{sx} * x{i}{sx};')
+            # the two chunks of a warp share c_ijk: their products are added before the coefficient is applied
             for (i, k) in ent:
-                L.append(f'          const float P_{i}_{k} = X{i} * g{pi}_{k};')
+                L.append(f'          const float P_{i}_{k} = ' +
+                         ' + '.join(f'X{i}{_sx(G, c)} * g{pi}_{k}{_sx(G, c)}' for c in range(G.cpw)) + ';')
             for (i, j, k, cf) in nnz:
                 q = p.l2 * p.l2 + j
                 if q not in touched:
@@ -363,8 +388,9 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append('        }')
         L.append(f'        float* dxr = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
         for m in range(G.d1):
-            st = f'dxr[{m * G.mul}] = dx{m};'
-            L.append(f'        if (on) {st}' if G.masked else f'        {st}')
+            for c in range(G.cpw):
+                st = f'dxr[{m * G.mul + c * 32}] = dx{m}{_sx(G, c)};'
+                L.append(f'        if (on) {st}' if G.masked else f'        {st}')
         if gr_in_butterfly:
             L.append(f'        dyv[{S}] = gr;')
         if nv_smem:
@@ -398,11 +424,11 @@ def _tab_ypad(spec: ConvSpec) -> int:
 
 
 def _tab_xy_floats(G: _Group, spec: ConvSpec) -> int:
-    return G.d1 * 32 + _tab_ypad(spec)
+    return G.d1 * 32 * G.cpw + _tab_ypad(spec)
 
 
 def _tab_w_floats(G: _Group) -> int:
-    return len(G.paths) * 128
+    return len(G.paths) * 128 * G.cpw
 
 
 # Where the table rows of the next edge wait: 'smem' = cp.async into the ring (rows cross the L1 data pipe twice:
@@ -439,7 +465,7 @@ def dy_smem_values(spec: ConvSpec) -> int:
 
 def tab_data_floats(spec: ConvSpec, bwd: bool) -> int:
     wd = 0 if tab_t_regs(bwd) else TAB_W_DEPTH
-    return max(TAB_XY_DEPTH * _tab_xy_floats(G, spec) + wd * _tab_w_floats(G) for G in make_groups(spec))
+    return max(TAB_XY_DEPTH * _tab_xy_floats(G, spec) + wd * _tab_w_floats(G) for G in make_groups(spec, tab=True))
 
 
 def tab_ring_floats(spec: ConvSpec, bwd: bool = False) -> int:
@@ -454,10 +480,11 @@ def _tab_issue_xy(L, G: _Group, spec: ConvSpec, ind, e, j, slot):
     if G.masked:
         L.append(f'{ind}  if (on) {{')
     for m in range(G.d1):
-        L.append(f'{ind}  CP_ASYNC4(sd + {m * 32}, xr + {m * G.mul});')
+        for c in range(G.cpw):
+            L.append(f'{ind}  CP_ASYNC4(sd + {(m * G.cpw + c) * 32}, xr + {m * G.mul + c * 32});')
     if G.masked:
         L.append(f'{ind}  }}')
-    L.append(f'{ind}  if (lane < {S + 1}) CP_ASYNC4(sd + {G.d1 * 32}, Yt + (size_t)({e}) * {S + 2} + lane);')
+    L.append(f'{ind}  if (lane < {S + 1}) CP_ASYNC4(sd + {G.d1 * 32 * G.cpw}, Yt + (size_t)({e}) * {S + 2} + lane);')
     L.append(f'{ind}}}')
 
 
@@ -468,7 +495,8 @@ def _tab_issue_w(L, G: _Group, spec: ConvSpec, ind, idx, slot):
     if G.masked:
         L.append(f'{ind}  if (on) {{')
     for q, (pi, p) in enumerate(G.paths):
-        L.append(f'{ind}  CP_ASYNC16(sd + {q * 128}, tr + {p.w_off});')
+        for c in range(G.cpw):
+            L.append(f'{ind}  CP_ASYNC16(sd + {(q * G.cpw + c) * 128}, tr + {p.w_off + c * 32});')
     if G.masked:
         L.append(f'{ind}  }}')
     L.append(f'{ind}}}')
@@ -508,10 +536,13 @@ def _tab_pipeline_smem(L, G: _Group, spec: ConvSpec, idx_of, xyf, wf, wbase):
     L.append(f'        const float* tw = ring + {wbase} + ((e - e0) & 1) * {wf} + lane * 4;')
     L.append(f'        slot = (slot + 1) & {DX - 1};')
     for m in range(G.d1):
-        L.append(f'        const float x{m} = {_on(G, f"sr[{m * 32} + lane]")};')
+        for c in range(G.cpw):
+            L.append(f'        const float x{m}{_sx(G, c)} = {_on(G, f"sr[{(m * G.cpw + c) * 32} + lane]")};')
     for q, (pi, p) in enumerate(G.paths):
         z = 'make_float4(0.f, 0.f, 0.f, 0.f)'
-        L.append(f'        const float4 T{pi} = {_on(G, f"*reinterpret_cast<const float4*>(tw + {q * 128})", z)};')
+        for c in range(G.cpw):
+            L.append(f'        const float4 T{pi}{_sx(G, c)} = '
+                     f'{_on(G, f"*reinterpret_cast<const float4*>(tw + {(q * G.cpw + c) * 128})", z)};')
 
 
 def _tab_pipeline_regs(L, G: _Group, spec: ConvSpec, idx_of, xyf):
@@ -526,16 +557,19 @@ def _tab_pipeline_regs(L, G: _Group, spec: ConvSpec, idx_of, xyf):
         L.append('      CP_ASYNC_COMMIT();')
     L.append(f'      const float4* tr0 = tab + (size_t)({idx_of("e0")}) * {spec.wn} + c32 + lane;')
     for pi, p in G.paths:
-        L.append(f'      float4 Tn{pi} = {_on(G, f"__ldg(tr0 + {p.w_off})", z)};')
+        for c in range(G.cpw):
+            L.append(f'      float4 Tn{pi}{_sx(G, c)} = {_on(G, f"__ldg(tr0 + {p.w_off + c * 32})", z)};')
     L.append(f'      int jn = col[e0 + {DX - 1} < e1 ? e0 + {DX - 1} : e1 - 1];')
     L.append(f'      int in = {idx_of("(e0 + 1 < e1 ? e0 + 1 : e1 - 1)")};')
     L.append('      int slot = 0;')
     L.append('      for (int e = e0; e < e1; ++e) {')
     for pi, p in G.paths:
-        L.append(f'        const float4 T{pi} = Tn{pi};')
+        for c in range(G.cpw):
+            L.append(f'        const float4 T{pi}{_sx(G, c)} = Tn{pi}{_sx(G, c)};')
     L.append(f'        {{ const float4* tr = tab + (size_t)(in) * {spec.wn} + c32 + lane;')
     for pi, p in G.paths:
-        L.append(f'          Tn{pi} = {_on(G, f"__ldg(tr + {p.w_off})", z)};')
+        for c in range(G.cpw):
+            L.append(f'          Tn{pi}{_sx(G, c)} = {_on(G, f"__ldg(tr + {p.w_off + c * 32})", z)};')
     L.append('        }')
     L.append(f'        CP_ASYNC_WAIT({DX - 2});')
     L.append('        __syncwarp();')
@@ -548,7 +582,8 @@ def _tab_pipeline_regs(L, G: _Group, spec: ConvSpec, idx_of, xyf):
     L.append(f'        const float* sr = ring + slot * {xyf};')
     L.append(f'        slot = (slot + 1) & {DX - 1};')
     for m in range(G.d1):
-        L.append(f'        const float x{m} = {_on(G, f"sr[{m * 32} + lane]")};')
+        for c in range(G.cpw):
+            L.append(f'        const float x{m}{_sx(G, c)} = {_on(G, f"sr[{(m * G.cpw + c) * 32} + lane]")};')
 
 
 def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
@@ -569,10 +604,12 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
     L.append(f'        const float4* tr = tab + (size_t){idx_of("e")} * {spec.wn} + c32 + lane;')
     L.append(f'        const float t = Yt[(size_t)e * {S2} + {S}];')
     for m in range(G.d1):
-        L.append(f'        const float x{m} = {_on(G, f"xr[{m * G.mul}]")};')
+        for c in range(G.cpw):
+            L.append(f'        const float x{m}{_sx(G, c)} = {_on(G, f"xr[{m * G.mul + c * 32}]")};')
     for pi, p in G.paths:
         z = 'float4{0.f, 0.f, 0.f, 0.f}'
-        L.append(f'        const float4 T{pi} = {_on(G, f"tr[{p.w_off}]", z)};')
+        for c in range(G.cpw):
+            L.append(f'        const float4 T{pi}{_sx(G, c)} = {_on(G, f"tr[{p.w_off + c * 32}]", z)};')
     for jj in G.ys:
         L.append(f'        const float y{jj} = Yt[(size_t)e * {S2} + {jj}];')
     L.append('#else')
@@ -580,7 +617,7 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
         _tab_pipeline_regs(L, G, spec, idx_of, xyf)
     else:
         _tab_pipeline_smem(L, G, spec, idx_of, xyf, wf, wbase)
-    ybase = G.d1 * 32
+    ybase = G.d1 * 32 * G.cpw
     for jj in G.ys:
         L.append(f'        const float y{jj} = sr[{ybase + jj}];')
     L.append(f'        const float t = sr[{ybase + S}];')
@@ -589,11 +626,15 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
     L.append('        const float u = 1.f - t, tt = t * t, uu = u * u;')
     L.append('        const float h00 = (1.f + 2.f * t) * uu, h10 = t * uu, h01 = tt * (3.f - 2.f * t), h11 = -tt * u;')
     for pi, p in G.paths:
-        L.append(f'        const float w{pi} = fmaf(T{pi}.x, h00, fmaf(T{pi}.y, h10, fmaf(T{pi}.z, h01, T{pi}.w * h11)));')
+        for c in range(G.cpw):
+            T = f'T{pi}{_sx(G, c)}'
+            L.append(f'        const float w{pi}{_sx(G, c)} = fmaf({T}.x, h00, fmaf({T}.y, h10, fmaf({T}.z, h01, {T}.w * h11)));')
     if bwd:
         L.append('        const float d00 = -6.f * t * u, d10 = u * (1.f - 3.f * t), d11 = t * (3.f * t - 2.f);')
         for pi, p in G.paths:
-            L.append(f'        const float wd{pi} = fmaf(d00, T{pi}.x - T{pi}.z, fmaf(d10, T{pi}.y, d11 * T{pi}.w));')
+            for c in range(G.cpw):
+                T = f'T{pi}{_sx(G, c)}'
+                L.append(f'        const float wd{pi}{_sx(G, c)} = fmaf(d00, {T}.x - {T}.z, fmaf(d10, {T}.y, d11 * {T}.w));')
 
 
 def signature(spec: ConvSpec) -> str:
@@ -604,27 +645,29 @@ def generate(spec: ConvSpec) -> str:
     sig = signature(spec)
     _cur_sig[0] = sig
     groups = make_groups(spec)
+    groups_tab = make_groups(spec, tab=True)
     nu = sum(G.nchunk for G in groups)
+    nu_tab = sum(G.nchunk // G.cpw for G in groups_tab)
     out = ['// GENERATED by sevennet_exp_b200/codegen/conv_codegen.py -- do not edit.',
            f'// x: {ir.irreps_str(spec.lx.groups)}  mid: {ir.irreps_str(spec.lmid.groups)}  '
            f'lmax_sh {spec.lmax_sh}  paths {len(spec.paths)}  wn {spec.wn}  units {nu}',
            '#include "conv_common.cuh"', '']
     out += gen_fwd(spec, groups, sig) + ['']
     out += gen_bwd(spec, groups, sig) + ['']
-    out += gen_fwd(spec, groups, sig, tab=True) + ['']
-    out += gen_bwd(spec, groups, sig, tab=True) + ['']
+    out += gen_fwd(spec, groups_tab, sig, tab=True) + ['']
+    out += gen_bwd(spec, groups_tab, sig, tab=True) + ['']
     rf, rb = tab_ring_floats(spec, False), tab_ring_floats(spec, True)
     out.append(f'extern "C" int sevenn_conv_fwd_tab_{sig}(const float* x, int ldx, const float* Yt, const float* tab,')
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, float* out, int ldo, void* stream) {')
     out.append('  if (n_dst <= 0) return 0;')
-    out.append(f'  LAUNCH_DYN(conv_fwd_tab_{sig}, n_dst, {nu}, {rf}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, out, ldo);')
+    out.append(f'  LAUNCH_DYN(conv_fwd_tab_{sig}, n_dst, {nu_tab}, {rf}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, out, ldo);')
     out.append('  return LAUNCH_STATUS();')
     out.append('}')
     out.append(f'extern "C" int sevenn_conv_bwd_tab_{sig}(const float* x, int ldx, const float* Yt, const float* tab,')
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, const float* gout, int ldo,')
     out.append('    float* dxe, int lddx, float* dY, long long dy_stride, void* stream) {')
     out.append('  if (n_dst <= 0) return 0;')
-    out.append(f'  LAUNCH_DYN(conv_bwd_tab_{sig}, n_dst, {nu}, {rb}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, gout, ldo, dxe, lddx, dY, dy_stride);')
+    out.append(f'  LAUNCH_DYN(conv_bwd_tab_{sig}, n_dst, {nu_tab}, {rb}, stream)(x, ldx, Yt, (const float4*)tab, rowptr, col, n_dst, inv_denom, gout, ldo, dxe, lddx, dY, dy_stride);')
     out.append('  return LAUNCH_STATUS();')
     out.append('}')
     out.append(f'extern "C" int sevenn_conv_fwd_{sig}(const float* x, int ldx, const float* Y, const float* w,')

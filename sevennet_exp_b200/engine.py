@@ -309,7 +309,7 @@ class Engine(Kernels):
                 'mlp': [f32(w) for w in Wm],
                 'mlpT': [f32(np.ascontiguousarray(w.T)) for w in Wm],
                 'inv_denom': 1.0 / float(sd[f'{L.conv.name}.denominator'][0]),
-                'sig': L.conv.signature(), 'units': conv_codegen.n_units(L.conv),
+                'sig': L.conv.signature(), 'units': conv_codegen.n_units(L.conv, tab=self.radial == 'table'),
                 'pieces': (_lib.GatePiece * len(L.gate.pieces))(*[
                     _lib.GatePiece(p.kind, p.l, p.mul, p.in_off, p.in_stride, p.gate_off, p.out_off,
                                    p.out_stride, p.act, p.cst) for p in L.gate.pieces]),
