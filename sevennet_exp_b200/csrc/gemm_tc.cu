@@ -731,6 +731,29 @@ static int tc_set_smem_attr(K kern, bool* done) {
 extern "C" int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args, const float* const* Bimgs, void* stream) {
   if (n <= 0) return 0;
   if (n > TC_MAX_GROUP) return SEVENN_ERR_BAD_ARG;
+  if (n > 1) {
+    // Sharing a launch pays for problems that cannot fill the GPU on their own (their launch / TMEM-allocation /
+    // pipeline-fill latencies overlap).  A problem with >= 2 tiles per SM runs alone on all SMs instead: a static
+    // split of the CTAs between problems of different K / N per tile is bound by its slowest member (measured on the
+    // l3i5 self-interaction at 32,768 atoms: 3.6 ms grouped vs 1.0 ms as separate launches).
+    sevenn_gemm_args small[TC_MAX_GROUP];
+    const float* small_img[TC_MAX_GROUP];
+    int ns = 0;
+    const int sms = tc_sm_count();
+    for (int i = 0; i < n; ++i) {
+      int Nt, n_tiles, KB, res;
+      if (args[i].M <= 0 || args[i].N <= 0) continue;
+      if (tc_plan(args[i].N, args[i].K, &Nt, &n_tiles, &KB, &res)) return SEVENN_ERR_BAD_ARG;
+      const long long t = ((args[i].M + TC_BM - 1) / TC_BM) * n_tiles;
+      if (t >= 2LL * sms) {
+        int rc = sevenn_gemm_tc_grouped(1, &args[i], &Bimgs[i], stream);
+        if (rc) return rc;
+      } else {
+        small[ns] = args[i]; small_img[ns] = Bimgs[i]; ++ns;
+      }
+    }
+    if (ns < n) return ns ? sevenn_gemm_tc_grouped(ns, small, small_img, stream) : 0;
+  }
   TcGroup G;
   G.n = 0;
   size_t smem = 0;

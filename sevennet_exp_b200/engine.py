@@ -104,6 +104,7 @@ class Kernels:
         self.lib = lib if lib is not None else _lib.load()
         self.n_launch = 0
         self._tc_cache = {}
+        self._tc_tiles, self._sms = {}, None
         # dense contractions: 'auto' = tcgen05 3xTF32 arm for big row counts, exact-fp32 SIMT arm otherwise
         self.gemm_mode = os.environ.get('SEVENN_GEMM', 'auto')
         self.tc_min_rows = int(os.environ.get('SEVENN_TC_MIN_ROWS', '1024'))
@@ -174,7 +175,26 @@ class Kernels:
             arr = (_lib.GemmArgs * len(part))(*[g for g, _ in part])
             imgs = (ctypes.c_void_p * len(part))(*[im.data_ptr() for _, im in part])
             self.lib.call('sevenn_gemm_tc_grouped', len(part), arr, imgs, self._stream())
-            self.n_launch += 1
+            self.n_launch += self._tc_group_launches([g for g, _ in part])
+
+    def _tc_group_launches(self, gs):
+        """Launches sevenn_gemm_tc_grouped makes for these problems (csrc/gemm_tc.cu: a member with >= 2 tiles per
+        SM runs alone, the others share one launch) -- kept in step with the library for the launch count."""
+        if len(gs) == 1:
+            return 1
+        if self._sms is None:
+            self._sms = torch.cuda.get_device_properties(self.dev).multi_processor_count if self.dev.type == 'cuda' else 1
+        big = 0
+        for g in gs:
+            key = (g.N, g.K)
+            if key not in self._tc_tiles:
+                nt, tiles, kb, fl = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_longlong()
+                self.lib.call('sevenn_gemm_tc_plan', g.N, g.K, ctypes.byref(nt), ctypes.byref(tiles), ctypes.byref(kb),
+                              ctypes.byref(fl))
+                self._tc_tiles[key] = tiles.value
+            if ((g.M + 127) // 128) * self._tc_tiles[key] >= 2 * self._sms:
+                big += 1
+        return big + (1 if big < len(gs) else 0)
 
     def _linear_fwd(self, lin: _Lin, x, n, y, accumulate=False, types=None):
         sp = lin.spec

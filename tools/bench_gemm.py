@@ -11,7 +11,12 @@ lib = L.load()
 st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 shapes = [(198356, 1, 64, 960, 0), (198356, 1, 960, 64, 3), (198356, 1, 64, 64, 2), (198356, 1, 8, 64, 2),
           (4096, 1, 224, 224, 0), (4096, 3, 384, 64, 0), (4096, 5, 352, 32, 0), (4096, 1, 128, 128, 0)]
-only = sys.argv[1:]
+only = [a for a in sys.argv[1:] if a in ('tc', 'simt')]
+if 'cfg3' in sys.argv:        # SevenNet-l3i5 inner layer at 32,768 atoms: si2 forward, then si2 input-gradient
+    shapes = [(32768, 1, 256, 256, 0), (32768, 3, 480, 64, 0), (32768, 5, 544, 32, 0), (32768, 7, 480, 32, 0),
+              (32768, 1, 256, 256, 0), (32768, 3, 64, 480, 0), (32768, 5, 32, 544, 0), (32768, 7, 32, 480, 0)]
+if 'one' in sys.argv:
+    shapes = [(32768, 5, 32, 544, 0)]
 flush = torch.empty(64 * 1024 * 1024, device='cuda')
 for (n, R, K, N, epi) in shapes:
     A = torch.randn(n, R * K, device='cuda')
