@@ -262,11 +262,11 @@ def run_single(args):
     # ("say which tensors were elided"); `achieved` keeps SURVEY 8d's figure so rounds stay comparable
     touched = alg - (E * 8 * inner.wn if tab else 0)
     # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this workload (ncu --set full):
-    # table mode profiles/r01g_conv_tab_fwd_bwd_raw.csv (156 MB + 380 MB), mlp mode r01c_conv_fwd_bwd_raw.csv
+    # table mode profiles/r01h_conv_tab_fwd_bwd_raw.csv (142 MB + 363 MB), mlp mode r01c_conv_fwd_bwd_raw.csv
     # (937 MB + 1,141 MB); below the algorithmic bytes because the gathered source rows are served by L2
     traffic = None
     if (n, inner.signature()) == (4096, 'c377d4386a8'):
-        traffic = 535.6e6 if tab else 2078e6
+        traffic = 505.2e6 if tab else 2078e6
     path_bytes_per_atom = 5.39e6          # forward + reverse, 5 layers, ~50 neighbours/atom
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': 1, 'steps': args.steps, 'warmup': args.warmup,
@@ -291,7 +291,7 @@ def run_single(args):
                      'elided': ('w and dW [E, wn] (radial weights interpolated from an L2-resident table inside the '
                                 'kernel)' if tab else None),
                      'touched_bytes': touched, 'touched_frac': touched / (dom_ms * 1e-3) / 1e9 / peak,
-                     'limiter': ('ncu r01g: issue slots 73 %, fp32 pipe 47 %, L1 data pipe 50 %, DRAM 11 % -> '
+                     'limiter': ('ncu r01h: issue slots 76 %, fma pipe 52 %, L1 data pipe 51 %, DRAM 13 % -> '
                                  'instruction bound, not HBM bound' if tab else
                                  'ncu r01c: DRAM 42 %, issue slots 63 %'),
                      'conv_fwd_achieved': fwd_ach, 'conv_fwd_frac': fwd_ach / peak,
