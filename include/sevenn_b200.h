@@ -121,6 +121,14 @@ int sevenn_segment_gather_sum(const float* src, int D, const int* cptr, const in
 /* halo pack / unpack-add: sevenn/pair_e3gnn/pair_e3gnn_parallel.cpp:787-897 */
 int sevenn_gather_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream);
 int sevenn_scatter_add_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream);
+/* halo push over peer memory: row i of the packed order (segment p = the rows for peer p, seg_off[p] <= i <
+ * seg_off[p+1], seg_off[n_peers] == n) is written to peer_base[p][(dst_row[p] + i - seg_off[p]) * D ..]; the source row
+ * is idx[i], or first_row + i when idx == NULL.  peer_base[] are device pointers valid on this device (own or
+ * P2P-mapped memory); peer_base / dst_row / seg_off are host arrays.  Replaces pack + MPI relay of
+ * pair_e3gnn_parallel.cpp:787-842 (forward_comm) and :844-897 (reverse_comm) by one kernel over NVLink. */
+#define SEVENN_MAX_PEERS 16
+int sevenn_push_rows_peers(const float* src, int D, const int* idx, long long first_row, long long n, int n_peers,
+                           float* const* peer_base, const long long* dst_row, const long long* seg_off, void* stream);
 
 /* ---- fused gather + uvu CG tensor product + segment sum (generated per irreps signature <sig>):
  *   int sevenn_conv_fwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo, stream)

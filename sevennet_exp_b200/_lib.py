@@ -53,6 +53,7 @@ SIGNATURES = {
     'sevenn_segment_gather_sum': ([c_p, c_i, c_p, c_p, c_ll, c_p, c_i, c_p], c_i),
     'sevenn_gather_rows': ([c_p, c_i, c_p, c_ll, c_p, c_p], c_i),
     'sevenn_scatter_add_rows': ([c_p, c_i, c_p, c_ll, c_p, c_p], c_i),
+    'sevenn_push_rows_peers': ([c_p, c_i, c_p, c_ll, c_ll, c_i, c_p, c_p, c_p, c_p], c_i),
 }
 CONV_FWD_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p]
 CONV_BWD_ARGS = [c_p, c_i, c_p, c_p, c_p, c_p, c_i, c_f, c_p, c_i, c_p, c_p, c_i, c_p, c_ll, c_p]

@@ -291,6 +291,35 @@ GKERNEL(scatter_add_rows_kernel)(const float* __restrict__ src, int D, const int
   // an owner row can be wanted by several peers (or as several periodic images): atomic accumulate
   GRID_STRIDE_LOOP(t, n * D) { ATOMIC_ADD_F32(out + (size_t)idx[t / D] * D + (t % D), src[t]); }
 }
+// Halo push over peer memory (NVLink): row i of the packed order belongs to segment p (seg_off[p] <= i < seg_off[p+1],
+// one segment per peer) and is written straight into that peer's halo buffer at row dst_row[p] + (i - seg_off[p]) --
+// pack and transfer in one kernel, no staging copy and no collective call (pair_e3gnn_parallel.cpp:787-842 packs
+// into a host buffer and hands it to MPI).  idx == nullptr: rows first_row + i (the contiguous ghost block).
+struct SevennPeerTable { float* base[SEVENN_MAX_PEERS]; long long dst_row[SEVENN_MAX_PEERS]; long long seg_off[SEVENN_MAX_PEERS + 1]; int n; };
+GKERNEL(push_rows_peers_kernel)(const float* __restrict__ src, int D, const int* __restrict__ idx, long long first_row,
+                                long long n, SevennPeerTable T) {
+  GRID_STRIDE_LOOP(t, n * D) {
+    const long long i = t / D;
+    const int c = (int)(t - i * D);
+    int p = 0;
+    while (p + 1 < T.n && i >= T.seg_off[p + 1]) ++p;
+    const long long r = idx ? (long long)idx[i] : first_row + i;
+    T.base[p][(size_t)(T.dst_row[p] + (i - T.seg_off[p])) * D + c] = src[(size_t)r * D + c];
+  }
+}
+extern "C" int sevenn_push_rows_peers(const float* src, int D, const int* idx, long long first_row, long long n,
+                                      int n_peers, float* const* peer_base, const long long* dst_row,
+                                      const long long* seg_off, void* stream) {
+  if (n <= 0) return 0;
+  if (n_peers <= 0 || n_peers > SEVENN_MAX_PEERS) return SEVENN_ERR_BAD_ARG;
+  SevennPeerTable T;
+  T.n = n_peers;
+  for (int p = 0; p < n_peers; ++p) { T.base[p] = peer_base[p]; T.dst_row[p] = dst_row[p]; T.seg_off[p] = seg_off[p]; }
+  T.seg_off[n_peers] = seg_off[n_peers];
+  if (T.seg_off[n_peers] != n) return SEVENN_ERR_BAD_ARG;
+  LAUNCH1D(push_rows_peers_kernel, n * D, stream)(src, D, idx, first_row, n, T);
+  return LAUNCH_STATUS();
+}
 extern "C" int sevenn_gather_rows(const float* src, int D, const int* idx, long long n, float* out, void* stream) {
   if (n <= 0) return 0;
   LAUNCH1D(gather_rows_kernel, n * D, stream)(src, D, idx, n, out);

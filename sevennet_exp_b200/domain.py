@@ -16,6 +16,7 @@ SevenNet patch of ``CommBrick`` (sevenn/pair_e3gnn/comm_brick.cpp:1057-1123):
     gloo in the CPU tests).  Pack = gather kernel into one send buffer, unpack-add = scatter-add kernel.
 """
 import ctypes
+import os
 from typing import List, Optional
 
 import numpy as np
@@ -112,6 +113,62 @@ class Halo:
         self.send_off = np.concatenate([[0], np.cumsum(self.send_count)]).astype(np.int64)
         self.recv_off = np.concatenate([[0], np.cumsum(self.recv_count)]).astype(np.int64)
         self.bytes_fwd = 0
+        self.peer = None
+        mode = os.environ.get('SEVENN_HALO', 'nccl')
+        if mode in ('p2p', 'auto') and self.world > 1 and self.dev.type == 'cuda':
+            try:
+                self._setup_peer(group)
+            except Exception as e:                      # no peer access between these GPUs: NCCL carries the rows
+                if mode == 'p2p':
+                    raise
+                print(f'[halo rank {self.rank}] peer-memory halo unavailable ({e}); using NCCL', flush=True)
+                self.peer = None
+
+    # ---- peer-memory halo (NVLink / NVSwitch): every rank owns a symmetric staging area of two slots; a sender
+    # packs its rows straight into the receiver's slot (one kernel for all peers), a device-side barrier over the
+    # signal pads orders the exchange, the receiver copies / scatter-adds out of its own slot.  Slots alternate per
+    # exchange: a peer can only write slot s for exchange k + 2 after it passed the barrier of exchange k + 1, which
+    # this rank enters (in stream order) after it has consumed slot s of exchange k.
+    def _setup_peer(self, group):
+        import torch.distributed._symmetric_memory as symm_mem
+        if self.world > 16:
+            raise RuntimeError('more than SEVENN_MAX_PEERS ranks')
+        grp = group if group is not None else dist.group.WORLD
+        rows = max(int(self.send_off[-1]), int(self.recv_off[-1]), 1)
+        cap = torch.tensor([rows], dtype=torch.int64, device=self.dev)
+        dist.all_reduce(cap, op=dist.ReduceOp.MAX, group=group)
+        self._slot_rows = int(cap.item())
+        self._slot_dim = int(os.environ.get('SEVENN_HALO_MAX_DIM', '1024'))
+        self._slot_floats = self._slot_rows * self._slot_dim
+        tables: List[Optional[list]] = [None] * self.world
+        dist.all_gather_object(tables, (self.send_off.tolist(), self.recv_off.tolist()), group=group)
+        # where my rows start inside peer p's slot: forward = p's receive offset for me, reverse = p's send offset
+        self._fwd_dst_row = [int(tables[p][1][self.rank]) for p in range(self.world)]
+        self._bwd_dst_row = [int(tables[p][0][self.rank]) for p in range(self.world)]
+        buf = symm_mem.empty(2 * self._slot_floats, dtype=torch.float32, device=self.dev)
+        hdl = symm_mem.rendezvous(buf, grp)
+        self._stage = buf
+        self._peer_ptrs = [int(q) for q in hdl.buffer_ptrs]
+        self._n_exchange = 0
+        self._ll = ctypes.c_longlong * self.world
+        self._llp1 = ctypes.c_longlong * (self.world + 1)
+        self._pp = ctypes.c_void_p * self.world
+        self._seg_fwd = self._llp1(*[int(v) for v in self.send_off])
+        self._seg_bwd = self._llp1(*[int(v) for v in self.recv_off])
+        self.peer = hdl
+        hdl.barrier(channel=0, timeout_ms=20000)
+
+    def _peer_push(self, src, D, idx, first_row, n, dst_row, seg):
+        if D > self._slot_dim:
+            raise ValueError(f'halo rows of {D} floats exceed SEVENN_HALO_MAX_DIM={self._slot_dim}')
+        slot = self._n_exchange & 1
+        self._n_exchange += 1
+        base = self._pp(*[q + 4 * slot * self._slot_floats for q in self._peer_ptrs])
+        self.lib.call('sevenn_push_rows_peers', ctypes.c_void_p(src.data_ptr()), D,
+                      ctypes.c_void_p(idx.data_ptr()) if idx is not None else None, first_row, n, self.world,
+                      base, self._ll(*dst_row), seg, self._stream())
+        self.peer.barrier(channel=0, timeout_ms=20000)
+        return self._stage[slot * self._slot_floats:]
 
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream) if self.dev.type == 'cuda' else None
@@ -149,6 +206,13 @@ class Halo:
         D = h.shape[1]
         nl = self.dec.n_local
         ns = int(self.send_off[-1])
+        if self.peer is not None:
+            nr = int(self.recv_off[-1])
+            mine = self._peer_push(h, D, self.send_idx, 0, ns, self._fwd_dst_row, self._seg_fwd)
+            if nr:
+                h[nl:nl + nr].copy_(mine[:nr * D].view(nr, D))
+            self.bytes_fwd += ns * D * 4
+            return
         buf = torch.empty(max(ns, 1), D, dtype=h.dtype, device=self.dev)
         if ns:
             self.lib.call('sevenn_gather_rows', ctypes.c_void_p(h.data_ptr()), D,
@@ -162,6 +226,14 @@ class Halo:
         D = dh.shape[1]
         nl = self.dec.n_local
         ns = int(self.send_off[-1])
+        if self.peer is not None:
+            # ghost rows are grouped by owner: segment p = dh[nl + recv_off[p] : nl + recv_off[p + 1]]
+            mine = self._peer_push(dh, D, None, nl, int(self.recv_off[-1]), self._bwd_dst_row, self._seg_bwd)
+            if ns:
+                self.lib.call('sevenn_scatter_add_rows', ctypes.c_void_p(mine.data_ptr()), D,
+                              ctypes.c_void_p(self.send_idx.data_ptr()), ns, ctypes.c_void_p(dh.data_ptr()),
+                              self._stream())
+            return
         buf = torch.empty(max(ns, 1), D, dtype=dh.dtype, device=self.dev)
         ghost = dh[nl:].contiguous()
         self._exchange(ghost, self.recv_count, self.recv_off, buf, self.send_count, self.send_off)
