@@ -114,7 +114,7 @@ class Halo:
         self.recv_off = np.concatenate([[0], np.cumsum(self.recv_count)]).astype(np.int64)
         self.bytes_fwd = 0
         self.peer = None
-        mode = os.environ.get('SEVENN_HALO', 'nccl')
+        mode = os.environ.get('SEVENN_HALO', 'auto')
         if mode in ('p2p', 'auto') and self.world > 1 and self.dev.type == 'cuda':
             try:
                 self._setup_peer(group)
@@ -143,18 +143,18 @@ class Halo:
         tables: List[Optional[list]] = [None] * self.world
         dist.all_gather_object(tables, (self.send_off.tolist(), self.recv_off.tolist()), group=group)
         # where my rows start inside peer p's slot: forward = p's receive offset for me, reverse = p's send offset
-        self._fwd_dst_row = [int(tables[p][1][self.rank]) for p in range(self.world)]
-        self._bwd_dst_row = [int(tables[p][0][self.rank]) for p in range(self.world)]
+        ll = ctypes.c_longlong * self.world
+        self._fwd_dst_row = ll(*[int(tables[p][1][self.rank]) for p in range(self.world)])
+        self._bwd_dst_row = ll(*[int(tables[p][0][self.rank]) for p in range(self.world)])
         buf = symm_mem.empty(2 * self._slot_floats, dtype=torch.float32, device=self.dev)
         hdl = symm_mem.rendezvous(buf, grp)
         self._stage = buf
         self._peer_ptrs = [int(q) for q in hdl.buffer_ptrs]
         self._n_exchange = 0
-        self._ll = ctypes.c_longlong * self.world
-        self._llp1 = ctypes.c_longlong * (self.world + 1)
-        self._pp = ctypes.c_void_p * self.world
-        self._seg_fwd = self._llp1(*[int(v) for v in self.send_off])
-        self._seg_bwd = self._llp1(*[int(v) for v in self.recv_off])
+        llp1, pp = ctypes.c_longlong * (self.world + 1), ctypes.c_void_p * self.world
+        self._seg_fwd = llp1(*[int(v) for v in self.send_off])
+        self._seg_bwd = llp1(*[int(v) for v in self.recv_off])
+        self._slot_base = [pp(*[q + 4 * slot * self._slot_floats for q in self._peer_ptrs]) for slot in (0, 1)]
         self.peer = hdl
         hdl.barrier(channel=0, timeout_ms=20000)
 
@@ -163,10 +163,9 @@ class Halo:
             raise ValueError(f'halo rows of {D} floats exceed SEVENN_HALO_MAX_DIM={self._slot_dim}')
         slot = self._n_exchange & 1
         self._n_exchange += 1
-        base = self._pp(*[q + 4 * slot * self._slot_floats for q in self._peer_ptrs])
         self.lib.call('sevenn_push_rows_peers', ctypes.c_void_p(src.data_ptr()), D,
                       ctypes.c_void_p(idx.data_ptr()) if idx is not None else None, first_row, n, self.world,
-                      base, self._ll(*dst_row), seg, self._stream())
+                      self._slot_base[slot], dst_row, seg, self._stream())
         self.peer.barrier(channel=0, timeout_ms=20000)
         return self._stage[slot * self._slot_floats:]
 
