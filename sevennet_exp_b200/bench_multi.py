@@ -148,6 +148,8 @@ def run(args):
                        'n_atoms': n_total, 'atoms_per_gpu': n_total // world, 'energy_per_atom_eV': float(E.item()) / n_total,
                        'ghosts_per_gpu_max': int(smax[1].item()), 'edges_total': int(stats[2].item()),
                        'halo_row_bytes': x_dim * 4,
+                       'halo': ('peer memory: pack + NVLink write into the neighbour\'s slot in one kernel, device-side '
+                                'barrier' if halo.peer is not None else 'NCCL all-to-all-v per exchange'),
                        'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)',
                        'step': 'device neighbour list (owned+ghost) + forward + reverse pass + halo exchanges'},
             'e2e': {'value': n_total / e2e_t, 'unit': B.UNIT, 'ms_per_step': e2e_t * 1e3,
