@@ -156,9 +156,14 @@ __global__ void colsum_stage1(const float* __restrict__ a, long long n, int D, d
     __syncthreads();
   }
 }
+// one warp per column: lanes stride over the block partials, fixed-order shuffle tree (bit-reproducible)
 __global__ void colsum_stage2(const double* __restrict__ part, int nb, int D, double* __restrict__ out) {
-  const int d = threadIdx.x;
-  if (d < D) { double s = 0.0; for (int b = 0; b < nb; ++b) s += part[b * D + d]; out[d] = s; }
+  const int d = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (d >= D) return;
+  double s = 0.0;
+  for (int b = lane; b < nb; b += 32) s += part[b * D + d];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+  if (lane == 0) out[d] = s;
 }
 #endif
 extern "C" int sevenn_colsum_f64(const float* a, long long n, int D, double* part /* >= 296*D */, double* out,
@@ -169,41 +174,42 @@ extern "C" int sevenn_colsum_f64(const float* a, long long n, int D, double* par
   return 0;
 #else
   colsum_stage1<<<COLSUM_BLOCKS, 256, 0, (cudaStream_t)stream>>>(a, n, D, part);
-  colsum_stage2<<<1, 32, 0, (cudaStream_t)stream>>>(part, COLSUM_BLOCKS, D, out);
+  colsum_stage2<<<1, 32 * D, 0, (cudaStream_t)stream>>>(part, COLSUM_BLOCKS, D, out);
   return (int)cudaGetLastError();
 #endif
 }
 
 // ---- forces and virial from per-edge dE/d(edge_vec)
 // F_k = sum_{e: centre k} f_e - sum_{e: neighbour k} f_e ; w_k[6] = sum_{e: centre k} (rx fx, ry fy, rz fz, rx fy, ry fz, rz fx)
+// One thread per (node, output component): 9 threads share a node's edge lists through L1 (the per-node form ran
+// 16 CTAs for 4,096 atoms); every component is still summed in ascending edge order, so results are unchanged.
 GKERNEL(force_virial_kernel)(const float* __restrict__ fvec, const float* __restrict__ vec,
                              const int* __restrict__ rowptr, int n_rows, const int* __restrict__ cptr,
                              const int* __restrict__ cedge, long long n_nodes, float* __restrict__ F,
                              float* __restrict__ vir) {
-  GRID_STRIDE_LOOP(k, n_nodes) {
-    float fx = 0.f, fy = 0.f, fz = 0.f, w0 = 0.f, w1 = 0.f, w2 = 0.f, w3 = 0.f, w4 = 0.f, w5 = 0.f;
-    if (k < n_rows) {
-      for (int e = rowptr[k]; e < rowptr[k + 1]; ++e) {
-        const float ax = fvec[3 * e], ay = fvec[3 * e + 1], az = fvec[3 * e + 2];
-        const float rx = vec[3 * e], ry = vec[3 * e + 1], rz = vec[3 * e + 2];
-        fx += ax; fy += ay; fz += az;
-        w0 += rx * ax; w1 += ry * ay; w2 += rz * az; w3 += rx * ay; w4 += ry * az; w5 += rz * ax;
-      }
+  GRID_STRIDE_LOOP(t, n_nodes * 9) {
+    const long long k = t / 9;
+    const int c = (int)(t - k * 9);
+    float s = 0.f;
+    if (c < 3) {
+      if (k < n_rows)
+        for (int e = rowptr[k]; e < rowptr[k + 1]; ++e) s += fvec[3 * e + c];
+      for (int a = cptr[k]; a < cptr[k + 1]; ++a) s -= fvec[3 * cedge[a] + c];
+      F[3 * k + c] = s;
+    } else {
+      // (xx, yy, zz, xy, yz, zx): r component (c - 3) % 3, f component (c - 3) % 3 or the next one
+      const int cr = (c - 3) % 3, cf = c < 6 ? cr : (cr + 1) % 3;
+      if (k < n_rows)
+        for (int e = rowptr[k]; e < rowptr[k + 1]; ++e) s += vec[3 * e + cr] * fvec[3 * e + cf];
+      vir[6 * k + (c - 3)] = s;
     }
-    for (int a = cptr[k]; a < cptr[k + 1]; ++a) {
-      const int e = cedge[a];
-      fx -= fvec[3 * e]; fy -= fvec[3 * e + 1]; fz -= fvec[3 * e + 2];
-    }
-    F[3 * k] = fx; F[3 * k + 1] = fy; F[3 * k + 2] = fz;
-    float* w = vir + 6 * k;
-    w[0] = w0; w[1] = w1; w[2] = w2; w[3] = w3; w[4] = w4; w[5] = w5;
   }
 }
 extern "C" int sevenn_force_virial(const float* fvec, const float* vec, const int* rowptr, int n_rows,
                                    const int* cptr, const int* cedge, long long n_nodes, float* F, float* vir,
                                    void* stream) {
   if (n_nodes <= 0) return 0;
-  LAUNCH1D(force_virial_kernel, n_nodes, stream)(fvec, vec, rowptr, n_rows, cptr, cedge, n_nodes, F, vir);
+  LAUNCH1D(force_virial_kernel, n_nodes * 9, stream)(fvec, vec, rowptr, n_rows, cptr, cedge, n_nodes, F, vir);
   return LAUNCH_STATUS();
 }
 
