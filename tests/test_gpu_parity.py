@@ -188,6 +188,43 @@ def test_l3i5_shape_small(lib):
     print(_engine_vs_oracle(cfg, model.state_dict(), model, numbers, pos, cell, [True] * 3))
 
 
+@pytest.mark.parametrize('cutoff_fn', [{'cutoff_function_name': 'XPLOR', 'cutoff_on': 4.5},
+                                       {'cutoff_function_name': 'poly_cut', 'poly_cut_p_value': 6}])
+def test_multi_cutoff_model_on_gpu(lib, cutoff_fn):
+    """MultiCutoffEdgeEmbedding (sevenn/nn/edge_embedding.py:220-257): per-layer cutoffs on one neighbour list, through
+    the calculator's default (tabulated) radial mode."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg.update(version='0.11.0', scale=[10.0] * cfg['_number_of_species'], cutoff_function=cutoff_fn,
+               multi_cutoff=[5.0, 3.5, 5.0])
+    torch.manual_seed(31)
+    model = S.build_model(cfg).eval()
+    numbers, pos, cell = random_cell(40, list(cfg['_type_map']), density=0.05, seed=9)
+    print(_engine_vs_oracle(cfg, model.state_dict(), model, numbers, pos, cell, [True] * 3))
+
+
+@pytest.mark.parametrize('pbc', [[False] * 3, [True, True, False]])
+def test_open_and_slab_boundaries_on_gpu(lib, pbc):
+    """Non-periodic directions (the reference inflates the cell, train/dataload.py:40-48): a cluster / slab cut out of
+    a random cell; energy, atomic energies and forces against the fp64 oracle on the same edge set."""
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cfg, model = _random_model('test-so3-l2')
+    numbers, pos, cell = random_cell(36, list(cfg['_type_map']), density=0.05, seed=5, triclinic=False)
+    calc = SevenNetCalculator((cfg, model.state_dict()), file_type='model_instance')
+    res = calc.compute(numbers, pos, cell, pbc)
+    import copy
+    torch.set_default_dtype(torch.float64)
+    try:
+        g = S.atoms_to_graph(numbers, pos, cell, pbc, cfg['cutoff'], dtype=torch.float64)
+        ref = copy.deepcopy(model).double()(dict(g))
+    finally:
+        torch.set_default_dtype(torch.float32)
+    assert res['n_edges'] == g[S.EDGE_IDX].shape[1]
+    assert abs(res['energy'] - ref[S.E_TOT].item()) / len(numbers) < 1e-5
+    assert np.abs(res['energies'] - ref[S.AE].detach().numpy().ravel()).max() < 1e-4
+    assert np.abs(res['forces'] - ref[S.FORCE].detach().numpy()).max() < 1e-4
+    assert np.abs(res['forces'].sum(0)).max() < 1e-4          # no net force on an isolated system
+
+
 def test_bitwise_reproducible_and_edge_cases(lib):
     from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
     cfg, model = _random_model('test-so3-l2')
