@@ -148,7 +148,7 @@ def cpu_oracle_sample(reps, steps, warmup):
         t0 = time.perf_counter()
         g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
         out = model(g)
-        float(out[S.E_TOT]); out[S.FORCE].sum().item()
+        float(out[S.E_TOT].detach()); out[S.FORCE].sum().item()
         if k >= warmup:
             ts.append(time.perf_counter() - t0)
     t = float(np.mean(ts))

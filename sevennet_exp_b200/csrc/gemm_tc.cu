@@ -103,26 +103,6 @@ __device__ __forceinline__ void sts128(uint32_t a, float4 v) {
 // element, which made the 128 x 64 SiLU epilogue (8,192 evaluations per tile) the bottleneck of the K <= 64 layers.
 __device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.f + __expf(-x)); }
 __device__ __forceinline__ float dsilu_f(float x) { const float s = __fdividef(1.f, 1.f + __expf(-x)); return s * (1.f + x * (1.f - s)); }
-__device__ __forceinline__ float tc_act_unused(int id, float x) {
-  switch (id) {
-    case 0: return x / (1.f + expf(-x));
-    case 1: return tanhf(x);
-    case 2: return fabsf(x);
-    case 3: return x > 0.f ? x : 0.f;
-    case 4: return 1.f / (1.f + expf(-x));
-    default: return (x > 20.f ? x : log1pf(expf(x))) - 0.6931471805599453f;
-  }
-}
-__device__ __forceinline__ float tc_dact_unused(int id, float x) {
-  switch (id) {
-    case 0: { const float s = 1.f / (1.f + expf(-x)); return s * (1.f + x * (1.f - s)); }
-    case 1: { const float t = tanhf(x); return 1.f - t * t; }
-    case 2: return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f);
-    case 3: return x > 0.f ? 1.f : 0.f;
-    case 4: { const float s = 1.f / (1.f + expf(-x)); return s * (1.f - s); }
-    default: return 1.f / (1.f + expf(-x));
-  }
-}
 
 // Epilogue of one 128-row tile for one warp (TMEM lanes 32*ew ..): tcgen05.ld 32 columns at a time, transpose through
 // XOR-swizzled smem, full-line coalesced 16 B accesses with the fused epilogue.
