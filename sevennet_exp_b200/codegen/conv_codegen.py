@@ -73,6 +73,9 @@ class _Group:
 # source-index / table-index loads, loop control and above all the per-edge dY lane reduction -- is paid once per pair.
 import os as _os0
 TAB_CPW = int(_os0.environ.get('SEVENN_TAB_CPW', '2'))
+# packed fp32 (fma.rn.f32x2) for the per-channel arithmetic of two-chunk units: the chunk pair (a, b) of a lane is one
+# float2; warp-uniform M entries and literals are free broadcast / immediate operands of FFMA2
+TAB_F2 = _os0.environ.get('SEVENN_TAB_F2', '0') == '1'
 
 
 def make_groups(spec: ConvSpec, tab: bool = False) -> List[_Group]:
@@ -256,19 +259,44 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
         L.append(f'UNIT_LOOP_BEGIN(n_dst, {sum(G.nchunk for G in groups)}, {ring_floats(spec)})')
     for gi, G in enumerate(groups):
         _unit_open(L, G, gi == 0, gi == len(groups) - 1)
+        f2 = tab and TAB_F2 and G.cpw == 2
         for pi, p in G.paths:
+            if f2:
+                L.append('    float2 ' + ', '.join(f'a{pi}_{k} = make_float2(0.f, 0.f)' for k in range(2 * p.l3 + 1)) + ';')
+                continue
             for c in range(G.cpw):
                 L.append('    float ' + ', '.join(f'a{pi}_{k}{_sx(G, c)} = 0.f' for k in range(2 * p.l3 + 1)) + ';')
         if tab:
             _tab_pipeline_open(L, G, spec, False)
         else:
             _pipeline_open(L, G, spec)
+        if f2:
+            for m in range(G.d1):
+                L.append(f'        const float2 x{m} = make_float2(x{m}_a, x{m}_b);')
+            for pi, p in G.paths:
+                L.append(f'        const float2 w{pi} = make_float2(w{pi}_a, w{pi}_b);')
         for pi, p in G.paths:
             ent, _ = _m_terms(p.l1, p.l2, p.l3)
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}, mul {p.mul}')
             _emit_M(L, ent, p.l2, '          ')
             rows = [i for i in range(G.d1) if any((i, k) in ent for k in range(2 * p.l3 + 1))]
-            for c in range(G.cpw):
+            if f2:
+                if 2 * p.l3 + 1 > len(rows):
+                    for i in rows:
+                        L.append(f'          const float2 X{i} = __fmul2_rn(w{pi}, x{i});')
+                    for k in range(2 * p.l3 + 1):
+                        for i in range(G.d1):
+                            if (i, k) in ent:
+                                L.append(f'          a{pi}_{k} = __ffma2_rn(F2B(M_{i}_{k}), X{i}, a{pi}_{k});')
+                else:
+                    for k in range(2 * p.l3 + 1):
+                        ii = [i for i in range(G.d1) if (i, k) in ent]
+                        if ii:
+                            t = f'__fmul2_rn(F2B(M_{ii[0]}_{k}), x{ii[0]})'
+                            for i in ii[1:]:
+                                t = f'__ffma2_rn(F2B(M_{i}_{k}), x{i}, {t})'
+                            L.append(f'          a{pi}_{k} = __ffma2_rn(w{pi}, {t}, a{pi}_{k});')
+            for c in range(0 if f2 else G.cpw):
                 sx = _sx(G, c)
                 if 2 * p.l3 + 1 > len(rows):
                     # fewer input than output components: scale the inputs once (nnz(M) + d1 operations) ...
@@ -293,7 +321,8 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             base = spec.lmid.group_off[p.gm] + p.u_off
             for k in range(2 * p.l3 + 1):
                 for c in range(G.cpw):
-                    st = f'orow[{base + k * Mg + c * 32}] = a{pi}_{k}{_sx(G, c)} * inv_denom;'
+                    acc = f'a{pi}_{k}.{"xy"[c]}' if f2 else f'a{pi}_{k}{_sx(G, c)}'
+                    st = f'orow[{base + k * Mg + c * 32}] = {acc} * inv_denom;'
                     L.append(f'    if (on) {st}' if G.masked else f'    {st}')
         L.append('  }')
     L.append('UNIT_LOOP_END')
@@ -337,13 +366,23 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
                 for c in range(G.cpw):
                     ld = _on(G, f'LDG(grow + {base + k * Mg + c * 32}) * inv_denom')
                     L.append(f'    const float g{pi}_{k}{_sx(G, c)} = {ld};')
+                if tab and TAB_F2 and G.cpw == 2:
+                    L.append(f'    const float2 g{pi}_{k} = make_float2(g{pi}_{k}_a, g{pi}_{k}_b);')
         if tab:
             _tab_pipeline_open(L, G, spec, True)
         else:
             _pipeline_open(L, G, spec)
         ndy = max(NP, nv_smem)
         L.append(f'        float dyv[{ndy}] = {{{", ".join(["0.f"] * ndy)}}};')
-        L.append('        float ' + ', '.join(f'dx{m}{_sx(G, c)} = 0.f' for m in range(G.d1) for c in range(G.cpw)) + ';')
+        f2 = tab and TAB_F2 and G.cpw == 2
+        if f2:
+            L.append('        float2 ' + ', '.join(f'dx{m} = make_float2(0.f, 0.f)' for m in range(G.d1)) + ', gr2 = make_float2(0.f, 0.f);')
+            for m in range(G.d1):
+                L.append(f'        const float2 x{m} = make_float2(x{m}_a, x{m}_b);')
+            for pi, p in G.paths:
+                L.append(f'        const float2 w{pi} = make_float2(w{pi}_a, w{pi}_b), wd{pi} = make_float2(wd{pi}_a, wd{pi}_b);')
+        else:
+            L.append('        float ' + ', '.join(f'dx{m}{_sx(G, c)} = 0.f' for m in range(G.d1) for c in range(G.cpw)) + ';')
         if tab:
             L.append('        float gr = 0.f;')
         else:
@@ -358,7 +397,22 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}')
             _emit_M(L, ent, p.l2, '          ')
             rows = [i for i in range(G.d1) if any((i, k) in ent for k in range(2 * p.l3 + 1))]
-            for c in range(G.cpw):
+            if f2:
+                for i in rows:
+                    kk = [k for k in range(2 * p.l3 + 1) if (i, k) in ent]
+                    t = f'__fmul2_rn(F2B(M_{i}_{kk[0]}), g{pi}_{kk[0]})'
+                    for k in kk[1:]:
+                        t = f'__ffma2_rn(F2B(M_{i}_{k}), g{pi}_{k}, {t})'
+                    L.append(f'          const float2 q{i} = {t};')
+                    L.append(f'          dx{i} = __ffma2_rn(w{pi}, q{i}, dx{i});')
+                if rows:
+                    t = f'__fmul2_rn(x{rows[0]}, q{rows[0]})'
+                    for i in rows[1:]:
+                        t = f'__ffma2_rn(x{i}, q{i}, {t})'
+                    L.append(f'          gr2 = __ffma2_rn({t}, wd{pi}, gr2);')
+                for i in rows:
+                    L.append(f'          const float2 X{i} = __fmul2_rn(w{pi}, x{i});')
+            for c in range(0 if f2 else G.cpw):
                 sx = _sx(G, c)
                 for i in rows:
                     terms = [f'M_{i}_{k}*g{pi}_{k}{sx}' for k in range(2 * p.l3 + 1) if (i, k) in ent]
@@ -375,6 +429,10 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
                     L.append(f'          const float X{i}{sx} = w{pi}{sx} * x{i}{sx};')
             # the two chunks of a warp share c_ijk: their products are added before the coefficient is applied
             for (i, k) in ent:
+                if f2:
+                    L.append(f'          const float2 PP_{i}_{k} = __fmul2_rn(X{i}, g{pi}_{k});')
+                    L.append(f'          const float P_{i}_{k} = PP_{i}_{k}.x + PP_{i}_{k}.y;')
+                    continue
                 L.append(f'          const float P_{i}_{k} = ' +
                          ' + '.join(f'X{i}{_sx(G, c)} * g{pi}_{k}{_sx(G, c)}' for c in range(G.cpw)) + ';')
             for (i, j, k, cf) in nnz:
@@ -387,9 +445,12 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
                     L.append(f'          dyv[{q}] = fmaf({_f(cf)}, P_{i}_{k}, dyv[{q}]);')
             L.append('        }')
         L.append(f'        float* dxr = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
+        if f2:
+            L.append('        gr = gr2.x + gr2.y;')
         for m in range(G.d1):
             for c in range(G.cpw):
-                st = f'dxr[{m * G.mul + c * 32}] = dx{m}{_sx(G, c)};'
+                val = f'dx{m}.{"xy"[c]}' if f2 else f'dx{m}{_sx(G, c)}'
+                st = f'dxr[{m * G.mul + c * 32}] = {val};'
                 L.append(f'        if (on) {st}' if G.masked else f'        {st}')
         if gr_in_butterfly:
             L.append(f'        dyv[{S}] = gr;')

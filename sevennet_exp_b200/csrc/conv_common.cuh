@@ -5,6 +5,8 @@
 #include <cstddef>
 #include <cmath>
 
+// warp-uniform scalar as both halves of a packed pair (a free broadcast operand of FFMA2 / FMUL2)
+#define F2B(v) make_float2((v), (v))
 #ifndef SEVENN_EMU
 #include <cuda_runtime.h>
 #define CONV_WARPS_PER_CTA 4
@@ -119,6 +121,11 @@ static inline void sevenn_dy_accumulate_smem(const float* v, int lane, float*, f
   for (int q = 0; q < NV; ++q) dst[q] += v[q];
 }
 struct float4 { float x, y, z, w; };
+// packed fp32 pairs (fma.rn.f32x2 on the device): component-wise single roundings, like the instruction
+struct float2 { float x, y; };
+static inline float2 make_float2(float x, float y) { float2 r = {x, y}; return r; }
+static inline float2 __ffma2_rn(float2 a, float2 b, float2 c) { return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
+static inline float2 __fmul2_rn(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
 #define UNIT_LOOP_BEGIN_DYN(n, nunits, ringf) UNIT_LOOP_BEGIN(n, nunits, ringf)
 #define LAUNCH_DYN(kern, n, nunits, ringf, stream) kern
 #define LAUNCH(kern, n, nunits, stream) kern

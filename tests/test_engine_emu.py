@@ -66,6 +66,26 @@ def test_engine_emu_so3_random_weights(name):
     print(_compare(cfg, model.state_dict(), numbers, pos, cell, [True] * 3, model))
 
 
+@pytest.mark.parametrize('packed', [False, True])
+def test_engine_emu_two_chunk_units(monkeypatch, packed):
+    """64 scalar channels: the tabulated kernels give one warp both 32-channel chunks of the l = 0 group
+    (conv_codegen.TAB_CPW; this is the SevenNet-0 / l3i5 situation, the small presets have one chunk per group).
+    packed = SEVENN_TAB_F2: the chunk pair's per-channel arithmetic as packed pairs (__ffma2_rn / __fmul2_rn;
+    component-wise fmaf in the emulation build).  Same parity gates as everything else."""
+    from sevennet_exp_b200.codegen import conv_codegen
+    monkeypatch.setattr(conv_codegen, 'TAB_F2', packed)
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg['irreps_manual'] = ['64x0e', '64x0e+32x1e+32x2e', '64x0e+32x1e+32x2e', '32x0e']
+    cfg['channel'] = 64
+    conv = sp.build_spec(cfg).layers[1].conv
+    assert [G.cpw for G in conv_codegen.make_groups(conv, True)] == [2, 1, 1]
+    assert ('float2' in conv_codegen.generate(conv)) == packed
+    torch.manual_seed(777)
+    model = S.build_model(cfg).eval()
+    numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=4)
+    print(_compare(cfg, model.state_dict(), numbers, pos, cell, [True] * 3, model))
+
+
 def test_engine_emu_reference_deployed_torchscript(golden_dir):
     """The reference's frozen TorchScript artefact (deployed_serial.pt): its weights, its frame -> our engine
     (emulation build) must give ITS outputs (tests/golden/deployed_serial_hfo2.npz), no oracle in between."""
