@@ -273,8 +273,6 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
         if f2:
             for m in range(G.d1):
                 L.append(f'        const float2 x{m} = make_float2(x{m}_a, x{m}_b);')
-            for pi, p in G.paths:
-                L.append(f'        const float2 w{pi} = make_float2(w{pi}_a, w{pi}_b);')
         for pi, p in G.paths:
             ent, _ = _m_terms(p.l1, p.l2, p.l3)
             L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}, mul {p.mul}')
@@ -379,8 +377,6 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append('        float2 ' + ', '.join(f'dx{m} = make_float2(0.f, 0.f)' for m in range(G.d1)) + ', gr2 = make_float2(0.f, 0.f);')
             for m in range(G.d1):
                 L.append(f'        const float2 x{m} = make_float2(x{m}_a, x{m}_b);')
-            for pi, p in G.paths:
-                L.append(f'        const float2 w{pi} = make_float2(w{pi}_a, w{pi}_b), wd{pi} = make_float2(wd{pi}_a, wd{pi}_b);')
         else:
             L.append('        float ' + ', '.join(f'dx{m}{_sx(G, c)} = 0.f' for m in range(G.d1) for c in range(G.cpw)) + ';')
         if tab:
@@ -686,16 +682,52 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
     # cubic Hermite basis (and its derivative) at t
     L.append('        const float u = 1.f - t, tt = t * t, uu = u * u;')
     L.append('        const float h00 = (1.f + 2.f * t) * uu, h10 = t * uu, h01 = tt * (3.f - 2.f * t), h11 = -tt * u;')
-    for pi, p in G.paths:
-        for c in range(G.cpw):
-            T = f'T{pi}{_sx(G, c)}'
-            L.append(f'        const float w{pi}{_sx(G, c)} = fmaf({T}.x, h00, fmaf({T}.y, h10, fmaf({T}.z, h01, {T}.w * h11)));')
-    if bwd:
-        L.append('        const float d00 = -6.f * t * u, d10 = u * (1.f - 3.f * t), d11 = t * (3.f * t - 2.f);')
+    f2 = TAB_F2 and G.cpw == 2
+    if f2:
+        # packed table layout of a channel pair (pack_table): T_a = (f_i, f_i', h f'_i, h f'_i'), T_b = the same at node
+        # i + 1 -- the halves of each 16-byte load are register pairs, the Hermite basis a free broadcast operand
+        for pi, p in G.paths:
+            A, B = f'T{pi}_a', f'T{pi}_b'
+            L.append(f'        const float2 w{pi} = __ffma2_rn(make_float2({A}.x, {A}.y), F2B(h00), '
+                     f'__ffma2_rn(make_float2({A}.z, {A}.w), F2B(h10), __ffma2_rn(make_float2({B}.x, {B}.y), F2B(h01), '
+                     f'__fmul2_rn(make_float2({B}.z, {B}.w), F2B(h11)))));')
+    else:
         for pi, p in G.paths:
             for c in range(G.cpw):
                 T = f'T{pi}{_sx(G, c)}'
+                L.append(f'        const float w{pi}{_sx(G, c)} = fmaf({T}.x, h00, fmaf({T}.y, h10, fmaf({T}.z, h01, {T}.w * h11)));')
+    if bwd:
+        L.append('        const float d00 = -6.f * t * u, d10 = u * (1.f - 3.f * t), d11 = t * (3.f * t - 2.f);')
+        if f2:
+            L.append('        const float nd00 = -d00;')
+        for pi, p in G.paths:
+            if f2:
+                A, B = f'T{pi}_a', f'T{pi}_b'
+                L.append(f'        const float2 wd{pi} = __ffma2_rn(make_float2({A}.x, {A}.y), F2B(d00), '
+                         f'__ffma2_rn(make_float2({B}.x, {B}.y), F2B(nd00), __ffma2_rn(make_float2({A}.z, {A}.w), F2B(d10), '
+                         f'__fmul2_rn(make_float2({B}.z, {B}.w), F2B(d11)))));')
+                continue
+            for c in range(G.cpw):
+                T = f'T{pi}{_sx(G, c)}'
                 L.append(f'        const float wd{pi}{_sx(G, c)} = fmaf(d00, {T}.x - {T}.z, fmaf(d10, {T}.y, d11 * {T}.w));')
+
+
+def pack_table(spec: ConvSpec, tab):
+    """Table layout the packed (TAB_F2) kernels read: for every channel pair (c, c' = c + 32) of a two-chunk unit the
+    two float4 (f_i, g_i, f_i+1, g_i+1)[c], [c'] become (f_i[c], f_i[c'], g_i[c], g_i[c']) at column c and the same
+    at node i + 1 at column c'.  ``tab``: numpy [n_int, wn, 4]; returns a new array."""
+    out = tab.copy()
+    for G in make_groups(spec, tab=True):
+        if G.cpw != 2:
+            continue
+        for pi, p in G.paths:
+            for o in range(p.w_off, p.w_off + G.mul, 64):
+                A, B = tab[:, o:o + 32, :], tab[:, o + 32:o + 64, :]
+                out[:, o:o + 32, 0], out[:, o:o + 32, 1] = A[..., 0], B[..., 0]
+                out[:, o:o + 32, 2], out[:, o:o + 32, 3] = A[..., 1], B[..., 1]
+                out[:, o + 32:o + 64, 0], out[:, o + 32:o + 64, 1] = A[..., 2], B[..., 2]
+                out[:, o + 32:o + 64, 2], out[:, o + 32:o + 64, 3] = A[..., 3], B[..., 3]
+    return out
 
 
 def signature(spec: ConvSpec) -> str:
@@ -747,4 +779,7 @@ def generate(spec: ConvSpec) -> str:
     out.append(f'extern "C" int sevenn_conv_info_{sig}(int* x_dim, int* mid_dim, int* wn, int* sh_dim, int* units) {{')
     out.append(f'  *x_dim = {spec.lx.dim}; *mid_dim = {spec.lmid.dim}; *wn = {spec.wn}; *sh_dim = {(spec.lmax_sh + 1) ** 2};')
     out.append(f'  *units = {nu}; return 0; }}')
+    packed = int(TAB_F2 and any(G.cpw == 2 for G in groups_tab))
+    out.append(f'// 1: the tabulated kernels of this unit read the packed channel-pair table layout (conv_codegen.pack_table)')
+    out.append(f'extern "C" int sevenn_conv_tab_packed_{sig}() {{ return {packed}; }}')
     return '\n'.join(out) + '\n'

@@ -346,9 +346,13 @@ class Engine(Kernels):
                     t_first = False
                 rc_t = spec.multi_cutoff[L.t] if spec.multi_cutoff else spec.cutoff
                 r_on_t = (rc_t - 1.0) if (spec.multi_cutoff and xplor) else spec.cutoff_on   # edge_embedding.py:244-246
-                lay['tab'] = f32(radial_table.build_table(
+                tab_np = radial_table.build_table(
                     sd[spec.coeff_key(L.t)], spec.cutoff_fn, rc_t, spec.cutoff_p, r_on_t, Wm, spec.act_radial,
-                    ir.normalize2mom_const(spec.act_radial), self.tab_n, grid_rc=spec.cutoff))
+                    ir.normalize2mom_const(spec.act_radial), self.tab_n, grid_rc=spec.cutoff)
+                packed = getattr(self.lib.cdll, f'sevenn_conv_tab_packed_{lay["sig"]}', None)
+                if packed is not None and packed():          # the library says which layout its kernels read
+                    tab_np = conv_codegen.pack_table(L.conv, tab_np)
+                lay['tab'] = f32(tab_np)
             if not self.lib.has_conv(lay['sig']):
                 raise _lib.SevennError(
                     f"no prebuilt conv kernel for signature {lay['sig']} ({ir.irreps_str(L.conv.lx.groups)}); "
