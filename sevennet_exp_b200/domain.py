@@ -17,6 +17,7 @@ SevenNet patch of ``CommBrick`` (sevenn/pair_e3gnn/comm_brick.cpp:1057-1123):
 """
 import ctypes
 import os
+import sys
 from typing import List, Optional
 
 import numpy as np
@@ -121,7 +122,7 @@ class Halo:
             except Exception as e:                      # no peer access between these GPUs: NCCL carries the rows
                 if mode == 'p2p':
                     raise
-                print(f'[halo rank {self.rank}] peer-memory halo unavailable ({e}); using NCCL', flush=True)
+                print(f'[halo rank {self.rank}] peer-memory halo unavailable ({e}); using NCCL', file=sys.stderr, flush=True)
                 self.peer = None
 
     # ---- peer-memory halo (NVLink / NVSwitch): every rank owns a symmetric staging area of two slots; a sender
