@@ -124,6 +124,11 @@ class Halo:
                     raise
                 print(f'[halo rank {self.rank}] peer-memory halo unavailable ({e}); using NCCL', file=sys.stderr, flush=True)
                 self.peer = None
+            # every rank must use the same transport: one failed rendezvous sends all of them to NCCL
+            ok = torch.tensor([1 if self.peer is not None else 0], dtype=torch.int32, device=self.dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()) == 0:
+                self.peer = None
 
     # ---- peer-memory halo (NVLink / NVSwitch): every rank owns a symmetric staging area of two slots; a sender
     # packs its rows straight into the receiver's slot (one kernel for all peers), a device-side barrier over the
