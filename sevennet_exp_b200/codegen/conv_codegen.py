@@ -8,7 +8,8 @@ structural zeros disappear at generation time.
 
 Mapping (both directions): one warp per (destination atom, unit) where a unit
 is a 32-channel chunk of one input-irrep group (SevenNet-0: 4 + 2 + 1 = 7 units
-per atom); lanes run over the chunk's channels u, the destination row's
+per atom; the tabulated kernels give one warp two chunks of the scalar group:
+2 + 2 + 1 = 5, see make_groups); lanes run over the chunk's channels u, the destination row's
 accumulators live in registers, the warp walks the dst-sorted CSR row, so the
 reduction over edges needs no atomics and is bit-reproducible.  All units run
 in one launch (blockIdx.y = unit).  The edge loop is software pipelined: the
