@@ -31,6 +31,31 @@ def test_properties_with_oracle_backend():
     print(out)
 
 
+def test_properties_fp32_emulation_bench_model():
+    """The bench model (SevenNet-0 shape, bench.random_state_dict) on a 96-atom HfO2 cell through the fp32 EMULATION build
+    of the kernel sources: the same tolerances the full-size GPU test uses hold with a wide margin."""
+    import bench as B
+    from sevennet_exp_b200 import spec as sp
+    from sevennet_exp_b200.engine import Engine
+    from tests.emu_util import build_full_emu, graph_from_edges
+    cfg = B.model_config()
+    spec = sp.build_spec(cfg)
+    eng = Engine(spec, B.random_state_dict(cfg), lib=build_full_emu([L.conv for L in spec.layers]), device='cpu',
+                 radial='table')
+    tmap = cfg['_type_map']
+
+    def compute(numbers, pos, cell):
+        g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+        types, vol = np.array([tmap[int(z)] for z in numbers]), float(g[S.VOL])
+        out = eng.evaluate(graph_from_edges(types, g[S.EDGE_IDX].numpy(), g[S.EDGE_VEC].detach().numpy(),
+                                            len(numbers), vol))
+        return {'energy': out['energy'].item(), 'forces': out['forces'].double().numpy(),
+                'inferred_stress': -(out['virial6'].numpy() / vol), 'n_edges': g[S.EDGE_IDX].shape[1]}
+
+    numbers, pos, cell = B.workload(reps=(2, 2, 2), n_remove=0)
+    print(check_properties(compute, numbers, pos, cell, tol_e=2e-6, tol_f=2e-5, tol_s_kbar=2e-3))
+
+
 @pytest.mark.gpu
 def test_properties_full_size_cfg2_on_gpu():
     """BASELINE config 2 at full size (the bench workload): 4,096-atom HfO2, SevenNet-0 hyper-parameters."""
