@@ -70,3 +70,18 @@ def test_properties_full_size_cfg2_on_gpu():
     out = check_properties(lambda z, x, c: calc.compute(z, x, c, [True] * 3), numbers, pos, cell,
                            tol_e=2e-6, tol_f=2e-5, tol_s_kbar=2e-3)
     print(out)
+
+
+@pytest.mark.gpu
+def test_properties_full_size_cfg3_on_gpu():
+    """BASELINE config 3 at full size: SevenNet-l3i5 hyper-parameters (lmax 3), 32,768-atom disordered Li-P-S cell."""
+    import bench as B
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    from tests.structures import jittered_lips
+    cfg = dict(presets.PRESETS['7net-l3i5'])
+    calc = SevenNetCalculator((cfg, B.random_state_dict(cfg)), file_type='model_instance')
+    numbers, pos, cell = jittered_lips()
+    assert len(numbers) == 32768
+    out = check_properties(lambda z, x, c: calc.compute(z, x, c, [True] * 3), numbers, pos, cell,
+                           tol_e=2e-6, tol_f=2e-5, tol_s_kbar=2e-3)
+    print(out)
