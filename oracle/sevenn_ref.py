@@ -27,6 +27,7 @@ FORCE, STRESS = 'inferred_force', 'inferred_stress'
 POS, CELL, SHIFT, VOL, NATOMS, BATCH, NLOCAL = (
     'pos', 'cell_lattice_vectors', 'pbc_shift', 'cell_volume', 'num_atoms', 'batch', 'nlocal')
 Z = 'atomic_numbers'
+MODAL_TYPE, MODAL_ATTR = 'modal_type', 'modal_attr'
 
 
 def shifted_softplus(x):
@@ -184,16 +185,25 @@ class OnehotEmbedding(nn.Module):
 
 
 class IrrepsLinear(nn.Module):
-    """sevenn/nn/linear.py:14-100 (no modality)"""
+    """sevenn/nn/linear.py:14-100.  num_modalities > 1 (:65-92): the modality one-hot (data['modal_attr'], one row
+    for the whole structure) is appended to the input as extra 0e channels."""
 
-    def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, biases=False):
+    def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, biases=False, num_modalities=0):
         super().__init__()
         self.key_input, self.key_output = data_key_in, data_key_out or data_key_in
-        self.irreps_in, self.irreps_out = Irreps(irreps_in), Irreps(irreps_out)
-        self.linear = o3.Linear(irreps_in, irreps_out, biases=biases)
+        self.num_modalities = num_modalities
+        irreps_in = Irreps(irreps_in)
+        if num_modalities > 1:
+            irreps_in = irreps_in + Irreps(f'{num_modalities}x0e')
+        self.irreps_in, self.irreps_out = irreps_in, Irreps(irreps_out)
+        self.linear = o3.Linear(self.irreps_in, irreps_out, biases=biases)
 
     def forward(self, data):
-        data[self.key_output] = self.linear(data[self.key_input])
+        x = data[self.key_input]
+        if self.num_modalities > 1:
+            onehot = data[MODAL_ATTR].reshape(1, self.num_modalities).to(x.dtype).expand(len(x), -1)
+            x = torch.cat([x, onehot], dim=1)
+        data[self.key_output] = self.linear(x)
         return data
 
 
@@ -331,6 +341,23 @@ class SpeciesWiseRescale(nn.Module):
     def forward(self, data):
         idx = data[ATOM_TYPE]
         data[AE] = data[SCALED_AE] * self.scale[idx].view(-1, 1) + self.shift[idx].view(-1, 1)
+        return data
+
+
+class ModalWiseRescale(nn.Module):
+    """sevenn/nn/scale.py:165-330: shift / scale are [n_modal, n_types] where modal wise, else [n_types]."""
+
+    def __init__(self, shift, scale, use_modal_wise_shift, use_modal_wise_scale, train_shift_scale=False):
+        super().__init__()
+        self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=train_shift_scale)
+        self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=train_shift_scale)
+        self.mw_shift, self.mw_scale = use_modal_wise_shift, use_modal_wise_scale
+
+    def forward(self, data):
+        idx, m = data[ATOM_TYPE], int(data[MODAL_TYPE])
+        shift = (self.shift[m] if self.mw_shift else self.shift)[idx]
+        scale = (self.scale[m] if self.mw_scale else self.scale)[idx]
+        data[AE] = data[SCALED_AE] * scale.view(-1, 1) + shift.view(-1, 1)
         return data
 
 
@@ -499,8 +526,13 @@ def build_model(config, parallel=False):
     layers['edge_embedding'] = ee
     irreps_x = Irreps(f'{C}x0e') if manual is None else manual[0]
     layers['onehot_idx_to_onehot'] = OnehotEmbedding(S, X, X, ATOM_TYPE, NODE_ATTR)
+    nm = cfg.get('_number_of_modalities', 0) if cfg.get('use_modality', False) else 0     # model_build.py:198-244
+    m_emb, m_si1 = (nm if cfg.get(k, False) else 0 for k in ('use_modal_node_embedding', 'use_modal_self_inter_intro'))
+    m_si2, m_out = (nm if cfg.get(k, False) else 0 for k in ('use_modal_self_inter_outro', 'use_modal_output_block'))
+    if nm:
+        layers['one_hot_modality'] = OnehotEmbedding(nm, MODAL_TYPE, MODAL_ATTR)
     layers['onehot_to_feature_x'] = IrrepsLinear(Irreps(f'{S}x0e'), irreps_x, X,
-                                                 biases=cfg['use_bias_in_linear'])
+                                                 biases=cfg['use_bias_in_linear'], num_modalities=m_emb)
     multi = cfg.get('multi_cutoff') or None
     basis0 = ee.basis_functions[0] if multi else ee.basis_function
     wnn = [basis0.num_basis] + list(cfg['weight_nn_hidden_neurons'])
@@ -517,7 +549,7 @@ def build_model(config, parallel=False):
         gate_in = gate.get_gate_irreps_in()
         layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, Irreps(f'{S}x0e'), gate_in)
         layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X,
-                                                         biases=cfg['use_bias_in_linear'])
+                                                         biases=cfg['use_bias_in_linear'], num_modalities=m_si1)
         ckeys = {}
         if multi:                                        # interaction_blocks.py:54-60
             ckeys = dict(data_key_filter=f'{EDGE_ATTR}{multi[t]}', data_key_weight_input=f'{EDGE_EMB}{multi[t]}',
@@ -526,18 +558,23 @@ def build_model(config, parallel=False):
             irreps_x, irreps_filter, irreps_out_tp, wnn, act_radial, denom[t],
             cfg['train_denominator'], is_parallel=parallel, **ckeys)
         layers[f'{t}_self_interaction_2'] = IrrepsLinear(
-            layers[f'{t}_convolution'].irreps_mid, gate_in, X, biases=cfg['use_bias_in_linear'])
+            layers[f'{t}_convolution'].irreps_mid, gate_in, X, biases=cfg['use_bias_in_linear'], num_modalities=m_si2)
         layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()
         layers[f'{t}_equivariant_gate'] = gate
         irreps_x = irreps_out
     hidden = Irreps([(irreps_x.dim // 2, (0, 1))])
-    layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X, biases=cfg['use_bias_in_linear'])
+    layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X, biases=cfg['use_bias_in_linear'],
+                                                    num_modalities=m_out)
     layers['reduce_hidden_to_energy'] = IrrepsLinear(hidden, Irreps('1x0e'), X, SCALED_AE,
                                                      biases=cfg['use_bias_in_linear'])
     shift, scale = cfg['shift'], cfg['scale']
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale
-    if isinstance(shift, float) and isinstance(scale, float):
+    if nm:                                               # model_build.py:173-184 (values already per modal / type)
+        layers['rescale_atomic_energy'] = ModalWiseRescale(
+            shift, scale, cfg.get('use_modal_wise_shift', False), cfg.get('use_modal_wise_scale', False),
+            cfg['train_shift_scale'])
+    elif isinstance(shift, float) and isinstance(scale, float):
         layers['rescale_atomic_energy'] = Rescale(shift, scale, cfg['train_shift_scale'])
     else:
         shift = shift * S if isinstance(shift, list) and len(shift) == 1 else shift

@@ -61,21 +61,24 @@ def _plain_sd(sd):
 
 
 def deploy(checkpoint, fname: str = 'deployed_serial.pt', modal: Optional[str] = None) -> str:
-    """sevenn/scripts/deploy.py:20-70."""
-    if modal is not None:
-        raise NotImplementedError('multi-modal checkpoints are outside this hot path')
+    """sevenn/scripts/deploy.py:20-70.  ``modal`` (:31-36): the modality a multi-modal checkpoint is frozen to."""
     spec, sd, cfg = _resolve(checkpoint)
+    if spec.n_modal:
+        if modal is None or modal not in (spec.modal_map or {}):
+            raise ValueError(f'modal must be one of {list(spec.modal_map or {})} for this checkpoint')
+    elif modal is not None:
+        raise ValueError('Modality given, but model has no modal_map')
     if not fname.endswith('.pt'):
         fname += '.pt'
     torch.save({'format': SERIAL_FORMAT, 'config': {**cfg, 'version': '0.11.0'}, 'model_state_dict': _plain_sd(sd),
-                'extra_files': extra_files(cfg, spec)}, fname)
+                'extra_files': extra_files(cfg, spec), 'modal': modal}, fname)
     return fname
 
 
 def deploy_parallel(checkpoint, fname: str = 'deployed_parallel', modal: Optional[str] = None) -> str:
     """sevenn/scripts/deploy.py:73-148: a directory of `deployed_parallel_{i}.pt`, one per segment."""
     if modal is not None:
-        raise NotImplementedError('multi-modal checkpoints are outside this hot path')
+        raise NotImplementedError('multi-modal checkpoints: serial deployment only (deploy(..., modal=...))')
     spec, sd, cfg = _resolve(checkpoint)
     comm = max(L.conv.lx.dim for L in spec.layers)          # widest ghost row exchanged (`_comm_size`)
     md = extra_files(cfg, spec, comm_size=comm)
@@ -92,13 +95,13 @@ class DeployedSerial:
     """Callable with the serial deployed-model contract; also usable as SevenNetCalculator(file_type='torchscript')."""
 
     def __init__(self, cfg: dict, sd: dict, device='cuda', extra: Optional[Dict[str, str]] = None, lib=None,
-                 radial: Optional[str] = None):
+                 radial: Optional[str] = None, modal: Optional[str] = None):
         from .engine import Engine
         cfg = patch_old_config(dict(cfg))
         self.spec = build_spec(cfg)
         self.config = cfg
         self.device = torch.device(device)
-        self.engine = Engine(self.spec, sd, lib=lib, device=self.device, radial=radial)
+        self.engine = Engine(self.spec, sd, lib=lib, device=self.device, radial=radial, modal=modal)
         self.extra_files = dict(extra) if extra is not None else extra_files(cfg, self.spec)
         self.cutoff, self.type_map = self.spec.cutoff, self.spec.type_map
 
@@ -229,7 +232,8 @@ def load_deployed(path: str, device='cuda', lib=None):
         raise ValueError(f'{path}: not a sevennet_exp_b200 deployed bundle ({e})') from e
     fmt = b.get('format') if isinstance(b, dict) else None
     if fmt == SERIAL_FORMAT:
-        m = DeployedSerial(b['config'], b['model_state_dict'], device=device, extra=b['extra_files'], lib=lib)
+        m = DeployedSerial(b['config'], b['model_state_dict'], device=device, extra=b['extra_files'], lib=lib,
+                           modal=b.get('modal'))
     elif fmt == PARALLEL_FORMAT:
         m = DeployedParallel(b['config'], b['model_state_dict'], device=device, extra=b['extra_files'])
     else:

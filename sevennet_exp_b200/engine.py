@@ -72,9 +72,15 @@ def tc_image_for(lib, W: np.ndarray) -> np.ndarray:
 class _Lin:
     """Device weights of one o3.Linear (or nequip FCTP) in block form."""
 
-    def __init__(self, spec: LinearSpec, flat: np.ndarray, dev, by_type_S: int = 0):
+    def __init__(self, spec: LinearSpec, flat: np.ndarray, dev, by_type_S: int = 0, modal: int = 0, bias=None):
         self.spec, self.by_type = spec, by_type_S
         self.W, self.WT = [], []
+        # constant row of the scalar blocks: fixed modality one-hot (sevenn/nn/linear.py:65-92) and / or o3.Linear bias
+        self.const = []
+        for b in spec.blocks:
+            row = None if by_type_S else spec.constant_row(np.asarray(flat, dtype=np.float64), b, modal, bias)
+            self.const.append(None if row is None else torch.tensor(row, dtype=torch.float32, device=dev))
+        self.has_const = any(c is not None for c in self.const)
         for b in spec.blocks:
             if by_type_S:
                 w = nequip_sc_dense(spec, flat, b, by_type_S)              # [S,K,N]
@@ -213,6 +219,11 @@ class Kernels:
                               n * R, R, b.N, b.K, 1 if accumulate else 0))
         if items:
             self._gemm_group(items)
+        if getattr(lin, 'has_const', False):
+            for b, c in zip(sp.blocks, lin.const):
+                if c is not None:            # l = 0 block: N contiguous columns per row
+                    o = sp.lout.group_off[b.g_out] + b.u_off_out
+                    y[:n, o:o + b.N] += c
 
     def _linear_bwd(self, lin: _Lin, dy, n, dx, accumulate=False, types=None):
         """dx (+)= dy @ W^T ; dx must be zero-initialised by the caller when lin.bwd_needs_zero."""
@@ -278,7 +289,7 @@ class Kernels:
 
 class Engine(Kernels):
     def __init__(self, spec: ModelSpec, state_dict: Dict[str, torch.Tensor], lib: Optional[_lib.Lib] = None,
-                 device='cuda', keep_weights: bool = True, radial: Optional[str] = None):
+                 device='cuda', keep_weights: bool = True, radial: Optional[str] = None, modal=None):
         """radial: 'table' (default) interpolates the radial weight function from per-layer tables built here
         (radial_table.py); 'mlp' evaluates the radial MLP per edge with the GEMM kernels, as the nn modules do.
         Non-smooth radial activations (abs, relu) always take 'mlp'."""
@@ -301,6 +312,21 @@ class Engine(Kernels):
                 raise ValueError(f'{k}: shape {sd[k].shape} != expected {shp}')
         dev = self.dev
         f32 = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32, device=dev).contiguous()  # noqa: E731
+        # modality (SevenNet-MF style checkpoints): fixed per engine, like the reference calculator's `modal` argument
+        if spec.n_modal:
+            if isinstance(modal, str):
+                if modal not in (spec.modal_map or {}):
+                    raise ValueError(f'Unknown modal {modal} (not in {list(spec.modal_map or {})})')
+                modal = spec.modal_map[modal]
+            if modal is None or not 0 <= int(modal) < spec.n_modal:
+                raise ValueError('modal must be given for a multi-modal checkpoint')
+            m_idx = int(modal)
+        else:
+            if modal is not None:
+                raise ValueError('Modality given, but model has no modal_map')
+            m_idx = 0
+        self.modal = m_idx
+        bias_of = lambda lin: (sd[lin.bias_key] if lin.n_bias else None)  # noqa: E731
         if spec.multi_cutoff:
             if self.radial != 'table':
                 raise NotImplementedError("multi_cutoff models run with radial='table' (per-layer tables on one grid)")
@@ -314,6 +340,9 @@ class Engine(Kernels):
             assert b.l == 0
             o = emb.lout.group_off[b.g_out] + b.u_off_out
             table[:, o:o + b.N] = emb.dense(sd[emb.key], b)
+            row = emb.constant_row(np.asarray(sd[emb.key], dtype=np.float64), b, m_idx, bias_of(emb))
+            if row is not None:
+                table[:, o:o + b.N] += row
         self.embed_table = f32(table)
         self.d0 = emb.lout.dim
         self.layers = []
@@ -324,8 +353,8 @@ class Engine(Kernels):
             lay = {
                 'spec': L,
                 'sc': _Lin(L.sc, sd[L.sc.key], dev, spec.n_species if L.sc_type == 'nequip' else 0),
-                'si1': _Lin(L.si1, sd[L.si1.key], dev),
-                'si2': _Lin(L.si2, sd[L.si2.key], dev),
+                'si1': _Lin(L.si1, sd[L.si1.key], dev, 0, m_idx, bias_of(L.si1)),
+                'si2': _Lin(L.si2, sd[L.si2.key], dev, 0, m_idx, bias_of(L.si2)),
                 'mlp': [f32(w) for w in Wm],
                 'mlpT': [f32(np.ascontiguousarray(w.T)) for w in Wm],
                 'inv_denom': 1.0 / float(sd[f'{L.conv.name}.denominator'][0]),
@@ -370,10 +399,11 @@ class Engine(Kernels):
             self.mlp_w1cat = f32(W1)
             self.mlp_w1catT = f32(np.ascontiguousarray(W1.T))
             self.mlp_h1 = hs[0][1]
-        self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev)
-        self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev)
-        self.scale = f32(sd['rescale_atomic_energy.scale'])
-        self.shift = f32(sd['rescale_atomic_energy.shift'])
+        self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev, 0, m_idx, bias_of(spec.read1))
+        self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev, 0, m_idx, bias_of(spec.read2))
+        scale, shift = sd['rescale_atomic_energy.scale'], sd['rescale_atomic_energy.shift']
+        self.scale = f32(scale[m_idx] if spec.modal_wise_scale else scale)      # ModalWiseRescale, nn/scale.py:165-330
+        self.shift = f32(shift[m_idx] if spec.modal_wise_shift else shift)
         self.act_radial = ACT_ID[spec.act_radial]
         self.cst_radial = ir.normalize2mom_const(spec.act_radial)
 

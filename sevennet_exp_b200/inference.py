@@ -227,14 +227,15 @@ def inference(checkpoint, targets: Union[str, List[str], List[dict]], output_dir
     from .sevennet_calculator import SevenNetCalculator
     if save_graph:
         raise NotImplementedError('save_graph: the torch_geometric graph cache (sevenn_data/*.pt) is not part of this package')
-    if modal:
-        raise ValueError('Modality given, but model has no modal_map')      # sevenn/scripts/inference.py:158-163
+    # `modal` (sevenn/scripts/inference.py:158-163): unknown / superfluous modality names raise ValueError in the engine
     if isinstance(checkpoint, SevenNetCalculator) or hasattr(checkpoint, 'compute_batch'):
         calc = checkpoint
+        if modal and getattr(calc, 'modal', None) != modal:
+            raise ValueError(f'calculator was built for modal {getattr(calc, "modal", None)!r}, not {modal!r}')
     elif isinstance(checkpoint, tuple):
-        calc = SevenNetCalculator(checkpoint, file_type='model_instance', device=device)
+        calc = SevenNetCalculator(checkpoint, file_type='model_instance', device=device, modal=modal)
     else:
-        calc = SevenNetCalculator(checkpoint, file_type='checkpoint', device=device)
+        calc = SevenNetCalculator(checkpoint, file_type='checkpoint', device=device, modal=modal)
     if isinstance(targets, str):
         targets = [targets]
     index = data_kwargs.pop('index', None)

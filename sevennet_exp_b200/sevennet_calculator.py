@@ -57,8 +57,6 @@ class SevenNetCalculator(_AseCalculator):
         super().__init__(**kwargs)
         if enable_cueq:
             raise ValueError('enable_cueq: the B200 backend replaces cuEquivariance, not combines with it')
-        if modal is not None:
-            raise NotImplementedError('multi-modal checkpoints are outside this hot path')
         file_type = file_type.lower()
         if file_type not in ('checkpoint', 'model_instance', 'torchscript'):
             raise ValueError('file_type should be checkpoint, model_instance or torchscript')
@@ -71,6 +69,7 @@ class SevenNetCalculator(_AseCalculator):
                 raise ValueError(f'{model}: not a serial model deployed by sevennet_exp_b200.deploy.deploy(); a '
                                  'TorchScript file written by the reference freezes the e3nn graph')
             model, file_type = (b['config'], b['model_state_dict']), 'model_instance'
+            modal = b.get('modal', modal)
         if device == 'auto':
             device = 'cuda'
         self.device = torch.device(device)
@@ -93,7 +92,10 @@ class SevenNetCalculator(_AseCalculator):
         self.sevennet_config = sevennet_config or cfg
         self.spec, self.cutoff = spec, spec.cutoff
         self.type_map = spec.type_map
-        self.engine = Engine(spec, sd, device=self.device, keep_weights=keep_weights)
+        # `modal` (sevennet_calculator.py:36-45,84-95): modality name of a multi-modal checkpoint; the engine folds the
+        # fixed one-hot into constant rows of the scalar blocks and picks the modal-wise shift / scale
+        self.modal = modal
+        self.engine = Engine(spec, sd, device=self.device, keep_weights=keep_weights, modal=modal)
         self.nl = NeighborList(device=self.device)
         lut = -np.ones(120, dtype=np.int64)
         for z, i in self.type_map.items():

@@ -41,6 +41,9 @@ class LinearBlock:
     N: int                    # output multiplicity of this output entry
     u_off_out: int            # column offset inside the output group
     segs: List[Tuple[int, int]]   # (flat weight offset, mul_in) stacked along K
+    fan_extra: int = 0        # modality one-hot channels that also feed this (0e) output: fan_in = K + fan_extra
+    modal_off: int = -1       # flat offset of their [n_modal, N] weights
+    bias_off: int = -1        # offset of this (0e) output entry inside o3.Linear's bias vector
 
 
 @dataclass
@@ -50,14 +53,32 @@ class LinearSpec:
     lout: Layout
     blocks: List[LinearBlock]
     numel: int
+    n_modal: int = 0          # sevenn/nn/linear.py:65-92: the input carries n_modal extra 0e one-hot channels
+    n_bias: int = 0           # o3.Linear(biases=True): one bias per 0e output channel (key + '.bias' next to '.weight')
 
     def dense(self, flat: np.ndarray, block: LinearBlock) -> np.ndarray:
         """[K, N] weight of one block, 1/sqrt(fan_in) folded in."""
         rows = [flat[o:o + m * block.N].reshape(m, block.N) for o, m in block.segs]
-        return np.concatenate(rows, axis=0) / math.sqrt(block.K)
+        return np.concatenate(rows, axis=0) / math.sqrt(block.K + block.fan_extra)
+
+    @property
+    def bias_key(self) -> str:
+        return self.key[:-len('weight')] + 'bias'
+
+    def constant_row(self, flat: np.ndarray, block: LinearBlock, modal: int = 0, bias=None):
+        """What a fixed modality and the bias add to every row of this block's output ([N], or None): the one-hot
+        picks row ``modal`` of the modality weights (normalised like all weights); the bias is added as is."""
+        row = None
+        if block.modal_off >= 0:
+            o = block.modal_off + modal * block.N
+            row = flat[o:o + block.N] / math.sqrt(block.K + block.fan_extra)
+        if block.bias_off >= 0 and bias is not None:
+            b = np.asarray(bias[block.bias_off:block.bias_off + block.N], dtype=np.float64)
+            row = b if row is None else row + b
+        return row
 
 
-def make_linear(key: str, irreps_in, irreps_out) -> LinearSpec:
+def make_linear(key: str, irreps_in, irreps_out, n_modal: int = 0, biases: bool = False) -> LinearSpec:
     lin, lout = Layout(irreps_in), Layout(irreps_out)
     # e3nn instruction order: for i_in, for i_out, if same irrep
     off, table = 0, {}
@@ -66,6 +87,16 @@ def make_linear(key: str, irreps_in, irreps_out) -> LinearSpec:
             if iri == iro:
                 table[(i, o)] = off
                 off += mi * mo
+    # the modality one-hot is the LAST input entry (irreps_in + 'Mx0e'): its instructions close the weight vector
+    modal_tab, bias_tab, b_off = {}, {}, 0
+    for o, (mo, iro) in enumerate(lout.entries):
+        if tuple(iro) == (0, 1):
+            if n_modal > 1:
+                modal_tab[o] = off
+                off += n_modal * mo
+            if biases:
+                bias_tab[o] = b_off
+                b_off += mo
     blocks = []
     for o, (mo, iro) in enumerate(lout.entries):
         segs = [(table[(i, o)], mi) for i, (mi, iri) in enumerate(lin.entries) if iri == iro]
@@ -74,8 +105,11 @@ def make_linear(key: str, irreps_in, irreps_out) -> LinearSpec:
         K = sum(m for _, m in segs)
         g_in = lin.group_of(iro)
         assert lin.groups[g_in][0] == K, 'inputs of one irrep must be contiguous'
-        blocks.append(LinearBlock(iro[0], g_in, lout.entry_group[o], K, mo, lout.entry_uoff[o], segs))
-    return LinearSpec(key, lin, lout, blocks, off)
+        blocks.append(LinearBlock(iro[0], g_in, lout.entry_group[o], K, mo, lout.entry_uoff[o], segs,
+                                  fan_extra=n_modal if o in modal_tab else 0, modal_off=modal_tab.get(o, -1),
+                                  bias_off=bias_tab.get(o, -1)))
+    assert all(any(b.modal_off == v for b in blocks) for v in modal_tab.values()), 'modal-only outputs unsupported'
+    return LinearSpec(key, lin, lout, blocks, off, n_modal=n_modal if n_modal > 1 else 0, n_bias=b_off)
 
 
 @dataclass
@@ -248,6 +282,16 @@ class ModelSpec:
     read2: LinearSpec
     rescale_species_wise: bool
     multi_cutoff: Optional[List[float]] = None     # per-layer cutoffs (MultiCutoffEdgeEmbedding), else None
+    n_modal: int = 0                                # number of modalities (model_build.py:198-244), 0 = none
+    modal_map: Optional[Dict[str, int]] = None      # modality name -> index
+    modal_wise_shift: bool = False                  # rescale_atomic_energy.shift is [n_modal, n_species]
+    modal_wise_scale: bool = False
+
+    def linears(self) -> List['LinearSpec']:
+        out = [self.embed]
+        for L in self.layers:
+            out += [L.sc, L.si1, L.si2]
+        return out + [self.read1, self.read2]
 
     def coeff_key(self, t: int) -> str:
         """state_dict key of the Bessel coefficients convolution layer ``t`` uses (model_build.py:87-103: one
@@ -269,15 +313,22 @@ class ModelSpec:
             out[L.si2.key] = (L.si2.numel,)
         out[self.read1.key] = (self.read1.numel,)
         out[self.read2.key] = (self.read2.numel,)
+        for lin in self.linears():
+            if lin.n_bias:
+                out[lin.bias_key] = (lin.n_bias,)
         n = self.n_species if self.rescale_species_wise else 1
-        out['rescale_atomic_energy.shift'] = (n,)
-        out['rescale_atomic_energy.scale'] = (n,)
+        out['rescale_atomic_energy.shift'] = (self.n_modal, n) if self.modal_wise_shift else (n,)
+        out['rescale_atomic_energy.scale'] = (self.n_modal, n) if self.modal_wise_scale else (n,)
         return out
 
 
 def build_spec(config: dict) -> ModelSpec:
     cfg = {**DEFAULTS, **copy.deepcopy(config)}
-    assert not cfg['use_bias_in_linear'], 'use_bias_in_linear is not supported by the B200 path'
+    bias = bool(cfg['use_bias_in_linear'])
+    nm = int(cfg.get('_number_of_modalities', 0)) if cfg.get('use_modality', False) else 0
+    m_emb, m_si1, m_si2, m_out = (nm if cfg.get(k, False) else 0 for k in (
+        'use_modal_node_embedding', 'use_modal_self_inter_intro', 'use_modal_self_inter_outro',
+        'use_modal_output_block'))
     assert not cfg['readout_as_fcn'], 'readout_as_fcn is not supported by the B200 path'
     assert cfg['radial_basis']['radial_basis_name'] == 'bessel'
     S, C, L = cfg['_number_of_species'], cfg['channel'], cfg['num_convolution_layer']
@@ -295,7 +346,7 @@ def build_spec(config: dict) -> ModelSpec:
     hidden = [nb] + list(cfg['weight_nn_hidden_neurons'])
     one_hot = [(S, (0, 1))]
     irreps_x = [(C, (0, 1))] if manual is None else manual[0]
-    embed = make_linear('onehot_to_feature_x.linear.weight', one_hot, irreps_x)
+    embed = make_linear('onehot_to_feature_x.linear.weight', one_hot, irreps_x, m_emb, bias)
     layers = []
     for t in range(L):
         parity_mode, lm = 'full', lmax_node
@@ -315,19 +366,19 @@ def build_spec(config: dict) -> ModelSpec:
             sc.numel *= S
         else:
             raise ValueError(sc_type)
-        si1 = make_linear(f'{t}_self_interaction_1.linear.weight', irreps_x, irreps_x)
+        si1 = make_linear(f'{t}_self_interaction_1.linear.weight', irreps_x, irreps_x, m_si1, bias)
         conv = make_conv(f'{t}_convolution', irreps_x, irreps_filter, irreps_out_tp, hidden)
-        si2 = make_linear(f'{t}_self_interaction_2.linear.weight', conv.lmid.entries, gate_in_s)
+        si2 = make_linear(f'{t}_self_interaction_2.linear.weight', conv.lmid.entries, gate_in_s, m_si2, bias)
         layers.append(LayerSpec(t, sc_type, sc, si1, conv, si2, gate, float(denom[t])))
         irreps_x = ir.simplify(gate_out)
         assert irreps_x == list(gate_out), 'gate output irreps must be simplified'
     hid = [(ir.irreps_dim(irreps_x) // 2, (0, 1))]
-    read1 = make_linear('reduce_input_to_hidden.linear.weight', irreps_x, hid)
-    read2 = make_linear('reduce_hidden_to_energy.linear.weight', hid, [(1, (0, 1))])
+    read1 = make_linear('reduce_input_to_hidden.linear.weight', irreps_x, hid, m_out, bias)
+    read2 = make_linear('reduce_hidden_to_energy.linear.weight', hid, [(1, (0, 1))], 0, bias)
     shift, scale = cfg['shift'], cfg['scale']
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale
-    species_wise = not (isinstance(shift, float) and isinstance(scale, float))
+    species_wise = bool(nm) or not (isinstance(shift, float) and isinstance(scale, float))
     cf = dict(cfg['cutoff_function'])
     name = cf['cutoff_function_name']
     return ModelSpec(
@@ -336,7 +387,10 @@ def build_spec(config: dict) -> ModelSpec:
         cutoff_fn=name, cutoff_p=float(cf.get('poly_cut_p_value', 6)),
         cutoff_on=float(cf.get('cutoff_on', 0.0)), act_radial=cfg['act_radial'], embed=embed,
         layers=layers, read1=read1, read2=read2, rescale_species_wise=species_wise,
-        multi_cutoff=[float(c) for c in cfg['multi_cutoff']] if cfg.get('multi_cutoff') else None)
+        multi_cutoff=[float(c) for c in cfg['multi_cutoff']] if cfg.get('multi_cutoff') else None,
+        n_modal=nm, modal_map=dict(cfg.get('_modal_map') or {}) or None,
+        modal_wise_shift=bool(nm and cfg.get('use_modal_wise_shift', False)),
+        modal_wise_scale=bool(nm and cfg.get('use_modal_wise_scale', False)))
 
 
 def nequip_sc_dense(spec: LinearSpec, flat: np.ndarray, block: LinearBlock, S: int) -> np.ndarray:

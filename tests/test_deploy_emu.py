@@ -158,3 +158,37 @@ def test_deployed_parallel_against_reference_parallel_artefacts(golden_dir):
     assert abs(E.item() - float(gold['energy'])) / len(numbers) < 1e-5
     assert np.abs(ae.numpy() - gold['atomic_energy']).max() < 1e-5
     assert np.abs(dE_dr.numpy() - gold['dE_dr']).max() < 1e-4
+
+
+def test_deploy_serial_freezes_a_modality(tmp_path):
+    """scripts/deploy.py:31-36: a multi-modal checkpoint is deployed for ONE modality; the bundle carries it and the
+    deployed model reproduces the oracle evaluated with that modality."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg.update(use_modality=True, _number_of_modalities=2, _modal_map={'pbe': 0, 'scan': 1},
+               use_modal_node_embedding=True, use_modal_self_inter_intro=True, use_modal_self_inter_outro=True,
+               use_modal_output_block=True, use_modal_wise_shift=True, use_modal_wise_scale=True,
+               shift=[[0.1, -0.2, 0.3], [0.5, 0.4, -0.1]], scale=[[1.0, 1.5, 0.7], [0.9, 1.1, 1.3]])
+    torch.manual_seed(3)
+    ref = S.build_model(cfg).eval()
+    lib = _emu_for(cfg)
+    with pytest.raises(ValueError):
+        D.deploy((cfg, ref.state_dict()), str(tmp_path / 'x'))                    # modality missing
+    with pytest.raises(ValueError):
+        D.deploy((dict(presets.PRESETS['test-so3-l2']), S.build_model(dict(presets.PRESETS['test-so3-l2'])).state_dict()),
+                 str(tmp_path / 'y'), modal='pbe')                                 # model has no modal_map
+    path = D.deploy((cfg, ref.state_dict()), str(tmp_path / 'mf'), modal='scan')
+    model, _ = D.load_deployed(path, device='cpu', lib=lib)
+    assert model.engine.modal == 1
+    numbers, pos, cell = random_cell(16, list(cfg['_type_map']), density=0.05, seed=8)
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+    g[S.MODAL_TYPE] = torch.tensor(1)
+    want = ref(dict(g))
+    ei, sh = g[S.EDGE_IDX], g[S.SHIFT]
+    out = model({'x': torch.tensor([cfg['_type_map'][int(z)] for z in numbers], dtype=torch.int64),
+                 'pos': torch.tensor(pos, dtype=torch.float32, requires_grad=True), 'edge_index': ei,
+                 'num_atoms': torch.tensor([len(numbers)], dtype=torch.int64),
+                 'cell_lattice_vectors': torch.tensor(cell, dtype=torch.float32),
+                 'cell_volume': torch.tensor(abs(np.linalg.det(cell)), dtype=torch.float32),
+                 'pbc_shift': sh.to(torch.float32)})
+    assert abs(out['inferred_total_energy'].item() - float(want[S.E_TOT].detach())) / len(numbers) < 1e-5
+    assert (out['inferred_force'] - want[S.FORCE].detach()).abs().max().item() < 1e-4

@@ -16,10 +16,12 @@ from tests.structures import random_cell
 KBAR = 1602.1766208
 
 
-def _compare(cfg, sd, numbers, pos, cell, pbc, oracle_model, tol_e=1e-5, tol_f=1e-4, tol_s=1e-3):
+def _compare(cfg, sd, numbers, pos, cell, pbc, oracle_model, tol_e=1e-5, tol_f=1e-4, tol_s=1e-3, modal=None):
     spec = sp.build_spec(cfg)
     lib = build_full_emu([L.conv for L in spec.layers])
     g = S.atoms_to_graph(numbers, pos, cell, pbc, cfg['cutoff'])
+    if modal is not None:
+        g[S.MODAL_TYPE] = torch.tensor(modal)
     ref = oracle_model(dict(g))
     tmap = cfg['_type_map']
     types = np.array([tmap[int(z)] for z in numbers])
@@ -28,7 +30,7 @@ def _compare(cfg, sd, numbers, pos, cell, pbc, oracle_model, tol_e=1e-5, tol_f=1
     n = len(numbers)
     res = {}
     for radial in ('mlp', 'table'):     # per-edge radial MLP (GEMM kernels) and the tabulated radial function
-        eng = Engine(spec, sd, lib=lib, device='cpu', radial=radial)
+        eng = Engine(spec, sd, lib=lib, device='cpu', radial=radial, modal=modal)
         assert eng.radial == radial
         out = eng.evaluate(gr)
         dE = abs(out['energy'].item() - ref[S.E_TOT].item()) / n
@@ -84,6 +86,49 @@ def test_engine_emu_two_chunk_units(monkeypatch, packed):
     model = S.build_model(cfg).eval()
     numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=4)
     print(_compare(cfg, model.state_dict(), numbers, pos, cell, [True] * 3, model))
+
+
+@pytest.mark.parametrize('bias', [False, True])
+def test_engine_emu_modality_and_bias(bias):
+    """SevenNet-MF style model (model_build.py:198-244, nn/linear.py:65-92, nn/scale.py:165-330): modality one-hot
+    appended to the inputs of the embedding / self-interaction / readout linears, modal-wise shift; optionally
+    `use_bias_in_linear`.  The engine folds the fixed modality and the biases into constant rows of the scalar blocks;
+    every modality must reproduce the oracle, and modalities must differ from each other."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    nm = 3
+    cfg.update(use_modality=True, _number_of_modalities=nm, _modal_map={'pbe': 0, 'scan': 1, 'r2scan': 2},
+               use_modal_node_embedding=True, use_modal_self_inter_intro=True, use_modal_self_inter_outro=True,
+               use_modal_output_block=True, use_modal_wise_shift=True, use_modal_wise_scale=False,
+               use_bias_in_linear=bias,
+               shift=[[0.1, -0.2, 0.3], [0.5, 0.4, -0.1], [-0.3, 0.2, 0.0]], scale=[1.0, 1.5, 0.7])
+    torch.manual_seed(11)
+    model = S.build_model(cfg).eval()
+    if bias:
+        with torch.no_grad():
+            for n_, p_ in model.named_parameters():
+                if n_.endswith('linear.bias'):
+                    p_.normal_(0.0, 0.3)
+    sd = model.state_dict()
+    spec = sp.build_spec(cfg)
+    assert spec.n_modal == nm and spec.embed.n_modal == nm and (spec.read2.n_bias == 1) == bias
+    assert {k: tuple(v.shape) for k, v in sd.items() if k in spec.expected_keys()} == spec.expected_keys()
+    numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=6)
+    energies = []
+    for m in range(nm):
+        _compare(cfg, sd, numbers, pos, cell, [True] * 3, model, modal=m)
+        g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+        g[S.MODAL_TYPE] = torch.tensor(m)
+        energies.append(float(model(dict(g))[S.E_TOT].detach()))
+    assert abs(energies[0] - energies[1]) > 1e-3 and abs(energies[1] - energies[2]) > 1e-3
+    lib = build_full_emu([L.conv for L in spec.layers])
+    with pytest.raises(ValueError):
+        Engine(spec, sd, lib=lib, device='cpu')                      # modal missing
+    with pytest.raises(ValueError):
+        Engine(spec, sd, lib=lib, device='cpu', modal='hse')          # unknown modal
+    assert Engine(spec, sd, lib=lib, device='cpu', modal='scan').modal == 1
+    plain = sp.build_spec(dict(presets.PRESETS['test-so3-l2']))
+    with pytest.raises(ValueError):
+        Engine(plain, S.build_model(dict(presets.PRESETS['test-so3-l2'])).state_dict(), lib=lib, device='cpu', modal='pbe')
 
 
 def test_engine_emu_reference_deployed_torchscript(golden_dir):
