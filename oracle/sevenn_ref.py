@@ -207,6 +207,21 @@ class IrrepsLinear(nn.Module):
         return data
 
 
+class FCN_e3nn(nn.Module):
+    """sevenn/nn/linear.py:145-180: e3nn FullyConnectedNet on scalar node features (readout_as_fcn)."""
+
+    def __init__(self, irreps_in, dim_out, hidden_neurons, activation, data_key_in, data_key_out=None):
+        super().__init__()
+        self.key_input, self.key_output = data_key_in, data_key_out or data_key_in
+        irreps_in = Irreps(irreps_in)
+        assert all(ir.is_scalar() for _, ir in irreps_in)
+        self.fcn = o3.FullyConnectedNet([irreps_in.dim] + list(hidden_neurons) + [dim_out], activation)
+
+    def forward(self, data):
+        data[self.key_output] = self.fcn(data[self.key_input])
+        return data
+
+
 class SelfConnectionIntro(nn.Module):
     """sevenn/nn/self_connection.py:10-64 ('nequip': FCTP of x with one-hot)"""
 
@@ -562,11 +577,15 @@ def build_model(config, parallel=False):
         layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()
         layers[f'{t}_equivariant_gate'] = gate
         irreps_x = irreps_out
-    hidden = Irreps([(irreps_x.dim // 2, (0, 1))])
-    layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X, biases=cfg['use_bias_in_linear'],
-                                                    num_modalities=m_out)
-    layers['reduce_hidden_to_energy'] = IrrepsLinear(hidden, Irreps('1x0e'), X, SCALED_AE,
-                                                     biases=cfg['use_bias_in_linear'])
+    if cfg['readout_as_fcn']:                            # model_build.py:141-155
+        layers['readout_FCN'] = FCN_e3nn(irreps_x, 1, cfg.get('readout_fcn_hidden_neurons', [30, 30]),
+                                         ACT[cfg.get('readout_fcn_activation', 'relu')], X, SCALED_AE)
+    else:
+        hidden = Irreps([(irreps_x.dim // 2, (0, 1))])
+        layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X, biases=cfg['use_bias_in_linear'],
+                                                        num_modalities=m_out)
+        layers['reduce_hidden_to_energy'] = IrrepsLinear(hidden, Irreps('1x0e'), X, SCALED_AE,
+                                                         biases=cfg['use_bias_in_linear'])
     shift, scale = cfg['shift'], cfg['scale']
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale

@@ -399,8 +399,16 @@ class Engine(Kernels):
             self.mlp_w1cat = f32(W1)
             self.mlp_w1catT = f32(np.ascontiguousarray(W1.T))
             self.mlp_h1 = hs[0][1]
-        self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev, 0, m_idx, bias_of(spec.read1))
-        self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev, 0, m_idx, bias_of(spec.read2))
+        self.readout_fcn = None
+        if spec.readout_fcn:
+            # readout_as_fcn: e3nn FullyConnectedNet on the scalar features -> the radial-MLP launch path on node rows
+            hs = spec.readout_fcn
+            Wr = [sd[f'readout_FCN.fcn.layer{k}.weight'] / math.sqrt(hs[k]) for k in range(len(hs) - 1)]
+            self.readout_fcn = {'mlp': [f32(w) for w in Wr], 'mlpT': [f32(np.ascontiguousarray(w.T)) for w in Wr],
+                                'act': ACT_ID[spec.readout_act], 'cst': ir.normalize2mom_const(spec.readout_act)}
+        else:
+            self.read1 = _Lin(spec.read1, sd[spec.read1.key], dev, 0, m_idx, bias_of(spec.read1))
+            self.read2 = _Lin(spec.read2, sd[spec.read2.key], dev, 0, m_idx, bias_of(spec.read2))
         scale, shift = sd['rescale_atomic_energy.scale'], sd['rescale_atomic_energy.shift']
         self.scale = f32(scale[m_idx] if spec.modal_wise_scale else scale)      # ModalWiseRescale, nn/scale.py:165-330
         self.shift = f32(shift[m_idx] if spec.modal_wise_shift else shift)
@@ -556,10 +564,15 @@ class Engine(Kernels):
             x, n_x = xo, nl
         self._mark('readout')
         # readout
-        r1 = self._empty(nl, sp.read1.lout.dim)
-        self._linear_fwd(self.read1, x, nl, r1)
-        es = self._empty(nl, 1)
-        self._linear_fwd(self.read2, r1, nl, es)
+        fcn_pres = None
+        if self.readout_fcn is not None:
+            xr = x[:nl] if x.shape[0] != nl else x
+            fcn_pres, _, es = self._mlp_fwd(self.readout_fcn, xr.contiguous(), nl)
+        else:
+            r1 = self._empty(nl, sp.read1.lout.dim)
+            self._linear_fwd(self.read1, x, nl, r1)
+            es = self._empty(nl, 1)
+            self._linear_fwd(self.read2, r1, nl, es)
         ae, seed = self._empty(nl), self._empty(nl, 1)
         lib.call('sevenn_rescale', _p(es), _p(g.types), nl, _p(self.scale), _p(self.shift),
                  int(sp.rescale_species_wise), _p(ae), _p(seed), st)
@@ -578,10 +591,14 @@ class Engine(Kernels):
         SD = S + 1 if table else S      # tabulated kernels: the radial term rides in the last column of dY
         dY = self._zeros(n_slab * max(E, 1), SD)
         demb = None if table else self._zeros(max(E, 1), sp.n_basis)
-        dr1 = self._empty(nl, sp.read1.lout.dim)
-        self._linear_bwd(self.read2, seed, nl, dr1)
-        dx = self._zeros(nl, sp.read1.lin.dim) if self.read1.bwd_needs_zero else self._empty(nl, sp.read1.lin.dim)
-        self._linear_bwd(self.read1, dr1, nl, dx)
+        if self.readout_fcn is not None:
+            dx = self._zeros(nl, sp.readout_fcn[0])
+            self._mlp_bwd(self.readout_fcn, seed, fcn_pres, dx, nl)
+        else:
+            dr1 = self._empty(nl, sp.read1.lout.dim)
+            self._linear_bwd(self.read2, seed, nl, dr1)
+            dx = self._zeros(nl, sp.read1.lin.dim) if self.read1.bwd_needs_zero else self._empty(nl, sp.read1.lin.dim)
+            self._linear_bwd(self.read1, dr1, nl, dx)
         dact1_all = None
         for t in range(len(self.layers) - 1, -1, -1):
             lay, sv = self.layers[t], saved[t]

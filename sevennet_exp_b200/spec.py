@@ -286,12 +286,14 @@ class ModelSpec:
     modal_map: Optional[Dict[str, int]] = None      # modality name -> index
     modal_wise_shift: bool = False                  # rescale_atomic_energy.shift is [n_modal, n_species]
     modal_wise_scale: bool = False
+    readout_fcn: Optional[List[int]] = None         # readout_as_fcn (model_build.py:141-155): [in, hidden..., 1]
+    readout_act: str = 'relu'
 
     def linears(self) -> List['LinearSpec']:
         out = [self.embed]
         for L in self.layers:
             out += [L.sc, L.si1, L.si2]
-        return out + [self.read1, self.read2]
+        return out + ([] if self.readout_fcn else [self.read1, self.read2])
 
     def coeff_key(self, t: int) -> str:
         """state_dict key of the Bessel coefficients convolution layer ``t`` uses (model_build.py:87-103: one
@@ -311,8 +313,12 @@ class ModelSpec:
                 out[f'{L.conv.name}.weight_nn.layer{k}.weight'] = (h[k], h[k + 1])
             out[f'{L.conv.name}.denominator'] = (1,)
             out[L.si2.key] = (L.si2.numel,)
-        out[self.read1.key] = (self.read1.numel,)
-        out[self.read2.key] = (self.read2.numel,)
+        if self.readout_fcn:
+            for k, (a, b) in enumerate(zip(self.readout_fcn, self.readout_fcn[1:])):
+                out[f'readout_FCN.fcn.layer{k}.weight'] = (a, b)
+        else:
+            out[self.read1.key] = (self.read1.numel,)
+            out[self.read2.key] = (self.read2.numel,)
         for lin in self.linears():
             if lin.n_bias:
                 out[lin.bias_key] = (lin.n_bias,)
@@ -329,7 +335,6 @@ def build_spec(config: dict) -> ModelSpec:
     m_emb, m_si1, m_si2, m_out = (nm if cfg.get(k, False) else 0 for k in (
         'use_modal_node_embedding', 'use_modal_self_inter_intro', 'use_modal_self_inter_outro',
         'use_modal_output_block'))
-    assert not cfg['readout_as_fcn'], 'readout_as_fcn is not supported by the B200 path'
     assert cfg['radial_basis']['radial_basis_name'] == 'bessel'
     S, C, L = cfg['_number_of_species'], cfg['channel'], cfg['num_convolution_layer']
     lmax_node = cfg['lmax_node'] if cfg['lmax_node'] > 0 else cfg['lmax']
@@ -375,6 +380,10 @@ def build_spec(config: dict) -> ModelSpec:
     hid = [(ir.irreps_dim(irreps_x) // 2, (0, 1))]
     read1 = make_linear('reduce_input_to_hidden.linear.weight', irreps_x, hid, m_out, bias)
     read2 = make_linear('reduce_hidden_to_energy.linear.weight', hid, [(1, (0, 1))], 0, bias)
+    readout_fcn = None
+    if cfg['readout_as_fcn']:
+        assert all(tuple(i) == (0, 1) for _, i in irreps_x), 'readout_as_fcn needs scalar node features'
+        readout_fcn = [ir.irreps_dim(irreps_x)] + list(cfg.get('readout_fcn_hidden_neurons', [30, 30])) + [1]
     shift, scale = cfg['shift'], cfg['scale']
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale
@@ -390,7 +399,8 @@ def build_spec(config: dict) -> ModelSpec:
         multi_cutoff=[float(c) for c in cfg['multi_cutoff']] if cfg.get('multi_cutoff') else None,
         n_modal=nm, modal_map=dict(cfg.get('_modal_map') or {}) or None,
         modal_wise_shift=bool(nm and cfg.get('use_modal_wise_shift', False)),
-        modal_wise_scale=bool(nm and cfg.get('use_modal_wise_scale', False)))
+        modal_wise_scale=bool(nm and cfg.get('use_modal_wise_scale', False)),
+        readout_fcn=readout_fcn, readout_act=cfg.get('readout_fcn_activation', 'relu'))
 
 
 def nequip_sc_dense(spec: LinearSpec, flat: np.ndarray, block: LinearBlock, S: int) -> np.ndarray:

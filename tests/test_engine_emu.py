@@ -131,6 +131,22 @@ def test_engine_emu_modality_and_bias(bias):
         Engine(plain, S.build_model(dict(presets.PRESETS['test-so3-l2'])).state_dict(), lib=lib, device='cpu', modal='pbe')
 
 
+@pytest.mark.parametrize('act', ['relu', 'silu'])
+def test_engine_emu_readout_as_fcn(act):
+    """readout_as_fcn (model_build.py:141-155, nn/linear.py:145-180): FullyConnectedNet readout on the scalar features,
+    forward and analytic reverse through the MLP launch path."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg.update(readout_as_fcn=True, readout_fcn_hidden_neurons=[16, 8], readout_fcn_activation=act)
+    torch.manual_seed(21)
+    model = S.build_model(cfg).eval()
+    spec = sp.build_spec(cfg)
+    assert spec.readout_fcn == [32, 16, 8, 1]
+    sd = model.state_dict()
+    assert {k: tuple(v.shape) for k, v in sd.items() if k in spec.expected_keys()} == spec.expected_keys()
+    numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=12)
+    print(_compare(cfg, sd, numbers, pos, cell, [True] * 3, model))
+
+
 def test_engine_emu_reference_deployed_torchscript(golden_dir):
     """The reference's frozen TorchScript artefact (deployed_serial.pt): its weights, its frame -> our engine
     (emulation build) must give ITS outputs (tests/golden/deployed_serial_hfo2.npz), no oracle in between."""
