@@ -46,9 +46,11 @@ def _perm(layout: ir.Layout, device):
 class _Weight(nn.Module):
     """Stand-in for the e3nn submodule that owns a flat ``weight`` (o3.Linear / FullyConnectedTensorProduct)."""
 
-    def __init__(self, numel):
+    def __init__(self, numel, n_bias=0):
         super().__init__()
         self.weight = nn.Parameter(torch.randn(numel))
+        if n_bias:
+            self.bias = nn.Parameter(torch.zeros(n_bias))
 
 
 class _LinearCore(nn.Module):
@@ -63,7 +65,9 @@ class _LinearCore(nn.Module):
         key = (w._version, w.data_ptr(), str(device))
         if self._cache is None or self._cache[0] != key:
             flat = w.detach().cpu().numpy().astype(np.float64)
-            self._cache = (key, _Lin(self._spec, flat, device, self._S))
+            lin = _Lin(self._spec, flat, device, self._S)
+            lin.has_const = False          # modality / bias terms are added by the module (they depend on the data)
+            self._cache = (key, lin)
         return self._cache[1]
 
     def _apply_linear(self, x, types=None):
@@ -203,24 +207,35 @@ class OnehotEmbedding(nn.Module):
 class IrrepsLinear(_LinearCore):
     """sevenn/nn/linear.py:14-100.  Same constructor and lazy-layer seam (`linear_cls`, `linear_kwargs`,
     `instantiate()`): `linear_cls(irreps_in, irreps_out, **linear_kwargs)` must return a module owning a flat e3nn
-    `weight`; the default is the B200 parameter holder.  Bias and modality variants are outside this hot path."""
+    `weight` (and `bias` with biases=True); the default is the B200 parameter holder.  Modality (:65-92): the one-hot
+    the reference concatenates to the input only reaches the scalar outputs, so its contribution (and the bias) is
+    added to the 0e output entries after the kernel: onehot @ W_modal / sqrt(fan_in + n_modal)."""
 
     def __init__(self, irreps_in, irreps_out, data_key_in, data_key_out=None, data_key_modal_attr='modal_attr',
                  num_modalities=0, lazy_layer_instantiate=False, **linear_kwargs):
         super().__init__()
-        if linear_kwargs.get('biases', False):
-            raise NotImplementedError('use_bias_in_linear is outside the B200 hot path')
-        if num_modalities > 1:
-            raise NotImplementedError('multi-modal checkpoints are outside the B200 hot path')
         self.key_input, self.key_output = data_key_in, data_key_out or data_key_in
-        self.key_modal_attr, self.num_modalities = data_key_modal_attr, num_modalities
+        self.key_modal_attr, self.num_modalities = data_key_modal_attr, 0
+        self._irreps_in_wo_modal = _irreps(irreps_in)
         self.irreps_in, self.irreps_out = _irreps(irreps_in), _irreps(irreps_out)
         self.linear_kwargs, self.linear_cls = linear_kwargs, None
         self.linear, self.layer_instantiated = None, False
         self._is_batch_data = True
-        self._lspec = sp.make_linear('linear.weight', self.irreps_in, self.irreps_out)
+        self._lspec = sp.make_linear('linear.weight', self._irreps_in_wo_modal, self.irreps_out, 0,
+                                     bool(linear_kwargs.get('biases', False)))
+        if num_modalities > 1:
+            self.set_num_modalities(num_modalities)
         if not lazy_layer_instantiate:
             self.instantiate()
+
+    def set_num_modalities(self, num_modalities):
+        """sevenn/nn/linear.py:65-70."""
+        if self.layer_instantiated:
+            raise ValueError('Layer already instantiated, can not change modalities')
+        self.num_modalities = num_modalities
+        self.irreps_in = self._irreps_in_wo_modal + [(num_modalities, (0, 1))]
+        self._lspec = sp.make_linear('linear.weight', self._irreps_in_wo_modal, self.irreps_out, num_modalities,
+                                     bool(self.linear_kwargs.get('biases', False)))
 
     def instantiate(self):
         if self.linear is not None:
@@ -228,13 +243,67 @@ class IrrepsLinear(_LinearCore):
         if self.linear_cls is not None:
             self.linear = self.linear_cls(self.irreps_in, self.irreps_out, **self.linear_kwargs)
         else:
-            self.linear = _Weight(self._lspec.numel)
+            self.linear = _Weight(self._lspec.numel, self._lspec.n_bias)
         self._setup(self._lspec, 'linear')
         self.layer_instantiated = True
 
+    def _constant_rows(self, data, y):
+        """Modality and bias terms of the scalar output entries (e3nn column order), small torch ops."""
+        spec, w = self._lspec, self.linear.weight
+        offs = np.concatenate([[0], np.cumsum([m * (2 * l + 1) for m, (l, _) in self.irreps_out])])
+        onehot = None
+        if spec.n_modal:
+            onehot = data[self.key_modal_attr].reshape(-1, spec.n_modal).to(y.dtype)
+            onehot = onehot[data['batch']] if (self._is_batch_data and 'batch' in data) else onehot.expand(len(y), -1)
+        for b in spec.blocks:
+            add = None
+            if b.modal_off >= 0:
+                Wm = w[b.modal_off:b.modal_off + spec.n_modal * b.N].reshape(spec.n_modal, b.N)
+                add = onehot @ (Wm.to(y.dtype) / math.sqrt(b.K + b.fan_extra))
+            if b.bias_off >= 0:
+                bias = self.linear.bias[b.bias_off:b.bias_off + b.N].to(y.dtype)
+                add = bias if add is None else add + bias
+            if add is not None:
+                a = int(offs[b.o_entry])
+                y = torch.cat([y[:, :a], y[:, a:a + b.N] + add, y[:, a + b.N:]], dim=1)
+        return y
+
     def forward(self, data):
         assert self.linear is not None, 'Layer is not instantiated'
-        data[self.key_output] = self._apply_linear(data[self.key_input])
+        y = self._apply_linear(data[self.key_input])
+        if self._lspec.n_modal or self._lspec.n_bias:
+            y = self._constant_rows(data, y)
+        data[self.key_output] = y
+        return data
+
+
+class FCN_e3nn(nn.Module):
+    """sevenn/nn/linear.py:145-180: e3nn FullyConnectedNet on scalar node features (readout_as_fcn); parameters
+    `fcn.layer{k}.weight`; evaluated by the MLP kernels (GEMM + fused activation, activation-gradient epilogue)."""
+
+    def __init__(self, irreps_in, dim_out, hidden_neurons, activation, data_key_in, data_key_out=None, **e3nn_kwargs):
+        super().__init__()
+        self.key_input, self.key_output = data_key_in, data_key_out or data_key_in
+        self.irreps_in = _irreps(irreps_in)
+        assert all(tuple(i) == (0, 1) for _, i in self.irreps_in), 'FCN_e3nn takes scalar features'
+        act = activation if isinstance(activation, str) else getattr(activation, '__name__', '')
+        self.fcn = _FCN([ir.irreps_dim(self.irreps_in)] + list(hidden_neurons) + [dim_out])
+        self._act, self._cst = sp.ACT_ID[act], ir.normalize2mom_const(act)
+        self._cache = None
+
+    def _layer(self, device):
+        ws = [getattr(self.fcn, f'layer{k}').weight for k in range(len(self.fcn.hs) - 1)]
+        key = tuple((w._version, w.data_ptr()) for w in ws) + (str(device),)
+        if self._cache is None or self._cache[0] != key:
+            Wm = [w.detach().cpu().double().numpy() / math.sqrt(self.fcn.hs[k]) for k, w in enumerate(ws)]
+            f32 = lambda a: torch.tensor(np.ascontiguousarray(a), dtype=torch.float32, device=device)  # noqa: E731
+            self._cache = (key, {'mlp': [f32(w) for w in Wm], 'mlpT': [f32(w.T) for w in Wm],
+                                 'act': self._act, 'cst': self._cst})
+        return self._cache[1]
+
+    def forward(self, data):
+        x = data[self.key_input]
+        data[self.key_output] = F.RadialMLPFn.apply(x.float(), self._layer(x.device))
         return data
 
 

@@ -44,6 +44,7 @@ class LinearBlock:
     fan_extra: int = 0        # modality one-hot channels that also feed this (0e) output: fan_in = K + fan_extra
     modal_off: int = -1       # flat offset of their [n_modal, N] weights
     bias_off: int = -1        # offset of this (0e) output entry inside o3.Linear's bias vector
+    o_entry: int = -1         # index of the output entry (e3nn order) this block writes
 
 
 @dataclass
@@ -107,7 +108,7 @@ def make_linear(key: str, irreps_in, irreps_out, n_modal: int = 0, biases: bool 
         assert lin.groups[g_in][0] == K, 'inputs of one irrep must be contiguous'
         blocks.append(LinearBlock(iro[0], g_in, lout.entry_group[o], K, mo, lout.entry_uoff[o], segs,
                                   fan_extra=n_modal if o in modal_tab else 0, modal_off=modal_tab.get(o, -1),
-                                  bias_off=bias_tab.get(o, -1)))
+                                  bias_off=bias_tab.get(o, -1), o_entry=o))
     assert all(any(b.modal_off == v for b in blocks) for v in modal_tab.values()), 'modal-only outputs unsupported'
     return LinearSpec(key, lin, lout, blocks, off, n_modal=n_modal if n_modal > 1 else 0, n_bias=b_off)
 

@@ -135,3 +135,52 @@ def test_multi_cutoff_edge_embedding_matches_oracle(cutoff_fn):
     numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=7)
     model = _run_pair(cfg, om.state_dict(), om, numbers, pos, cell)
     assert isinstance(model.edge_embedding, bnn.MultiCutoffEdgeEmbedding)
+
+
+def test_irreps_linear_modality_bias_and_fcn_modules():
+    """nn.IrrepsLinear with num_modalities / biases (sevenn/nn/linear.py:14-100) and nn.FCN_e3nn (:145-180) against the
+    oracle modules of the same name: same flat weights, values and input gradients."""
+    bnn.set_lib(build_full_emu([]))
+    torch.manual_seed(4)
+    irr_in, irr_out, M = '24x0e+8x1e', '16x0e+8x1e', 3
+    ref = S.IrrepsLinear(S.Irreps(irr_in), S.Irreps(irr_out), S.X, biases=True, num_modalities=M)
+    with torch.no_grad():
+        ref.linear.bias.normal_(0.0, 0.5)
+    mod = bnn.IrrepsLinear(irr_in, irr_out, S.X, num_modalities=M, biases=True)
+    assert mod.num_modalities == M and mod.linear.weight.shape == ref.linear.weight.shape
+    with pytest.raises(ValueError):
+        mod.set_num_modalities(2)                       # already instantiated (linear.py:66-67)
+    mod.load_state_dict(ref.state_dict())
+    n = 40
+    x = torch.randn(n, 24 + 24)
+    batch = torch.randint(0, 2, (n,))
+    onehot = torch.nn.functional.one_hot(torch.tensor([2, 0]), M).float()          # two graphs, two modalities
+    for is_batch in (True, False):
+        mod._is_batch_data = is_batch
+        oh = onehot if is_batch else onehot[:1]
+        xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+        # the oracle restates the single-structure form: evaluate it per graph
+        want = torch.zeros(n, 16 + 24)
+        for gidx in range(2 if is_batch else 1):
+            sel = (batch == gidx) if is_batch else torch.ones(n, dtype=torch.bool)
+            want[sel] = ref({S.X: xa[sel], S.MODAL_ATTR: oh[gidx]})[S.X]
+        data = {S.X: xb, 'modal_attr': oh}
+        if is_batch:
+            data['batch'] = batch
+        got = mod(data)[S.X]
+        assert (got - want).abs().max().item() < 2e-5
+        gsel = torch.randn(n, 16 + 24)
+        (ga,) = torch.autograd.grad((want * gsel).sum(), xa)
+        (gb,) = torch.autograd.grad((got * gsel).sum(), xb)
+        assert (ga - gb).abs().max().item() < 2e-5
+    # FullyConnectedNet readout
+    for act in ('relu', 'silu'):
+        rf = S.FCN_e3nn(S.Irreps('32x0e'), 1, [16, 8], S.ACT[act], S.X, S.SCALED_AE)
+        mf = bnn.FCN_e3nn('32x0e', 1, [16, 8], act, S.X, S.SCALED_AE)
+        mf.load_state_dict(rf.state_dict())
+        xa, xb = (torch.randn(50, 32, generator=torch.Generator().manual_seed(1)).requires_grad_(True) for _ in range(2))
+        ya, yb = rf({S.X: xa})[S.SCALED_AE], mf({S.X: xb})[S.SCALED_AE]
+        assert (ya - yb).abs().max().item() < 2e-5
+        (ga,) = torch.autograd.grad(ya.sum(), xa)
+        (gb,) = torch.autograd.grad(yb.sum(), xb)
+        assert (ga - gb).abs().max().item() < 2e-5
