@@ -739,8 +739,12 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
     layers['edge_embedding'] = ee
     one_hot = [(S, (0, 1))]
     irreps_x = [(C, (0, 1))] if manual is None else manual[0]
+    if cfg.get('use_modality', False):
+        raise NotImplementedError('multi-modal checkpoints: use SevenNetCalculator(modal=...) / deploy(modal=...); the '
+                                  'module seam has no ModalWiseRescale')
+    bias = bool(cfg['use_bias_in_linear'])               # interaction_blocks.py:50,82; model_build.py:130,137,457
     layers['onehot_idx_to_onehot'] = OnehotEmbedding(S, X, X, ATOM_TYPE, NODE_ATTR)
-    layers['onehot_to_feature_x'] = IrrepsLinear(one_hot, irreps_x, X, biases=cfg['use_bias_in_linear'])
+    layers['onehot_to_feature_x'] = IrrepsLinear(one_hot, irreps_x, X, biases=bias)
     multi = cfg.get('multi_cutoff') or None
     wnn = [(ee.basis_functions[0] if multi else ee.basis_function).num_basis] + list(cfg['weight_nn_hidden_neurons'])
     for t in range(L):
@@ -754,7 +758,7 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
         gate = EquivariantGate(irreps_out, cfg['act_scalar'], cfg['act_gate'])
         gate_in = gate.get_gate_irreps_in()
         layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, irreps_operand=one_hot, irreps_out=gate_in)
-        layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X)
+        layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X, biases=bias)
         layers[f'{t}_convolution'] = IrrepsConvolution(irreps_x, irreps_filter, irreps_out_tp, wnn,
                                                        cfg['act_radial'], denom[t], cfg['train_denominator'],
                                                        is_parallel=parallel,
@@ -763,13 +767,17 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
                                                            data_key_weight_input=f'{EDGE_EMB}{multi[t]}',
                                                            data_key_edge_idx=f'{EDGE_IDX}{multi[t]}')))
         layers[f'{t}_self_interaction_2'] = IrrepsLinear(layers[f'{t}_convolution'].irreps_mid,
-                                                         ir.simplify(gate_in), X)
+                                                         ir.simplify(gate_in), X, biases=bias)
         layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()
         layers[f'{t}_equivariant_gate'] = gate
         irreps_x = ir.simplify(gate._irreps_out)
-    hidden = [(ir.irreps_dim(irreps_x) // 2, (0, 1))]
-    layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X)
-    layers['reduce_hidden_to_energy'] = IrrepsLinear(hidden, [(1, (0, 1))], X, SCALED_AE)
+    if cfg['readout_as_fcn']:                            # model_build.py:141-155
+        layers['readout_FCN'] = FCN_e3nn(irreps_x, 1, cfg.get('readout_fcn_hidden_neurons', [30, 30]),
+                                         cfg.get('readout_fcn_activation', 'relu'), X, SCALED_AE)
+    else:
+        hidden = [(ir.irreps_dim(irreps_x) // 2, (0, 1))]
+        layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X, biases=bias)
+        layers['reduce_hidden_to_energy'] = IrrepsLinear(hidden, [(1, (0, 1))], X, SCALED_AE, biases=bias)
     shift, scale = cfg['shift'], cfg['scale']
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale

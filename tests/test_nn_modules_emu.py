@@ -184,3 +184,24 @@ def test_irreps_linear_modality_bias_and_fcn_modules():
         (ga,) = torch.autograd.grad(ya.sum(), xa)
         (gb,) = torch.autograd.grad(yb.sum(), xb)
         assert (ga - gb).abs().max().item() < 2e-5
+
+
+@pytest.mark.parametrize('variant', ['bias', 'fcn'])
+def test_sequential_bias_and_fcn_readout_variants(variant):
+    """build_E3_equivariant_model with use_bias_in_linear / readout_as_fcn: same state_dict as the oracle model, same
+    E / F / S."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    if variant == 'bias':
+        cfg['use_bias_in_linear'] = True
+    else:
+        cfg.update(readout_as_fcn=True, readout_fcn_hidden_neurons=[16, 8], readout_fcn_activation='silu')
+    torch.manual_seed(9)
+    model = S.build_model(cfg).eval()
+    with torch.no_grad():
+        for n_, p_ in model.named_parameters():
+            if n_.endswith('linear.bias'):
+                p_.normal_(0.0, 0.3)
+    numbers, pos, cell = random_cell(18, list(cfg['_type_map']), density=0.05, seed=13)
+    ours = _run_pair(cfg, model.state_dict(), model, numbers, pos, cell)
+    assert (set(k for k, v in ours.named_parameters() if v.numel()) ==
+            set(k for k, v in model.named_parameters() if v.numel()))
