@@ -549,6 +549,74 @@ class SpeciesWiseRescale(nn.Module):
         return data
 
 
+class ModalWiseRescale(nn.Module):
+    """sevenn/nn/scale.py:165-360: shift / scale per (modality, species) where modal wise, else per species."""
+
+    def __init__(self, shift, scale, data_key_in=SCALED_AE, data_key_out=AE, data_key_modal_indices='modal_type',
+                 data_key_atom_indices=ATOM_TYPE, use_modal_wise_shift=False, use_modal_wise_scale=False,
+                 train_shift_scale=False):
+        super().__init__()
+        self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=False)
+        self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=False)
+        self.key_input, self.key_output = data_key_in, data_key_out
+        self.key_atom_indices, self.key_modal_indices = data_key_atom_indices, data_key_modal_indices
+        self.use_modal_wise_shift, self.use_modal_wise_scale = use_modal_wise_shift, use_modal_wise_scale
+        self._is_batch_data = True
+
+    def _resolved(self, which, modal_wise, type_map, modal_map):
+        v = getattr(self, which).detach().cpu().tolist()
+        per_type = lambda row: row if type_map is None else {z: row[i] for z, i in type_map.items()}  # noqa: E731
+        if not modal_wise:
+            return per_type(v)
+        if modal_map is None:
+            return [per_type(row) for row in v]
+        return {m: per_type(v[i]) for m, i in modal_map.items()}
+
+    def get_shift(self, type_map=None, modal_map=None):
+        return self._resolved('shift', self.use_modal_wise_shift, type_map, modal_map)
+
+    def get_scale(self, type_map=None, modal_map=None):
+        return self._resolved('scale', self.use_modal_wise_scale, type_map, modal_map)
+
+    @staticmethod
+    def from_mappers(shift, scale, use_modal_wise_shift, use_modal_wise_scale, type_map, modal_map, **kwargs):
+        """scale.py:238-338: floats broadcast; {modality: value | per-species list} dicts and lists in modality /
+        type order resolve to [n_modal][n_types] (modal wise) or [n_types]."""
+        nt, nmod = len(type_map), len(modal_map)
+
+        def species(v):
+            if isinstance(v, dict):
+                return [float(v[z]) for z, _ in sorted(type_map.items(), key=lambda kv: kv[1])]
+            if isinstance(v, (list, tuple)):
+                assert len(v) == nt, f'Invalid shift or scale {v}'
+                return [float(t) for t in v]
+            return [float(v)] * nt
+
+        def solve(v, mw):
+            if not mw:
+                return species(v)
+            if isinstance(v, dict):
+                return [species(v[m]) for m, _ in sorted(modal_map.items(), key=lambda kv: kv[1])]
+            if isinstance(v, (list, tuple)) and len(v) == nmod and isinstance(v[0], (list, tuple)):
+                return [species(row) for row in v]
+            if isinstance(v, (list, tuple)) and len(v) == nmod and nmod != nt:
+                return [[float(t)] * nt for t in v]
+            return [species(v)] * nmod
+        return ModalWiseRescale(solve(shift, use_modal_wise_shift), solve(scale, use_modal_wise_scale),
+                                use_modal_wise_shift=use_modal_wise_shift, use_modal_wise_scale=use_modal_wise_scale,
+                                **kwargs)
+
+    def forward(self, data):
+        modal = data[self.key_modal_indices]
+        if self._is_batch_data and 'batch' in data:
+            modal = modal.reshape(-1)[data['batch']]
+        atom = data[self.key_atom_indices]
+        shift = self.shift[modal, atom] if self.use_modal_wise_shift else self.shift[atom]
+        scale = self.scale[modal, atom] if self.use_modal_wise_scale else self.scale[atom]
+        data[self.key_output] = data[self.key_input] * scale.view(-1, 1) + shift.view(-1, 1)
+        return data
+
+
 class AtomReduce(nn.Module):
     """sevenn/nn/linear.py:104-141 (single graph; fp64 accumulation)."""
 
@@ -739,12 +807,17 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
     layers['edge_embedding'] = ee
     one_hot = [(S, (0, 1))]
     irreps_x = [(C, (0, 1))] if manual is None else manual[0]
-    if cfg.get('use_modality', False):
-        raise NotImplementedError('multi-modal checkpoints: use SevenNetCalculator(modal=...) / deploy(modal=...); the '
-                                  'module seam has no ModalWiseRescale')
+    nm = int(cfg.get('_number_of_modalities', 0)) if cfg.get('use_modality', False) else 0   # model_build.py:198-244
+    if nm and parallel:
+        raise NotImplementedError('multi-modal checkpoints: serial models only')
+    m_emb, m_si1, m_si2, m_out = (nm if cfg.get(k, False) else 0 for k in (
+        'use_modal_node_embedding', 'use_modal_self_inter_intro', 'use_modal_self_inter_outro',
+        'use_modal_output_block'))
     bias = bool(cfg['use_bias_in_linear'])               # interaction_blocks.py:50,82; model_build.py:130,137,457
     layers['onehot_idx_to_onehot'] = OnehotEmbedding(S, X, X, ATOM_TYPE, NODE_ATTR)
-    layers['onehot_to_feature_x'] = IrrepsLinear(one_hot, irreps_x, X, biases=bias)
+    if nm:
+        layers['one_hot_modality'] = OnehotEmbedding(nm, 'modal_type', 'modal_attr', None, None)
+    layers['onehot_to_feature_x'] = IrrepsLinear(one_hot, irreps_x, X, biases=bias, num_modalities=m_emb)
     multi = cfg.get('multi_cutoff') or None
     wnn = [(ee.basis_functions[0] if multi else ee.basis_function).num_basis] + list(cfg['weight_nn_hidden_neurons'])
     for t in range(L):
@@ -758,7 +831,7 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
         gate = EquivariantGate(irreps_out, cfg['act_scalar'], cfg['act_gate'])
         gate_in = gate.get_gate_irreps_in()
         layers[f'{t}_self_connection_intro'] = sc_cls(irreps_x, irreps_operand=one_hot, irreps_out=gate_in)
-        layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X, biases=bias)
+        layers[f'{t}_self_interaction_1'] = IrrepsLinear(irreps_x, irreps_x, X, biases=bias, num_modalities=m_si1)
         layers[f'{t}_convolution'] = IrrepsConvolution(irreps_x, irreps_filter, irreps_out_tp, wnn,
                                                        cfg['act_radial'], denom[t], cfg['train_denominator'],
                                                        is_parallel=parallel,
@@ -767,7 +840,8 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
                                                            data_key_weight_input=f'{EDGE_EMB}{multi[t]}',
                                                            data_key_edge_idx=f'{EDGE_IDX}{multi[t]}')))
         layers[f'{t}_self_interaction_2'] = IrrepsLinear(layers[f'{t}_convolution'].irreps_mid,
-                                                         ir.simplify(gate_in), X, biases=bias)
+                                                         ir.simplify(gate_in), X, biases=bias,
+                                                         num_modalities=m_si2)
         layers[f'{t}_self_connection_outro'] = SelfConnectionOutro()
         layers[f'{t}_equivariant_gate'] = gate
         irreps_x = ir.simplify(gate._irreps_out)
@@ -776,12 +850,16 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
                                          cfg.get('readout_fcn_activation', 'relu'), X, SCALED_AE)
     else:
         hidden = [(ir.irreps_dim(irreps_x) // 2, (0, 1))]
-        layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X, biases=bias)
+        layers['reduce_input_to_hidden'] = IrrepsLinear(irreps_x, hidden, X, biases=bias, num_modalities=m_out)
         layers['reduce_hidden_to_energy'] = IrrepsLinear(hidden, [(1, (0, 1))], X, SCALED_AE, biases=bias)
     shift, scale = cfg['shift'], cfg['scale']
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale
-    if isinstance(shift, float) and isinstance(scale, float):
+    if nm:                                               # model_build.py:173-184
+        layers['rescale_atomic_energy'] = ModalWiseRescale.from_mappers(
+            shift, scale, cfg.get('use_modal_wise_shift', False), cfg.get('use_modal_wise_scale', False),
+            type_map=cfg['_type_map'], modal_map=cfg['_modal_map'], train_shift_scale=cfg['train_shift_scale'])
+    elif isinstance(shift, float) and isinstance(scale, float):
         layers['rescale_atomic_energy'] = Rescale(shift, scale, train_shift_scale=cfg['train_shift_scale'])
     else:
         shift = shift * S if isinstance(shift, list) and len(shift) == 1 else shift

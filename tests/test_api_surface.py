@@ -6,9 +6,9 @@ import inspect
 import json
 import os
 
-# the multi-modal rescale module and the modal deploy hook of the sequential are SURVEY 8f-4 items the module seam does
-# not carry (the engine / calculator / deploy() handle a frozen modality, tests/test_engine_emu.py)
-OUT_OF_SCOPE_CLASSES = {'ModalWiseRescale'}
+# the modal deploy hook of the sequential is the one SURVEY 8f-4 item the module seam does not carry (deploy(modal=...)
+# freezes a modality through the engine instead, tests/test_deploy_emu.py)
+OUT_OF_SCOPE_CLASSES = set()
 OUT_OF_SCOPE_METHODS = {('AtomGraphSequential', 'prepare_modal_deploy')}
 
 

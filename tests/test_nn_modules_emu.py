@@ -205,3 +205,37 @@ def test_sequential_bias_and_fcn_readout_variants(variant):
     ours = _run_pair(cfg, model.state_dict(), model, numbers, pos, cell)
     assert (set(k for k, v in ours.named_parameters() if v.numel()) ==
             set(k for k, v in model.named_parameters() if v.numel()))
+
+
+def test_sequential_multi_modal_matches_oracle():
+    """build_E3_equivariant_model on a multi-modal config: one_hot_modality + IrrepsLinear(num_modalities) +
+    ModalWiseRescale, data['modal_type'] selects the modality (single-structure data, as the calculator feeds it)."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg.update(use_modality=True, _number_of_modalities=2, _modal_map={'pbe': 0, 'scan': 1},
+               use_modal_node_embedding=True, use_modal_self_inter_intro=True, use_modal_self_inter_outro=True,
+               use_modal_output_block=True, use_modal_wise_shift=True, use_modal_wise_scale=True,
+               shift=[[0.1, -0.2, 0.3], [0.5, 0.4, -0.1]], scale=[[1.0, 1.5, 0.7], [0.9, 1.1, 1.3]])
+    torch.manual_seed(17)
+    ref = S.build_model(cfg).eval()
+    spec = sp.build_spec(cfg)
+    bnn.set_lib(build_full_emu([L.conv for L in spec.layers]))
+    model = bnn.build_E3_equivariant_model(cfg).eval()
+    missing, _ = model.load_state_dict(ref.state_dict(), strict=False)
+    assert not missing, missing
+    model.set_is_batch_data(False)
+    resc = model.rescale_atomic_energy
+    assert resc.get_shift(cfg['_type_map'], cfg['_modal_map'])['scan'][15] == pytest.approx(0.4)
+    numbers, pos, cell = random_cell(18, list(cfg['_type_map']), density=0.05, seed=14)
+    energies = []
+    for m in (0, 1):
+        g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+        g[S.MODAL_TYPE] = torch.tensor(m)
+        want = ref({k: (v.clone() if torch.is_tensor(v) else v) for k, v in g.items()})
+        got = model({k: (v.clone() if torch.is_tensor(v) else v) for k, v in g.items()})
+        assert abs(got[S.E_TOT].item() - want[S.E_TOT].item()) / len(numbers) < 1e-5
+        assert (got[S.FORCE] - want[S.FORCE].detach()).abs().max().item() < 1e-4
+        assert (got[S.STRESS] - want[S.STRESS].detach()).abs().max().item() * KBAR < 1e-2
+        energies.append(got[S.E_TOT].item())
+    assert abs(energies[0] - energies[1]) > 1e-3
+    with pytest.raises(NotImplementedError):
+        bnn.build_E3_equivariant_model(cfg, parallel=True)
