@@ -708,22 +708,34 @@ class ForceOutput(ForceStressOutputFromEdge):
 
 
 # ----------------------------------------------------------- sequential --
+class _ModalInputPrepare(nn.Module):
+    """sevenn/nn/sequential.py:22-38: writes the frozen modality index of a deployed single-modality model."""
+
+    def __init__(self, modal_idx: int):
+        super().__init__()
+        self.modal_idx = modal_idx
+
+    def forward(self, data):
+        data['modal_type'] = torch.tensor(self.modal_idx, dtype=torch.int64, device=data['x'].device)
+        return data
+
+
 class AtomGraphSequential(nn.Sequential):
     """sevenn/nn/sequential.py:41-205: the model container (same constructor, same helper methods)."""
 
     def __init__(self, modules, cutoff=0.0, type_map=None, modal_map=None, eval_type_map=True,
                  eval_modal_map=False, data_key_atomic_numbers=Z, data_key_node_feature=X, data_key_grad=None):
         modules = modules if isinstance(modules, OrderedDict) else OrderedDict(modules)
-        if eval_modal_map or modal_map is not None:
-            raise NotImplementedError('multi-modal models are outside the B200 hot path')
+        if eval_modal_map and modal_map is None:
+            raise ValueError('eval_modal_map is True but modal_map is None')          # sequential.py:86-87
         for m in modules.values():                        # sequential.py:_instantiate_modules (lazy-layer seam)
             if not getattr(m, 'layer_instantiated', True):
                 m.instantiate()
         super().__init__(modules)
-        self.cutoff, self.type_map, self.modal_map, self.key_grad = cutoff, type_map, None, data_key_grad
+        self.cutoff, self.type_map, self.modal_map, self.key_grad = cutoff, type_map, modal_map, data_key_grad
         self.key_atomic_numbers, self.key_node_feature = data_key_atomic_numbers, data_key_node_feature
         self.eval_type_map = eval_type_map and type_map is not None
-        self.eval_modal_map, self.is_batch_data = False, False
+        self.eval_modal_map, self.is_batch_data = eval_modal_map, False
         if type_map is not None:
             lut = -torch.ones(120, dtype=torch.long)
             for z, i in type_map.items():
@@ -743,8 +755,11 @@ class AtomGraphSequential(nn.Sequential):
         return None
 
     def prepand_module(self, key, module):
+        rest = [(k, v) for k, v in self._modules.items() if k != key]
+        self._modules.clear()                 # torch keeps `_modules` as a plain (insertion-ordered) dict
         self._modules[key] = module
-        self._modules.move_to_end(key, last=False)
+        for k, v in rest:
+            self._modules[k] = v
 
     def replace_module(self, key, module):
         self._modules[key] = module
@@ -758,9 +773,21 @@ class AtomGraphSequential(nn.Sequential):
     def _preprocess(self, data):
         if self.eval_type_map:
             data[self.key_node_feature] = self._atomic_numbers_to_onehot(data[self.key_atomic_numbers])
+        if self.eval_modal_map:                              # sequential.py:139-154: data_modality name(s) -> index
+            name = data['data_modality']
+            idx = self.modal_map[name] if isinstance(name, str) else [self.modal_map[n] for n in name]
+            data['modal_type'] = torch.tensor(idx, dtype=torch.int64, device=data[self.key_node_feature].device)
         if self.key_grad is not None:
             data[self.key_grad].requires_grad_(True)
         return data
+
+    def prepare_modal_deploy(self, modal: str):
+        """sequential.py:170-176: freeze the model to one modality (single-structure data from then on)."""
+        if self.modal_map is None:
+            return
+        self.eval_modal_map = False
+        self.set_is_batch_data(False)
+        self.prepand_module('modal_input_prepare', _ModalInputPrepare(self.modal_map[modal]))
 
     def forward(self, data: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
         data = self._preprocess(data)
@@ -869,7 +896,7 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
     layers['force_output'] = ForceStressOutputFromEdge()
     common = dict(cutoff=cfg['cutoff'], type_map=cfg['_type_map'], data_key_grad=EDGE_VEC)
     if not parallel:
-        return AtomGraphSequential(layers, **common)
+        return AtomGraphSequential(layers, modal_map=cfg.get('_modal_map') if nm else None, **common)
     return [AtomGraphSequential(seg, eval_type_map=False, **common) for seg in _parallel_segments(layers, cfg, S, L)]
 
 

@@ -6,10 +6,9 @@ import inspect
 import json
 import os
 
-# the modal deploy hook of the sequential is the one SURVEY 8f-4 item the module seam does not carry (deploy(modal=...)
-# freezes a modality through the engine instead, tests/test_deploy_emu.py)
+# nothing of the reference's module seam is left out (the multi-modal pieces: tests/test_nn_modules_emu.py)
 OUT_OF_SCOPE_CLASSES = set()
-OUT_OF_SCOPE_METHODS = {('AtomGraphSequential', 'prepare_modal_deploy')}
+OUT_OF_SCOPE_METHODS = set()
 
 
 def _params(fn):

@@ -239,3 +239,14 @@ def test_sequential_multi_modal_matches_oracle():
     assert abs(energies[0] - energies[1]) > 1e-3
     with pytest.raises(NotImplementedError):
         bnn.build_E3_equivariant_model(cfg, parallel=True)
+    # sequential.py:139-176: modality by name from the data, then frozen for deployment
+    assert model.modal_map == cfg['_modal_map']
+    model.eval_modal_map = True
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+    g['data_modality'] = 'scan'
+    assert abs(model(g)[S.E_TOT].item() - energies[1]) < 1e-4
+    model.prepare_modal_deploy('pbe')
+    assert not model.eval_modal_map and next(iter(model._modules)) == 'modal_input_prepare'
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+    g[S.X] = model._atomic_numbers_to_onehot(g[S.Z])          # _ModalInputPrepare reads data['x'].device
+    assert abs(model(g)[S.E_TOT].item() - energies[0]) < 1e-4
