@@ -112,6 +112,16 @@ int sevenn_rescale(const float* e_scaled, const int* types, long long n, const f
                    int species_wise, float* atomic_energy, float* seed, void* stream);
 /* AtomReduce (sevenn/nn/linear.py:104-141) and the stress sum: deterministic column sums in fp64 */
 int sevenn_colsum_f64(const float* a, long long n, int D, double* part /* >= 296*D */, double* out, void* stream);
+/* No-allocation variant of sevenn_colsum_f64.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid it).  Same kernels and results as sevenn_colsum_f64, but the stage-1 partials live in a file-scope
+ * `static __device__` array of SEVENN_COLSUM_NOALLOC_MAX_D * 296 doubles (18,944 B per GPU, held until exit) instead of
+ * a caller-provided `part`; D > SEVENN_COLSUM_NOALLOC_MAX_D returns SEVENN_ERR_BAD_ARG.  Calls cudaGetDevice /
+ * cudaGetSymbolAddress (once per device) and two kernel launches, nothing that allocates.  All calls on one device
+ * share the array: calls that overlap on the GPU (different streams) race; calls ordered on a stream do not (every
+ * partial that is read is rewritten first, nothing has to start at zero). */
+#define SEVENN_COLSUM_NOALLOC_MAX_D 8
+int sevenn_colsum_f64_noalloc(const float* a, long long n, int D, double* out, void* stream);
 /* ForceStressOutputFromEdge scatter part: sevenn/nn/force_output.py:185-222 */
 int sevenn_force_virial(const float* f_edge, const float* edge_vec, const int* rowptr, int n_rows, const int* cptr,
                         const int* cedge, long long n_nodes, float* F /* n_nodes,3 */, float* vir /* n_nodes,6 */,

@@ -49,6 +49,7 @@ SIGNATURES = {
     'sevenn_gate_bwd': ([c_p, c_i, c_p, c_i, c_p, c_ll, ctypes.POINTER(GatePiece), c_i, c_p], c_i),
     'sevenn_rescale': ([c_p, c_p, c_ll, c_p, c_p, c_i, c_p, c_p, c_p], c_i),
     'sevenn_colsum_f64': ([c_p, c_ll, c_i, c_p, c_p, c_p], c_i),
+    'sevenn_colsum_f64_noalloc': ([c_p, c_ll, c_i, c_p, c_p], c_i),
     'sevenn_force_virial': ([c_p, c_p, c_p, c_i, c_p, c_p, c_ll, c_p, c_p, c_p], c_i),
     'sevenn_segment_gather_sum': ([c_p, c_i, c_p, c_p, c_ll, c_p, c_i, c_p], c_i),
     'sevenn_gather_rows': ([c_p, c_i, c_p, c_ll, c_p, c_p], c_i),

@@ -8,6 +8,9 @@
 //   gather_rows / scatter_add_rows : halo pack / unpack-add (pair_e3gnn_parallel.cpp:787-897)
 // All HBM-bound; grid-stride, coalesced along the channel index.
 #include "sevenn_common.cuh"
+#ifndef SEVENN_EMU
+#include <atomic>
+#endif
 #include "../../include/sevenn_b200.h"
 
 HD float act_f(int id, float x) {
@@ -173,6 +176,41 @@ extern "C" int sevenn_colsum_f64(const float* a, long long n, int D, double* par
   for (int d = 0; d < D; ++d) { double s = 0; for (long long i = 0; i < n; ++i) s += a[i * D + d]; out[d] = s; }
   return 0;
 #else
+  colsum_stage1<<<COLSUM_BLOCKS, 256, 0, (cudaStream_t)stream>>>(a, n, D, part);
+  colsum_stage2<<<1, 32 * D, 0, (cudaStream_t)stream>>>(part, COLSUM_BLOCKS, D, out);
+  return (int)cudaGetLastError();
+#endif
+}
+
+// ---- no-allocation variant of sevenn_colsum_f64 (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops).  The stage-1 block
+// partials live in a file-scope device array (SEVENN_COLSUM_NOALLOC_MAX_D * 296 doubles = 18,944 B, held by every
+// GPU that loads the library until exit).  In host code `g_colsum_scratch` is only a stand-in for the symbol, not a
+// device address: the device address is looked up once per device, with that device current, by
+// cudaGetSymbolAddress and cached.  Every call on a device shares the array: stage 1 overwrites all 296 * D
+// partials it later reads, so nothing has to start at zero, but two calls that overlap on the GPU (different
+// streams) race on it.
+#ifndef SEVENN_EMU
+static __device__ __align__(256) double g_colsum_scratch[COLSUM_BLOCKS * SEVENN_COLSUM_NOALLOC_MAX_D];
+#define COLSUM_MAX_DEVICES 64
+static std::atomic<double*> g_colsum_scratch_ptr[COLSUM_MAX_DEVICES];   // per device; every writer stores the same value
+#endif
+extern "C" int sevenn_colsum_f64_noalloc(const float* a, long long n, int D, double* out, void* stream) {
+  if (D < 1 || D > SEVENN_COLSUM_NOALLOC_MAX_D || n < 0) return SEVENN_ERR_BAD_ARG;
+#ifdef SEVENN_EMU
+  for (int d = 0; d < D; ++d) { double s = 0; for (long long i = 0; i < n; ++i) s += a[i * D + d]; out[d] = s; }
+  return 0;
+#else
+  int dev = -1;
+  cudaError_t rc = cudaGetDevice(&dev);
+  if (rc != cudaSuccess) return (int)rc;
+  if (dev < 0 || dev >= COLSUM_MAX_DEVICES) return SEVENN_ERR_BAD_ARG;
+  double* part = g_colsum_scratch_ptr[dev].load(std::memory_order_acquire);
+  if (part == nullptr) {
+    rc = cudaGetSymbolAddress((void**)&part, g_colsum_scratch);
+    if (rc != cudaSuccess || part == nullptr) return rc != cudaSuccess ? (int)rc : SEVENN_ERR_BAD_ARG;
+    g_colsum_scratch_ptr[dev].store(part, std::memory_order_release);
+  }
   colsum_stage1<<<COLSUM_BLOCKS, 256, 0, (cudaStream_t)stream>>>(a, n, D, part);
   colsum_stage2<<<1, 32 * D, 0, (cudaStream_t)stream>>>(part, COLSUM_BLOCKS, D, out);
   return (int)cudaGetLastError();
