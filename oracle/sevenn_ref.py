@@ -589,7 +589,17 @@ def build_model(config, parallel=False):
     shift, scale = cfg['shift'], cfg['scale']
     shift = shift.tolist() if hasattr(shift, 'tolist') else shift
     scale = scale.tolist() if hasattr(scale, 'tolist') else scale
-    if nm:                                               # model_build.py:173-184 (values already per modal / type)
+    if nm:                                               # model_build.py:173-184
+        # ModalWiseRescale.from_mappers (nn/scale.py:238-330): a float broadcasts to [n_modal, n_types] (modal wise) or
+        # [n_types]; a per-modality list broadcasts over types; everything else is taken as it is
+        def _bcast(v, mw):
+            if isinstance(v, float):
+                return [[v] * S] * nm if mw else [v] * S
+            if mw and isinstance(v, list) and isinstance(v[0], float) and len(v) == nm:
+                return [[t] * S for t in v]
+            return v
+        shift = _bcast(shift, cfg.get('use_modal_wise_shift', False))
+        scale = _bcast(scale, cfg.get('use_modal_wise_scale', False))
         layers['rescale_atomic_energy'] = ModalWiseRescale(
             shift, scale, cfg.get('use_modal_wise_shift', False), cfg.get('use_modal_wise_scale', False),
             cfg['train_shift_scale'])

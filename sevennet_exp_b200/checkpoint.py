@@ -32,6 +32,7 @@ def patch_state_dict(spec: ModelSpec, sd: Dict[str, torch.Tensor], version) -> D
     sd = dict(sd)
     if _ver(version) >= (0, 11, 0):
         return sd
+    flipped = set()
     for L in spec.layers:
         conv = L.conv
         key = f'{conv.name}.weight_nn.layer{len(conv.hidden) - 2}.weight'
@@ -48,8 +49,11 @@ def patch_state_dict(spec: ModelSpec, sd: Dict[str, torch.Tensor], version) -> D
                 if not torch.allclose(sd[wkey], now, atol=1e-6):
                     assert torch.allclose(sd[wkey], -now, atol=1e-6), wkey
                     blk = -blk
+                    flipped.add(wkey)
             new[:, p.w_off:p.w_off + mul] = blk
         sd[key] = new
+    for wkey in flipped:          # like the reference (`stct[conv_w3j_key] *= -1`): the stored buffers follow the weights
+        sd[wkey] = -sd[wkey]
     return sd
 
 
@@ -63,4 +67,9 @@ def load_checkpoint(path: str):
     sd = patch_state_dict(spec, cp['model_state_dict'], cfg.get('version', '0.0.0'))
     missing = [k for k in spec.expected_keys() if k not in sd]
     assert not missing, f'checkpoint misses {missing}'
+    # The returned pair is in today's layout: say so, so that handing (cfg, sd) back to the `(config, state_dict)`
+    # entry points (SevenNetCalculator(file_type='model_instance'), deploy()) does not sort / flip a second time.
+    if _ver(cfg.get('version', '0.0.0')) < (0, 11, 0):
+        cfg['_checkpoint_version'] = cfg.get('version')
+        cfg['version'] = '0.11.0'
     return spec, sd, cfg

@@ -109,7 +109,7 @@ class Kernels:
         self.dev = torch.device(device)
         self.lib = lib if lib is not None else _lib.load()
         self.n_launch = 0
-        self._tc_cache = {}
+        self.n_tc_launch = 0       # launches that went to the tcgen05 arm (tests / smoke assert it is exercised)
         self._tc_tiles, self._sms = {}, None
         # dense contractions: 'auto' = tcgen05 3xTF32 arm for big row counts, exact-fp32 SIMT arm otherwise
         self.gemm_mode = os.environ.get('SEVENN_GEMM', 'auto')
@@ -142,11 +142,14 @@ class Kernels:
 
     def _tc_image(self, B):
         """Pre-swizzled (hi, lo) K-major image of a weight matrix for the tcgen05 arm (csrc/gemm_tc.cu)."""
-        key = B.data_ptr()
-        if key not in self._tc_cache:
+        # The image lives ON the weight tensor (dropped with it) and is tagged with the tensor's version counter: a
+        # cache keyed on data_ptr() alone would hand a recycled address the previous owner's weights.
+        tag = getattr(B, '_sevenn_tc_img', None)
+        if tag is None or tag[0] != B._version:
             W = B.detach().cpu().numpy().astype(np.float32)
-            self._tc_cache[key] = torch.from_numpy(tc_image_for(self.lib, W)).to(self.dev).contiguous()
-        return self._tc_cache[key]
+            tag = (B._version, torch.from_numpy(tc_image_for(self.lib, W)).to(self.dev).contiguous())
+            B._sevenn_tc_img = tag
+        return tag[1]
 
     def _gemm_args(self, A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi=0, act=0, cst=1.0, C2=None, P=None):
         g = _lib.GemmArgs(A.data_ptr() + 4 * a_off, sAn, sAm, B.data_ptr(), N, C.data_ptr() + 4 * c_off, sCn, sCm,
@@ -161,6 +164,7 @@ class Kernels:
         g, tc = self._gemm_args(A, a_off, sAn, sAm, B, C, c_off, sCn, sCm, M, R, N, K, epi, act, cst, C2, P)
         if tc:
             self.lib.call('sevenn_gemm_tc', ctypes.byref(g), _p(self._tc_image(B)), self._stream())
+            self.n_tc_launch += 1
         else:
             self.lib.call('sevenn_gemm_f32', ctypes.byref(g), self._stream())
         self.n_launch += 1
@@ -181,7 +185,9 @@ class Kernels:
             arr = (_lib.GemmArgs * len(part))(*[g for g, _ in part])
             imgs = (ctypes.c_void_p * len(part))(*[im.data_ptr() for _, im in part])
             self.lib.call('sevenn_gemm_tc_grouped', len(part), arr, imgs, self._stream())
-            self.n_launch += self._tc_group_launches([g for g, _ in part])
+            k_l = self._tc_group_launches([g for g, _ in part])
+            self.n_launch += k_l
+            self.n_tc_launch += k_l
 
     def _tc_group_launches(self, gs):
         """Launches sevenn_gemm_tc_grouped makes for these problems (csrc/gemm_tc.cu: a member with >= 2 tiles per

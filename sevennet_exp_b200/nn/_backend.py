@@ -24,6 +24,8 @@ def get_lib():
 
 def kernels(device) -> Kernels:
     device = torch.device(device)
+    if device.type == 'cuda' and device.index is None:
+        device = torch.device('cuda', torch.cuda.current_device())
     key = (device.type, device.index)
     if key not in _kernels:
         _kernels[key] = Kernels(get_lib(), device)

@@ -86,7 +86,7 @@ class BesselBasis(nn.Module):
         super().__init__()
         self.num_basis, self.cutoff_length = bessel_basis_num, cutoff_length
         c = torch.FloatTensor([n * math.pi / cutoff_length for n in range(1, bessel_basis_num + 1)])
-        self.coeffs = nn.Parameter(c, requires_grad=False) if trainable_coeff else c
+        self.coeffs = nn.Parameter(c) if trainable_coeff else c      # trainable, edge_embedding.py:96-100
 
 
 class PolynomialCutoff(nn.Module):
@@ -430,7 +430,7 @@ class IrrepsConvolution(nn.Module):
         self.key_weight_input, self.key_edge_idx = data_key_weight_input, data_key_edge_idx
         self.layer_instantiated = True       # the fused kernel has no separate e3nn TensorProduct to build lazily
         act = weight_layer_act if isinstance(weight_layer_act, str) else getattr(weight_layer_act, '__name__', '')
-        self.denominator = nn.Parameter(torch.FloatTensor([denominator]), requires_grad=False)
+        self.denominator = nn.Parameter(torch.FloatTensor([denominator]), requires_grad=train_denominator)
         self.is_parallel = is_parallel
         hidden = list(weight_layer_input_to_hidden)
         self._conv = sp.make_conv('convolution', ir.simplify(_irreps(irreps_x)), _irreps(irreps_filter),
@@ -495,8 +495,8 @@ class Rescale(nn.Module):
 
     def __init__(self, shift, scale, data_key_in=SCALED_AE, data_key_out=AE, train_shift_scale=False):
         super().__init__()
-        self.shift = nn.Parameter(torch.FloatTensor([shift]), requires_grad=False)
-        self.scale = nn.Parameter(torch.FloatTensor([scale]), requires_grad=False)
+        self.shift = nn.Parameter(torch.FloatTensor([shift]), requires_grad=train_shift_scale)
+        self.scale = nn.Parameter(torch.FloatTensor([scale]), requires_grad=train_shift_scale)
         self.key_input, self.key_output = data_key_in, data_key_out
 
     def get_shift(self):
@@ -520,8 +520,8 @@ class SpeciesWiseRescale(nn.Module):
         n = len(shift) if isinstance(shift, list) else len(scale)
         shift = [shift] * n if isinstance(shift, float) else shift
         scale = [scale] * n if isinstance(scale, float) else scale
-        self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=False)
-        self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=False)
+        self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=train_shift_scale)
+        self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=train_shift_scale)
 
     def get_shift(self, type_map=None):
         v = self.shift.detach().cpu().tolist()
@@ -556,8 +556,8 @@ class ModalWiseRescale(nn.Module):
                  data_key_atom_indices=ATOM_TYPE, use_modal_wise_shift=False, use_modal_wise_scale=False,
                  train_shift_scale=False):
         super().__init__()
-        self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=False)
-        self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=False)
+        self.shift = nn.Parameter(torch.FloatTensor(shift), requires_grad=train_shift_scale)
+        self.scale = nn.Parameter(torch.FloatTensor(scale), requires_grad=train_shift_scale)
         self.key_input, self.key_output = data_key_in, data_key_out
         self.key_atom_indices, self.key_modal_indices = data_key_atom_indices, data_key_modal_indices
         self.use_modal_wise_shift, self.use_modal_wise_scale = use_modal_wise_shift, use_modal_wise_scale

@@ -413,3 +413,147 @@ def test_deployed_entry_points_on_gpu(lib, golden_dir, tmp_path):
     F = torch.zeros(n + len(owner), 3, device='cuda').index_add_(0, eit[0], dE_dr).index_add_(0, eit[1], -dE_dr)
     F = F[:n].index_add_(0, own_t, F[n:])
     assert np.abs(F.cpu().numpy() - gold['force']).max() < 1e-4
+
+
+# ---- the path the bench times: tcgen05 3xTF32 GEMM arm + tabulated radial weights at >= 1,000 atoms, against the fp64
+# oracle (outputs committed by tests/golden/make_large_oracle_fixtures.py: the oracle needs minutes / tens of GB there)
+def _large_case(golden_dir, tag):
+    from tests.golden.make_large_oracle_fixtures import state_sha1
+    fx = np.load(os.path.join(golden_dir, f'large_oracle_{tag}.npz'))
+    cfg, model = _random_model(str(fx['preset']))
+    assert state_sha1(model.state_dict()) == str(fx['state_sha1']), 'seeded weights differ from the fixture\'s'
+    return cfg, model, fx
+
+
+@pytest.mark.parametrize('tag', ['7net0_hfo2_324', '7net0_hfo2_1500', 'l3i5_lips_1000'])
+def test_bench_path_vs_fp64_oracle_fixture(lib, golden_dir, tag):
+    """SevenNet-0 shape on 324- and 1,500-atom fluorite HfO2 at the bench density, SevenNet-l3i5 shape on a 1,000-atom
+    Li-P-S cell; weights scaled so forces are O(0.1 eV/A).  Every combination of radial mode (table = bench default,
+    mlp) and GEMM arm selection (default threshold, everything forced onto the tcgen05 arm) against the fp64 oracle
+    at north_star's tolerances -- not against another arm of this library."""
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cfg, model, fx = _large_case(golden_dir, tag)
+    numbers, pos, cell = fx['numbers'], fx['pos'], fx['cell']
+    n = len(numbers)
+    worst = {}
+    for radial in ('table', 'mlp'):
+        for tc_min_rows in (None, 1):
+            os.environ['SEVENN_RADIAL'] = radial
+            try:
+                calc = SevenNetCalculator((dict(cfg), model.state_dict()), file_type='model_instance')
+            finally:
+                os.environ.pop('SEVENN_RADIAL')
+            if tc_min_rows is not None:
+                calc.engine.tc_min_rows = tc_min_rows
+            res = calc.compute(numbers, pos, cell, [True] * 3)
+            assert calc.engine.n_tc_launch > 0, 'the tcgen05 arm did not run'
+            assert res['n_edges'] == int(fx['n_edges'])
+            dE = abs(res['energy'] - float(fx['energy'])) / n
+            dAE = np.abs(res['energies'] - fx['atomic_energy']).max()
+            dF = np.abs(res['forces'] - fx['forces']).max()
+            dS = np.abs(res['inferred_stress'] - fx['stress']).max() * KBAR
+            worst[(radial, tc_min_rows)] = (dE, dAE, dF, dS, calc.engine.n_tc_launch)
+            assert dE < 1e-5, (tag, radial, tc_min_rows, dE)
+            assert dAE < 1e-4, (tag, radial, tc_min_rows, dAE)
+            assert dF < 1e-4, (tag, radial, tc_min_rows, dF)
+            assert dS < 1e-3 * max(1.0, np.abs(fx['stress']).max() * KBAR * 1e-3), (tag, radial, tc_min_rows, dS)
+    print(tag, 'max|F| %.3f eV/A' % np.abs(fx['forces']).max(), worst)
+
+
+def test_tc_weight_image_follows_the_weights(lib):
+    """Two models of one architecture built back to back (the caching allocator hands the second one the first one's
+    addresses) and an in-place weight update: the tcgen05 arm must use the CURRENT weights (its pre-swizzled image is
+    tied to the weight tensor and its version, not to data_ptr)."""
+    import copy
+    from sevennet_exp_b200 import nn as bnn
+    from sevennet_exp_b200.nn import _backend
+    numbers, pos, cell = random_cell(64, list(presets.PRESETS['test-so3-l2']['_type_map']), density=0.05, seed=8)
+    kern = _backend.kernels('cuda')
+    outs = {}
+    for seed in (1, 2, 3):
+        cfg, om = _random_model('test-so3-l2', seed=seed)
+        g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+        assert g[S.EDGE_IDX].shape[1] >= 1024          # radial-MLP GEMMs are over the tc threshold
+        for mode in ('tc', 'simt'):
+            kern.gemm_mode, n0 = ('auto' if mode == 'tc' else 'simt'), kern.n_tc_launch
+            model = bnn.build_E3_equivariant_model(cfg).eval()
+            assert not model.load_state_dict(om.state_dict(), strict=False)[0]
+            model = model.cuda()
+            out = model({k: (v.cuda() if torch.is_tensor(v) else v) for k, v in copy.deepcopy(g).items()})
+            outs[(seed, mode)] = (out[S.E_TOT].item(), out[S.FORCE].detach().cpu().numpy())
+            assert (kern.n_tc_launch > n0) == (mode == 'tc')
+            if seed == 3 and mode == 'tc':           # in-place update of live parameters, same addresses
+                with torch.no_grad():
+                    for p_ in model.parameters():
+                        p_.mul_(1.05)
+                out = model({k: (v.cuda() if torch.is_tensor(v) else v) for k, v in copy.deepcopy(g).items()})
+                outs['inplace'] = (out[S.E_TOT].item(), out[S.FORCE].detach().cpu().numpy())
+            del model, out
+    kern.gemm_mode = 'auto'
+    for seed in (1, 2, 3):
+        (e_tc, f_tc), (e_s, f_s) = outs[(seed, 'tc')], outs[(seed, 'simt')]
+        assert abs(e_tc - e_s) / len(numbers) < 5e-6 and np.abs(f_tc - f_s).max() < 5e-5, seed
+    assert abs(outs[(1, 'tc')][0] - outs[(2, 'tc')][0]) > 1e-3       # the models really differ
+    assert np.abs(outs['inplace'][1] - outs[(3, 'tc')][1]).max() > 1e-4
+
+
+# ---- SURVEY 8f-4 variants on hardware: multi-modal checkpoints, biases in the linears, FCN readout
+def _modal_cfg(bias):
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    zs = list(cfg['_type_map'])
+    assert len(zs) == 3
+    cfg.update(version='0.11.0', use_modality=True, _number_of_modalities=3, _modal_map={'pbe': 0, 'scan': 1, 'r2scan': 2},
+               use_modal_node_embedding=True, use_modal_self_inter_intro=True, use_modal_self_inter_outro=True,
+               use_modal_output_block=True, use_modal_wise_shift=True, use_modal_wise_scale=False,
+               use_bias_in_linear=bias,
+               shift=[[0.1, -0.2, 0.3], [0.5, 0.4, -0.1], [-0.3, 0.2, 0.0]], scale=[10.0, 15.0, 7.0])
+    return cfg
+
+
+@pytest.mark.parametrize('bias', [False, True])
+def test_multi_modal_and_bias_on_gpu(lib, bias):
+    """SevenNet-MF style checkpoint (modality one-hot into embedding / self-interaction / readout linears, modal-wise
+    shift) with and without o3.Linear biases: every modality through SevenNetCalculator(modal=...) vs the fp64 oracle."""
+    import copy
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cfg = _modal_cfg(bias)
+    torch.manual_seed(11)
+    model = S.build_model(cfg).eval()
+    if bias:
+        with torch.no_grad():
+            for n_, p_ in model.named_parameters():
+                if n_.endswith('linear.bias'):
+                    p_.normal_(0.0, 0.3)
+    numbers, pos, cell = random_cell(40, list(cfg['_type_map']), density=0.05, seed=6)
+    energies = []
+    for name, m in cfg['_modal_map'].items():
+        calc = SevenNetCalculator((dict(cfg), model.state_dict()), file_type='model_instance', modal=name)
+        res = calc.compute(numbers, pos, cell, [True] * 3)
+        torch.set_default_dtype(torch.float64)
+        try:
+            g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'], dtype=torch.float64)
+            g[S.MODAL_TYPE] = torch.tensor(m)
+            ref = copy.deepcopy(model).double()(dict(g))
+        finally:
+            torch.set_default_dtype(torch.float32)
+        n = len(numbers)
+        assert abs(res['energy'] - ref[S.E_TOT].item()) / n < 1e-5, (name, bias)
+        assert np.abs(res['forces'] - ref[S.FORCE].detach().numpy()).max() < 1e-4, (name, bias)
+        sref = ref[S.STRESS].detach().numpy()
+        assert np.abs(res['inferred_stress'] - sref).max() * KBAR < 1e-3 * max(1.0, np.abs(sref).max() * KBAR * 1e-3)
+        energies.append(res['energy'])
+    assert abs(energies[0] - energies[1]) > 1e-3 and abs(energies[1] - energies[2]) > 1e-3
+    with pytest.raises(ValueError):
+        SevenNetCalculator((dict(cfg), model.state_dict()), file_type='model_instance')          # modal missing
+
+
+@pytest.mark.parametrize('act', ['relu', 'silu'])
+def test_readout_as_fcn_on_gpu(lib, act):
+    """readout_as_fcn (model_build.py:141-155, nn/linear.py:145-180) on the GPU kernels vs the fp64 oracle."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg.update(version='0.11.0', readout_as_fcn=True, readout_fcn_hidden_neurons=[16, 8], readout_fcn_activation=act,
+               scale=[10.0] * cfg['_number_of_species'])
+    torch.manual_seed(21)
+    model = S.build_model(cfg).eval()
+    numbers, pos, cell = random_cell(40, list(cfg['_type_map']), density=0.05, seed=12)
+    print(_engine_vs_oracle(cfg, model.state_dict(), model, numbers, pos, cell, [True] * 3))

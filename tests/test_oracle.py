@@ -149,3 +149,29 @@ def test_oracle_reproduces_reference_deployed_torchscript(golden_dir):
     assert np.abs(out[S.FORCE].detach().numpy() - gold['force']).max() < 2e-5      # eV/A
     # the artefact's stress comes from dE/d(strain): same (xx,yy,zz,xy,yz,zx) order as the edge virial
     assert np.abs(out[S.STRESS].detach().numpy() - gold['stress']).max() * 1602.1766208 < 1e-3 * 10   # kbar, fp32 ref
+
+
+def test_large_fixture_generator_is_the_oracle(golden_dir):
+    """tests/golden/make_large_oracle_fixtures.py wraps the oracle's convolution in torch.utils.checkpoint (memory only):
+    on a small cell it must give exactly what the plain oracle gives, and the committed fixtures must belong to the
+    weights the GPU tests rebuild from the seed."""
+    import copy
+    from tests.golden import make_large_oracle_fixtures as M
+    from tests.structures import random_cell
+    from tests.test_gpu_parity import _random_model
+    cfg, model = _random_model('test-so3-l2')
+    numbers, pos, cell = random_cell(24, list(cfg['_type_map']), density=0.05, seed=3)
+    g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
+    plain = model(dict(g))
+    keep = S.IrrepsConvolution.forward
+    try:
+        S.IrrepsConvolution.forward = M._conv_forward_checkpointed
+        ck = copy.deepcopy(model)(dict(S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])))
+    finally:
+        S.IrrepsConvolution.forward = keep
+    # same arithmetic; only the order in which autograd accumulates edge_vec gradients differs (fp32 round-off)
+    assert torch.equal(plain[S.E_TOT], ck[S.E_TOT])
+    assert (plain[S.FORCE] - ck[S.FORCE]).abs().max() < 2e-6 * plain[S.FORCE].abs().max()
+    for tag, (name, _) in M.CASES.items():
+        fx = np.load(os.path.join(golden_dir, f'large_oracle_{tag}.npz'))
+        assert str(fx['state_sha1']) == M.state_sha1(_random_model(name)[1].state_dict()), tag
