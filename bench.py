@@ -1,15 +1,17 @@
 #!/usr/bin/env python
 """bench.py -- atom-steps/s of one SevenNet-0 energy+forces+stress evaluation (BASELINE.json metric).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload si1m|cfg1|cfg2|cfg3]
 
-N = 1  : BASELINE config 2 -- 4,096-atom synthetic bulk HfO2 cell (fluorite 7x7x7, a = 4.80 A, 20 vacancies,
-         sigma = 0.05 A rattle, ~50 neighbours/atom at rc = 5 A), SevenNet-0 hyper-parameters, random-init
-         weights (torch.manual_seed(777)); a step = neighbour list + forward + analytic reverse pass.
-N > 1  : the same cell replicated over a brick of N sub-domains (weak scaling, 4,096 owned atoms per GPU),
-         LAMMPS-style spatial decomposition with ghost-atom feature exchange per layer (domain.py).
---impl reference : the CPU restatement oracle (oracle/, kind "port": the reference itself needs e3nn/ase,
-         which are not installable here) on the host cores, bounded sample of the same workload.
+Default workload for EVERY N (north_star's target, BASELINE config 4): ONE 1,000,000-atom bulk-Si cell (50^3 diamond
+cells, a = 5.431 A, sigma = 0.05 A rattle), SevenNet-0 hyper-parameters, random-init weights (seed 777), strong scaling:
+N = 1 evaluates the periodic cell on one GPU, N > 1 cuts it into the LAMMPS brick grid (2x1x1, 2x2x1, 2x2x2) with
+ghost-atom feature exchange per layer (domain.py).  A step = device neighbour list + forward + analytic reverse pass.
+Other workloads (logged under profiles/, not the driver's line): cfg1 = 64-atom Si, cfg2 = 4,096-atom HfO2 (N > 1: weak
+scaling, the cell replicated over the brick grid), cfg3 = SevenNet-l3i5 on 32,768 Li-P-S atoms.
+--impl reference : the CPU restatement oracle (oracle/, kind "port": the reference itself needs e3nn/ase, which are
+         not installable here) on the host cores, on a bounded sample of the same workload (same sample as the
+         `cpu_baseline` block of the default line).
 """
 import argparse
 import json
@@ -134,58 +136,191 @@ def conv_fwd_algorithmic_bytes(conv, n_dst, n_edges):
     return n_edges * 4 * (conv.wn + S + 1 + conv.lx.dim) + n_dst * (4 * conv.lmid.dim + 4)
 
 
-def cpu_oracle_sample(reps, steps, warmup):
-    """Times the CPU restatement (oracle/) on a bounded HfO2 sample of the same density."""
+def kdtree_graph(numbers, pos, cell, cutoff):
+    """CPU-baseline graph build for an orthorhombic periodic cell with scipy's cKDTree (C code, like the matscipy /
+    ase neighbour lists the reference calls, sevenn/train/dataload.py:32-88) -> the oracle's graph dict.  The
+    brute-force O(N^2 x images) list of oracle/ is an edge-set checker, not a fair timing stand-in."""
+    from scipy.spatial import cKDTree
     from oracle import sevenn_ref as S
-    cfg = model_config()
+    L = np.diag(cell)
+    assert np.allclose(cell, np.diag(L)) and (L > 2 * cutoff).all()
+    w = pos - np.floor(pos / L) * L
+    w = np.where(w >= L, w - L, w)
+    tree = cKDTree(w, boxsize=L)
+    pairs = tree.query_pairs(cutoff, output_type='ndarray')
+    i = np.concatenate([pairs[:, 0], pairs[:, 1]])
+    j = np.concatenate([pairs[:, 1], pairs[:, 0]])
+    d = w[j] - w[i]
+    D = d - np.round(d / L) * L
+    keep = (D ** 2).sum(1) < cutoff * cutoff
+    i, j, D = i[keep], j[keep], D[keep]
+    order = np.lexsort((j, i))
+    i, j, D = i[order], j[order], D[order]
+    sh = np.round((D - (pos[j] - pos[i])) / L)          # D = pos_j + S.cell - pos_i for the unwrapped positions
+    return {S.X: torch.as_tensor(numbers, dtype=torch.int64), S.Z: torch.as_tensor(numbers, dtype=torch.int64),
+            S.POS: torch.as_tensor(pos, dtype=torch.float32), S.EDGE_IDX: torch.as_tensor(np.stack([i, j])),
+            S.EDGE_VEC: torch.as_tensor(D, dtype=torch.float32), S.CELL: torch.as_tensor(cell, dtype=torch.float32),
+            S.SHIFT: torch.as_tensor(sh, dtype=torch.float32),
+            S.VOL: torch.tensor(float(np.prod(L)), dtype=torch.float32),
+            S.NATOMS: torch.tensor(len(numbers), dtype=torch.int64)}
+
+
+def cpu_sample_structure(workload_name):
+    """Bounded sample of the workload for the CPU legs: same lattice, density and model shape, >= 1,000 atoms (host
+    memory permitting: the oracle keeps ~16 KB per edge and layer alive for autograd, like e3nn does)."""
+    from tests.structures import diamond_si, jittered_lips
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available / 2 ** 30
+    except Exception:  # noqa: BLE001
+        avail = 32.0
+    big = avail >= 96.0          # the SevenNet-0 oracle holds ~27 GB at 1,728 Si atoms
+    if workload_name in ('si1m', 'cfg1'):
+        r = 6 if big else 4
+        numbers, pos, cell = diamond_si((r, r, r))
+        return model_config(), numbers, pos, cell, f'bulk Si {r}x{r}x{r} diamond cells'
+    if workload_name == 'cfg3':
+        ns = 10 if big else 8
+        numbers, pos, cell = jittered_lips(n_side=ns)
+        return dict(presets.PRESETS['7net-l3i5']), numbers, pos, cell, f'disordered Li-P-S, {ns}^3 sites'
+    r = 5 if big else 3
+    numbers, pos, cell = fluorite_hfo2((r, r, r), a=A_LAT, sigma=0.05, seed=0)
+    return model_config(), numbers, pos, cell, f'fluorite HfO2 {r}x{r}x{r} cells'
+
+
+def cpu_oracle_leg(workload_name, steps, warmup, device='cpu'):
+    """The CPU restatement (oracle/) timed on the host cores: `warmup` untimed + `steps` timed full evaluations (graph
+    build + forward + autograd forces/stress), MEDIAN.  device='cuda' runs the same PyTorch program on the GPU (ATen
+    library kernels: what the reference's e3nn path would launch) as an informational comparator."""
+    from oracle import sevenn_ref as S
+    cfg, numbers, pos, cell, what = cpu_sample_structure(workload_name)
     torch.manual_seed(777)
     model = S.build_model(cfg).eval()
-    numbers, pos, cell = fluorite_hfo2(reps, a=A_LAT, sigma=0.05, seed=0)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     ts = []
-    for k in range(warmup + steps):
-        t0 = time.perf_counter()
-        g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
-        out = model(g)
-        float(out[S.E_TOT].detach()); out[S.FORCE].sum().item()
-        if k >= warmup:
-            ts.append(time.perf_counter() - t0)
-    t = float(np.mean(ts))
-    return len(numbers) / t, t, cores, len(numbers), int(g[S.EDGE_IDX].shape[1])
+    if device != 'cpu':
+        torch.set_default_device(device)
+        model = model.to(device)
+        if hasattr(model, 'z_to_onehot_tensor'):
+            model.z_to_onehot_tensor = model.z_to_onehot_tensor.to(device)
+    try:
+        for k in range(warmup + steps):
+            t0 = time.perf_counter()
+            g = kdtree_graph(numbers, pos, cell, cfg['cutoff'])
+            if device != 'cpu':
+                g = {k_: v.to(device) for k_, v in g.items()}
+            out = model(g)
+            float(out[S.E_TOT].detach()); out[S.FORCE].sum().item(); out[S.STRESS].sum().item()
+            if k >= warmup:
+                ts.append(time.perf_counter() - t0)
+            n_edges = int(g[S.EDGE_IDX].shape[1])
+            del out, g
+    finally:
+        if device != 'cpu':
+            torch.set_default_device('cpu')
+    t = float(np.median(ts))
+    n = len(numbers)
+    sample = (f'oracle/ (CPU restatement of the reference path, fp32) on {n} atoms of {what} at the workload density '
+              f'({n_edges / n:.1f} neighbours/atom): cKDTree graph + forward + autograd forces/stress, '
+              f'{warmup} warm-up + {steps} timed evaluations, median {t:.2f} s')
+    return {'value': n / t, 'unit': UNIT, 'cores': cores if device == 'cpu' else 0, 'kind': 'port', 'sample': sample,
+            'n_atoms': n, 'n_edges': n_edges, 's_per_eval': t}
+
+
+WORKLOAD_TEXT = {
+    'si1m': 'SevenNet-0 (lmax2, 5 layers, 128x0e+64x1e+32x2e, rc=5A, random-init weights) E+F+S, ONE bulk-Si cell of '
+            '{n} atoms ({c}^3 diamond cells, a=5.431A, rattle 0.05A), {nb:.1f} neighbours/atom',
+    'cfg1': 'SevenNet-0 E+F+S, 64-atom bulk Si (2x2x2 diamond cells), {nb:.1f} neighbours/atom (BASELINE config 1)',
+    'cfg2': 'SevenNet-0 (lmax2, 5 layers, 128x0e+64x1e+32x2e, rc=5A, random-init weights) E+F+S, {n}-atom bulk HfO2 '
+            '(fluorite 7x7x7, a=4.8A, 20 vacancies), {nb:.1f} neighbours/atom (BASELINE config 2)',
+    'cfg3': 'SevenNet-l3i5 (lmax3, 5 layers, 128x0e+64x1e+32x2e+32x3e, rc=5A, random-init weights) E+F+S, {n}-atom '
+            'disordered Li-P-S cell (3:1:4, 0.048 atoms/A^3, hard core 1.95 A), {nb:.1f} neighbours/atom (BASELINE config 3)',
+}
 
 
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    v, t, cores, n, e = cpu_oracle_sample((2, 2, 2), args.steps, args.warmup)
-    sample = (f'{n}-atom fluorite HfO2 2x2x2 cell at the workload density ({e / n:.1f} neighbours/atom), full '
-              f'neighbour list + forward + autograd forces/stress per step')
-    line = {'impl': 'reference', 'metric': METRIC, 'value': v, 'unit': UNIT, 'n_gpus': args.gpus,
-            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': t * 1e3, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': 'SevenNet-0 E+F+S, bulk HfO2, ~50 neighbours/atom, rc=5A (CPU sample: 96 atoms)'},
-            'cpu_baseline': {'value': v, 'unit': UNIT, 'cores': cores, 'kind': 'port', 'sample': sample},
-            'e2e': {'value': v, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    r = cpu_oracle_leg(args.workload, args.steps, args.warmup)
+    line = {'impl': 'reference', 'metric': METRIC, 'value': r['value'], 'unit': UNIT, 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': r['s_per_eval'] * 1e3, 'higher_is_better': True,
+            'scaling': 'weak' if args.workload == 'cfg2' else 'strong', 'vs_baseline': None, 'dtype': 'f32',
+            'data': 'synthetic',
+            'config': {'workload': WORKLOAD_TEXT[args.workload].split('{')[0] + f'... CPU sample: {r["n_atoms"]} atoms '
+                                   '(per-atom cost of this path does not depend on the cell size)',
+                       'n_atoms': r['n_atoms'], 'n_edges': r['n_edges']},
+            'cpu_baseline': {k: r[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
+            'e2e': {'value': r['value'], 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    if args.workload == 'cfg3':
+        line['metric'] = 'atom-steps/s (E+F+S) SevenNet-l3i5'
     print(json.dumps(line), flush=True)
+
+
+def make_workload(name, si_cells=50):
+    """(model config, numbers, positions, cell) of a BASELINE configuration (SURVEY 8d's generators and seeds)."""
+    from tests.structures import diamond_si, jittered_lips
+    if name == 'si1m':
+        nc = int(si_cells)
+        numbers, pos, cell = diamond_si((nc, nc, nc))
+        pos = pos + np.random.default_rng(2).normal(0.0, 0.05, pos.shape)
+        return model_config(), numbers, pos, cell
+    if name == 'cfg1':
+        return (model_config(),) + tuple(diamond_si((2, 2, 2)))
+    if name == 'cfg3':
+        return (dict(presets.PRESETS['7net-l3i5']),) + tuple(jittered_lips())
+    return (model_config(),) + tuple(workload())
+
+
+def ncu_capture(kernel, n_edges):
+    """dram bytes / tensor-pipe utilisation of ONE launch of `kernel` on this workload from the committed ncu --set full
+    capture (profiles/ncu_captures.json: written from the raw CSVs under profiles/), or None."""
+    try:
+        for row in json.load(open(os.path.join(ROOT, 'profiles', 'ncu_captures.json'))):
+            if row['kernel'] == kernel and abs(row['n_edges'] - n_edges) <= 0.001 * n_edges:
+                return row
+    except Exception:  # noqa: BLE001
+        pass
+    return None
+
+
+def gemm_roofline(spec, stage, n_atoms, peak_hbm):
+    """north_star asks for tensor-pipe utilisation per GEMM: the dominant node linear is self_interaction_2 (mid ->
+    gate input, per-l blocks, accumulating onto the self connection).  A + C bytes and 3xTF32 MMA flops of all layers
+    over the CUDA-event time of the `si2_fwd` stage."""
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:  # noqa: BLE001
+        pass
+    tf32_peak = float(peaks.get('bf16_tflops_sustained', 1400.0)) / 2.0      # dense tf32 = half the bf16 rate
+    bytes_, flops = 0.0, 0.0
+    for L in spec.layers:
+        bytes_ += n_atoms * 4.0 * (L.conv.lmid.dim + 2 * L.gate.lin.dim)          # read A, read + write C
+        flops += sum(2.0 * n_atoms * (2 * b.l + 1) * b.K * b.N for b in L.si2.blocks)
+    ms = stage.get('si2_fwd')
+    if not ms:
+        return None
+    cap = ncu_capture('gemm_tc_kernel', 0)
+    return {'bound': 'hbm', 'kernel': 'gemm_tc_kernel (tcgen05 3xTF32), self_interaction_2 forward of all layers',
+            'achieved': bytes_ / (ms * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s',
+            'frac': bytes_ / (ms * 1e-3) / 1e9 / peak_hbm, 'algorithmic_bytes': bytes_, 'ms': ms,
+            'tensor': {'tflops_tf32_mma': 3.0 * flops / (ms * 1e-3) / 1e12, 'peak_tf32': tf32_peak,
+                       'frac': 3.0 * flops / (ms * 1e-3) / 1e12 / tf32_peak,
+                       'note': '3 tf32 MMAs per fp32 product (hi*hi + hi*lo + lo*hi); K <= 352 per block: these '
+                               'GEMMs are bound by streaming A and C, not by the tensor pipe',
+                       'ncu_tensor_pipe_pct': cap.get('tensor_pipe_pct') if cap else None}}
 
 
 def run_single(args):
     from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
     dev = torch.device('cuda:0')
     torch.cuda.set_device(dev)
-    cfg3 = args.workload == 'cfg3'
-    if cfg3:
-        # BASELINE config 3: SevenNet-l3i5 (lmax 3) on a 32,768-atom disordered Li-P-S cell (not the default line)
-        from tests.structures import jittered_lips
-        cfg = dict(presets.PRESETS['7net-l3i5'])
-        numbers, pos, cell = jittered_lips()
-    else:
-        cfg = model_config()
-        numbers, pos, cell = workload()
+    wl = args.workload
+    cfg, numbers, pos, cell = make_workload(wl, args.si_cells)
     sd = random_state_dict(cfg)
-    calc = SevenNetCalculator((cfg, sd), file_type='model_instance', device=dev)
+    calc = SevenNetCalculator((cfg, sd), file_type='model_instance', device=dev, keep_weights=False)
     n = len(numbers)
     pbc = [True] * 3
     types_dev = torch.from_numpy(calc._lut[numbers].astype(np.int32)).to(dev)
@@ -198,6 +333,7 @@ def run_single(args):
 
     for _ in range(args.warmup):
         g, out = step()
+        del out
     torch.cuda.synchronize()
     sampler = ClockSampler()
     sampler.start()
@@ -211,6 +347,7 @@ def run_single(args):
         g, out = step()
         b.record()
         evs.append((a, b))
+        del out
     torch.cuda.synchronize()
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
     launches = calc.engine.n_launch + calc.nl.n_launch - l0
@@ -232,7 +369,7 @@ def run_single(args):
 
     # per-stage device times (separate pass, CUDA events on the launch stream)
     stage = {}
-    reps_prof = 5
+    reps_prof = 3
     for _ in range(reps_prof):
         flush.fill_(1.0)
         calc.engine.prof = []
@@ -251,79 +388,80 @@ def run_single(args):
     achieved = alg / (dom_ms * 1e-3) / 1e9
     fwd_ach = conv_fwd_algorithmic_bytes(inner, n, E) / (stage[key_f] / n_inner * 1e-3) / 1e9
     stage_sorted = dict(sorted(((k, round(v, 4)) for k, v in stage.items()), key=lambda kv: -kv[1]))
-
-    if cfg3 or os.environ.get('SEVENN_BENCH_NO_CPU'):      # tuning runs (tools/gpu_ab.sh) skip the CPU oracle leg
-        cpu_v = None
-    else:
-        cpu_v, cpu_t, cores, cn, ce = cpu_oracle_sample((3, 3, 3), 1, 0)
     tab = calc.engine.radial == 'table'
-    S_sh = (inner.lmax_sh + 1) ** 2
+    kname = f'conv_bwd_{"tab_" if tab else ""}{inner.signature()}'
+    cap = ncu_capture(kname, E)
     # bytes the launch really has to move through HBM: the tabulated kernels neither read w nor write dW
     # ("say which tensors were elided"); `achieved` keeps SURVEY 8d's figure so rounds stay comparable
     touched = alg - (E * 8 * inner.wn if tab else 0)
-    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this kernel on this workload (ncu --set full):
-    # table mode profiles/r01h_conv_tab_fwd_bwd_raw.csv (142 MB + 363 MB), mlp mode r01c_conv_fwd_bwd_raw.csv
-    # (937 MB + 1,141 MB); below the algorithmic bytes because the gathered source rows are served by L2
-    traffic = None
-    if (n, inner.signature()) == (4096, 'c377d4386a8'):
-        traffic = 505.2e6 if tab else 2078e6
-    path_bytes_per_atom = 5.39e6          # forward + reverse, 5 layers, ~50 neighbours/atom
+    # SURVEY 8d whole-path algorithmic bytes per atom (forward + reverse, 5 layers): 3.16 MB at 28 neighbours (Si),
+    # 5.39 MB at ~50 (HfO2), l3i5 5.06 MB at 26
+    path_bytes_per_atom = {'si1m': 3.16e6, 'cfg1': 3.16e6, 'cfg2': 5.39e6, 'cfg3': 5.06e6}[wl]
+
+    cpu = gpu_torch = None
+    if not os.environ.get('SEVENN_BENCH_NO_CPU'):      # tuning runs skip the CPU legs
+        del g
+        torch.cuda.empty_cache()
+        cpu = cpu_oracle_leg(wl, 5, 3)
+        try:
+            gpu_torch = cpu_oracle_leg(wl, 5, 3, device='cuda')
+            gpu_torch['kind'] = 'oracle port on cuda:0 (ATen library kernels, autograd): informational'
+            gpu_torch.pop('cores')
+        except Exception as e:  # noqa: BLE001
+            gpu_torch = {'unavailable': f'{type(e).__name__}: {e}'[:200]}
     line = {
         'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': 1, 'steps': args.steps, 'warmup': args.warmup,
-        'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
-        'data': 'synthetic',
-        'config': {'workload': (f'SevenNet-l3i5 (lmax3, 5 layers, 128x0e+64x1e+32x2e+32x3e, rc=5A, random-init weights) '
-                                f'E+F+S, {n}-atom disordered Li-P-S cell (3:1:4, 0.048 atoms/A^3, hard core 1.95 A), '
-                                f'{E / n:.1f} neighbours/atom' if cfg3 else
-                                f'SevenNet-0 (lmax2, 5 layers, 128x0e+64x1e+32x2e, rc=5A, random-init weights) E+F+S, '
-                                f'{n}-atom bulk HfO2 (fluorite 7x7x7, a={A_LAT}A, 20 vacancies), {E / n:.1f} neighbours/atom'),
+        'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak' if wl == 'cfg2' else 'strong',
+        'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': WORKLOAD_TEXT[wl].format(n=n, c=args.si_cells, nb=E / n),
                    'n_atoms': n, 'n_edges': E, 'step': 'device neighbour list + forward + analytic reverse pass',
-                   'radial': calc.engine.radial,
+                   'radial': calc.engine.radial, 'parallelism': 'single GPU, whole periodic cell',
+                   'energy_per_atom_eV': res['energy'] / n,
                    'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)'},
         'e2e': {'value': n / e2e_t, 'unit': UNIT, 'ms_per_step': e2e_t * 1e3,
                 'h2d_bytes_per_step': int(pos.nbytes + n * 4), 'd2h_bytes_per_step': int((1 + 6 + 3 * n + n) * 8)},
         'gpu_launches': int(launches),
         'clocks': sampler.summary(),
         'roofline': {'bound': 'hbm',
-                     'kernel': f'conv_bwd_{"tab_" if tab else ""}{inner.signature()} (inner layers, one launch per layer)',
+                     'kernel': f'{kname} (inner layers, one launch per layer)',
                      'achieved': achieved, 'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': achieved / peak,
-                     'algorithmic_bytes': alg, 'ms': dom_ms, 'traffic': traffic,
+                     'algorithmic_bytes': alg, 'ms': dom_ms,
+                     'traffic': cap['dram_bytes'] if cap else None,
+                     'traffic_source': cap.get('source') if cap else None,
                      'elided': ('w and dW [E, wn] (radial weights interpolated from an L2-resident table inside the '
                                 'kernel)' if tab else None),
                      'touched_bytes': touched, 'touched_frac': touched / (dom_ms * 1e-3) / 1e9 / peak,
-                     'limiter': ('ncu r01h: issue slots 76 %, fma pipe 52 %, L1 data pipe 51 %, DRAM 13 % -> '
-                                 'instruction bound, not HBM bound' if tab else
-                                 'ncu r01c: DRAM 42 %, issue slots 63 %'),
+                     'limiter': cap.get('limiter') if cap else None,
                      'conv_fwd_achieved': fwd_ach, 'conv_fwd_frac': fwd_ach / peak,
-                     'path': {'bytes_per_atom': path_bytes_per_atom, 'ceiling_atom_steps_s': peak * 1e9 / path_bytes_per_atom,
+                     'path': {'bytes_per_atom': path_bytes_per_atom,
+                              'ceiling_atom_steps_s': peak * 1e9 / path_bytes_per_atom,
                               'frac': value / (peak * 1e9 / path_bytes_per_atom)}},
+        'roofline_gemm': gemm_roofline(calc.spec, stage, n, peak),
         'stage_ms': stage_sorted,
-        'cpu_baseline': None if cpu_v is None else {
-            'value': cpu_v, 'unit': UNIT, 'cores': cores, 'kind': 'port',
-            'sample': f'oracle (CPU restatement of the reference path) on a {cn}-atom HfO2 3x3x3 cell, '
-                      f'{ce / cn:.1f} neighbours/atom, 1 evaluation = {cpu_t:.1f} s'},
+        'cpu_baseline': None if cpu is None else {k: cpu[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
+        'torch_gpu_baseline': gpu_torch,
     }
-    if cfg3:
+    if wl == 'cfg3':
         line['metric'] = 'atom-steps/s (E+F+S) SevenNet-l3i5'
-        line['roofline']['path'] = None
     print(json.dumps(line), flush=True)
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours')
-    ap.add_argument('--workload', default='cfg2', help="'cfg2' (default: BASELINE config 2; weak scaling for N>1); "
-                    "'cfg3' (N=1: BASELINE config 3, SevenNet-l3i5 on 32,768 Li-P-S atoms); 'si1m' (N>1: BASELINE "
-                    "config 4, strong scaling: one 1M-atom bulk-Si cell (50^3 diamond cells) cut over the N GPUs)")
+    ap.add_argument('--workload', default='si1m', choices=['si1m', 'cfg1', 'cfg2', 'cfg3'],
+                    help="'si1m' (default, every N: BASELINE config 4, one 1M-atom bulk-Si cell, strong scaling); "
+                         "'cfg1' (64-atom Si); 'cfg2' (4,096-atom HfO2; N > 1: weak scaling over the brick grid); "
+                         "'cfg3' (N = 1: SevenNet-l3i5 on 32,768 Li-P-S atoms)")
     ap.add_argument('--si-cells', type=int, default=50)
     args = ap.parse_args()
-    args.warmup = max(args.warmup, 3) if args.impl != 'reference' else args.warmup
     if args.impl == 'reference':
         return run_reference(args)
-    if args.gpus > 1 or int(os.environ.get('WORLD_SIZE', '1')) > 1 or args.workload == 'si1m':
+    args.warmup = max(args.warmup, 3)
+    if args.gpus > 1 or int(os.environ.get('WORLD_SIZE', '1')) > 1:
         from sevennet_exp_b200 import bench_multi
         return bench_multi.run(args)
     run_single(args)

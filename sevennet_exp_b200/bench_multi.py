@@ -26,14 +26,11 @@ def run(args):
         os.environ.setdefault('MASTER_PORT', '29555')
         dist.init_process_group('nccl', rank=rank, world_size=world, device_id=dev)
     grid = brick_grid(world)
-    strong = getattr(args, 'workload', 'cfg2') == 'si1m'
+    strong = getattr(args, 'workload', 'si1m') == 'si1m'
     if strong:
         # BASELINE config 4: one bulk-Si cell (50^3 conventional cells = 1,000,000 atoms, rattle 0.05 A, seed 2),
         # strong scaling: the same cell is cut into `world` bricks
-        from tests.structures import diamond_si
-        nc = int(args.si_cells)
-        numbers, pos, cell = diamond_si((nc, nc, nc))
-        pos = pos + np.random.default_rng(2).normal(0.0, 0.05, pos.shape)
+        _, numbers, pos, cell = B.make_workload('si1m', args.si_cells)
     else:
         numbers0, pos0, cell0 = B.workload()
         reps = np.array(grid)
@@ -46,7 +43,15 @@ def run(args):
     cfg = B.model_config()
     calc = SevenNetCalculator((cfg, B.random_state_dict(cfg)), file_type='model_instance', device=dev,
                               keep_weights=not strong)
+    # decomposed == single-domain evaluation of the whole cell on one GPU (the gate of the reference's
+    # tests/lammps_tests/test_lammps.py:278-316), always on, outside the timed region: every rank evaluates the whole
+    # periodic cell by itself first (it fits one B200), keeps E, the forces of the atoms it will own and the stress
+    ref = calc.compute(numbers, pos, cell, [True] * 3)
+    ref_E, ref_S = ref['energy'], ref['inferred_stress']
     dec = Decomposition(numbers, pos, cell, calc.cutoff, grid, rank)
+    ref_F = ref['forces'][dec.local_ids]
+    del ref
+    torch.cuda.empty_cache()
     halo = Halo(dec, calc.engine.lib, dev)
     types_dev = torch.from_numpy(calc._lut[dec.numbers].astype(np.int32)).to(dev)
     pos_dev = torch.from_numpy(dec.pos).to(dev)
@@ -57,14 +62,14 @@ def run(args):
 
     for _ in range(max(args.warmup, 3)):
         E, F, vir, g = step()
-    if os.environ.get('SEVENN_CHECK') and not strong:
-        # decomposed == single-domain evaluation of the whole cell on one GPU (test_lammps.py:278-316 gate)
-        ref = calc.compute(numbers, pos, cell, [True] * 3)
-        dE = abs(E.item() - ref['energy']) / n_total
-        dF = np.abs(F.cpu().numpy() - ref['forces'][dec.local_ids]).max()
-        dS = np.abs(-(vir.cpu().numpy() / dec.volume) - ref['inferred_stress']).max() * 1602.1766208
-        print(f'[check rank {rank}] |dE|/atom={dE:.2e} max|dF|={dF:.2e} max|dS|={dS:.2e} kbar', flush=True)
-        assert dE < 1e-5 and dF < 1e-4 and dS < 1e-3
+    chk = torch.tensor([abs(E.item() - ref_E) / n_total, float(np.abs(F.cpu().numpy() - ref_F).max()),
+                        float(np.abs(-(vir.cpu().numpy() / dec.volume) - ref_S).max() * 1602.1766208)],
+                       dtype=torch.float64, device=dev)
+    dist.all_reduce(chk, op=dist.ReduceOp.MAX)
+    check = {'dE_eV_per_atom': chk[0].item(), 'dF_eV_per_A': chk[1].item(), 'dS_kbar': chk[2].item(),
+             'against': 'single-GPU evaluation of the whole periodic cell, max over ranks',
+             'ok': bool(chk[0].item() < 1e-5 and chk[1].item() < 1e-4 and chk[2].item() < 1e-3)}
+    del ref_F
     sampler = B.ClockSampler(local) if rank == 0 else None
     if sampler:
         sampler.start()
@@ -140,12 +145,12 @@ def run(args):
             'metric': B.METRIC, 'value': n_total / (ms_step * 1e-3), 'unit': B.UNIT, 'n_gpus': world,
             'steps': args.steps, 'warmup': max(args.warmup, 3), 'ms_per_step': ms_step, 'higher_is_better': True,
             'scaling': 'strong' if strong else 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': {'workload': (f'SevenNet-0 E+F+S, bulk Si {args.si_cells}^3 diamond cells ({n_total} atoms) cut into '
-                                    f'{grid[0]}x{grid[1]}x{grid[2]} bricks, ghost feature exchange per layer'
+            'config': {'workload': (B.WORKLOAD_TEXT['si1m'].format(n=n_total, c=args.si_cells, nb=stats[2].item() / n_total)
+                                    + f', cut into {grid[0]}x{grid[1]}x{grid[2]} bricks, ghost feature exchange per layer'
                                     if strong else
                                     f'SevenNet-0 E+F+S, bulk HfO2 cfg2 cell replicated {grid[0]}x{grid[1]}x{grid[2]} '
                                     f'({n_total} atoms), brick domain decomposition, ghost feature exchange per layer'),
-                       'n_atoms': n_total, 'atoms_per_gpu': n_total // world, 'energy_per_atom_eV': float(E.item()) / n_total,
+                       'n_atoms': n_total, 'atoms_per_gpu': n_total // world, 'parallelism': f'dd{world} (spatial bricks {grid[0]}x{grid[1]}x{grid[2]})', 'energy_per_atom_eV': float(E.item()) / n_total,
                        'ghosts_per_gpu_max': int(smax[1].item()), 'edges_total': int(stats[2].item()),
                        'halo_row_bytes': x_dim * 4,
                        'halo': ('peer memory: pack + NVLink write into the neighbour\'s slot in one kernel, device-side '
@@ -156,7 +161,7 @@ def run(args):
                     'h2d_bytes_per_step': int(pos_host.numel() * 8),
                     'd2h_bytes_per_step': int((7 + 3 * dec.n_local) * 8)},
             'gpu_launches': int(launches), 'clocks': sampler.summary() if sampler else None,
-            'roofline': roofline, 'stage_ms_rank0': stage_sorted, 'cpu_baseline': None,
+            'check': check, 'roofline': roofline, 'stage_ms_rank0': stage_sorted, 'cpu_baseline': None,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()
