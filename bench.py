@@ -327,7 +327,14 @@ def run_single(args):
     pos_dev = torch.from_numpy(pos).to(dev)
     flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
 
+    native = calc.native           # C++ whole-model host (csrc/model.cu): the product path of SevenNetCalculator
+
+    def n_launches():
+        return native.n_launch if native is not None else calc.engine.n_launch + calc.nl.n_launch
+
     def step():
+        if native is not None:
+            return None, native.evaluate_graphed(types_dev, pos_dev, cell, pbc)
         g = calc.nl.graph(types_dev, None, cell, pbc, calc.cutoff, pos_dev=pos_dev)
         return g, calc.engine.evaluate(g)
 
@@ -337,7 +344,7 @@ def run_single(args):
     torch.cuda.synchronize()
     sampler = ClockSampler()
     sampler.start()
-    l0 = calc.engine.n_launch + calc.nl.n_launch
+    l0 = n_launches()
     evs = []
     torch.cuda.synchronize()
     for _ in range(args.steps):
@@ -347,12 +354,15 @@ def run_single(args):
         g, out = step()
         b.record()
         evs.append((a, b))
-        del out
     torch.cuda.synchronize()
     total_ms = sum(a.elapsed_time(b) for a, b in evs)
-    launches = calc.engine.n_launch + calc.nl.n_launch - l0
+    launches = n_launches() - l0
     ms_step = total_ms / args.steps
     value = n / (ms_step * 1e-3)
+    if native is not None:          # the status word of the last step: the edge capacity held
+        _, _, overflow, found = native.parse_header(out['header'].cpu().numpy())
+        assert not overflow, 'edge capacity overflow during the timed steps'
+    del out
 
     # end to end through the public calculator call: host arrays in, host E/F/S out
     for _ in range(2):
@@ -367,9 +377,14 @@ def run_single(args):
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
-    # per-stage device times (separate pass, CUDA events on the launch stream)
+    # per-stage device times (separate pass through the per-launch Python driver: the same kernels in the same order,
+    # CUDA events between stages on the launch stream)
     stage = {}
     reps_prof = 3
+    if native is not None:
+        native._ws = None
+        torch.cuda.empty_cache()
+    g = calc.nl.graph(types_dev, None, cell, pbc, calc.cutoff, pos_dev=pos_dev)
     for _ in range(reps_prof):
         flush.fill_(1.0)
         calc.engine.prof = []
@@ -415,6 +430,7 @@ def run_single(args):
         'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': {'workload': WORKLOAD_TEXT[wl].format(n=n, c=args.si_cells, nb=E / n),
                    'n_atoms': n, 'n_edges': E, 'step': 'device neighbour list + forward + analytic reverse pass',
+                   'host': 'C++ (sevenn_model_evaluate_positions: no host sync, the repeated step replayed from a CUDA graph)' if native is not None else 'python per-launch driver',
                    'radial': calc.engine.radial, 'parallelism': 'single GPU, whole periodic cell',
                    'energy_per_atom_eV': res['energy'] / n,
                    'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)'},

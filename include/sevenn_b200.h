@@ -140,6 +140,70 @@ int sevenn_scatter_add_rows(const float* src, int D, const int* idx, long long n
 int sevenn_push_rows_peers(const float* src, int D, const int* idx, long long first_row, long long n, int n_peers,
                            float* const* peer_base, const long long* dst_row, const long long* seg_off, void* stream);
 
+/* device-side edge count variants (n_edges_dev, e.g. &rowptr[n_rows]; launches and buffers bounded by max_edges): for
+ * hosts that never wait for the neighbour-list size (csrc/model.cu).  Same kernels as the entries above. */
+int sevenn_edge_fwd_tab_dev(const float* edge_vec, long long max_edges, const int* n_edges_dev, int lmax, int normalize,
+                            float inv_h, int n_int, float* Yt, void* stream);
+int sevenn_edge_bwd_tab_dev(const float* edge_vec, long long max_edges, const int* n_edges_dev, int lmax, int normalize,
+                            float inv_h, const float* dY, int n_slabs, long long slab_stride, float* f_edge, void* stream);
+int sevenn_csc_build_dev(const int* col, long long max_edges, const int* n_edges_dev, int n_nodes, int* cnt, int* fill,
+                         int* cptr, unsigned long long* keys, int* cedge, int* scan_tmp, void* stream);
+/* sevenn_nl_fill with the edge arrays bounded by max_edges: rowptr is clamped first, *status |= 1 on overflow; rows
+ * for atoms [0, n_rows) only (owned atoms of a sub-domain) */
+int sevenn_nl_fill_capped(const double* pos_wrapped, const int* wrap, const int* atom_bin, const int* bin_start,
+                          const int* bin_atoms, int n_rows, const double* dpar, const int* ipar, int* rowptr,
+                          long long max_edges, int* status, unsigned long long* keys, const double* pos, int* center,
+                          int* col, int* shift, float* edge_vec, void* stream);
+
+/* ---- whole model behind one call (csrc/model.cu): replaces what the reference runs per MD step in
+ * sevenn/sevennet_calculator.py:163-202 (graph build + AtomGraphSequential.forward + autograd forces / stress) and
+ * sevenn/pair_e3gnn/pair_e3gnn.cpp:71-274 / pair_e3gnn_parallel.cpp:191-525 (edge loop, torch::jit forward per segment,
+ * ghost communication, result unpacking).  No allocation per call (caller-owned workspace), no host synchronisation
+ * (the edge count stays on the device), launches only: capturable in a CUDA graph.
+ * The model is the (int32 program, fp32 data) pair written by sevennet_exp_b200/host.py::pack_engine (tabulated-radial
+ * mode); sevenn_model_create uploads the weights once. */
+#define SEVENN_ERR_WORKSPACE 10002
+typedef struct sevenn_model sevenn_model;
+typedef struct {                /* CSR by centre (edge_index[0]) + CSC by neighbour, device pointers */
+  long long n_local, n_nodes;   /* owned atoms (rows), owned + ghost atoms */
+  long long max_edges;          /* capacity of the edge arrays */
+  const int* n_edges_dev;       /* device: valid edges (== rowptr[n_local]) */
+  const int* types;             /* n_nodes */
+  const float* edge_vec;        /* max_edges x 3: pos[col] + shift.cell - pos[centre] */
+  const int *rowptr, *col, *cptr, *cedge;
+} sevenn_graph;
+typedef struct {                /* device outputs; forces == NULL skips the reverse pass */
+  double* energy;               /* 1 */
+  float* atomic_energy;         /* n_local */
+  float* forces;                /* n_nodes x 3 (ghost rows: what is owed to their owners) */
+  double* virial6;              /* 6: sum_e (rx fx, ry fy, rz fz, rx fy, ry fz, rz fx); stress = -virial / V */
+  float* virial_atoms;          /* optional n_nodes x 6 */
+  int* status;                  /* 2 ints (evaluate_positions): [0] bit 0 = edge capacity exceeded, [1] = edges found */
+} sevenn_outputs;
+typedef struct {                /* per-layer ghost exchange of a domain-decomposed host (may be NULL) */
+  void* user;
+  int (*forward)(void* user, int layer, float* h /* n_nodes x dim; fill rows >= n_local */, int dim, void* stream);
+  int (*backward)(void* user, int layer, float* dh /* add ghost rows into their owners */, int dim, void* stream);
+} sevenn_halo_hooks;
+int sevenn_model_create(const int* prog /* host */, long long n_prog, const float* data /* host */, long long n_data,
+                        sevenn_model** out);
+int sevenn_model_destroy(sevenn_model* model);
+int sevenn_model_set_tc_min_rows(sevenn_model* model, int rows);
+long long sevenn_model_launches(const sevenn_model* model);      /* library calls made so far (launch groups) */
+long long sevenn_model_tc_launches(const sevenn_model* model);   /* ... of which on the tcgen05 GEMM arm */
+long long sevenn_model_workspace_bytes(sevenn_model* model, long long n_local, long long n_nodes, long long max_edges,
+                                       int with_neighbor_list);
+int sevenn_model_count_edges(sevenn_model* model, long long n_rows, long long n_nodes, const double* pos,
+                             const double* pos_host, const double* cell, const int* pbc, void* workspace,
+                             long long workspace_bytes, void* stream, long long* n_edges /* host */);
+int sevenn_model_evaluate_graph(sevenn_model* model, const sevenn_graph* graph, const sevenn_halo_hooks* halo,
+                                void* workspace, long long workspace_bytes, void* stream, const sevenn_outputs* out);
+/* pos: device fp64 [n_nodes, 3]; pos_host: the same on the host, needed only when a direction is not periodic */
+int sevenn_model_evaluate_positions(sevenn_model* model, long long n_local, long long n_nodes, const double* pos,
+                                    const double* pos_host, const double* cell /* host 9 */, const int* pbc /* host 3 */,
+                                    const int* types, long long max_edges, const sevenn_halo_hooks* halo,
+                                    void* workspace, long long workspace_bytes, void* stream, const sevenn_outputs* out);
+
 /* ---- fused gather + uvu CG tensor product + segment sum (generated per irreps signature <sig>):
  *   int sevenn_conv_fwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo, stream)
  *   int sevenn_conv_bwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY, dy_stride, stream)

@@ -50,6 +50,20 @@ SIGNATURES = {
     'sevenn_rescale': ([c_p, c_p, c_ll, c_p, c_p, c_i, c_p, c_p, c_p], c_i),
     'sevenn_colsum_f64': ([c_p, c_ll, c_i, c_p, c_p, c_p], c_i),
     'sevenn_colsum_f64_noalloc': ([c_p, c_ll, c_i, c_p, c_p], c_i),
+    'sevenn_edge_fwd_tab_dev': ([c_p, c_ll, c_p, c_i, c_i, c_f, c_i, c_p, c_p], c_i),
+    'sevenn_edge_bwd_tab_dev': ([c_p, c_ll, c_p, c_i, c_i, c_f, c_p, c_i, c_ll, c_p, c_p], c_i),
+    'sevenn_csc_build_dev': ([c_p, c_ll, c_p, c_i, c_p, c_p, c_p, c_p, c_p, c_p, c_p], c_i),
+    'sevenn_nl_fill_capped': ([c_p, c_p, c_p, c_p, c_p, c_i, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_p, c_p, c_p, c_p,
+                               c_p], c_i),
+    'sevenn_model_create': ([c_p, c_ll, c_p, c_ll, c_p], c_i),
+    'sevenn_model_destroy': ([c_p], c_i),
+    'sevenn_model_set_tc_min_rows': ([c_p, c_i], c_i),
+    'sevenn_model_launches': ([c_p], c_ll),
+    'sevenn_model_tc_launches': ([c_p], c_ll),
+    'sevenn_model_workspace_bytes': ([c_p, c_ll, c_ll, c_ll, c_i], c_ll),
+    'sevenn_model_count_edges': ([c_p, c_ll, c_ll, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p], c_i),
+    'sevenn_model_evaluate_graph': ([c_p, c_p, c_p, c_p, c_ll, c_p, c_p], c_i),
+    'sevenn_model_evaluate_positions': ([c_p, c_ll, c_ll, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_p, c_p], c_i),
     'sevenn_force_virial': ([c_p, c_p, c_p, c_i, c_p, c_p, c_ll, c_p, c_p, c_p], c_i),
     'sevenn_segment_gather_sum': ([c_p, c_i, c_p, c_p, c_ll, c_p, c_i, c_p], c_i),
     'sevenn_gather_rows': ([c_p, c_i, c_p, c_ll, c_p, c_p], c_i),

@@ -14,10 +14,8 @@ CSRC = os.path.join(HERE, 'csrc')
 GEN = os.path.join(CSRC, 'generated')
 LIBDIR = os.path.join(HERE, '_lib')
 LIB = os.path.join(LIBDIR, 'libsevenn_b200.so')
-NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
-              '-Xcompiler', '-fPIC', '--use_fast_math=false']
-NVCC_FLAGS = [f for f in NVCC_FLAGS if f != '--use_fast_math=false']
-STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu']
+NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC']
+STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu', 'model.cu']
 
 
 def nvcc():
@@ -76,9 +74,6 @@ def build(extra_specs=None, verbose=True):
     objdir = os.path.join(LIBDIR, 'obj')
     os.makedirs(objdir, exist_ok=True)
     specs = conv_specs(prebuilt_configs())
-    # keep signatures that were JIT-added earlier
-    for f in sorted(os.listdir(GEN)) if os.path.isdir(GEN) else []:
-        pass
     if extra_specs:
         specs.update(extra_specs)
     srcs = [os.path.join(CSRC, u) for u in STATIC_UNITS] + write_generated(specs)
@@ -91,7 +86,7 @@ def build(extra_specs=None, verbose=True):
     with ThreadPoolExecutor(max_workers=os.cpu_count() or 4) as ex:
         list(ex.map(lambda a: _compile(*a), zip(srcs, objs)))
     tmp = LIB + '.tmp'
-    subprocess.check_call([nvcc(), '-shared', '-o', tmp] + objs + ['-lcudart'])
+    subprocess.check_call([nvcc(), '-gencode', 'arch=compute_100a,code=sm_100a', '-shared', '-o', tmp] + objs + ['-lcudart', '-ldl'])
     os.replace(tmp, LIB)
     if verbose:
         print(f'built {LIB} ({len(srcs)} units, {len(specs)} conv signatures)')

@@ -137,9 +137,10 @@ GKERNEL(edge_bwd_kernel)(const float* __restrict__ vec, long long n, EdgeParams 
 
 // Tabulated-radial variant (codegen/conv_codegen.py "Tabulated radial weights"): per edge
 // Yt[e] = (Y_0 .. Y_{S-1}, t, bits(i)) with r = (i + t) h the position of the edge length in the table.
-GKERNEL(edge_fwd_tab_kernel)(const float* __restrict__ vec, long long n, int lmax, int normalize, float inv_h,
-                             int n_int, float* __restrict__ Yt) {
+GKERNEL(edge_fwd_tab_kernel)(const float* __restrict__ vec, long long n, const int* __restrict__ n_dev, int lmax,
+                             int normalize, float inv_h, int n_int, float* __restrict__ Yt) {
   const int S = (lmax + 1) * (lmax + 1);
+  if (n_dev != nullptr && *n_dev < n) n = *n_dev;       // edge count known on the device only (sync-free host)
   GRID_STRIDE_LOOP(e, n) {
     const float x = vec[3 * e], y = vec[3 * e + 1], z = vec[3 * e + 2];
     const float r = sqrtf(x * x + y * y + z * z);
@@ -158,10 +159,11 @@ GKERNEL(edge_fwd_tab_kernel)(const float* __restrict__ vec, long long n, int lma
 }
 
 // dY rows carry S + 1 values: d/dY and the radial term sum_c dE/dw_c * h dw_c/dr (one slab per convolution unit).
-GKERNEL(edge_bwd_tab_kernel)(const float* __restrict__ vec, long long n, int lmax, int normalize, float inv_h,
-                             const float* __restrict__ dY, int n_slabs, long long slab_stride,
-                             float* __restrict__ fvec) {
+GKERNEL(edge_bwd_tab_kernel)(const float* __restrict__ vec, long long n, const int* __restrict__ n_dev, int lmax,
+                             int normalize, float inv_h, const float* __restrict__ dY, int n_slabs,
+                             long long slab_stride, float* __restrict__ fvec) {
   const int S = (lmax + 1) * (lmax + 1), S1 = S + 1;
+  if (n_dev != nullptr && *n_dev < n) n = *n_dev;
   GRID_STRIDE_LOOP(e, n) {
     const float x = vec[3 * e], y = vec[3 * e + 1], z = vec[3 * e + 2];
     const float r = sqrtf(x * x + y * y + z * z), ir = 1.f / r;
@@ -214,7 +216,7 @@ extern "C" int sevenn_edge_fwd_tab(const float* vec, long long n_edges, int lmax
                                    int n_int, float* Yt, void* stream) {
   if (n_edges <= 0) return 0;
   if (lmax < 0 || lmax > 3 || n_int < 1 || !(inv_h > 0.f)) return SEVENN_ERR_BAD_ARG;
-  LAUNCH1D(edge_fwd_tab_kernel, n_edges, stream)(vec, n_edges, lmax, normalize, inv_h, n_int, Yt);
+  LAUNCH1D(edge_fwd_tab_kernel, n_edges, stream)(vec, n_edges, nullptr, lmax, normalize, inv_h, n_int, Yt);
   return LAUNCH_STATUS();
 }
 
@@ -222,6 +224,25 @@ extern "C" int sevenn_edge_bwd_tab(const float* vec, long long n_edges, int lmax
                                    const float* dY, int n_slabs, long long slab_stride, float* fvec, void* stream) {
   if (n_edges <= 0) return 0;
   if (lmax < 0 || lmax > 3 || n_slabs < 1) return SEVENN_ERR_BAD_ARG;
-  LAUNCH1D(edge_bwd_tab_kernel, n_edges, stream)(vec, n_edges, lmax, normalize, inv_h, dY, n_slabs, slab_stride, fvec);
+  LAUNCH1D(edge_bwd_tab_kernel, n_edges, stream)(vec, n_edges, nullptr, lmax, normalize, inv_h, dY, n_slabs, slab_stride, fvec);
+  return LAUNCH_STATUS();
+}
+
+// Same kernels with the edge count read on the device (n_edges_dev, e.g. &rowptr[n_rows]); `max_edges` bounds the launch
+// and the buffers.  For hosts that never wait for the neighbour-list size (csrc/model.cu).
+extern "C" int sevenn_edge_fwd_tab_dev(const float* vec, long long max_edges, const int* n_edges_dev, int lmax,
+                                       int normalize, float inv_h, int n_int, float* Yt, void* stream) {
+  if (max_edges <= 0) return 0;
+  if (lmax < 0 || lmax > 3 || n_int < 1 || !(inv_h > 0.f) || n_edges_dev == nullptr) return SEVENN_ERR_BAD_ARG;
+  LAUNCH1D(edge_fwd_tab_kernel, max_edges, stream)(vec, max_edges, n_edges_dev, lmax, normalize, inv_h, n_int, Yt);
+  return LAUNCH_STATUS();
+}
+extern "C" int sevenn_edge_bwd_tab_dev(const float* vec, long long max_edges, const int* n_edges_dev, int lmax,
+                                       int normalize, float inv_h, const float* dY, int n_slabs, long long slab_stride,
+                                       float* fvec, void* stream) {
+  if (max_edges <= 0) return 0;
+  if (lmax < 0 || lmax > 3 || n_slabs < 1 || n_edges_dev == nullptr) return SEVENN_ERR_BAD_ARG;
+  LAUNCH1D(edge_bwd_tab_kernel, max_edges, stream)(vec, max_edges, n_edges_dev, lmax, normalize, inv_h, dY, n_slabs,
+                                                  slab_stride, fvec);
   return LAUNCH_STATUS();
 }

@@ -12,8 +12,6 @@
 #include "../../include/sevenn_b200.h"
 
 #ifndef SEVENN_EMU
-#define BM 64
-#define BN 64
 #define BK 16
 
 __device__ __forceinline__ float g_act(int id, float x) {
@@ -37,59 +35,84 @@ __device__ __forceinline__ float g_dact(int id, float x) {
   }
 }
 
+// 256 threads as a 16 x 16 grid, TM x TN outputs per thread: tile (16 TM) x (16 TN).  The next k-slab is fetched into
+// registers while the current one is multiplied (one barrier pair per slab, global latency hidden).  Small problems
+// take the small tiles: a 64 x 64 tile with K = 224 keeps ONE SM busy for ~4 us while 140 others idle, which is what a
+// 64-atom system's node linears consisted of.
+template <int TM, int TN>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(sevenn_gemm_args g) {
-  __shared__ float As[BK][BM + 4];
-  __shared__ float Bs[BK][BN + 4];
+  constexpr int TBM = 16 * TM, TBN = 16 * TN;
+  constexpr int NA = (TBM * BK + 255) / 256, NB = (TBN * BK + 255) / 256;
+  __shared__ float As[BK][TBM + 4];
+  __shared__ float Bs[BK][TBN + 4];
   const int tid = threadIdx.x;
   const int ty = tid / 16, tx = tid % 16;
-  const long long row0 = (long long)blockIdx.x * BM;
-  const int col0 = blockIdx.y * BN;
-  float acc[4][4];
+  const long long row0 = (long long)blockIdx.x * TBM;
+  const int col0 = blockIdx.y * TBN;
+  float acc[TM][TN];
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < TM; ++a)
 #pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    for (int b = 0; b < TN; ++b) acc[a][b] = 0.f;
 
-  // A loader: thread -> (row = tid/4, k4 = (tid%4)*4)
-  const int arow = tid / 4, ak = (tid % 4) * 4;
-  const long long ar = row0 + arow;
-  const float* aptr = nullptr;
-  if (ar < g.M) aptr = g.A + (ar / g.R) * g.sAn + (ar % g.R) * (long long)g.sAm;
-  // B loader: thread -> (k = tid/16, c4 = (tid%16)*4)
-  const int bk = tid / 16, bc = (tid % 16) * 4;
-
+  // A loader: element q of this thread -> (row = idx / BK, k = idx % BK), idx = tid + 256 q (coalesced along K)
+  const float* aptr[NA];
+#pragma unroll
+  for (int q = 0; q < NA; ++q) {
+    const int idx = tid + 256 * q;
+    const long long ar = row0 + idx / BK;
+    aptr[q] = (idx < TBM * BK && ar < g.M) ? g.A + (ar / g.R) * g.sAn + (ar % g.R) * (long long)g.sAm + idx % BK : nullptr;
+  }
+  float ra[NA], rb[NB];
+  auto fetch = [&](int k0) {
+#pragma unroll
+    for (int q = 0; q < NA; ++q) {
+      const int k = k0 + (tid + 256 * q) % BK;
+      ra[q] = (aptr[q] != nullptr && k < g.K) ? __ldg(aptr[q] + k0) : 0.f;
+    }
+#pragma unroll
+    for (int q = 0; q < NB; ++q) {
+      const int idx = tid + 256 * q;
+      const int k = k0 + idx / TBN, c = col0 + idx % TBN;
+      rb[q] = (idx < TBN * BK && k < g.K && c < g.N) ? __ldg(g.B + (size_t)k * g.ldb + c) : 0.f;
+    }
+  };
+  fetch(0);
   for (int k0 = 0; k0 < g.K; k0 += BK) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int k = k0 + ak + q;
-      As[ak + q][arow] = (aptr && k < g.K) ? __ldg(aptr + k) : 0.f;
+    for (int q = 0; q < NA; ++q) {
+      const int idx = tid + 256 * q;
+      if (idx < TBM * BK) As[idx % BK][idx / BK] = ra[q];
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int k = k0 + bk, c = col0 + bc + q;
-      Bs[bk][bc + q] = (k < g.K && c < g.N) ? __ldg(g.B + (size_t)k * g.ldb + c) : 0.f;
+    for (int q = 0; q < NB; ++q) {
+      const int idx = tid + 256 * q;
+      if (idx < TBN * BK) Bs[idx / TBN][idx % TBN] = rb[q];
     }
     __syncthreads();
+    if (k0 + BK < g.K) fetch(k0 + BK);
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
-      float a[4], b[4];
+      float a[TM], b[TN];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) { a[q] = As[k][ty * 4 + q]; b[q] = Bs[k][tx * 4 + q]; }
+      for (int q = 0; q < TM; ++q) a[q] = As[k][ty * TM + q];
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int q = 0; q < TN; ++q) b[q] = Bs[k][tx * TN + q];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      for (int i = 0; i < TM; ++i)
+#pragma unroll
+        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const long long r = row0 + ty * 4 + i;
+  for (int i = 0; i < TM; ++i) {
+    const long long r = row0 + ty * TM + i;
     if (r >= g.M) continue;
     const long long off = (r / g.R) * g.sCn + (r % g.R) * (long long)g.sCm;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int c = col0 + tx * 4 + j;
+    for (int j = 0; j < TN; ++j) {
+      const int c = col0 + tx * TN + j;
       if (c >= g.N) continue;
       const float v = acc[i][j];
       switch (g.epi) {
@@ -102,13 +125,23 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(sevenn_gemm_args g) {
   }
 }
 
+template <int TM, int TN>
+static int gemm_simt_launch(const sevenn_gemm_args& g, cudaStream_t st) {
+  dim3 grid((unsigned)((g.M + 16 * TM - 1) / (16 * TM)), (unsigned)((g.N + 16 * TN - 1) / (16 * TN)));
+  gemm_simt_kernel<TM, TN><<<grid, 256, 0, st>>>(g);
+  return (int)cudaGetLastError();
+}
+
 extern "C" int sevenn_gemm_f32(const sevenn_gemm_args* args, void* stream) {
   const sevenn_gemm_args g = *args;
   if (g.M <= 0 || g.N <= 0) return 0;
   if (g.K <= 0 || g.R <= 0 || g.epi < 0 || g.epi > 3) return SEVENN_ERR_BAD_ARG;
-  dim3 grid((unsigned)((g.M + BM - 1) / BM), (unsigned)((g.N + BN - 1) / BN));
-  gemm_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g);
-  return (int)cudaGetLastError();
+  cudaStream_t st = (cudaStream_t)stream;
+  // the largest tile that still gives every SM work (results do not depend on the tile: each output is one k-ordered sum)
+  const long long t64 = ((g.M + 63) / 64) * ((g.N + 63) / 64), t32 = ((g.M + 31) / 32) * ((g.N + 31) / 32);
+  if (t64 >= 148) return gemm_simt_launch<4, 4>(g, st);
+  if (t32 >= 148) return gemm_simt_launch<2, 2>(g, st);
+  return gemm_simt_launch<1, 2>(g, st);
 }
 #endif
 

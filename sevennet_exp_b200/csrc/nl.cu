@@ -64,7 +64,7 @@ template <bool FILL>
 GKERNEL(nl_walk_kernel)(const double* __restrict__ pw, const int* __restrict__ wrap,
                         const int* __restrict__ atom_bin, const int* __restrict__ bin_start,
                         const int* __restrict__ bin_atoms, int n, NlParams P, int* __restrict__ count,
-                        const int* __restrict__ rowptr, unsigned long long* __restrict__ keys) {
+                        const int* __restrict__ rowptr, unsigned long long* __restrict__ keys, long long cap) {
   GRID_STRIDE_LOOP(i, n) {
     const double xi = pw[3 * i], yi = pw[3 * i + 1], zi = pw[3 * i + 2];
     const int bin = atom_bin[i];
@@ -91,7 +91,7 @@ GKERNEL(nl_walk_kernel)(const double* __restrict__ pw, const int* __restrict__ w
             const double dx = pw[3 * j] + ox, dy = pw[3 * j + 1] + oy, dz = pw[3 * j + 2] + oz;
             const double d2v = dx * dx + dy * dy + dz * dz;
             if (d2v < P.rc2 && !(j == (int)i && s0 == 0 && s1 == 0 && s2 == 0)) {
-              if (FILL) {
+              if (FILL && base + cnt < cap) {
                 const int S0 = s0 - wrap[3 * j] + wi0, S1 = s1 - wrap[3 * j + 1] + wi1,
                           S2 = s2 - wrap[3 * j + 2] + wi2;
                 keys[base + cnt] = ((unsigned long long)j << 24) | ((unsigned long long)(S0 + 128) << 16) |
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(128) nl_walk_warp_kernel(const double* __restr
                                                            const int* __restrict__ bin_start,
                                                            const int* __restrict__ bin_atoms, int n, NlParams P,
                                                            int* __restrict__ count, const int* __restrict__ rowptr,
-                                                           unsigned long long* __restrict__ keys) {
+                                                           unsigned long long* __restrict__ keys, long long cap) {
   const int lane = threadIdx.x & 31;
   for (long long i = blockIdx.x * 4ll + (threadIdx.x >> 5); i < n; i += gridDim.x * 4ll) {
     const double xi = pw[3 * i], yi = pw[3 * i + 1], zi = pw[3 * i + 2];
@@ -151,7 +151,7 @@ __global__ void __launch_bounds__(128) nl_walk_warp_kernel(const double* __restr
               ok = (dx * dx + dy * dy + dz * dz) < P.rc2 && !(home && j == (int)i);
             }
             const unsigned mask = __ballot_sync(0xffffffffu, ok);
-            if (FILL && ok) {
+            if (FILL && ok && base + cnt + __popc(mask & ((1u << lane) - 1u)) < cap) {   // cap: edge-array capacity
               const int S0 = s0 - wrap[3 * j] + wi0, S1 = s1 - wrap[3 * j + 1] + wi1, S2 = s2 - wrap[3 * j + 2] + wi2;
               keys[base + cnt + __popc(mask & ((1u << lane) - 1u))] =
                   ((unsigned long long)j << 24) | ((unsigned long long)(S0 + 128) << 16) |
@@ -253,18 +253,31 @@ GKERNEL(nl_decode_kernel)(const unsigned long long* __restrict__ keys, const int
 }
 
 // ---- CSC (edges grouped by neighbour j), segments sorted by edge id -> deterministic sums
-GKERNEL(hist_kernel)(const int* __restrict__ idx, long long n, int* cnt) {
+GKERNEL(hist_kernel)(const int* __restrict__ idx, long long n, const int* __restrict__ n_dev, int* cnt) {
+  if (n_dev != nullptr && *n_dev < n) n = *n_dev;
   GRID_STRIDE_LOOP(e, n) { ATOMIC_ADD_I32(cnt + idx[e], 1); }
 }
-GKERNEL(csc_scatter_kernel)(const int* __restrict__ col, long long n, const int* __restrict__ cptr, int* fill,
-                            unsigned long long* __restrict__ keys) {
+GKERNEL(csc_scatter_kernel)(const int* __restrict__ col, long long n, const int* __restrict__ n_dev,
+                            const int* __restrict__ cptr, int* fill, unsigned long long* __restrict__ keys) {
+  if (n_dev != nullptr && *n_dev < n) n = *n_dev;
   GRID_STRIDE_LOOP(e, n) {
     const int j = col[e];
     keys[cptr[j] + ATOMIC_ADD_I32(fill + j, 1)] = (unsigned long long)e;
   }
 }
-GKERNEL(u64_to_i32_kernel)(const unsigned long long* __restrict__ k, long long n, int* __restrict__ out) {
+GKERNEL(u64_to_i32_kernel)(const unsigned long long* __restrict__ k, long long n, const int* __restrict__ n_dev,
+                           int* __restrict__ out) {
+  if (n_dev != nullptr && *n_dev < n) n = *n_dev;
   GRID_STRIDE_LOOP(e, n) { out[e] = (int)k[e]; }
+}
+// rowptr (n + 1 entries) clamped to the edge-array capacity; *status |= 1 when the list did not fit
+GKERNEL(clamp_rowptr_kernel)(int* __restrict__ rowptr, int n, int cap, int* __restrict__ status) {
+  GRID_STRIDE_LOOP(i, (long long)n + 1) {
+    if (rowptr[i] > cap) {
+      rowptr[i] = cap;
+      if (i == n) *status = 1;
+    }
+  }
 }
 
 // ---- exclusive scan of int32 (out has n+1 entries, out[n] = total) ------------------------
@@ -367,30 +380,61 @@ extern "C" int sevenn_nl_count(const double* pw, const int* wrap, const int* ato
                                void* stream) {
   if (n <= 0) return 0;
   LAUNCH_WALK(false, n, stream)(pw, wrap, atom_bin, bin_start, bin_atoms, n, make_params(dpar, ipar),
-                                             count, nullptr, nullptr);
+                                             count, nullptr, nullptr, 0);
+  return LAUNCH_STATUS();
+}
+static int nl_fill_impl(const double* pw, const int* wrap, const int* atom_bin, const int* bin_start,
+                        const int* bin_atoms, int n, const double* dpar, const int* ipar, const int* rowptr,
+                        unsigned long long* keys, const double* pos, int* center, int* col, int* shift, float* vec,
+                        long long cap, void* stream) {
+  if (n <= 0) return 0;
+  NlParams P = make_params(dpar, ipar);
+  LAUNCH_WALK(true, n, stream)(pw, wrap, atom_bin, bin_start, bin_atoms, n, P, nullptr, rowptr, keys, cap);
+  LAUNCH_SEGSORT(n, stream)(keys, rowptr, n);
+  LAUNCH1D(nl_decode_kernel, (long long)n * 32, stream)(keys, rowptr, n, pos, P, center, col, shift, vec);
   return LAUNCH_STATUS();
 }
 extern "C" int sevenn_nl_fill(const double* pw, const int* wrap, const int* atom_bin, const int* bin_start,
                               const int* bin_atoms, int n, const double* dpar, const int* ipar, const int* rowptr,
                               unsigned long long* keys, const double* pos, int* center, int* col, int* shift,
                               float* vec, void* stream) {
-  if (n <= 0) return 0;
-  NlParams P = make_params(dpar, ipar);
-  LAUNCH_WALK(true, n, stream)(pw, wrap, atom_bin, bin_start, bin_atoms, n, P, nullptr, rowptr, keys);
-  LAUNCH_SEGSORT(n, stream)(keys, rowptr, n);
-  LAUNCH1D(nl_decode_kernel, (long long)n * 32, stream)(keys, rowptr, n, pos, P, center, col, shift, vec);
-  return LAUNCH_STATUS();
+  return nl_fill_impl(pw, wrap, atom_bin, bin_start, bin_atoms, n, dpar, ipar, rowptr, keys, pos, center, col, shift,
+                      vec, 0x7fffffffffffffffLL, stream);
+}
+// Capacity-bounded fill for hosts that never read the edge count: rowptr (from the scan of the counts) is first
+// clamped to max_edges (status word |= 1 on overflow: results are then memory-safe garbage and the caller re-runs
+// with a larger workspace), the rows of atoms 0 .. n_rows-1 are filled (n_rows <= atoms: rows for owned atoms only).
+extern "C" int sevenn_nl_fill_capped(const double* pw, const int* wrap, const int* atom_bin, const int* bin_start,
+                                     const int* bin_atoms, int n_rows, const double* dpar, const int* ipar,
+                                     int* rowptr, long long max_edges, int* status, unsigned long long* keys,
+                                     const double* pos, int* center, int* col, int* shift, float* vec, void* stream) {
+  if (n_rows <= 0) return 0;
+  if (max_edges <= 0 || max_edges > 0x7fffffffLL || status == nullptr) return SEVENN_ERR_BAD_ARG;
+  LAUNCH1D(clamp_rowptr_kernel, n_rows + 1, stream)(rowptr, n_rows, (int)max_edges, status);
+  return nl_fill_impl(pw, wrap, atom_bin, bin_start, bin_atoms, n_rows, dpar, ipar, rowptr, keys, pos, center, col,
+                      shift, vec, max_edges, stream);
 }
 // cnt: n_nodes+1 ints zeroed by the caller; fill: n_nodes ints zeroed by the caller
-extern "C" int sevenn_csc_build(const int* col, long long n_edges, int n_nodes, int* cnt, int* fill, int* cptr,
-                                unsigned long long* keys, int* cedge, int* scan_tmp, void* stream) {
-  if (n_edges > 0) LAUNCH1D(hist_kernel, n_edges, stream)(col, n_edges, cnt);
+static int csc_build_impl(const int* col, long long n_edges, const int* n_dev, int n_nodes, int* cnt, int* fill,
+                          int* cptr, unsigned long long* keys, int* cedge, int* scan_tmp, void* stream) {
+  if (n_edges > 0) LAUNCH1D(hist_kernel, n_edges, stream)(col, n_edges, n_dev, cnt);
   int rc = sevenn_scan_i32(cnt, cptr, n_nodes, scan_tmp, stream);
   if (rc) return rc;
   if (n_edges > 0) {
-    LAUNCH1D(csc_scatter_kernel, n_edges, stream)(col, n_edges, cptr, fill, keys);
+    LAUNCH1D(csc_scatter_kernel, n_edges, stream)(col, n_edges, n_dev, cptr, fill, keys);
     LAUNCH_SEGSORT(n_nodes, stream)(keys, cptr, n_nodes);
-    LAUNCH1D(u64_to_i32_kernel, n_edges, stream)(keys, n_edges, cedge);
+    LAUNCH1D(u64_to_i32_kernel, n_edges, stream)(keys, n_edges, n_dev, cedge);
   }
   return LAUNCH_STATUS();
+}
+extern "C" int sevenn_csc_build(const int* col, long long n_edges, int n_nodes, int* cnt, int* fill, int* cptr,
+                                unsigned long long* keys, int* cedge, int* scan_tmp, void* stream) {
+  return csc_build_impl(col, n_edges, nullptr, n_nodes, cnt, fill, cptr, keys, cedge, scan_tmp, stream);
+}
+// edge count read on the device (n_edges_dev), launches and buffers bounded by max_edges
+extern "C" int sevenn_csc_build_dev(const int* col, long long max_edges, const int* n_edges_dev, int n_nodes, int* cnt,
+                                    int* fill, int* cptr, unsigned long long* keys, int* cedge, int* scan_tmp,
+                                    void* stream) {
+  if (n_edges_dev == nullptr) return SEVENN_ERR_BAD_ARG;
+  return csc_build_impl(col, max_edges, n_edges_dev, n_nodes, cnt, fill, cptr, keys, cedge, scan_tmp, stream);
 }

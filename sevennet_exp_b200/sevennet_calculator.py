@@ -97,10 +97,26 @@ class SevenNetCalculator(_AseCalculator):
         self.modal = modal
         self.engine = Engine(spec, sd, device=self.device, keep_weights=keep_weights, modal=modal)
         self.nl = NeighborList(device=self.device)
+        # C++ whole-model host (csrc/model.cu): one call per step, no per-kernel Python, no host sync before the result
+        # copy.  SEVENN_HOST=python keeps the per-launch Python driver (engine.py), which also serves the variants the
+        # C++ host does not run (radial='mlp', readout_as_fcn).
+        self.native = None
+        from . import host
+        if os.environ.get('SEVENN_HOST', 'native') != 'python' and host.supported(self.engine) is None:
+            self.native = host.NativeModel(self.engine)
         lut = -np.ones(120, dtype=np.int64)
         for z, i in self.type_map.items():
             lut[int(z)] = i
         self._lut = lut
+
+    @property
+    def n_tc_launch(self):
+        """launches on the tcgen05 GEMM arm so far (C++ host + per-launch driver)"""
+        return self.engine.n_tc_launch + (self.native.n_tc_launch if self.native is not None else 0)
+
+    @property
+    def n_launch(self):
+        return self.engine.n_launch + self.nl.n_launch + (self.native.n_launch if self.native is not None else 0)
 
     # ---- plain-array API (also what bench.py times end to end)
     def compute(self, numbers, positions, cell, pbc):
@@ -110,10 +126,20 @@ class SevenNetCalculator(_AseCalculator):
             bad = sorted({int(z) for z in numbers[types < 0]})
             raise ValueError(f'Unknown atomic numbers {bad} for this model')   # sevennet_calculator.py:153-161
         pos = np.ascontiguousarray(np.asarray(positions, dtype=np.float64))
+        n = len(numbers)
+        if self.native is not None and n > 0:
+            if self.native.lib.cdll.sevenn_model_set_tc_min_rows(self.native.handle, int(self.engine.tc_min_rows)):
+                raise RuntimeError('sevenn_model_set_tc_min_rows failed')
+            r = self.native.evaluate_host(types.astype(np.int32), pos, cell, pbc)
+            vol = abs(float(np.linalg.det(np.asarray(cell, dtype=np.float64).reshape(3, 3))))
+            vol = float(np.finfo(float).eps) if vol == 0 else vol
+            stress_model = -r['virial6'] / vol
+            return {'energy': r['energy'], 'free_energy': r['energy'], 'forces': r['forces'].astype(np.float64),
+                    'stress': -stress_model[[0, 1, 2, 4, 5, 3]], 'energies': r['atomic_energy'].astype(np.float64),
+                    'inferred_stress': stress_model, 'n_edges': r['n_edges']}
         types_dev = torch.from_numpy(types.astype(np.int32)).to(self.device, non_blocking=True)
         g = self.nl.graph(types_dev, pos, cell, pbc, self.cutoff)
         out = self.engine.evaluate(g)
-        n = len(numbers)
         host = torch.cat([out['energy'].reshape(1), out['virial6'],
                           out['forces'][:n].reshape(-1).double(), out['atomic_energy'].double()]).cpu().numpy()
         energy, vir = float(host[0]), host[1:7]
