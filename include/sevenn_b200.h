@@ -204,6 +204,17 @@ int sevenn_model_evaluate_positions(sevenn_model* model, long long n_local, long
                                     const int* types, long long max_edges, const sevenn_halo_hooks* halo,
                                     void* workspace, long long workspace_bytes, void* stream, const sevenn_outputs* out);
 
+/* deployed-model contract: the tensors the LAMMPS pair style puts into the TorchScript input dict
+ * (sevenn/pair_e3gnn/pair_e3gnn.cpp:218-225) as device pointers -- x int64 [n] (type index), pos fp32 [n, 3],
+ * edge_index int64 [2, E] (row 0 = centre, row 1 = neighbour, any order), cell_lattice_vectors fp32 [3, 3],
+ * pbc_shift fp32 [E, 3].  Replaces EdgePreprocess + model + ForceStressOutput (sevenn/nn/edge_embedding.py:13-78,
+ * sevenn/nn/force_output.py:55-136).  csrc/torch_op.cpp wraps it as torch.ops.sevenn_b200.evaluate. */
+long long sevenn_model_edges_workspace_bytes(sevenn_model* model, long long n_atoms, long long n_edges);
+int sevenn_model_evaluate_edges(sevenn_model* model, long long n_atoms, const long long* x, const float* pos,
+                                const long long* edge_index, long long n_edges, const float* cell,
+                                const float* pbc_shift, void* workspace, long long workspace_bytes, void* stream,
+                                const sevenn_outputs* out);
+
 /* ---- fused gather + uvu CG tensor product + segment sum (generated per irreps signature <sig>):
  *   int sevenn_conv_fwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo, stream)
  *   int sevenn_conv_bwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY, dy_stride, stream)

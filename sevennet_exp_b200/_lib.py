@@ -62,6 +62,8 @@ SIGNATURES = {
     'sevenn_model_tc_launches': ([c_p], c_ll),
     'sevenn_model_workspace_bytes': ([c_p, c_ll, c_ll, c_ll, c_i], c_ll),
     'sevenn_model_count_edges': ([c_p, c_ll, c_ll, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p], c_i),
+    'sevenn_model_edges_workspace_bytes': ([c_p, c_ll, c_ll], c_ll),
+    'sevenn_model_evaluate_edges': ([c_p, c_ll, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_ll, c_p, c_p], c_i),
     'sevenn_model_evaluate_graph': ([c_p, c_p, c_p, c_p, c_ll, c_p, c_p], c_i),
     'sevenn_model_evaluate_positions': ([c_p, c_ll, c_ll, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_p, c_p], c_i),
     'sevenn_force_virial': ([c_p, c_p, c_p, c_i, c_p, c_p, c_ll, c_p, c_p, c_p], c_i),

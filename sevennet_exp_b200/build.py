@@ -14,6 +14,8 @@ CSRC = os.path.join(HERE, 'csrc')
 GEN = os.path.join(CSRC, 'generated')
 LIBDIR = os.path.join(HERE, '_lib')
 LIB = os.path.join(LIBDIR, 'libsevenn_b200.so')
+TORCH_LIB = os.path.join(LIBDIR, 'libsevenn_b200_torch.so')      # torch.ops.sevenn_b200.* (csrc/torch_op.cpp)
+MD_HOST = os.path.join(LIBDIR, 'sevenn_md_host')                  # torch-free C++ host on the C ABI (csrc/md_host.cpp)
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC']
 STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu', 'model.cu']
 
@@ -93,5 +95,47 @@ def build(extra_specs=None, verbose=True):
     return LIB
 
 
+def build_torch_op(verbose=True):
+    """libsevenn_b200_torch.so: the TORCH_LIBRARY registration of torch.ops.sevenn_b200.evaluate (csrc/torch_op.cpp, the one
+    unit that includes torch headers) linked against libsevenn_b200.so next to it ($ORIGIN rpath)."""
+    import sysconfig
+    import torch
+    import torch.utils.cpp_extension as ce
+    src = os.path.join(CSRC, 'torch_op.cpp')
+    hdr = os.path.join(HERE, '..', 'include', 'sevenn_b200.h')
+    if os.path.exists(TORCH_LIB) and os.path.getmtime(TORCH_LIB) >= max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        return TORCH_LIB
+    tlib = os.path.join(os.path.dirname(torch.__file__), 'lib')
+    cuda_home = os.environ.get('CUDA_HOME', '/usr/local/cuda')
+    cmd = ['g++', '-O2', '-std=c++17', '-fPIC', '-shared', f'-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}']
+    for inc in ce.include_paths() + [os.path.join(cuda_home, 'include'), sysconfig.get_paths()['include']]:
+        cmd += ['-I', inc]
+    cmd += [src, '-o', TORCH_LIB + '.tmp', '-L', LIBDIR, '-lsevenn_b200', '-L', tlib, '-ltorch', '-ltorch_cpu',
+            '-lc10', '-ltorch_cuda', '-lc10_cuda', '-Wl,-rpath,$ORIGIN', f'-Wl,-rpath,{tlib}']
+    subprocess.check_call(cmd)
+    os.replace(TORCH_LIB + '.tmp', TORCH_LIB)
+    if verbose:
+        print(f'built {TORCH_LIB}')
+    return TORCH_LIB
+
+
+def build_md_host(verbose=True):
+    """sevenn_md_host: a C++ program (no torch, no Python) that drives libsevenn_b200.so the way a pair style would."""
+    src = os.path.join(CSRC, 'md_host.cpp')
+    hdr = os.path.join(HERE, '..', 'include', 'sevenn_b200.h')
+    if os.path.exists(MD_HOST) and os.path.getmtime(MD_HOST) >= max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        return MD_HOST
+    cuda_home = os.environ.get('CUDA_HOME', '/usr/local/cuda')
+    subprocess.check_call(['g++', '-O2', '-std=c++17', src, '-o', MD_HOST + '.tmp', '-I', os.path.join(cuda_home, 'include'),
+                           '-L', LIBDIR, '-lsevenn_b200', '-L', os.path.join(cuda_home, 'lib64'), '-lcudart',
+                           '-Wl,-rpath,$ORIGIN', f'-Wl,-rpath,{os.path.join(cuda_home, "lib64")}'])
+    os.replace(MD_HOST + '.tmp', MD_HOST)
+    if verbose:
+        print(f'built {MD_HOST}')
+    return MD_HOST
+
+
 if __name__ == '__main__':
     build()
+    build_torch_op()
+    build_md_host()

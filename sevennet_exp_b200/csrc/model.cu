@@ -631,3 +631,72 @@ extern "C" int sevenn_model_count_edges(sevenn_model* m, long long n_rows, long 
   *n_edges = e;
   return 0;
 }
+
+// ---- deployed-model entry: the dict the LAMMPS pair style hands to the TorchScript module
+// (sevenn/pair_e3gnn/pair_e3gnn.cpp:218-225: x, pos, edge_index, cell_lattice_vectors, pbc_shift) -> E / F / virial /
+// atomic energies.  Replaces EdgePreprocess (sevenn/nn/edge_embedding.py:13-78) + the model + ForceStressOutput by
+// autograd over positions and strain (sevenn/nn/force_output.py:55-136); the edge list may come in any order.
+namespace {
+__global__ void i64_to_i32_kernel(const long long* __restrict__ in, long long n, int* __restrict__ out) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    out[i] = (int)in[i];
+}
+// edges regrouped by centre (perm = edge ids grouped by centre, ascending): neighbour index and edge vector
+__global__ void edge_gather_kernel(const int* __restrict__ perm, long long n_edges, const long long* __restrict__ ei,
+                                   const float* __restrict__ pos, const float* __restrict__ cell,
+                                   const float* __restrict__ shift, int* __restrict__ col, float* __restrict__ vec) {
+  for (long long k = blockIdx.x * (long long)blockDim.x + threadIdx.x; k < n_edges; k += (long long)gridDim.x * blockDim.x) {
+    const long long e = perm[k];
+    const long long i = ei[e], j = ei[n_edges + e];
+    col[k] = (int)j;
+    const float s0 = shift[3 * e], s1 = shift[3 * e + 1], s2 = shift[3 * e + 2];
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+      vec[3 * k + c] = pos[3 * j + c] - pos[3 * i + c] + (s0 * cell[c] + s1 * cell[3 + c] + s2 * cell[6 + c]);
+  }
+}
+}  // namespace
+
+extern "C" long long sevenn_model_edges_workspace_bytes(sevenn_model* m, long long n_atoms, long long n_edges) {
+  const long long base = sevenn_model_workspace_bytes(m, n_atoms, n_atoms, n_edges, 0);
+  if (base < 0) return -1;
+  const long long ints = 6 * (n_atoms + 64) + 2 * sevenn_scan_tmp_ints((int)(n_atoms + 1)) + 5 * (n_edges + 64);
+  return base + 4 * ints + 12 * (n_edges + 64) + 8 * (n_edges + 64) + 64 * 256;
+}
+
+extern "C" int sevenn_model_evaluate_edges(sevenn_model* m, long long n_atoms, const long long* x, const float* pos,
+                                           const long long* edge_index, long long n_edges, const float* cell,
+                                           const float* pbc_shift, void* workspace, long long workspace_bytes,
+                                           void* stream, const sevenn_outputs* out) {
+  int rc = check_args(m, workspace, workspace_bytes);
+  if (rc || out == nullptr || out->energy == nullptr || out->atomic_energy == nullptr || n_atoms < 0 || n_edges < 0 ||
+      n_edges > 0x7fffffffLL)
+    return SEVENN_ERR_BAD_ARG;
+  if (sevenn_model_edges_workspace_bytes(m, n_atoms, n_edges) > workspace_bytes) return SEVENN_ERR_WORKSPACE;
+  if (n_atoms == 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  Arena A{(char*)workspace, (size_t)workspace_bytes, false};
+  const long long n = n_atoms, E = n_edges, n_tmp = sevenn_scan_tmp_ints((int)(n + 1)) + 1;
+  int* types = A.i32(n);
+  int* center = A.i32(E);
+  const size_t z0 = A.mark();
+  int* cnt = A.i32(n + 1); int* fill = A.i32(n); int* cnt2 = A.i32(n + 1); int* fill2 = A.i32(n);
+  const size_t z1 = A.mark();
+  int* rowptr = A.i32(n + 1); int* cptr = A.i32(n + 1); int* tmp = A.i32(n_tmp);
+  int* perm = A.i32(E); int* col = A.i32(E); int* cedge = A.i32(E);
+  float* vec = A.f32(3 * E);
+  unsigned long long* keys = (unsigned long long*)A.raw((size_t)(E > 0 ? E : 1) * 8);
+  cudaMemsetAsync(A.base + align_up(z0, 256), 0, z1 - align_up(z0, 256), st);
+  i64_to_i32_kernel<<<sevenn_grid_for(n), 256, 0, st>>>(x, n, types);
+  if (E > 0) i64_to_i32_kernel<<<sevenn_grid_for(E), 256, 0, st>>>(edge_index, E, center);
+  rc = sevenn_csc_build(center, E, (int)n, cnt, fill, rowptr, keys, perm, tmp, stream);      // CSR by centre
+  if (rc) return rc;
+  if (E > 0) edge_gather_kernel<<<sevenn_grid_for(E), 256, 0, st>>>(perm, E, edge_index, pos, cell, pbc_shift, col, vec);
+  rc = sevenn_csc_build(col, E, (int)n, cnt2, fill2, cptr, keys, cedge, tmp, stream);         // CSC by neighbour
+  if (rc) return rc;
+  m->n_launch += 4;
+  GraphView g{n, n, E, types, vec, rowptr, col, cptr, cedge, rowptr + n};
+  rc = evaluate_graph(m, A, g, nullptr, st, out->energy, out->atomic_energy, out->forces, out->virial6, out->virial_atoms);
+  if (rc) return rc;
+  return A.fail ? SEVENN_ERR_WORKSPACE : (int)cudaGetLastError();
+}

@@ -15,7 +15,11 @@ same *calling contract* -- `forward(Dict[str, Tensor]) -> Dict[str, Tensor]` wit
   features / ghost gradients in between.  `DeployedParallel.compute()` is that loop (pair_e3gnn_parallel.cpp:
   331-437) with the two communications as callbacks.
 
-File format: a `torch.save` bundle {format, config, model_state_dict, extra_files} (weights only, no code).
+File format (serial): a TorchScript archive written by `torch.jit.save` whose scripted forward calls the custom op
+`torch.ops.sevenn_b200.evaluate` (csrc/torch_op.cpp -> the C++ whole-model host, csrc/model.cu) and whose buffers hold
+the packed model; `_extra_files` carries the reference's metadata keys plus the weights-only bundle {format, config,
+model_state_dict, extra_files} for the Python driver.  Parallel segments stay weights-only bundles (their consumer
+differentiates them with autograd segment by segment).
 """
 import datetime
 import os
@@ -60,8 +64,54 @@ def _plain_sd(sd):
     return {k: (v.detach().cpu().clone() if torch.is_tensor(v) else torch.as_tensor(v)) for k, v in sd.items()}
 
 
-def deploy(checkpoint, fname: str = 'deployed_serial.pt', modal: Optional[str] = None) -> str:
-    """sevenn/scripts/deploy.py:20-70.  ``modal`` (:31-36): the modality a multi-modal checkpoint is frozen to."""
+TORCH_OP_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_lib', 'libsevenn_b200_torch.so')
+_op_loaded = False
+
+
+def load_torch_op():
+    """Registers torch.ops.sevenn_b200.evaluate (csrc/torch_op.cpp).  A C++ host does the same with one dlopen of
+    libsevenn_b200_torch.so before torch::jit::load (INTEGRATION.md)."""
+    global _op_loaded
+    if not _op_loaded:
+        if not os.path.exists(TORCH_OP_LIB):
+            raise RuntimeError(f'{TORCH_OP_LIB} is missing: run `python -m sevennet_exp_b200.build`')
+        torch.ops.load_library(TORCH_OP_LIB)
+        _op_loaded = True
+
+
+class _SerialScriptModule(torch.nn.Module):
+    """What gets scripted and saved: the packed model as buffers + a forward with the reference's dict contract
+    (inputs pair_e3gnn.cpp:218-225, outputs :230-264) that hands the tensors to torch.ops.sevenn_b200.evaluate."""
+
+    def __init__(self, prog: torch.Tensor, data: torch.Tensor):
+        super().__init__()
+        self.register_buffer('prog', prog)
+        self.register_buffer('data', data)
+
+    def forward(self, data: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        energy, force, virial, atomic = torch.ops.sevenn_b200.evaluate(
+            self.prog, self.data, data['x'], data['pos'], data['edge_index'], data['cell_lattice_vectors'],
+            data['pbc_shift'])
+        vol = data['cell_volume'].to(virial.device).to(virial.dtype)
+        # forces and stress are analytic, not autograd: nothing here is part of a graph (pos arrives with requires_grad)
+        data['inferred_total_energy'] = energy.detach()
+        data['inferred_force'] = force.detach()
+        data['inferred_stress'] = (-virial / vol).detach()    # (xx, yy, zz, xy, yz, zx), force_output.py:120-134
+        data['atomic_energy'] = atomic.detach()
+        return data
+
+
+def deploy(checkpoint, fname: str = 'deployed_serial.pt', modal: Optional[str] = None, **kwargs) -> str:
+    """sevenn/scripts/deploy.py:20-70: a TorchScript file (`torch.jit.load` / `torch::jit::load`) with the reference's
+    `_extra_files` metadata.  Its forward calls torch.ops.sevenn_b200.evaluate, so the loading process registers the op
+    first (`load_torch_op()` / dlopen of libsevenn_b200_torch.so).  ``modal`` (:31-36): the modality a multi-modal
+    checkpoint is frozen to.  ``format='bundle'`` writes the weights-only torch.save bundle instead (models the C++ host
+    does not run: radial='mlp'-only activations, readout_as_fcn); the TorchScript file carries the same bundle as the
+    extra file `sevenn_b200_bundle`, which is what `load_deployed(..., lib=...)` and the Python driver read."""
+    import io
+    format = kwargs.pop('format', 'torchscript')
+    if kwargs:
+        raise TypeError(f'unexpected arguments {list(kwargs)}')
     spec, sd, cfg = _resolve(checkpoint)
     if spec.n_modal:
         if modal is None or modal not in (spec.modal_map or {}):
@@ -70,8 +120,28 @@ def deploy(checkpoint, fname: str = 'deployed_serial.pt', modal: Optional[str] =
         raise ValueError('Modality given, but model has no modal_map')
     if not fname.endswith('.pt'):
         fname += '.pt'
-    torch.save({'format': SERIAL_FORMAT, 'config': {**cfg, 'version': '0.11.0'}, 'model_state_dict': _plain_sd(sd),
-                'extra_files': extra_files(cfg, spec), 'modal': modal}, fname)
+    bundle = {'format': SERIAL_FORMAT, 'config': {**cfg, 'version': '0.11.0'}, 'model_state_dict': _plain_sd(sd),
+              'extra_files': extra_files(cfg, spec), 'modal': modal}
+    if format == 'bundle':
+        torch.save(bundle, fname)
+        return fname
+    if format != 'torchscript':
+        raise ValueError("format must be 'torchscript' or 'bundle'")
+    from . import _lib, host
+    from .engine import Engine
+    # weights are packed on the CPU (no GPU needed to deploy): the library is only asked for its GEMM tile geometry
+    eng = Engine(spec, sd, lib=_lib.Lib(_lib.load_for_symbol_check()), device='cpu', radial='table', modal=modal)
+    why = host.supported(eng)
+    if why:
+        raise NotImplementedError(f"{why}: deploy(..., format='bundle') keeps this model on the Python driver")
+    prog, data = host.pack_engine(eng)
+    load_torch_op()
+    module = torch.jit.script(_SerialScriptModule(torch.from_numpy(prog.copy()), torch.from_numpy(data.copy())))
+    buf = io.BytesIO()
+    torch.save(bundle, buf)
+    md = dict(bundle['extra_files'])
+    md['sevenn_b200_bundle'] = buf.getvalue()
+    torch.jit.save(module, fname, _extra_files=md)
     return fname
 
 
@@ -222,15 +292,44 @@ def run_parallel_segments(segments, x: torch.Tensor, x_ghost: torch.Tensor, edge
     return energy.detach(), dE_dr.detach(), out['atomic_energy'].detach()
 
 
-def load_deployed(path: str, device='cuda', lib=None):
-    """`torch.jit.load(path, _extra_files=...)` of the reference -> (model, extra_files)."""
-    if os.path.isdir(path):
-        path = os.path.join(path, 'deployed_parallel_0.pt')
+EXTRA_KEYS = ('chemical_symbols_to_index', 'cutoff', 'num_species', 'model_type', 'version', 'dtype', 'time')
+
+
+def _read_bundle(path: str):
+    """(bundle dict, is_torchscript) of a file written by deploy() / deploy_parallel()."""
+    import io
+    import zipfile
+    if zipfile.is_zipfile(path):
+        with zipfile.ZipFile(path) as z:
+            names = z.namelist()
+            extra = [n for n in names if n.endswith('extra/sevenn_b200_bundle')]
+            if extra:
+                return torch.load(io.BytesIO(z.read(extra[0])), weights_only=False, map_location='cpu'), True
+            if any(n.endswith('constants.pkl') or '/code/' in n for n in names):
+                raise ValueError(f'{path}: a TorchScript file written by the reference freezes the e3nn graph and cannot '
+                                 'run on the B200 kernels; deploy the checkpoint with sevennet_exp_b200.deploy.deploy()')
     try:
         b = torch.load(path, weights_only=False, map_location='cpu')
     except Exception as e:  # noqa: BLE001
-        raise ValueError(f'{path}: not a sevennet_exp_b200 deployed bundle ({e})') from e
+        raise ValueError(f'{path}: not a sevennet_exp_b200 deployed model ({e})') from e
+    return b, False
+
+
+def load_deployed(path: str, device='cuda', lib=None, scripted: Optional[bool] = None):
+    """`torch.jit.load(path, _extra_files=...)` of the reference -> (model, extra_files).
+
+    A serial model deployed as TorchScript comes back as the `torch.jit.ScriptModule` itself (its forward runs the
+    C++ host through torch.ops.sevenn_b200.evaluate) unless ``scripted=False`` or an explicit ``lib`` asks for the
+    Python driver (`DeployedSerial`) on the bundle stored inside the file."""
+    if os.path.isdir(path):
+        path = os.path.join(path, 'deployed_parallel_0.pt')
+    b, is_ts = _read_bundle(path)
     fmt = b.get('format') if isinstance(b, dict) else None
+    if fmt == SERIAL_FORMAT and is_ts and lib is None and scripted is not False:
+        load_torch_op()
+        md = {k: '' for k in EXTRA_KEYS}
+        m = torch.jit.load(path, map_location='cpu', _extra_files=md)
+        return m, {k: (v.decode() if isinstance(v, bytes) else v) for k, v in md.items()}
     if fmt == SERIAL_FORMAT:
         m = DeployedSerial(b['config'], b['model_state_dict'], device=device, extra=b['extra_files'], lib=lib,
                            modal=b.get('modal'))

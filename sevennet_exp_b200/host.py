@@ -108,6 +108,16 @@ def pack_engine(engine: Engine):
     return np.asarray(w.ints, dtype=np.int32), np.concatenate(w.chunks) if w.chunks else np.zeros(1, np.float32)
 
 
+def save_model(path: str, engine: Engine):
+    """model.bin for torch-free C++ hosts (csrc/md_host.cpp): int64 magic, n_prog, n_data | int32 program | fp32 data."""
+    prog, data = pack_engine(engine)
+    with open(path, 'wb') as f:
+        np.asarray([MAGIC, prog.size, data.size], dtype=np.int64).tofile(f)
+        prog.tofile(f)
+        data.tofile(f)
+    return path
+
+
 class Outputs(ctypes.Structure):
     _fields_ = [('energy', ctypes.c_void_p), ('atomic_energy', ctypes.c_void_p), ('forces', ctypes.c_void_p),
                 ('virial6', ctypes.c_void_p), ('virial_atoms', ctypes.c_void_p), ('status', ctypes.c_void_p)]

@@ -896,7 +896,9 @@ def build_E3_equivariant_model(config: dict, parallel: bool = False) -> AtomGrap
     layers['force_output'] = ForceStressOutputFromEdge()
     common = dict(cutoff=cfg['cutoff'], type_map=cfg['_type_map'], data_key_grad=EDGE_VEC)
     if not parallel:
-        return AtomGraphSequential(layers, modal_map=cfg.get('_modal_map') if nm else None, **common)
+        model = AtomGraphSequential(layers, modal_map=cfg.get('_modal_map') if nm else None, **common)
+        model._sevenn_config = copy.deepcopy(config)      # lets SevenNetCalculator(file_type='model_instance') take the module
+        return model
     return [AtomGraphSequential(seg, eval_type_map=False, **common) for seg in _parallel_segments(layers, cfg, S, L)]
 
 

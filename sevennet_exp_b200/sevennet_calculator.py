@@ -60,14 +60,20 @@ class SevenNetCalculator(_AseCalculator):
         file_type = file_type.lower()
         if file_type not in ('checkpoint', 'model_instance', 'torchscript'):
             raise ValueError('file_type should be checkpoint, model_instance or torchscript')
+        self._ts_model = None
         if file_type == 'torchscript':
-            # the reference loads a deployed serial model here (sevennet_calculator.py:103-125); ours is the bundle
-            # written by sevennet_exp_b200.deploy.deploy() (a file frozen by the reference raises ValueError)
-            from .deploy import SERIAL_FORMAT
-            b = torch.load(model, weights_only=False, map_location='cpu') if os.path.isfile(str(model)) else None
-            if not (isinstance(b, dict) and b.get('format') == SERIAL_FORMAT):
-                raise ValueError(f'{model}: not a serial model deployed by sevennet_exp_b200.deploy.deploy(); a '
-                                 'TorchScript file written by the reference freezes the e3nn graph')
+            # the reference does torch.jit.load here and calls the module on the graph dict
+            # (sevennet_calculator.py:103-125, 176-190); so do we -- the file is the TorchScript archive written by
+            # sevennet_exp_b200.deploy.deploy(), whose forward runs torch.ops.sevenn_b200.evaluate (a file frozen by
+            # the reference itself raises ValueError: it inlines the e3nn graph)
+            from . import deploy as _deploy
+            if not os.path.isfile(str(model)):
+                raise FileNotFoundError(str(model))
+            b, is_ts = _deploy._read_bundle(str(model))
+            if not (isinstance(b, dict) and b.get('format') == _deploy.SERIAL_FORMAT):
+                raise ValueError(f'{model}: not a serial model deployed by sevennet_exp_b200.deploy.deploy()')
+            if is_ts:
+                self._ts_model, self._ts_extra = _deploy.load_deployed(str(model))
             model, file_type = (b['config'], b['model_state_dict']), 'model_instance'
             modal = b.get('modal', modal)
         if device == 'auto':
@@ -85,6 +91,14 @@ class SevenNetCalculator(_AseCalculator):
             else:
                 raise FileNotFoundError(str(model))
         else:
+            if isinstance(model, torch.nn.Module):
+                # reference sevennet_calculator.py:111-124: an AtomGraphSequential instance.  Ours carries the config it
+                # was built from (nn.build_E3_equivariant_model stores it), so the whole-model engine takes its weights
+                cfg = getattr(model, '_sevenn_config', None)
+                if cfg is None:
+                    raise ValueError('model_instance: the module has no `_sevenn_config` (build it with '
+                                     'sevennet_exp_b200.nn.build_E3_equivariant_model, or pass (config, state_dict))')
+                model = (dict(cfg, version='0.11.0'), {k: v.detach().cpu() for k, v in model.state_dict().items()})
             cfg, sd = model
             cfg = patch_old_config(cfg)
             spec = build_spec(cfg)
@@ -127,6 +141,8 @@ class SevenNetCalculator(_AseCalculator):
             raise ValueError(f'Unknown atomic numbers {bad} for this model')   # sevennet_calculator.py:153-161
         pos = np.ascontiguousarray(np.asarray(positions, dtype=np.float64))
         n = len(numbers)
+        if self._ts_model is not None and n > 0:
+            return self._compute_torchscript(types, pos, cell, pbc)
         if self.native is not None and n > 0:
             if self.native.lib.cdll.sevenn_model_set_tc_min_rows(self.native.handle, int(self.engine.tc_min_rows)):
                 raise RuntimeError('sevenn_model_set_tc_min_rows failed')
@@ -149,6 +165,28 @@ class SevenNetCalculator(_AseCalculator):
         stress = -stress_model[[0, 1, 2, 4, 5, 3]]           # ASE Voigt, sevennet_calculator.py:196-201
         return {'energy': energy, 'free_energy': energy, 'forces': forces, 'stress': stress,
                 'energies': energies, 'inferred_stress': stress_model, 'n_edges': g.n_edges}
+
+    def _compute_torchscript(self, types, pos, cell, pbc):
+        """file_type='torchscript': graph on the GPU, then the loaded ScriptModule with the deployed-model dict
+        (reference sevennet_calculator.py:176-202)."""
+        dev = self.device
+        r = self.nl.build(pos, cell, pbc, self.cutoff)
+        cell_t = torch.as_tensor(np.asarray(cell, dtype=np.float64).reshape(3, 3), dtype=torch.float32, device=dev)
+        data = {'x': torch.as_tensor(types, dtype=torch.int64, device=dev),
+                'pos': torch.as_tensor(pos, dtype=torch.float32, device=dev),
+                'edge_index': torch.stack([r['center'], r['col']]).to(torch.int64),
+                'num_atoms': torch.tensor([len(types)], device=dev),
+                'cell_lattice_vectors': cell_t,
+                'cell_volume': torch.tensor(r['volume'], dtype=torch.float32, device=dev),
+                'pbc_shift': r['shift'].to(torch.float32)}
+        out = self._ts_model(data)
+        energy = float(out['inferred_total_energy'].item())
+        stress_model = out['inferred_stress'].detach().cpu().numpy().astype(np.float64)
+        return {'energy': energy, 'free_energy': energy,
+                'forces': out['inferred_force'].detach().cpu().numpy().astype(np.float64),
+                'stress': -stress_model[[0, 1, 2, 4, 5, 3]],
+                'energies': out['atomic_energy'].detach().cpu().numpy().reshape(-1).astype(np.float64),
+                'inferred_stress': stress_model, 'n_edges': r['n_edges']}
 
     def compute_batch(self, structures):
         """Several structures in one evaluation (the reference batches graphs with torch_geometric's Collater,

@@ -384,6 +384,8 @@ def test_deployed_entry_points_on_gpu(lib, golden_dir, tmp_path):
     cfg, sd, numbers, pos, cell, gold = deployed_serial_case(golden_dir)
     path = D.deploy((cfg, sd), str(tmp_path / 'serial.pt'))
     model, extra = D.load_deployed(path)
+    assert isinstance(model, torch.jit.ScriptModule)           # a real TorchScript archive (torch.jit.load)
+    assert extra['chemical_symbols_to_index'] == 'Hf O ' and float(extra['cutoff']) == 4.0
     n = len(numbers)
     data = {'x': torch.tensor([cfg['_type_map'][int(z)] for z in numbers]),
             'pos': torch.tensor(pos, dtype=torch.float32), 'edge_index': torch.tensor(gold['edge_index']),
@@ -557,3 +559,61 @@ def test_readout_as_fcn_on_gpu(lib, act):
     model = S.build_model(cfg).eval()
     numbers, pos, cell = random_cell(40, list(cfg['_type_map']), density=0.05, seed=12)
     print(_engine_vs_oracle(cfg, model.state_dict(), model, numbers, pos, cell, [True] * 3))
+
+
+def test_torchscript_artifact_in_a_fresh_process(lib, golden_dir, tmp_path):
+    """What a C++ host does (sevenn/pair_e3gnn/pair_e3gnn.cpp:306-335, 218-264): load the op library, torch.jit.load
+    the deployed file with its `_extra_files`, call forward on the input dict -- in a new interpreter that never imports
+    this package -- and get the outputs of the REFERENCE's own deployed model on the same frame
+    (tests/golden/deployed_serial_hfo2.npz).  The edge list is handed over in shuffled order."""
+    import subprocess
+    import sys
+    from sevennet_exp_b200 import deploy as D
+    from tests.test_oracle import deployed_serial_case
+    cfg, sd, numbers, pos, cell, gold = deployed_serial_case(golden_dir)
+    path = D.deploy((cfg, sd), str(tmp_path / 'deployed_serial.pt'))
+    np.savez(tmp_path / 'inp.npz', x=np.array([cfg['_type_map'][int(z)] for z in numbers]), pos=pos, cell=cell,
+             edge_index=gold['edge_index'], pbc_shift=gold['pbc_shift'])
+    code = f"""
+import numpy as np, torch
+torch.ops.load_library({D.TORCH_OP_LIB!r})
+md = {{'chemical_symbols_to_index': '', 'cutoff': '', 'num_species': '', 'model_type': '', 'version': '', 'dtype': '', 'time': ''}}
+m = torch.jit.load({path!r}, _extra_files=md)
+assert md['model_type'].decode() == 'E3_equivariant_model' and md['chemical_symbols_to_index'].decode() == 'Hf O '
+d = np.load({str(tmp_path / 'inp.npz')!r})
+p = np.random.default_rng(0).permutation(d['edge_index'].shape[1])
+dev = 'cuda'
+cell = torch.tensor(d['cell'], dtype=torch.float32)
+data = {{'x': torch.tensor(d['x']).to(dev), 'pos': torch.tensor(d['pos'], dtype=torch.float32).to(dev).requires_grad_(True),
+        'edge_index': torch.tensor(d['edge_index'][:, p]).to(dev), 'num_atoms': torch.tensor([len(d['x'])]).to(dev),
+        'cell_lattice_vectors': cell.to(dev), 'cell_volume': torch.dot(cell[0], torch.cross(cell[1], cell[2], dim=0)).to(dev),
+        'pbc_shift': torch.tensor(d['pbc_shift'][p], dtype=torch.float32).to(dev)}}
+out = m(data)
+np.savez({str(tmp_path / 'out.npz')!r}, energy=out['inferred_total_energy'].item(), force=out['inferred_force'].cpu().numpy(),
+         stress=out['inferred_stress'].cpu().numpy(), atomic_energy=out['atomic_energy'].cpu().numpy())
+import sys
+assert 'sevennet_exp_b200' not in sys.modules
+"""
+    r = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = np.load(tmp_path / 'out.npz')
+    n = len(numbers)
+    assert abs(float(out['energy']) - float(gold['energy'])) / n < 1e-5
+    assert np.abs(out['atomic_energy'].reshape(-1) - gold['atomic_energy'].reshape(-1)).max() < 1e-5
+    assert np.abs(out['force'] - gold['force']).max() < 1e-4
+    assert np.abs(out['stress'] - gold['stress']).max() * KBAR < 1e-2            # the reference ran in fp32
+
+
+def test_calculator_takes_an_nn_module_instance(lib):
+    """reference sevennet_calculator.py:111-124: SevenNetCalculator(model=<AtomGraphSequential>, file_type='model_instance')."""
+    from sevennet_exp_b200 import nn as bnn
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    cfg, om = _random_model('test-so3-l2')
+    model = bnn.build_E3_equivariant_model(cfg)
+    assert not model.load_state_dict(om.state_dict(), strict=False)[0]
+    numbers, pos, cell = random_cell(48, list(cfg['_type_map']), density=0.05, seed=3)
+    a = SevenNetCalculator(model, file_type='model_instance').compute(numbers, pos, cell, [True] * 3)
+    b = SevenNetCalculator((cfg, om.state_dict()), file_type='model_instance').compute(numbers, pos, cell, [True] * 3)
+    assert a['energy'] == b['energy'] and np.array_equal(a['forces'], b['forces'])
+    with pytest.raises(ValueError):
+        SevenNetCalculator(torch.nn.Linear(2, 2), file_type='model_instance')

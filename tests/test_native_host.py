@@ -103,3 +103,47 @@ def test_native_edge_capacity_overflow_recovers():
     finally:
         os.environ.pop('SEVENN_HOST')
     assert b['n_edges'] == ref['n_edges'] and b['energy'] == ref['energy'] and np.array_equal(b['forces'], ref['forces'])
+
+
+def test_cpp_md_host_without_torch_or_python(tmp_path):
+    """sevenn_md_host (csrc/md_host.cpp): a C++ program that links libsevenn_b200.so only -- the calls a LAMMPS pair style
+    would make (sevenn/pair_e3gnn/pair_e3gnn.cpp:71-274) -- runs velocity-Verlet steps on SevenNet-0-shaped Si-64.
+    Step-0 energy / forces / virial must be the calculator's (same kernels: bit-identical in fp32), and the total
+    energy must be conserved along the trajectory (forces are the exact gradient of the energy)."""
+    import subprocess
+    from sevennet_exp_b200 import build, host
+    from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
+    exe = build.MD_HOST
+    assert os.path.exists(exe), 'run python -m sevennet_exp_b200.build'
+    cfg, model = _random_model('7net-0')
+    calc = SevenNetCalculator((cfg, model.state_dict()), file_type='model_instance')
+    numbers, pos, cell = diamond_si((2, 2, 2))
+    n = len(numbers)
+    host.save_model(str(tmp_path / 'model.bin'), calc.engine)
+    rng = np.random.default_rng(0)
+    vel = rng.normal(0.0, 0.004, (n, 3))                     # A/fs, ~ 400 K for Si
+    vel -= vel.mean(0)
+    with open(tmp_path / 'structure.bin', 'wb') as f:
+        np.asarray([n], dtype=np.int64).tofile(f)
+        np.asarray(cell, dtype=np.float64).reshape(9).tofile(f)
+        np.asarray([1, 1, 1], dtype=np.int32).tofile(f)
+        calc._lut[numbers].astype(np.int32).tofile(f)
+        np.asarray(pos, dtype=np.float64).tofile(f)
+        np.full(n, 28.0855).tofile(f)
+        vel.tofile(f)
+    steps = 40
+    r = subprocess.run([exe, str(tmp_path / 'model.bin'), str(tmp_path / 'structure.bin'), str(steps), '1.0',
+                        str(tmp_path / 'out.bin')], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    raw = np.fromfile(tmp_path / 'out.bin', dtype=np.float64)
+    rec, f0 = raw[:8 * (steps + 1)].reshape(steps + 1, 8), raw[8 * (steps + 1):].reshape(n, 3)
+    ref = calc.compute(numbers, pos, cell, [True] * 3)
+    assert rec[0, 0] == ref['energy']
+    assert np.array_equal(f0, ref['forces'])
+    vol = abs(np.linalg.det(cell))
+    assert np.array_equal(-rec[0, 2:] / vol, ref['inferred_stress'])
+    etot = rec[:, 0] + rec[:, 1]
+    swing = np.ptp(rec[:, 1])
+    print(r.stdout[-400:], 'kinetic swing', swing, 'drift', np.abs(etot - etot[0]).max())
+    assert swing > 1e-4                                        # atoms really moved
+    assert np.abs(etot - etot[0]).max() < 0.02 * swing + 1e-6
