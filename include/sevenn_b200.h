@@ -215,6 +215,30 @@ int sevenn_model_evaluate_edges(sevenn_model* model, long long n_atoms, const lo
                                 const float* pbc_shift, void* workspace, long long workspace_bytes, void* stream,
                                 const sevenn_outputs* out);
 
+/* ---- training step (csrc/train.cu): what loss.backward() through forces and stress needs on top of the first-order
+ * kernels (sevenn/train/trainer.py:156-170, sevenn/nn/force_output.py:173-178 `create_graph=self.training`).  Second
+ * order is composed from the first-order kernels in sevennet_exp_b200/nn/functional.py (every op is multilinear or
+ * elementwise); these are the missing pieces. */
+/* out = (m ? m : 1) * cst * f^(order)(x), order 0..2, f = activation `act` (e3nn radial MLP / gate non-linearities) */
+int sevenn_act_mul(const float* x, const float* m, long long n, int act, float cst, int order, float* out, void* stream);
+/* derivative of sevenn_gate_bwd: given c = cotangent of dpre, d_dout = d<c,dpre>/d(dout), d_pre = d<c,dpre>/d(pre) */
+int sevenn_gate_bwd2(const float* pre, int din, const float* dout, int dout_dim, const float* c, long long n,
+                     const sevenn_gate_piece* pieces /* host */, int n_pieces, float* d_dout, float* d_pre, void* stream);
+/* c == NULL: G[e,k] = demb[e,k] * d emb_k/d coeff_k (trainable Bessel coefficients, edge_embedding.py:96-100).
+ * c != NULL: JY = dY/d(edge_vec).c, Jemb = d emb/d(edge_vec).c per edge, G[e,k] = demb[e,k] d/d coeff_k(d emb_k/d vec . c) */
+int sevenn_edge_train(const float* edge_vec, long long n_edges, int lmax, int normalize, int n_basis, int cutoff_kind,
+                      float rc, float p, float r_on, const float* bessel_coeffs, const float* demb, const float* c,
+                      float* JY, float* Jemb, float* G, void* stream);
+/* weight gradient G[K,N] (+)= scale * sum_rows A[row,:K]^T B[row,:N] (rows (node, m) strided like sevenn_gemm_args;
+ * types != NULL keeps nodes of species type_sel only); deterministic two-stage reduction through `part` */
+int sevenn_gemm_tn_splits(long long M);
+int sevenn_gemm_tn(const float* A, long long sAn, int sAm, const float* B, long long sBn, int sBm, long long M, int R,
+                   int K, int N, const int* types, int type_sel, float scale, int accumulate,
+                   float* part /* >= sevenn_gemm_tn_splits(M) * K * N */, float* out /* K x N */, void* stream);
+/* torch.optim.Adam's update on one flat parameter (sevenn/train/optim.py 'adam'); step >= 1 */
+int sevenn_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, int step, float lr,
+                     float beta1, float beta2, float eps, float weight_decay, void* stream);
+
 /* ---- fused gather + uvu CG tensor product + segment sum (generated per irreps signature <sig>):
  *   int sevenn_conv_fwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo, stream)
  *   int sevenn_conv_bwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, gout, ldo, dW, dxe, lddx, dY, dy_stride, stream)

@@ -66,6 +66,12 @@ SIGNATURES = {
     'sevenn_model_evaluate_edges': ([c_p, c_ll, c_p, c_p, c_p, c_ll, c_p, c_p, c_p, c_ll, c_p, c_p], c_i),
     'sevenn_model_evaluate_graph': ([c_p, c_p, c_p, c_p, c_ll, c_p, c_p], c_i),
     'sevenn_model_evaluate_positions': ([c_p, c_ll, c_ll, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_p, c_p], c_i),
+    'sevenn_act_mul': ([c_p, c_p, c_ll, c_i, c_f, c_i, c_p, c_p], c_i),
+    'sevenn_gate_bwd2': ([c_p, c_i, c_p, c_i, c_p, c_ll, ctypes.POINTER(GatePiece), c_i, c_p, c_p, c_p], c_i),
+    'sevenn_edge_train': ([c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p], c_i),
+    'sevenn_gemm_tn_splits': ([c_ll], c_i),
+    'sevenn_gemm_tn': ([c_p, c_ll, c_i, c_p, c_ll, c_i, c_ll, c_i, c_i, c_i, c_p, c_i, c_f, c_i, c_p, c_p, c_p], c_i),
+    'sevenn_adam_step': ([c_p, c_p, c_p, c_p, c_ll, c_i, c_f, c_f, c_f, c_f, c_f, c_p], c_i),
     'sevenn_force_virial': ([c_p, c_p, c_p, c_i, c_p, c_p, c_ll, c_p, c_p, c_p], c_i),
     'sevenn_segment_gather_sum': ([c_p, c_i, c_p, c_p, c_ll, c_p, c_i, c_p], c_i),
     'sevenn_gather_rows': ([c_p, c_i, c_p, c_ll, c_p, c_p], c_i),

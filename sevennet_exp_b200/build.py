@@ -17,7 +17,7 @@ LIB = os.path.join(LIBDIR, 'libsevenn_b200.so')
 TORCH_LIB = os.path.join(LIBDIR, 'libsevenn_b200_torch.so')      # torch.ops.sevenn_b200.* (csrc/torch_op.cpp)
 MD_HOST = os.path.join(LIBDIR, 'sevenn_md_host')                  # torch-free C++ host on the C ABI (csrc/md_host.cpp)
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC']
-STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu', 'model.cu']
+STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu', 'model.cu', 'train.cu']
 
 
 def nvcc():

@@ -19,6 +19,7 @@ from .. import spec as sp
 from ..codegen import conv_codegen
 from ..engine import _Lin
 from . import functional as F
+from . import train_functional as T
 from ._backend import get_lib, kernels, ptr
 
 # data keys (sevenn/_keys.py:26-86)
@@ -41,6 +42,11 @@ def _irreps(x):
 def _perm(layout: ir.Layout, device):
     p = torch.as_tensor(layout.perm_to_e3nn(), device=device)
     return p, torch.argsort(p)
+
+
+def _train_mode(module) -> bool:
+    """Parameter gradients / double backward wanted: the module is in training mode and autograd is recording."""
+    return module.training and torch.is_grad_enabled()
 
 
 class _Weight(nn.Module):
@@ -70,11 +76,30 @@ class _LinearCore(nn.Module):
             self._cache = (key, lin)
         return self._cache[1]
 
+    def _dense_blocks(self):
+        """Dense per-block weights as differentiable torch ops on the flat e3nn parameter (training path): o3.Linear
+        blocks [K, N] / sqrt(fan_in); FullyConnectedTensorProduct(x, one_hot) blocks [S, K, N] (spec.nequip_sc_dense)."""
+        w, spec, S = getattr(self, self._owner).weight, self._spec, self._S
+        out = []
+        for b in spec.blocks:
+            if S:
+                rows = [w[o * S:o * S + m * S * b.N].reshape(m, S, b.N) for o, m in b.segs]
+                sign = 1.0 if ir.wigner_3j(b.l, 0, b.l)[0, 0, 0] > 0 else -1.0
+                c = abs(float(ir.wigner_3j(b.l, 0, b.l)[0, 0, 0])) * math.sqrt(2 * b.l + 1)
+                out.append((torch.cat(rows, 0).permute(1, 0, 2) * (sign * c / math.sqrt(b.K * S))).contiguous())
+            else:
+                rows = [w[o:o + m * b.N].reshape(m, b.N) for o, m in b.segs]
+                out.append((torch.cat(rows, 0) / math.sqrt(b.K + b.fan_extra)).contiguous())
+        return out
+
     def _apply_linear(self, x, types=None):
         dev = x.device
         p_in, inv_in = _perm(self._spec.lin, dev)
         p_out, _ = _perm(self._spec.lout, dev)
-        y = F.LinearFn.apply(x.float()[:, inv_in], self._lin(dev), types)
+        if _train_mode(self):
+            y = T.BlockMM.apply(T._c(x[:, inv_in]), self._spec, False, types, self._S, *self._dense_blocks())
+        else:
+            y = F.LinearFn.apply(x.float()[:, inv_in], self._lin(dev), types)
         return y[:, p_out]
 
 
@@ -128,7 +153,10 @@ class EdgeEmbedding(nn.Module):
         rvec = data[EDGE_VEC]
         b, c, s = self.basis_function, self.cutoff_function, self.spherical
         args = (s.lmax, bool(s.normalize), b.num_basis, c.kind, c.cutoff_length, c.p, c.r_on)
-        Y, emb = F.EdgeEmbedFn.apply(rvec, b.coeffs.to(rvec.device), args)
+        if _train_mode(self):
+            Y, emb = T.EdgeFn.apply(T._c(rvec), T._c(b.coeffs.to(rvec.device)), args)
+        else:
+            Y, emb = F.EdgeEmbedFn.apply(rvec, b.coeffs.to(rvec.device), args)
         data[EDGE_LEN] = torch.linalg.norm(rvec.detach(), dim=-1)
         data[EDGE_EMB], data[EDGE_ATTR] = emb, Y
         return data
@@ -303,7 +331,10 @@ class FCN_e3nn(nn.Module):
 
     def forward(self, data):
         x = data[self.key_input]
-        data[self.key_output] = F.RadialMLPFn.apply(x.float(), self._layer(x.device))
+        if _train_mode(self):
+            data[self.key_output] = _fcn_train(self.fcn, x, self._act, self._cst)
+        else:
+            data[self.key_output] = F.RadialMLPFn.apply(x.float(), self._layer(x.device))
         return data
 
 
@@ -401,11 +432,28 @@ class EquivariantGate(nn.Module):
         x = data[self.key_x]
         _, inv_in = _perm(self._gspec.lin, x.device)
         p_out, _ = _perm(self._gspec.lout, x.device)
-        data[self.key_x] = F.GateFn.apply(x[:, inv_in], self._gate)[:, p_out]
+        if _train_mode(self):
+            data[self.key_x] = T.GateFn.apply(T._c(x[:, inv_in]), self._gate)[:, p_out]
+        else:
+            data[self.key_x] = F.GateFn.apply(x[:, inv_in], self._gate)[:, p_out]
         return data
 
 
 # ---------------------------------------------------------- convolution --
+def _fcn_train(fcn, x, act, cst):
+    """e3nn FullyConnectedNet with parameter gradients and double backward: BlockMM + ActMul per layer."""
+    hs = fcn.hs
+    if not hasattr(fcn, '_specs'):
+        fcn._specs = [sp.make_linear('w', [(hs[k], (0, 1))], [(hs[k + 1], (0, 1))]) for k in range(len(hs) - 1)]
+    h = T._c(x)
+    for k in range(len(hs) - 1):
+        W = (getattr(fcn, f'layer{k}').weight / math.sqrt(hs[k])).contiguous()
+        h = T.BlockMM.apply(h, fcn._specs[k], False, None, 0, W)
+        if k < len(hs) - 2:
+            h = T.ActMul.apply(h, None, act, cst, 0)
+    return h
+
+
 class _FCN(nn.Module):
     """Parameter holder mirroring e3nn.nn.FullyConnectedNet: layer{k}.weight of shape [h_in, h_out]."""
 
@@ -479,12 +527,22 @@ class IrrepsConvolution(nn.Module):
         emb, Y = data[self.key_weight_input], data[self.key_filter]
         if perm is not None:
             emb, Y = emb[perm], Y[perm]
-        w = F.RadialMLPFn.apply(emb, self._layer(dev))
         _, inv_x = _perm(self._conv.lx, dev)
         p_mid, _ = _perm(self._conv.lmid, dev)
         meta = dict(sig=self._sig, dx=self._conv.lx.dim, dmid=self._conv.lmid.dim, wn=self._conv.wn,
                     units=conv_codegen.n_units(self._conv), inv_denom=1.0 / float(self.denominator.item()))
-        out = F.ConvFn.apply(x.float()[:, inv_x], Y, w, graph, meta)
+        if _train_mode(self):
+            # training: radial MLP and convolution through the second-order-capable Functions (train_functional.py);
+            # a trainable denominator divides outside the kernel so that it receives its gradient
+            w = _fcn_train(self.weight_nn, emb, self._act, self._cst)
+            if self.denominator.requires_grad:
+                meta['inv_denom'] = 1.0
+            out = T.ConvT.apply(T._c(x[:, inv_x]), T._c(Y), T._c(w), graph, meta)
+            if self.denominator.requires_grad:
+                out = out / self.denominator
+        else:
+            w = F.RadialMLPFn.apply(emb, self._layer(dev))
+            out = F.ConvFn.apply(x.float()[:, inv_x], Y, w, graph, meta)
         data[self.key_x] = out[:, p_mid]
         return data
 
@@ -649,9 +707,33 @@ class ForceStressOutputFromEdge(nn.Module):
     def get_grad_key(self):
         return EDGE_VEC
 
-    def forward(self, data):
+    def _forward_train(self, data):
+        """force_output.py:173-222 verbatim in torch ops: `create_graph=True` keeps dE/d(edge_vec) in the graph so that a
+        loss on forces / stress back-propagates through the reverse kernels (nn/train_functional.py)."""
+        tot = int(torch.sum(data[NATOMS]))
+        rij, ei = data[EDGE_VEC], data[EDGE_IDX]
+        fij = torch.autograd.grad([data[E_TOT].sum()], [rij], create_graph=True, allow_unused=True)[0]
+        for k in [k for k in data if isinstance(k, str) and k.startswith(GRAPH)]:
+            del data[k]
+        if fij is None:
+            return data
+        pf = torch.zeros(tot, 3, dtype=fij.dtype, device=fij.device).index_add(0, ei[0], fij)
+        nf = torch.zeros(tot, 3, dtype=fij.dtype, device=fij.device).index_add(0, ei[1], fij)
+        data[FORCE] = pf - nf
+        vir = torch.cat([rij * fij, (rij[:, 0] * fij[:, 1]).unsqueeze(-1), (rij[:, 1] * fij[:, 2]).unsqueeze(-1),
+                         (rij[:, 2] * fij[:, 0]).unsqueeze(-1)], dim=-1)
+        s = torch.zeros(tot, 6, dtype=fij.dtype, device=fij.device).index_add(0, ei[1], vir)
         if self._is_batch_data:
-            raise NotImplementedError('batched graphs are SURVEY 8f-1 (training path)')
+            b = data[BATCH]
+            sout = torch.zeros(int(b.max()) + 1, 6, dtype=fij.dtype, device=fij.device).index_add(0, b, s)
+        else:
+            sout = s.sum(dim=0)
+        data[STRESS] = torch.neg(sout) / data[VOL].to(fij.dtype).unsqueeze(-1)
+        return data
+
+    def forward(self, data):
+        if _train_mode(self):
+            return self._forward_train(data)
         tot = int(torch.sum(data[NATOMS]))
         rij = data[EDGE_VEC]
         fij = torch.autograd.grad([data[E_TOT].sum()], [rij], allow_unused=True)[0]
@@ -675,7 +757,12 @@ class ForceStressOutputFromEdge(nn.Module):
         k.n_launch += 1
         data[FORCE] = Fo
         vol = data[VOL]
-        data[STRESS] = (torch.neg(vir.double().sum(dim=0)) / vol.double().reshape(-1)[0]).to(f.dtype)
+        if self._is_batch_data:               # per-graph stress, force_output.py:210-219
+            b = data[BATCH]
+            sout = torch.zeros(int(b.max()) + 1, 6, dtype=torch.float64, device=dev).index_add_(0, b, vir.double())
+            data[STRESS] = (torch.neg(sout) / vol.double().reshape(-1, 1)).to(f.dtype)
+        else:
+            data[STRESS] = (torch.neg(vir.double().sum(dim=0)) / vol.double().reshape(-1)[0]).to(f.dtype)
         return data
 
 

@@ -40,7 +40,7 @@ def build_full_emu(conv_specs):
     """All static units + the given conv signatures, emulation flavour, as a sevennet_exp_b200._lib.Lib."""
     from sevennet_exp_b200 import _lib
     from sevennet_exp_b200.codegen import conv_codegen
-    units = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu']
+    units = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu', 'train.cu']
     text = ''
     for u in units:
         text += f'// ---- {u}\n' + open(os.path.join(CSRC, u)).read() + '\n'
