@@ -313,6 +313,141 @@ def gemm_roofline(spec, stage, n_atoms, peak_hbm):
                        'ncu_tensor_pipe_pct': cap.get('tensor_pipe_pct') if cap else None}}
 
 
+def cfg5_structures(n_struct=32, seed=5):
+    """BASELINE config 5: 32 MPtrj-shaped structures, 64-256 atoms each, random species out of the model's 89,
+    density 0.03-0.08 atoms/A^3 (jittered simple-cubic sites: no overlapping atoms), labels E, F, S ~ N(0, 1)."""
+    rng = np.random.default_rng(seed)
+    zs = np.array(sorted(presets.PRESETS['7net-0']['_type_map']))
+    out = []
+    for _ in range(n_struct):
+        n = int(rng.integers(64, 257))
+        rho = rng.uniform(0.03, 0.08)
+        side = int(np.ceil(n ** (1 / 3)))
+        a = (1.0 / rho) ** (1 / 3) * (n / side ** 3) ** (1 / 3)
+        sites = np.stack(np.meshgrid(*[np.arange(side)] * 3, indexing='ij'), -1).reshape(-1, 3)
+        sites = sites[rng.permutation(len(sites))[:n]].astype(np.float64)
+        pos = sites * a + rng.uniform(-0.12 * a, 0.12 * a, (n, 3))
+        cell = np.eye(3) * side * a
+        numbers = rng.choice(zs, n)
+        out.append((numbers, pos, cell, rng.normal(), rng.normal(size=(n, 3)), rng.normal(size=6) * 1e-2))
+    return out
+
+
+def run_train(args):
+    """--workload cfg5: one training step (forward, force/stress loss, backward through the reverse kernels, Adam) on a
+    batch of 32 structures; graphs are built beforehand, as the reference's dataset does (train/dataload.py)."""
+    from sevennet_exp_b200 import nn as bnn, train as TR
+    from sevennet_exp_b200.neighbor import NeighborList
+    dev = torch.device('cuda:0')
+    torch.cuda.set_device(dev)
+    cfg = model_config()
+    model = bnn.build_E3_equivariant_model(cfg)
+    sd = random_state_dict(cfg)
+    missing, _ = model.load_state_dict(sd, strict=False)
+    assert not missing, missing
+    model = model.to(dev)
+    structs = cfg5_structures()
+    nl = NeighborList(device=dev)
+    tmap = cfg['_type_map']
+    graphs = []
+    for numbers, pos, cell, e, f, st in structs:
+        r = nl.build(pos, cell, [True] * 3, cfg['cutoff'])
+        graphs.append({TR.K_X: torch.tensor([tmap[int(z)] for z in numbers]), TR.K_Z: torch.tensor(numbers),
+                       TR.K_POS: torch.tensor(pos, dtype=torch.float32),
+                       TR.K_EI: torch.stack([r['center'], r['col']]).long().cpu(), TR.K_EV: r['edge_vec'].cpu(),
+                       TR.K_VOL: torch.tensor(r['volume'], dtype=torch.float32), TR.K_NATOMS: torch.tensor(len(numbers)),
+                       TR.K_E: torch.tensor(e, dtype=torch.float32), TR.K_F: torch.tensor(f, dtype=torch.float32),
+                       TR.K_S: torch.tensor(st, dtype=torch.float32)})
+    for g in graphs:
+        g[TR.K_X] = g[TR.K_Z]            # the model maps atomic numbers to type indices itself (sequential.py:156-168)
+    config = {'force_loss_weight': 1.0, 'stress_loss_weight': 0.1, 'is_train_stress': True, 'optim_param': {}}
+    trainer = TR.Trainer(model, config)
+    host = {k: v.pin_memory() for k, v in TR.collate(graphs, device='cpu').items()}
+    batch = {k: v.to(dev) for k, v in host.items()}
+    n_atoms, n_edges = int(batch[TR.K_NATOMS].sum()), int(batch[TR.K_EI].shape[1])
+    from sevennet_exp_b200.nn._backend import kernels
+    kern = kernels(dev)
+    flush = torch.empty(256 * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+    for _ in range(args.warmup):
+        loss0 = trainer.train_step(batch)
+    torch.cuda.synchronize()
+    sampler = ClockSampler()
+    sampler.start()
+    l0, evs = kern.n_launch, []
+    for _ in range(args.steps):
+        flush.fill_(1.0)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        loss = trainer.train_step(batch)
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ms_step = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+    launches = kern.n_launch - l0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.fill_(1.0)
+        batch_e = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        loss = trainer.train_step(batch_e)          # returns the loss as a host float (device -> host read)
+    torch.cuda.synchronize()
+    e2e_t = (time.perf_counter() - t0) / args.steps
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+    h2d = int(sum(v.numel() * v.element_size() for v in host.values()))
+    cpu = None
+    if not os.environ.get('SEVENN_BENCH_NO_CPU'):
+        cpu = cpu_train_leg(cfg, graphs[:2], config, 3, 1)
+    peak, how = measured_peak()
+    line = {
+        'metric': 'atom-steps/s (training step: forward + force/stress loss backward + Adam) SevenNet-0',
+        'value': n_atoms / (ms_step * 1e-3), 'unit': UNIT, 'n_gpus': 1, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': ms_step, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32',
+        'data': 'synthetic',
+        'config': {'workload': f'SevenNet-0 training step, batch of {len(graphs)} synthetic MPtrj-shaped structures '
+                               f'(64-256 atoms, 89 species, 0.03-0.08 atoms/A^3): {n_atoms} atoms, {n_edges} edges '
+                               '(BASELINE config 5)', 'n_atoms': n_atoms, 'n_edges': n_edges, 'global_batch': len(graphs),
+                   'step': 'forward + autograd.grad(E, edge_vec, create_graph=True) + MSE(E/N, F, S) backward + Adam; '
+                           'graphs prebuilt (dataset), as in the reference',
+                   'final_loss': loss, 'first_loss': loss0,
+                   'l2': '256 MiB write between timed steps (outside the CUDA-event brackets)'},
+        'e2e': {'value': n_atoms / e2e_t, 'unit': UNIT, 'ms_per_step': e2e_t * 1e3, 'h2d_bytes_per_step': h2d,
+                'd2h_bytes_per_step': 4},
+        'gpu_launches': int(launches), 'clocks': sampler.summary(),
+        'roofline': {'bound': 'hbm', 'kernel': 'whole step (second order composed from ~6 first-order conv launches per layer)',
+                     'achieved': None, 'peak': peak, 'peak_source': how, 'unit': 'GB/s', 'frac': None, 'traffic': None,
+                     'note': 'no per-kernel roofline for the training step yet: launch-bound at this batch size'},
+        'cpu_baseline': cpu,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def cpu_train_leg(cfg, graphs, config, steps, warmup):
+    """The oracle (CPU restatement) doing the same training step under torch autograd on a bounded sample."""
+    from oracle import sevenn_ref as S
+    from sevennet_exp_b200 import train as TR
+    torch.manual_seed(777)
+    om = S.build_model(cfg).train()
+    om.set_is_batch_data(True)
+    opt = torch.optim.Adam([p for p in om.parameters() if p.requires_grad])
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ts = []
+    n = int(sum(int(g[TR.K_NATOMS]) for g in graphs))
+    for k in range(warmup + steps):
+        t0 = time.perf_counter()
+        opt.zero_grad()
+        out = om(TR.collate(graphs, device='cpu'))
+        loss = TR.loss_from_config(out, config)
+        loss.backward()
+        opt.step()
+        if k >= warmup:
+            ts.append(time.perf_counter() - t0)
+    t = float(np.median(ts))
+    return {'value': n / t, 'unit': UNIT, 'cores': cores, 'kind': 'port',
+            'sample': f'oracle/ training step (autograd double backward + torch Adam) on {len(graphs)} of the structures '
+                      f'({n} atoms), {warmup} warm-up + {steps} timed, median {t:.2f} s'}
+
+
 def run_single(args):
     from sevennet_exp_b200.sevennet_calculator import SevenNetCalculator
     dev = torch.device('cuda:0')
@@ -468,15 +603,17 @@ def main():
     ap.add_argument('--steps', type=int, default=10)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='ours')
-    ap.add_argument('--workload', default='si1m', choices=['si1m', 'cfg1', 'cfg2', 'cfg3'],
+    ap.add_argument('--workload', default='si1m', choices=['si1m', 'cfg1', 'cfg2', 'cfg3', 'cfg5'],
                     help="'si1m' (default, every N: BASELINE config 4, one 1M-atom bulk-Si cell, strong scaling); "
                          "'cfg1' (64-atom Si); 'cfg2' (4,096-atom HfO2; N > 1: weak scaling over the brick grid); "
-                         "'cfg3' (N = 1: SevenNet-l3i5 on 32,768 Li-P-S atoms)")
+                         "'cfg3' (N = 1: SevenNet-l3i5 on 32,768 Li-P-S atoms); 'cfg5' (N = 1: training step on 32 structures)")
     ap.add_argument('--si-cells', type=int, default=50)
     args = ap.parse_args()
     if args.impl == 'reference':
         return run_reference(args)
     args.warmup = max(args.warmup, 3)
+    if args.workload == 'cfg5':
+        return run_train(args)
     if args.gpus > 1 or int(os.environ.get('WORLD_SIZE', '1')) > 1:
         from sevennet_exp_b200 import bench_multi
         return bench_multi.run(args)

@@ -228,46 +228,73 @@ extern "C" int sevenn_edge_train(const float* edge_vec, long long n_edges, int l
 // sevenn_gemm_args).  types != nullptr keeps only the nodes of species `type_sel` (species-indexed linears).
 // Two stages, fixed order: split s sums its rows into part[s][K][N], then the splits are added in order.
 #ifndef SEVENN_EMU
-#define TN_T 32
+#define TN_T 64          // output tile (K x N) per CTA
+#define TN_R 16          // rows staged per iteration
 __global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ A, long long sAn, int sAm,
                                                       const float* __restrict__ B, long long sBn, int sBm, long long M,
                                                       int R, int K, int N, const int* __restrict__ types, int type_sel,
                                                       int n_split, float* __restrict__ part) {
-  __shared__ float As[TN_T][TN_T + 1];
-  __shared__ float Bs[TN_T][TN_T + 1];
+  __shared__ float As[TN_R][TN_T + 4];
+  __shared__ float Bs[TN_R][TN_T + 4];
   const int k0 = blockIdx.x * TN_T, n0 = blockIdx.y * TN_T, sp = blockIdx.z;
   const int tid = threadIdx.x, ty = tid / 16, tx = tid % 16;
   const long long per = (M + n_split - 1) / n_split;
   const long long r_begin = sp * per, r_end = (r_begin + per < M) ? r_begin + per : M;
-  float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-  for (long long r0 = r_begin; r0 < r_end; r0 += TN_T) {
-    for (int idx = tid; idx < TN_T * TN_T; idx += 256) {
-      const int rr = idx / TN_T, cc = idx % TN_T;
-      const long long r = r0 + rr;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  // loader: 4 elements of A and 4 of B per thread and iteration; consecutive threads read consecutive columns
+  const int lr = tid / 64, lc = tid % 64;          // rows lr, lr + 4, lr + 8, lr + 12; column lc
+  // (node, m) of this thread's four rows, advanced incrementally (a 64-bit division per element would cost more
+  // instructions than the 64 FMAs it feeds)
+  long long node_q[4]; int m_q[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) { const long long r = r_begin + lr + 4 * q; node_q[q] = r / R; m_q[q] = (int)(r - node_q[q] * R); }
+  const int step_n = TN_R / R, step_m = TN_R % R;
+  float ra[4], rb[4];
+  auto fetch = [&](long long r0) {            // next slab into registers while the current one is multiplied
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const long long r = r0 + lr + 4 * q;
       float a = 0.f, b = 0.f;
       if (r < r_end) {
-        const long long node = r / R;
-        const int m = (int)(r % R);
+        const long long node = node_q[q];
+        const int m = m_q[q];
         if (types == nullptr || types[node] == type_sel) {
-          if (k0 + cc < K) a = A[node * sAn + (long long)m * sAm + k0 + cc];
-          if (n0 + cc < N) b = B[node * sBn + (long long)m * sBm + n0 + cc];
+          if (k0 + lc < K) a = __ldg(A + node * sAn + (long long)m * sAm + k0 + lc);
+          if (n0 + lc < N) b = __ldg(B + node * sBn + (long long)m * sBm + n0 + lc);
         }
       }
-      As[rr][cc] = a;
-      Bs[rr][cc] = b;
+      ra[q] = a; rb[q] = b;
+      node_q[q] += step_n; m_q[q] += step_m;
+      if (m_q[q] >= R) { m_q[q] -= R; ++node_q[q]; }
     }
+  };
+  fetch(r_begin);
+  for (long long r0 = r_begin; r0 < r_end; r0 += TN_R) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) { As[lr + 4 * q][lc] = ra[q]; Bs[lr + 4 * q][lc] = rb[q]; }
     __syncthreads();
-#pragma unroll 8
-    for (int rr = 0; rr < TN_T; ++rr) {
-      const float a0 = As[rr][ty * 2], a1 = As[rr][ty * 2 + 1], b0 = Bs[rr][tx * 2], b1 = Bs[rr][tx * 2 + 1];
-      acc[0][0] = fmaf(a0, b0, acc[0][0]); acc[0][1] = fmaf(a0, b1, acc[0][1]);
-      acc[1][0] = fmaf(a1, b0, acc[1][0]); acc[1][1] = fmaf(a1, b1, acc[1][1]);
+    if (r0 + TN_R < r_end) fetch(r0 + TN_R);
+#pragma unroll
+    for (int rr = 0; rr < TN_R; ++rr) {
+      float a[4], b[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { a[q] = As[rr][ty * 4 + q]; b[q] = Bs[rr][tx * 4 + q]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
     __syncthreads();
   }
-  for (int i = 0; i < 2; ++i)
-    for (int j = 0; j < 2; ++j) {
-      const int k = k0 + ty * 2 + i, nn = n0 + tx * 2 + j;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + ty * 4 + i, nn = n0 + tx * 4 + j;
       if (k < K && nn < N) part[((size_t)sp * K + k) * N + nn] = acc[i][j];
     }
 }
@@ -281,8 +308,8 @@ __global__ void gemm_tn_reduce_kernel(const float* __restrict__ part, int n_spli
 }
 #endif
 extern "C" int sevenn_gemm_tn_splits(long long M) {
-  long long s = (M + 511) / 512;
-  return (int)(s < 1 ? 1 : (s > 128 ? 128 : s));
+  long long s = (M + 255) / 256;
+  return (int)(s < 1 ? 1 : (s > 256 ? 256 : s));
 }
 extern "C" int sevenn_gemm_tn(const float* A, long long sAn, int sAm, const float* B, long long sBn, int sBm, long long M,
                               int R, int K, int N, const int* types, int type_sel, float scale, int accumulate,

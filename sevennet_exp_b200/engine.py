@@ -158,7 +158,10 @@ class Kernels:
                           M, R, N, K, epi, act, cst,
                           (C2.data_ptr() + 4 * c_off) if C2 is not None else None,
                           (P.data_ptr() + 4 * c_off) if P is not None else None)
-        tc = (self.gemm_mode != 'simt' and M >= self.tc_min_rows and (epi < 2 or act == 0) and K % 4 == 0
+        # weights that change every step (training) stay on the SIMT arm: their pre-swizzled tcgen05 image is built on
+        # the host
+        tc = (self.gemm_mode != 'simt' and not getattr(B, '_sevenn_dynamic', False) and M >= self.tc_min_rows
+              and (epi < 2 or act == 0) and K % 4 == 0
               and sAn % 4 == 0 and sAm % 4 == 0 and (A.data_ptr() + 4 * a_off) % 16 == 0)
         return g, tc
 

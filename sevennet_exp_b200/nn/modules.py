@@ -39,9 +39,36 @@ def _irreps(x):
     return ir.parse_irreps(x if isinstance(x, (str, list, tuple)) else str(x))
 
 
+_PERM_CACHE = {}
+
+
 def _perm(layout: ir.Layout, device):
-    p = torch.as_tensor(layout.perm_to_e3nn(), device=device)
-    return p, torch.argsort(p)
+    key = (id(layout), str(device))
+    hit = _PERM_CACHE.get(key)
+    if hit is None or hit[0] is not layout:
+        p = torch.as_tensor(layout.perm_to_e3nn(), device=device)
+        hit = _PERM_CACHE[key] = (layout, p, torch.argsort(p))
+    return hit[1], hit[2]
+
+
+class _PermCols(torch.autograd.Function):
+    """x[:, p] for a PERMUTATION p of the columns (e3nn <-> device irreps layout).  torch's own backward of an index is a
+    sort-based index_put (0.7 ms per call, half the GPU time of a training step); for a permutation it is simply the
+    inverse gather, and the Function is its own derivative family (second order for the training path)."""
+
+    @staticmethod
+    def forward(ctx, x, p, inv):
+        ctx.p, ctx.inv = p, inv
+        return x.index_select(1, p)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _PermCols.apply(g, ctx.inv, ctx.p), None, None
+
+
+def _pcols(x, layout, device, to_e3nn: bool):
+    p, inv = _perm(layout, device)
+    return _PermCols.apply(x, p, inv) if to_e3nn else _PermCols.apply(x, inv, p)
 
 
 def _train_mode(module) -> bool:
@@ -94,13 +121,12 @@ class _LinearCore(nn.Module):
 
     def _apply_linear(self, x, types=None):
         dev = x.device
-        p_in, inv_in = _perm(self._spec.lin, dev)
-        p_out, _ = _perm(self._spec.lout, dev)
+        xin = _pcols(x.float(), self._spec.lin, dev, False)
         if _train_mode(self):
-            y = T.BlockMM.apply(T._c(x[:, inv_in]), self._spec, False, types, self._S, *self._dense_blocks())
+            y = T.BlockMM.apply(T._c(xin), self._spec, False, types, self._S, *self._dense_blocks())
         else:
-            y = F.LinearFn.apply(x.float()[:, inv_in], self._lin(dev), types)
-        return y[:, p_out]
+            y = F.LinearFn.apply(xin, self._lin(dev), types)
+        return _pcols(y, self._spec.lout, dev, True)
 
 
 # ------------------------------------------------------------------ edge --
@@ -430,12 +456,12 @@ class EquivariantGate(nn.Module):
 
     def forward(self, data):
         x = data[self.key_x]
-        _, inv_in = _perm(self._gspec.lin, x.device)
-        p_out, _ = _perm(self._gspec.lout, x.device)
+        xin = _pcols(x, self._gspec.lin, x.device, False)
         if _train_mode(self):
-            data[self.key_x] = T.GateFn.apply(T._c(x[:, inv_in]), self._gate)[:, p_out]
+            out = T.GateFn.apply(T._c(xin), self._gate)
         else:
-            data[self.key_x] = F.GateFn.apply(x[:, inv_in], self._gate)[:, p_out]
+            out = F.GateFn.apply(xin, self._gate)
+        data[self.key_x] = _pcols(out, self._gspec.lout, x.device, True)
         return data
 
 
@@ -527,8 +553,7 @@ class IrrepsConvolution(nn.Module):
         emb, Y = data[self.key_weight_input], data[self.key_filter]
         if perm is not None:
             emb, Y = emb[perm], Y[perm]
-        _, inv_x = _perm(self._conv.lx, dev)
-        p_mid, _ = _perm(self._conv.lmid, dev)
+        xin = _pcols(x.float(), self._conv.lx, dev, False)
         meta = dict(sig=self._sig, dx=self._conv.lx.dim, dmid=self._conv.lmid.dim, wn=self._conv.wn,
                     units=conv_codegen.n_units(self._conv), inv_denom=1.0 / float(self.denominator.item()))
         if _train_mode(self):
@@ -537,13 +562,13 @@ class IrrepsConvolution(nn.Module):
             w = _fcn_train(self.weight_nn, emb, self._act, self._cst)
             if self.denominator.requires_grad:
                 meta['inv_denom'] = 1.0
-            out = T.ConvT.apply(T._c(x[:, inv_x]), T._c(Y), T._c(w), graph, meta)
+            out = T.ConvT.apply(T._c(xin), T._c(Y), T._c(w), graph, meta)
             if self.denominator.requires_grad:
                 out = out / self.denominator
         else:
             w = F.RadialMLPFn.apply(emb, self._layer(dev))
-            out = F.ConvFn.apply(x.float()[:, inv_x], Y, w, graph, meta)
-        data[self.key_x] = out[:, p_mid]
+            out = F.ConvFn.apply(xin, Y, w, graph, meta)
+        data[self.key_x] = _pcols(out, self._conv.lmid, dev, True)
         return data
 
 

@@ -41,6 +41,8 @@ class _DenseLin:
         self.spec, self.by_type = spec, by_type_S
         self.W = [_c(w.detach()) for w in Ws]
         self.WT = [_c(w.detach().transpose(-1, -2)) for w in Ws]
+        for t in self.W + self.WT:
+            t._sevenn_dynamic = True          # no host-built tcgen05 image for per-step weights (engine._gemm_args)
         self.const, self.has_const = [None] * len(Ws), False
         cover = [0] * len(spec.lin.groups)
         for b in spec.blocks:
