@@ -12,7 +12,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 GEN = os.path.join(CSRC, 'generated')
-LIBDIR = os.path.join(HERE, '_lib')
+LIBDIR = os.path.join(HERE, '_build')
 LIB = os.path.join(LIBDIR, 'libsevenn_b200.so')
 TORCH_LIB = os.path.join(LIBDIR, 'libsevenn_b200_torch.so')      # torch.ops.sevenn_b200.* (csrc/torch_op.cpp)
 MD_HOST = os.path.join(LIBDIR, 'sevenn_md_host')                  # torch-free C++ host on the C ABI (csrc/md_host.cpp)

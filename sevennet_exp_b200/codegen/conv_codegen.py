@@ -77,6 +77,9 @@ TAB_CPW = int(_os0.environ.get('SEVENN_TAB_CPW', '2'))
 # packed fp32 (fma.rn.f32x2) for the per-channel arithmetic of two-chunk units: the chunk pair (a, b) of a lane is one
 # float2; warp-uniform M entries and literals are free broadcast / immediate operands of FFMA2
 TAB_F2 = _os0.environ.get('SEVENN_TAB_F2', '0') == '1'
+# table rows as monomial coefficients (c0, c1, c2, c3) of t instead of Hermite nodes (radial_table.build_table layout='poly')
+# A/B on B200 (tools/gpu_ab2.sh, r02): cfg2 3.84 -> 3.75 ms, 216 k-atom Si 106.1 -> 103.9 ms, cfg3 32.6 -> 32.1 ms per step
+TAB_POLY = _os0.environ.get('SEVENN_TAB_POLY', '1') == '1' and not TAB_F2
 
 
 def make_groups(spec: ConvSpec, tab: bool = False) -> List[_Group]:
@@ -472,6 +475,10 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
 # Per edge the kernels read Yt[e] = (Y_0 .. Y_{S-1}, t, bits(i)) (edge.cu: sevenn_edge_fwd_tab).  The backward
 # contracts dE/dw with dw/dr in registers and emits one scalar per (unit, edge) next to dY -- no dW array, no
 # reverse radial MLP.
+# edge-loop unroll of the tabulated kernels by signature: helps SevenNet-l3i5's inner layers (cfg3 32.1 -> 31.6 ms per
+# step), hurts SevenNet-0's (cfg2 3.75 -> 4.10 ms: the doubled loop body falls out of the instruction cache)
+TAB_UNROLL_BY_SIG = {'c703e622066': 2}
+_TAB_UNROLL_ENV = _os0.environ.get('SEVENN_TAB_UNROLL')
 TAB_XY_DEPTH = 4     # ring slots for x_j / Y (3 edges in flight)
 TAB_W_DEPTH = 2      # ring slots for the table rows (1 edge in flight: they come from L2)
 
@@ -620,6 +627,11 @@ def _tab_pipeline_regs(L, G: _Group, spec: ConvSpec, idx_of, xyf):
     L.append(f'      int jn = col[e0 + {DX - 1} < e1 ? e0 + {DX - 1} : e1 - 1];')
     L.append(f'      int in = {idx_of("(e0 + 1 < e1 ? e0 + 1 : e1 - 1)")};')
     L.append('      int slot = 0;')
+    TAB_UNROLL = int(_TAB_UNROLL_ENV) if _TAB_UNROLL_ENV else TAB_UNROLL_BY_SIG.get(_cur_sig[0], 1)
+    if TAB_UNROLL > 1:
+        # two edges per trip: ptxas renames the (T, Tn) register sets between the copies instead of moving 24 registers
+        # per edge (18 of the 139 instructions of the scalar-group forward loop were MOVs)
+        L.append(f'#pragma unroll {TAB_UNROLL}')
     L.append('      for (int e = e0; e < e1; ++e) {')
     for pi, p in G.paths:
         for c in range(G.cpw):
@@ -681,6 +693,18 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
     L.append(f'        const float t = sr[{ybase + S}];')
     L.append('#endif')
     # cubic Hermite basis (and its derivative) at t
+    if TAB_POLY:
+        for pi, p in G.paths:
+            for c in range(G.cpw):
+                T = f'T{pi}{_sx(G, c)}'
+                L.append(f'        const float w{pi}{_sx(G, c)} = fmaf(fmaf(fmaf({T}.w, t, {T}.z), t, {T}.y), t, {T}.x);')
+        if bwd:
+            L.append('        const float t2 = t + t, t3 = 3.f * t * t;')
+            for pi, p in G.paths:
+                for c in range(G.cpw):
+                    T = f'T{pi}{_sx(G, c)}'
+                    L.append(f'        const float wd{pi}{_sx(G, c)} = fmaf(t3, {T}.w, fmaf(t2, {T}.z, {T}.y));')
+        return
     L.append('        const float u = 1.f - t, tt = t * t, uu = u * u;')
     L.append('        const float h00 = (1.f + 2.f * t) * uu, h10 = t * uu, h01 = tt * (3.f - 2.f * t), h11 = -tt * u;')
     f2 = TAB_F2 and G.cpw == 2
@@ -780,7 +804,7 @@ def generate(spec: ConvSpec) -> str:
     out.append(f'extern "C" int sevenn_conv_info_{sig}(int* x_dim, int* mid_dim, int* wn, int* sh_dim, int* units) {{')
     out.append(f'  *x_dim = {spec.lx.dim}; *mid_dim = {spec.lmid.dim}; *wn = {spec.wn}; *sh_dim = {(spec.lmax_sh + 1) ** 2};')
     out.append(f'  *units = {nu}; return 0; }}')
-    packed = int(TAB_F2 and any(G.cpw == 2 for G in groups_tab))
+    packed = 2 if TAB_POLY else int(TAB_F2 and any(G.cpw == 2 for G in groups_tab))     # table layout the kernels read
     out.append(f'// 1: the tabulated kernels of this unit read the packed channel-pair table layout (conv_codegen.pack_table)')
     out.append(f'extern "C" int sevenn_conv_tab_packed_{sig}() {{ return {packed}; }}')
     return '\n'.join(out) + '\n'

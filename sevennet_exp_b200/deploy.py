@@ -64,7 +64,7 @@ def _plain_sd(sd):
     return {k: (v.detach().cpu().clone() if torch.is_tensor(v) else torch.as_tensor(v)) for k, v in sd.items()}
 
 
-TORCH_OP_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_lib', 'libsevenn_b200_torch.so')
+TORCH_OP_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_build', 'libsevenn_b200_torch.so')
 _op_loaded = False
 
 

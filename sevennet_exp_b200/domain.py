@@ -267,12 +267,10 @@ def evaluate_decomposed(calc, dec: Decomposition, halo: Halo, types_dev=None, po
         types_dev = torch.from_numpy(calc._lut[dec.numbers].astype(np.int32)).to(dev)
     # owned + ghost atoms as an open (non-periodic) point set: rows are needed for owned atoms only,
     # and those come first, so the CSR is simply truncated
-    r = calc.nl.build(dec.pos, np.eye(3), [False] * 3, calc.cutoff, pos_dev=pos_dev)
+    # rows for the owned atoms only (they come first); ghosts are neighbours, never centres
     nl = dec.n_local
-    n_e = int(r['rowptr'][nl].item())
-    from .neighbor import csc_build
-    cptr, cedge = csc_build(calc.nl.lib, r['col'][:n_e], len(dec.numbers), dev, calc.nl._stream())
-    g = Graph(types_dev, r['edge_vec'][:n_e], r['rowptr'][:nl + 1], r['col'][:n_e], cptr, cedge, nl, dec.volume)
+    r = calc.nl.build(dec.pos, np.eye(3), [False] * 3, calc.cutoff, pos_dev=pos_dev, n_rows=nl)
+    g = Graph(types_dev, r['edge_vec'], r['rowptr'], r['col'], r['cptr'], r['cedge'], nl, dec.volume)
     out = calc.engine.evaluate(g, halo=halo)
     F = halo.fold_forces(out['forces'])
     tot = torch.cat([out['energy'].reshape(1), out['virial6']])

@@ -386,11 +386,13 @@ class Engine(Kernels):
                     t_first = False
                 rc_t = spec.multi_cutoff[L.t] if spec.multi_cutoff else spec.cutoff
                 r_on_t = (rc_t - 1.0) if (spec.multi_cutoff and xplor) else spec.cutoff_on   # edge_embedding.py:244-246
+                packed = getattr(self.lib.cdll, f'sevenn_conv_tab_packed_{lay["sig"]}', None)
+                layout = packed() if packed is not None else 0       # the library says which layout its kernels read
                 tab_np = radial_table.build_table(
                     sd[spec.coeff_key(L.t)], spec.cutoff_fn, rc_t, spec.cutoff_p, r_on_t, Wm, spec.act_radial,
-                    ir.normalize2mom_const(spec.act_radial), self.tab_n, grid_rc=spec.cutoff)
-                packed = getattr(self.lib.cdll, f'sevenn_conv_tab_packed_{lay["sig"]}', None)
-                if packed is not None and packed():          # the library says which layout its kernels read
+                    ir.normalize2mom_const(spec.act_radial), self.tab_n, grid_rc=spec.cutoff,
+                    layout='poly' if layout == 2 else 'hermite')
+                if layout == 1:
                     tab_np = conv_codegen.pack_table(L.conv, tab_np)
                 lay['tab'] = f32(tab_np)
             if not self.lib.has_conv(lay['sig']):
@@ -539,7 +541,8 @@ class Engine(Kernels):
             # self interaction 1 -> convolution input for all nodes
             h = self._empty(nn, dx_in) if lay['si1'].fwd_full else self._zeros(nn, dx_in)
             self._linear_fwd(lay['si1'], x, n_x, h)
-            if n_x < nn:
+            if halo is not None and t > 0 and (n_x < nn or getattr(halo, 'world', 1) > 1):
+                # collective: every rank enters it, also one whose brick has no ghosts (vacuum side of a slab)
                 halo.forward(t, h)    # fills rows [n_local, n_nodes)
             self._mark('mlp_fwd')
             if table:
@@ -669,7 +672,7 @@ class Engine(Kernels):
             lib.call('sevenn_segment_gather_sum', _p(dxe), dx_in, _p(g.cptr), _p(g.cedge), nn, _p(dh), 0, st)
             self.n_launch += 1
             del dxe
-            if nl < nn:
+            if halo is not None and (nl < nn or getattr(halo, 'world', 1) > 1):
                 halo.backward(t, dh)  # ghost rows -> owners (added into rows [0, n_local))
             self._mark('si1_sc_bwd')
             dxn = self._zeros(nl, dx_in) if lay['si1'].bwd_needs_zero else self._empty(nl, dx_in)

@@ -62,8 +62,9 @@ class NeighborList:
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream) if self.dev.type == 'cuda' else None
 
-    def build(self, pos, cell, pbc, cutoff, pos_dev=None):
-        """pos: host float64 [n,3] (pos_dev: the same on the device, optional).
+    def build(self, pos, cell, pbc, cutoff, pos_dev=None, n_rows=None):
+        """pos: host float64 [n,3] (pos_dev: the same on the device, optional).  n_rows < n: rows (centres) for the first
+        n_rows atoms only -- the owned atoms of a sub-domain; the others (ghosts) are neighbours only.
         Returns dict(rowptr, center, col, shift, edge_vec, cptr, cedge, n_edges, volume)."""
         lib, dev, st = self.lib, self.dev, self._stream()
         if pos is None:           # positions live on the device only (fully periodic cells need no host pass)
@@ -75,12 +76,13 @@ class NeighborList:
             n = len(pos)
             cell_eff, dpar, ipar = nl_params(pos, cell, pbc, cutoff, max_bins=max(8 * n, 64))
         nbins = int(ipar[3] * ipar[4] * ipar[5])
+        nr = n if n_rows is None else int(n_rows)
         if pos_dev is None:
             pos_dev = torch.from_numpy(pos).to(dev, non_blocking=True)
         pw = torch.empty(n, 3, dtype=torch.float64, device=dev)
         # every per-atom / per-bin int32 array out of ONE zero-filled workspace (one fill launch instead of ten)
         n_tmp = int(lib.cdll.sevenn_scan_tmp_ints(max(nbins, n) + 1)) + 1
-        sizes = [3 * n, n, nbins + 1, nbins + 1, nbins, n, n_tmp, n + 1, n + 1]
+        sizes = [3 * n, n, nbins + 1, nbins + 1, nbins, n, n_tmp, nr + 1, nr + 1]
         offs = np.concatenate([[0], np.cumsum([(s_ + 3) // 4 * 4 for s_ in sizes])])
         ws = torch.zeros(int(offs[-1]), dtype=torch.int32, device=dev)
         wrap, atom_bin, bin_count, bin_start, bin_fill, bin_atoms, tmp, count, rowptr = (
@@ -90,15 +92,15 @@ class NeighborList:
         lib.call('sevenn_nl_bin', _p(pos_dev), n, dp, ip, _p(pw), _p(wrap), _p(atom_bin), _p(bin_count), st)
         lib.call('sevenn_scan_i32', _p(bin_count), _p(bin_start), nbins, _p(tmp), st)
         lib.call('sevenn_nl_scatter', _p(atom_bin), n, _p(bin_start), _p(bin_fill), _p(bin_atoms), st)
-        lib.call('sevenn_nl_count', _p(pw), _p(wrap), _p(atom_bin), _p(bin_start), _p(bin_atoms), n, dp, ip,
+        lib.call('sevenn_nl_count', _p(pw), _p(wrap), _p(atom_bin), _p(bin_start), _p(bin_atoms), nr, dp, ip,
                  _p(count), st)
-        lib.call('sevenn_scan_i32', _p(count), _p(rowptr), n, _p(tmp), st)
-        E = int(rowptr[n].item())               # the one host sync of the build
+        lib.call('sevenn_scan_i32', _p(count), _p(rowptr), nr, _p(tmp), st)
+        E = int(rowptr[nr].item())              # the one host sync of the build
         keys = torch.empty(max(E, 1), dtype=torch.int64, device=dev)
         ebuf = torch.empty(5 * max(E, 1), dtype=torch.int32, device=dev)       # written in full by the decode kernel
         center, col, shift = ebuf[:max(E, 1)], ebuf[max(E, 1):2 * max(E, 1)], ebuf[2 * max(E, 1):].view(max(E, 1), 3)
         vec = torch.empty(max(E, 1), 3, dtype=torch.float32, device=dev)
-        lib.call('sevenn_nl_fill', _p(pw), _p(wrap), _p(atom_bin), _p(bin_start), _p(bin_atoms), n, dp, ip,
+        lib.call('sevenn_nl_fill', _p(pw), _p(wrap), _p(atom_bin), _p(bin_start), _p(bin_atoms), nr, dp, ip,
                  _p(rowptr), _p(keys), _p(pos_dev), _p(center), _p(col), _p(shift), _p(vec), st)
         cptr, cedge = csc_build(lib, col[:E], n, dev, st)
         self.n_launch += 19        # 1 bin + 3 scan + 1 scatter + 1 count + 3 scan + 3 fill/sort/decode + 7 csc

@@ -83,3 +83,17 @@ def test_conv_fwd_bwd_emu(case):
     assert torch.allclose(torch.from_numpy(dY).double().sum(0), gY, atol=2e-4, rtol=1e-4)
     dx = torch.zeros(n, conv.lx.dim, dtype=torch.float64).index_add_(0, src, torch.from_numpy(dxe).double())
     assert torch.allclose(conv.lx.to_e3nn(dx), gx, atol=2e-4, rtol=1e-4)
+
+
+def test_committed_generated_kernels_match_the_generator():
+    """csrc/generated/*.cu is generator output kept in the tree (the hot kernels, readable and diffable): regenerating
+    every prebuilt signature must give byte-identical files, so the committed text cannot drift from conv_codegen.py."""
+    import os
+    from sevennet_exp_b200 import build
+    from sevennet_exp_b200.codegen import conv_codegen
+    specs = build.conv_specs(build.prebuilt_configs())
+    assert len(specs) >= 5
+    for sig, spec in specs.items():
+        path = os.path.join(build.GEN, f'conv_{sig}.cu')
+        assert os.path.exists(path), path
+        assert open(path).read() == conv_codegen.generate(spec), f'{path} differs from the generator output'

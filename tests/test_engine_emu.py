@@ -76,6 +76,7 @@ def test_engine_emu_two_chunk_units(monkeypatch, packed):
     component-wise fmaf in the emulation build).  Same parity gates as everything else."""
     from sevennet_exp_b200.codegen import conv_codegen
     monkeypatch.setattr(conv_codegen, 'TAB_F2', packed)
+    monkeypatch.setattr(conv_codegen, 'TAB_POLY', not packed)      # the packed variant reads Hermite rows, the default monomial ones
     cfg = dict(presets.PRESETS['test-so3-l2'])
     cfg['irreps_manual'] = ['64x0e', '64x0e+32x1e+32x2e', '64x0e+32x1e+32x2e', '32x0e']
     cfg['channel'] = 64

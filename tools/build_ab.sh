@@ -7,7 +7,7 @@ set -e
 tag=$1; shift
 mkdir -p tools/ab
 env "$@" python -m sevennet_exp_b200.build | tail -1
-cp sevennet_exp_b200/_lib/libsevenn_b200.so tools/ab/libsevenn_b200_$tag.so
+cp sevennet_exp_b200/_build/libsevenn_b200.so tools/ab/libsevenn_b200_$tag.so
 python -m sevennet_exp_b200.build | tail -1
-[ -f tools/ab/libsevenn_b200_ref.so ] || cp sevennet_exp_b200/_lib/libsevenn_b200.so tools/ab/libsevenn_b200_ref.so
+[ -f tools/ab/libsevenn_b200_ref.so ] || cp sevennet_exp_b200/_build/libsevenn_b200.so tools/ab/libsevenn_b200_ref.so
 ls -la tools/ab
