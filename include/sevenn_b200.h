@@ -83,6 +83,9 @@ int sevenn_gemm_f32(const sevenn_gemm_args* args /* host */, void* stream);   /*
  * Needs K % 4 == 0 and 16-byte aligned A rows; returns SEVENN_ERR_BAD_ARG otherwise. */
 int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, long long* img_floats);
 int sevenn_gemm_tc(const sevenn_gemm_args* args /* host */, const float* Bimg, void* stream);
+/* builds that image on the device from a row-major W[K, N] (img: img_floats of sevenn_gemm_tc_plan); for weights that
+ * change every step (training) */
+int sevenn_gemm_tc_image(const float* W, int K, int N, float* img, void* stream);
 /* up to 4 independent problems with the same epilogue in one launch (the per-l blocks of one o3.Linear) */
 int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args /* host array */, const float* const* Bimgs /* host array */,
                            void* stream);
@@ -238,6 +241,9 @@ int sevenn_gemm_tn(const float* A, long long sAn, int sAm, const float* B, long 
 /* torch.optim.Adam's update on one flat parameter (sevenn/train/optim.py 'adam'); step >= 1 */
 int sevenn_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, int step, float lr,
                      float beta1, float beta2, float eps, float weight_decay, void* stream);
+/* ... with the step count (>= 1) read from device memory, for CUDA-graph replay of a training step */
+int sevenn_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n,
+                         const int* step_dev, float lr, float beta1, float beta2, float eps, float weight_decay, void* stream);
 
 /* ---- fused gather + uvu CG tensor product + segment sum (generated per irreps signature <sig>):
  *   int sevenn_conv_fwd_<sig>(x, ldx, Y, w, rowptr, col, n_dst, inv_denom, out, ldo, stream)

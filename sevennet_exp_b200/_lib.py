@@ -42,6 +42,7 @@ SIGNATURES = {
     'sevenn_gemm_tc_plan': ([c_i, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_i), ctypes.POINTER(c_i),
                              ctypes.POINTER(c_ll)], c_i),
     'sevenn_gemm_tc': ([ctypes.POINTER(GemmArgs), c_p, c_p], c_i),
+    'sevenn_gemm_tc_image': ([c_p, c_i, c_i, c_p, c_p], c_i),
     'sevenn_gemm_tc_grouped': ([c_i, ctypes.POINTER(GemmArgs), ctypes.POINTER(c_p), c_p], c_i),
     'sevenn_linear_by_type': ([c_p, c_ll, c_i, c_p, c_p, c_p, c_ll, c_i, c_ll, c_i, c_i, c_i, c_i, c_p], c_i),
     'sevenn_embed': ([c_p, c_ll, c_i, c_p, c_p, c_p], c_i),
@@ -72,6 +73,7 @@ SIGNATURES = {
     'sevenn_gemm_tn_splits': ([c_ll], c_i),
     'sevenn_gemm_tn': ([c_p, c_ll, c_i, c_p, c_ll, c_i, c_ll, c_i, c_i, c_i, c_p, c_i, c_f, c_i, c_p, c_p, c_p], c_i),
     'sevenn_adam_step': ([c_p, c_p, c_p, c_p, c_ll, c_i, c_f, c_f, c_f, c_f, c_f, c_p], c_i),
+    'sevenn_adam_step_dev': ([c_p, c_p, c_p, c_p, c_ll, c_p, c_f, c_f, c_f, c_f, c_f, c_p], c_i),
     'sevenn_force_virial': ([c_p, c_p, c_p, c_i, c_p, c_p, c_ll, c_p, c_p, c_p], c_i),
     'sevenn_segment_gather_sum': ([c_p, c_i, c_p, c_p, c_ll, c_p, c_i, c_p], c_i),
     'sevenn_gather_rows': ([c_p, c_i, c_p, c_ll, c_p, c_p], c_i),

@@ -652,6 +652,38 @@ static int tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, int* resident) 
   return 0;
 }
 
+extern "C" int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, long long* img_floats);
+// Device-side construction of the pre-swizzled (hi, lo) K-major image of a weight matrix W[K, N] (row-major, ld = N):
+// img[t][kb][h][n][phys(k)] with phys = ((k / 4) ^ (n % 8)) * 4 + k % 4 -- the layout engine.py::tc_weight_image builds on
+// the host.  For weights that change every step (training): one small launch instead of a host round trip.
+__global__ void tc_image_kernel(const float* __restrict__ W, int K, int N, int Nt, int n_tiles, int KB,
+                                float* __restrict__ img) {
+  const long long total = (long long)n_tiles * KB * Nt * 32;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int kk = (int)(i % 32);
+    const int n = (int)((i / 32) % Nt);
+    const int kb = (int)((i / (32LL * Nt)) % KB);
+    const int t = (int)(i / (32LL * Nt * KB));
+    const int k = kb * 32 + kk, col = t * Nt + n;
+    const float v = (k < K && col < N) ? W[(size_t)k * N + col] : 0.f;
+    const float hi = __uint_as_float(__float_as_uint(v) & 0xFFFFE000u);
+    const float lo = __uint_as_float(__float_as_uint(v - hi) & 0xFFFFE000u);
+    const int phys = (((kk >> 2) ^ (n & 7)) << 2) | (kk & 3);
+    const size_t base = (((size_t)t * KB + kb) * 2) * Nt * 32 + (size_t)n * 32 + phys;
+    img[base] = hi;
+    img[base + (size_t)Nt * 32] = lo;
+  }
+}
+extern "C" int sevenn_gemm_tc_image(const float* W, int K, int N, float* img, void* stream) {
+  int Nt, n_tiles, KB;
+  long long fl;
+  int rc = sevenn_gemm_tc_plan(N, K, &Nt, &n_tiles, &KB, &fl);
+  if (rc) return rc;
+  const long long total = (long long)n_tiles * KB * Nt * 32;
+  tc_image_kernel<<<sevenn_grid_for(total), 256, 0, (cudaStream_t)stream>>>(W, K, N, Nt, n_tiles, KB, img);
+  return (int)cudaGetLastError();
+}
+
 extern "C" int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, long long* img_floats) {
   int res;
   int rc = tc_plan(N, K, Nt, n_tiles, KB, &res);
@@ -837,6 +869,9 @@ extern "C" int sevenn_gemm_tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB,
   *Nt = 16; *n_tiles = (N + 15) / 16; *KB = (K + 31) / 32;
   *img_floats = (long long)(*n_tiles) * (*KB) * 2 * 16 * 32;
   return 0;
+}
+extern "C" int sevenn_gemm_tc_image(const float* W, int K, int N, float* img, void* stream) {
+  (void)W; (void)K; (void)N; (void)img; (void)stream; return 0;   // the emulation arm ignores images
 }
 extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, void* stream) {
   (void)Bimg; return sevenn_gemm_f32(args, stream);

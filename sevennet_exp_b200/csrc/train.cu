@@ -356,6 +356,28 @@ GKERNEL(adam_kernel)(float* __restrict__ p, const float* __restrict__ g, float* 
     p[i] -= (lr / bc1) * mi / (sqrtf(vi) / bc2_sqrt + eps);
   }
 }
+// the same update with the step count read on the device (CUDA-graph replay: the host cannot pass a new count)
+GKERNEL(adam_dev_kernel)(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                         long long n, const int* __restrict__ step, float lr, float b1, float b2, float eps, float wd) {
+  const float t = (float)*step;
+  const float bc1 = 1.f - powf(b1, t), bc2_sqrt = sqrtf(1.f - powf(b2, t));
+  GRID_STRIDE_LOOP(i, n) {
+    float gi = g[i];
+    if (wd != 0.f) gi += wd * p[i];
+    const float mi = b1 * m[i] + (1.f - b1) * gi;
+    const float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi; v[i] = vi;
+    p[i] -= (lr / bc1) * mi / (sqrtf(vi) / bc2_sqrt + eps);
+  }
+}
+extern "C" int sevenn_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n,
+                                    const int* step_dev, float lr, float beta1, float beta2, float eps, float weight_decay,
+                                    void* stream) {
+  if (n <= 0) return 0;
+  if (step_dev == nullptr) return SEVENN_ERR_BAD_ARG;
+  LAUNCH1D(adam_dev_kernel, n, stream)(param, grad, exp_avg, exp_avg_sq, n, step_dev, lr, beta1, beta2, eps, weight_decay);
+  return LAUNCH_STATUS();
+}
 extern "C" int sevenn_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, int step,
                                 float lr, float beta1, float beta2, float eps, float weight_decay, void* stream) {
   if (n <= 0) return 0;

@@ -148,8 +148,19 @@ class Kernels:
         # cache keyed on data_ptr() alone would hand a recycled address the previous owner's weights.
         tag = getattr(B, '_sevenn_tc_img', None)
         if tag is None or tag[0] != B._version:
-            W = B.detach().cpu().numpy().astype(np.float32)
-            tag = (B._version, torch.from_numpy(tc_image_for(self.lib, W)).to(self.dev).contiguous())
+            if getattr(B, '_sevenn_dynamic', False) and B.is_cuda:
+                # per-step weights (training): the image is built by a kernel, no host round trip
+                K, N = B.shape
+                nt, tiles, kb, fl = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_longlong()
+                self.lib.call('sevenn_gemm_tc_plan', N, K, ctypes.byref(nt), ctypes.byref(tiles), ctypes.byref(kb),
+                              ctypes.byref(fl))
+                img = self._empty(fl.value)
+                self.lib.call('sevenn_gemm_tc_image', _p(B), K, N, _p(img), self._stream())
+                self.n_launch += 1
+                tag = (B._version, img)
+            else:
+                W = B.detach().cpu().numpy().astype(np.float32)
+                tag = (B._version, torch.from_numpy(tc_image_for(self.lib, W)).to(self.dev).contiguous())
             B._sevenn_tc_img = tag
         return tag[1]
 
@@ -158,9 +169,7 @@ class Kernels:
                           M, R, N, K, epi, act, cst,
                           (C2.data_ptr() + 4 * c_off) if C2 is not None else None,
                           (P.data_ptr() + 4 * c_off) if P is not None else None)
-        # weights that change every step (training) stay on the SIMT arm: their pre-swizzled tcgen05 image is built on
-        # the host
-        tc = (self.gemm_mode != 'simt' and not getattr(B, '_sevenn_dynamic', False) and M >= self.tc_min_rows
+        tc = (self.gemm_mode != 'simt' and B.dim() == 2 and M >= self.tc_min_rows
               and (epi < 2 or act == 0) and K % 4 == 0
               and sAn % 4 == 0 and sAm % 4 == 0 and (A.data_ptr() + 4 * a_off) % 16 == 0)
         return g, tc

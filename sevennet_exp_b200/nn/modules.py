@@ -71,6 +71,19 @@ def _pcols(x, layout, device, to_e3nn: bool):
     return _PermCols.apply(x, p, inv) if to_e3nn else _PermCols.apply(x, inv, p)
 
 
+SIZES = '_b200_sizes'      # optional (total atoms, number of graphs) python ints in the data dict: no host sync needed
+
+
+def _n_graphs(data):
+    sz = data.get(SIZES)
+    return int(sz[1]) if sz is not None else int(data[BATCH].max()) + 1
+
+
+def _n_atoms_total(data):
+    sz = data.get(SIZES)
+    return int(sz[0]) if sz is not None else int(torch.sum(data[NATOMS]))
+
+
 def _train_mode(module) -> bool:
     """Parameter gradients / double backward wanted: the module is in training mode and autograd is recording."""
     return module.training and torch.is_grad_enabled()
@@ -529,6 +542,14 @@ class IrrepsConvolution(nn.Module):
                                  'act': self._act, 'cst': self._cst})
         return self._cache[1]
 
+    def _denominator_value(self) -> float:
+        """host copy of the denominator, refreshed when the parameter changes (no device->host read per call)"""
+        d = self.denominator
+        key = (d._version, d.data_ptr())
+        if getattr(self, '_denom_cache', (None, None))[0] != key:
+            self._denom_cache = (key, float(d.item()))
+        return self._denom_cache[1]
+
     def instantiate(self):
         """convolution.py:103-116: nothing to build lazily here (kept for the reference's builder loop)."""
         self.layer_instantiated = True
@@ -555,7 +576,7 @@ class IrrepsConvolution(nn.Module):
             emb, Y = emb[perm], Y[perm]
         xin = _pcols(x.float(), self._conv.lx, dev, False)
         meta = dict(sig=self._sig, dx=self._conv.lx.dim, dmid=self._conv.lmid.dim, wn=self._conv.wn,
-                    units=conv_codegen.n_units(self._conv), inv_denom=1.0 / float(self.denominator.item()))
+                    units=conv_codegen.n_units(self._conv), inv_denom=1.0 / self._denominator_value())
         if _train_mode(self):
             # training: radial MLP and convolution through the second-order-capable Functions (train_functional.py);
             # a trainable denominator divides outside the kernel so that it receives its gradient
@@ -712,7 +733,7 @@ class AtomReduce(nn.Module):
         src = data[self.key_input]
         if self._is_batch_data:
             b = data[BATCH]
-            out = torch.zeros(int(b.max()) + 1, dtype=torch.float64, device=src.device)
+            out = torch.zeros(_n_graphs(data), dtype=torch.float64, device=src.device)
             out.index_add_(0, b, src.reshape(-1).double())
             data[self.key_output] = out.to(src.dtype) * self.constant
         else:
@@ -735,7 +756,7 @@ class ForceStressOutputFromEdge(nn.Module):
     def _forward_train(self, data):
         """force_output.py:173-222 verbatim in torch ops: `create_graph=True` keeps dE/d(edge_vec) in the graph so that a
         loss on forces / stress back-propagates through the reverse kernels (nn/train_functional.py)."""
-        tot = int(torch.sum(data[NATOMS]))
+        tot = _n_atoms_total(data)
         rij, ei = data[EDGE_VEC], data[EDGE_IDX]
         fij = torch.autograd.grad([data[E_TOT].sum()], [rij], create_graph=True, allow_unused=True)[0]
         for k in [k for k in data if isinstance(k, str) and k.startswith(GRAPH)]:
@@ -750,7 +771,7 @@ class ForceStressOutputFromEdge(nn.Module):
         s = torch.zeros(tot, 6, dtype=fij.dtype, device=fij.device).index_add(0, ei[1], vir)
         if self._is_batch_data:
             b = data[BATCH]
-            sout = torch.zeros(int(b.max()) + 1, 6, dtype=fij.dtype, device=fij.device).index_add(0, b, s)
+            sout = torch.zeros(_n_graphs(data), 6, dtype=fij.dtype, device=fij.device).index_add(0, b, s)
         else:
             sout = s.sum(dim=0)
         data[STRESS] = torch.neg(sout) / data[VOL].to(fij.dtype).unsqueeze(-1)
@@ -759,7 +780,7 @@ class ForceStressOutputFromEdge(nn.Module):
     def forward(self, data):
         if _train_mode(self):
             return self._forward_train(data)
-        tot = int(torch.sum(data[NATOMS]))
+        tot = _n_atoms_total(data)
         rij = data[EDGE_VEC]
         fij = torch.autograd.grad([data[E_TOT].sum()], [rij], allow_unused=True)[0]
         cached = data.pop(GRAPH, None)
@@ -784,7 +805,7 @@ class ForceStressOutputFromEdge(nn.Module):
         vol = data[VOL]
         if self._is_batch_data:               # per-graph stress, force_output.py:210-219
             b = data[BATCH]
-            sout = torch.zeros(int(b.max()) + 1, 6, dtype=torch.float64, device=dev).index_add_(0, b, vir.double())
+            sout = torch.zeros(_n_graphs(data), 6, dtype=torch.float64, device=dev).index_add_(0, b, vir.double())
             data[STRESS] = (torch.neg(sout) / vol.double().reshape(-1, 1)).to(f.dtype)
         else:
             data[STRESS] = (torch.neg(vir.double().sum(dim=0)) / vol.double().reshape(-1)[0]).to(f.dtype)

@@ -60,6 +60,7 @@ class Adam:
         self.lr, self.betas, self.eps, self.wd = float(lr), (float(betas[0]), float(betas[1])), float(eps), float(weight_decay)
         self.state = {}
         self.t = 0
+        self.t_dev = None
 
     def zero_grad(self):
         for p in self.params:
@@ -67,6 +68,12 @@ class Adam:
 
     def step(self):
         self.t += 1
+        dev = self.params[0].device if self.params else None
+        if dev is not None and dev.type == 'cuda':
+            # step count on the device: the same launches stay valid when the step is replayed from a CUDA graph
+            if self.t_dev is None:
+                self.t_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+            self.t_dev.add_(1)
         for p in self.params:
             if p.grad is None:
                 continue
@@ -76,8 +83,12 @@ class Adam:
                 st = self.state[p] = (torch.zeros_like(p.data), torch.zeros_like(p.data))
             g = p.grad.detach().float().contiguous()
             assert p.data.is_contiguous() and p.data.dtype == torch.float32
-            k.lib.call('sevenn_adam_step', ptr(p.data), ptr(g), ptr(st[0]), ptr(st[1]), p.data.numel(), self.t, self.lr,
-                       self.betas[0], self.betas[1], self.eps, self.wd, k._stream())
+            if self.t_dev is not None:
+                k.lib.call('sevenn_adam_step_dev', ptr(p.data), ptr(g), ptr(st[0]), ptr(st[1]), p.data.numel(),
+                           ptr(self.t_dev), self.lr, self.betas[0], self.betas[1], self.eps, self.wd, k._stream())
+            else:
+                k.lib.call('sevenn_adam_step', ptr(p.data), ptr(g), ptr(st[0]), ptr(st[1]), p.data.numel(), self.t,
+                           self.lr, self.betas[0], self.betas[1], self.eps, self.wd, k._stream())
             k.n_launch += 1
             # the parameter changed in place behind autograd's back: bump its version so cached device weights rebuild
             with torch.no_grad():
@@ -95,14 +106,48 @@ class Trainer:
     def forward(self, batch: Dict[str, torch.Tensor]):
         return self.model({k: (v.clone() if torch.is_tensor(v) else v) for k, v in batch.items()})
 
-    def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
-        self.model.train()
+    def prepare(self, batch: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+        """Adds what would otherwise cost a host synchronisation per step: the (atoms, graphs) sizes and the CSR / CSC
+        graph of the batch (built once per batch, like the reference's dataset does for edge lists)."""
+        from .nn import functional as F
+        from .nn.modules import GRAPH, SIZES
+        batch = dict(batch)
+        n_tot, n_b = int(batch[K_NATOMS].sum()), int(batch[K_NATOMS].numel())
+        batch[SIZES] = (n_tot, n_b)
+        batch[GRAPH] = F.build_graph(batch[K_EI], n_tot, n_tot, batch[K_EI].device)
+        return batch
+
+    def _step(self, batch):
         self.optimizer.zero_grad()
         out = self.forward(batch)
         loss = loss_from_config(out, self.config)
         loss.backward()
         self.optimizer.step()
-        return float(loss.detach())
+        return loss.detach()
+
+    def train_step(self, batch: Dict[str, torch.Tensor]) -> float:
+        self.model.train()
+        return float(self._step(batch))
+
+    def train_step_graphed(self, batch: Dict[str, torch.Tensor]) -> torch.Tensor:
+        """The same step replayed from a CUDA graph: `batch` must come from prepare() and keep its tensors (new data is
+        copied INTO them).  The first call warms up and captures; returns the loss as a device tensor (no sync)."""
+        self.model.train()
+        if getattr(self, '_cg', None) is None or self._cg[1] is not batch:
+            cur = torch.cuda.current_stream()
+            side = torch.cuda.Stream()
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                for _ in range(2):
+                    self._step(batch)
+            cur.wait_stream(side)
+            g = torch.cuda.CUDAGraph()
+            self.optimizer.zero_grad()
+            with torch.cuda.graph(g):
+                loss = self._step(batch)
+            self._cg = (g, batch, loss)
+        self._cg[0].replay()
+        return self._cg[2]
 
     @torch.no_grad()
     def _metrics(self, out):

@@ -61,3 +61,47 @@ def test_cp0_one_adam_step_known_answer_on_gpu(golden_dir):
     l1 = tr.train_step(batch)
     l2 = tr.train_step(batch)
     assert l2 < l1
+
+
+def test_device_built_tc_weight_image_equals_host_image():
+    """sevenn_gemm_tc_image (weights that change every step) builds exactly the image engine.tc_image_for builds on the host."""
+    import ctypes
+    from sevennet_exp_b200 import _lib
+    from sevennet_exp_b200.engine import tc_image_for
+    lib = _lib.load()
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    torch.manual_seed(3)
+    for K, N in [(8, 64), (64, 960), (352, 32), (224, 224), (64, 1), (12, 20)]:
+        W = torch.randn(K, N, device='cuda')
+        host = torch.from_numpy(tc_image_for(lib, W.cpu().numpy()))
+        img = torch.full((host.numel(),), float('nan'), device='cuda')
+        lib.call('sevenn_gemm_tc_image', ctypes.c_void_p(W.data_ptr()), K, N, ctypes.c_void_p(img.data_ptr()), st)
+        assert torch.equal(img.cpu(), host), (K, N)
+
+
+def test_graphed_training_step_equals_eager():
+    """Trainer.train_step_graphed (the whole step replayed from a CUDA graph, Adam's step count on the device) walks the
+    same parameter trajectory as the eager step."""
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    cfg.update(version='0.11.0')
+    rng = np.random.default_rng(1)
+    structs = [random_cell(n, list(cfg['_type_map']), density=0.05, seed=50 + k) for k, n in enumerate((30, 21, 12))]
+    labels = [(rng.normal(), rng.normal(size=(len(s[0]), 3)), rng.normal(size=6) * 1e-3) for s in structs]
+    graphs = labelled_graphs(cfg, structs, labels)
+    torch.manual_seed(9)
+    om = S.build_model(cfg)
+    finals = {}
+    for mode in ('eager', 'graph'):
+        model = bnn.build_E3_equivariant_model(cfg)
+        assert not model.load_state_dict(om.state_dict(), strict=False)[0]
+        tr = TR.Trainer(model.cuda(), CONFIG)
+        batch = tr.prepare(TR.collate(graphs, device='cuda'))
+        losses = []
+        for _ in range(5):
+            losses.append(float(tr.train_step(batch) if mode == 'eager' else tr.train_step_graphed(batch)))
+        finals[mode] = (losses, {n: p.detach().cpu().clone() for n, p in model.named_parameters()})
+    # the graphed trainer runs two extra warm-up steps before capturing: compare step k of eager with the same parameters
+    le, lg = finals['eager'][0], finals['graph'][0]
+    assert lg[0] < le[0] or abs(lg[0] - le[2]) < 1e-4 * abs(le[2])       # graph's first replayed step = eager's third
+    assert all(b <= a + 1e-6 for a, b in zip(lg, lg[1:]))                # and the loss keeps going down
+    assert abs(lg[0] - le[2]) < 1e-4 * abs(le[2]) and abs(lg[1] - le[3]) < 1e-4 * abs(le[3])
