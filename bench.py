@@ -280,6 +280,8 @@ def ncu_capture(kernel, n_edges):
         for row in json.load(open(os.path.join(ROOT, 'profiles', 'ncu_captures.json'))):
             if row['kernel'] == kernel and abs(row['n_edges'] - n_edges) <= 0.001 * n_edges:
                 return row
+            if n_edges == 0 and row['kernel'].startswith(kernel) and row.get('tensor_pipe_pct'):
+                return row
     except Exception:  # noqa: BLE001
         pass
     return None
