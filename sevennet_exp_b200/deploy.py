@@ -43,7 +43,7 @@ def _resolve(model):
     """checkpoint path | (config, state_dict) -> (spec, engine-ready state_dict, config)."""
     if isinstance(model, (tuple, list)):
         cfg, sd = model
-        cfg = patch_old_config(dict(cfg))
+        cfg = patch_old_config(dict(cfg), require_version=False)
         spec = build_spec(cfg)
         return spec, patch_state_dict(spec, sd, cfg.get('version', '0.11.0')), cfg
     return load_checkpoint(model)
@@ -167,7 +167,7 @@ class DeployedSerial:
     def __init__(self, cfg: dict, sd: dict, device='cuda', extra: Optional[Dict[str, str]] = None, lib=None,
                  radial: Optional[str] = None, modal: Optional[str] = None):
         from .engine import Engine
-        cfg = patch_old_config(dict(cfg))
+        cfg = patch_old_config(dict(cfg), require_version=False)
         self.spec = build_spec(cfg)
         self.config = cfg
         self.device = torch.device(device)
@@ -217,7 +217,7 @@ class DeployedParallel:
 
     def __init__(self, cfg: dict, sd: dict, device='cuda', extra: Optional[Dict[str, str]] = None):
         from . import nn as bnn
-        cfg = patch_old_config(dict(cfg))
+        cfg = patch_old_config(dict(cfg), require_version=False)
         self.spec, self.config, self.device = build_spec(cfg), cfg, torch.device(device)
         self.segments = bnn.build_E3_equivariant_model(cfg, parallel=True)
         full = dict(sd)

@@ -100,7 +100,7 @@ class SevenNetCalculator(_AseCalculator):
                                      'sevennet_exp_b200.nn.build_E3_equivariant_model, or pass (config, state_dict))')
                 model = (dict(cfg, version='0.11.0'), {k: v.detach().cpu() for k, v in model.state_dict().items()})
             cfg, sd = model
-            cfg = patch_old_config(cfg)
+            cfg = patch_old_config(cfg, require_version=False)
             spec = build_spec(cfg)
             sd = patch_state_dict(spec, sd, cfg.get('version', '0.11.0'))
         self.sevennet_config = sevennet_config or cfg

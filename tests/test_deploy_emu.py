@@ -29,7 +29,7 @@ def _reset_lib():
 
 
 def _emu_for(cfg):
-    lib = build_full_emu([L.conv for L in sp.build_spec(patch_old_config(dict(cfg))).layers])
+    lib = build_full_emu([L.conv for L in sp.build_spec(patch_old_config(dict(cfg), require_version=False)).layers])
     bnn.set_lib(lib)
     return lib
 
