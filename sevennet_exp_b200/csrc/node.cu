@@ -97,70 +97,6 @@ GKERNEL(gate_bwd_kernel)(const float* __restrict__ pre, int din, const float* __
   }
 }
 
-#ifndef SEVENN_EMU
-// Column-stationary variants: a thread owns one output column (forward) / one channel (backward), decodes its gate
-// piece ONCE and then walks the rows with a CTA stride -- the per-element 64-bit division, piece search and integer
-// divisions of the generic kernels above cost more issue slots than the activation itself (gate stages ran at 1/4 of the
-// HBM rate).  Loads and stores stay coalesced along the channel index.
-__global__ void __launch_bounds__(512) gate_fwd_cols_kernel(const float* __restrict__ pre, int din, float* __restrict__ out,
-                                                            int dout, long long n, GateTable T) {
-  for (int c0 = threadIdx.x; c0 < dout; c0 += blockDim.x) {
-    int c = c0, q = 0;
-    for (; q < T.n; ++q) {
-      const int sz = T.p[q].mul * (2 * T.p[q].l + 1);
-      if (c < sz) break;
-      c -= sz;
-    }
-    if (q == T.n) continue;
-    const sevenn_gate_piece P = T.p[q];
-    const int m = c / P.mul, u = c - m * P.mul;
-    const int a_off = P.kind == 0 ? P.in_off + u : P.gate_off + u;
-    const int x_off = P.in_off + m * P.in_stride + u;
-    const int o_off = P.out_off + m * P.out_stride + u;
-    for (long long i = blockIdx.x; i < n; i += gridDim.x) {
-      const float* row = pre + i * din;
-      float v = P.cst * act_f(P.act, row[a_off]);
-      if (P.kind != 0) v *= row[x_off];
-      out[i * dout + o_off] = v;
-    }
-  }
-}
-__global__ void __launch_bounds__(256) gate_bwd_cols_kernel(const float* __restrict__ pre, int din,
-                                                            const float* __restrict__ dout_, int dout,
-                                                            float* __restrict__ dpre, long long n, GateTable T, int nch) {
-  for (int c0 = threadIdx.x; c0 < nch; c0 += blockDim.x) {
-    int u = c0, q = 0;
-    for (; q < T.n; ++q) {
-      if (u < T.p[q].mul) break;
-      u -= T.p[q].mul;
-    }
-    if (q == T.n) continue;
-    const sevenn_gate_piece P = T.p[q];
-    const int R = 2 * P.l + 1;
-    for (long long i = blockIdx.x; i < n; i += gridDim.x) {
-      const float* row = pre + i * din; const float* go = dout_ + i * dout; float* gi = dpre + i * din;
-      if (P.kind == 0) {
-        gi[P.in_off + u] = go[P.out_off + u] * P.cst * dact_f(P.act, row[P.in_off + u]);
-      } else {
-        const float gpre = row[P.gate_off + u];
-        const float gate = P.cst * act_f(P.act, gpre);
-        float acc = 0.f;
-        for (int m = 0; m < R; ++m) {
-          const float g = go[P.out_off + m * P.out_stride + u];
-          acc += g * row[P.in_off + m * P.in_stride + u];
-          gi[P.in_off + m * P.in_stride + u] = g * gate;
-        }
-        gi[P.gate_off + u] = acc * P.cst * dact_f(P.act, gpre);
-      }
-    }
-  }
-}
-static inline int gate_rows_grid(long long n) {
-  const long long cap = 148LL * 8;
-  return (int)(n < cap ? (n < 1 ? 1 : n) : cap);
-}
-#endif
-
 static int load_gate(GateTable& T, const sevenn_gate_piece* pieces, int n_pieces) {
   if (n_pieces < 0 || n_pieces > SEVENN_MAX_GATE_PIECES) return SEVENN_ERR_BAD_ARG;
   T.n = n_pieces;
@@ -177,11 +113,7 @@ extern "C" int sevenn_gate_fwd(const float* pre, int din, float* out, int dout, 
                                const sevenn_gate_piece* pieces, int n_pieces, void* stream) {
   GateTable T; int rc = load_gate(T, pieces, n_pieces); if (rc) return rc;
   if (n <= 0) return 0;
-#ifndef SEVENN_EMU
-  gate_fwd_cols_kernel<<<gate_rows_grid(n), dout < 512 ? ((dout + 31) / 32) * 32 : 512, 0, (cudaStream_t)stream>>>(pre, din, out, dout, n, T);
-#else
   LAUNCH1D(gate_fwd_kernel, n * dout, stream)(pre, din, out, dout, n, T);
-#endif
   return LAUNCH_STATUS();
 }
 extern "C" int sevenn_gate_bwd(const float* pre, int din, const float* dout_, int dout, float* dpre, long long n,
@@ -189,11 +121,7 @@ extern "C" int sevenn_gate_bwd(const float* pre, int din, const float* dout_, in
   GateTable T; int rc = load_gate(T, pieces, n_pieces); if (rc) return rc;
   if (n <= 0) return 0;
   int nch = 0; for (int k = 0; k < n_pieces; ++k) nch += pieces[k].mul;
-#ifndef SEVENN_EMU
-  gate_bwd_cols_kernel<<<gate_rows_grid(n), nch < 256 ? ((nch + 31) / 32) * 32 : 256, 0, (cudaStream_t)stream>>>(pre, din, dout_, dout, dpre, n, T, nch);
-#else
   LAUNCH1D(gate_bwd_kernel, n * nch, stream)(pre, din, dout_, dout, dpre, n, T, nch);
-#endif
   return LAUNCH_STATUS();
 }
 
