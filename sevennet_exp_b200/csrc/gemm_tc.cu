@@ -29,10 +29,12 @@
 #define TC_BM 128
 #define TC_BK 32                      // fp32 per k-block = one 128 B swizzle row
 #define TC_PRODUCERS 256
-#define TC_THREADS 416
-#define TC_MMA_WARP 12
+#define TC_THREADS 576                 // gemm_tc_kernel: 8 producer + 8 epilogue + 2 MMA-issuing warps
+#define TC_MMA_WARP 12                 // gemm_tca_kernel (448 threads): warps 12, 13 issue
+#define TC_MMA2_WARP 16                // gemm_tc_kernel: warps 16, 17 issue (even / odd row tiles)
 #define TC_EPI_WARP0 8
-#define TC_EPI_BYTES (4 * 32 * 128)  // per-warp 32 rows x 128 B transpose buffers
+#define TC_EPI_BYTES (4 * 32 * 128)  // per-warp 32 rows x 128 B transpose buffers (gemm_tca_kernel: 4 epilogue warps)
+#define TC_EPI8_BYTES (8 * 32 * 128) // gemm_tc_kernel: 8 epilogue warps
 
 struct TcParams {
   sevenn_gemm_args g;
@@ -90,6 +92,18 @@ __device__ __forceinline__ long long row_offset(long long r, int R, long long sn
   const unsigned n = (unsigned)r / (unsigned)R, m = (unsigned)r - n * (unsigned)R;
   return (long long)n * sn + (long long)m * sm;
 }
+// (node, m) of a row that advances by a fixed number of rows per step, without a division per step
+struct RowWalk {
+  int n, m, dn, dm;
+  __device__ __forceinline__ void init(long long r, int R, long long step) {
+    n = (int)((unsigned)r / (unsigned)R); m = (int)((unsigned)r - (unsigned)n * (unsigned)R);
+    dn = (int)((unsigned)step / (unsigned)R); dm = (int)((unsigned)step - (unsigned)dn * (unsigned)R);
+  }
+  __device__ __forceinline__ void next(int R) { n += dn; m += dm; if (m >= R) { m -= R; ++n; } }
+  __device__ __forceinline__ void add(int R, int sn_, int sm_) { n += sn_; m += sm_; if (m >= R) { m -= R; ++n; } }
+  __device__ __forceinline__ long long row(int R) const { return (long long)n * R + m; }
+  __device__ __forceinline__ long long off(long long sn, int sm) const { return (long long)n * sn + (long long)m * sm; }
+};
 __device__ __forceinline__ float4 lds128(uint32_t a) {
   float4 v;
   asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a) : "memory");
@@ -109,9 +123,9 @@ __device__ __forceinline__ float dsilu_f(float x) { const float s = __fdividef(1
 template <int EPI>
 __device__ __forceinline__ void tc_epilogue_tile(const sevenn_gemm_args& g, uint32_t d_taddr, uint8_t* tb, int ew, int lane,
                                                  const long long (&roff)[8], int n0, int ncols, int vec4, int mode,
-                                                 int part2_cols = 0) {
+                                                 int part2_cols = 0, int cc0 = 0, int cstep = 32) {
   const int sub = lane >> 3, ch = lane & 7; (void)sub;
-  for (int cc = 0; cc < ncols; cc += 32) {
+  for (int cc = cc0; cc < ncols; cc += cstep) {
     uint32_t v[32];
     const uint32_t taddr = d_taddr + ((uint32_t)(ew * 32) << 16) + (uint32_t)cc;
     asm volatile(
@@ -150,51 +164,57 @@ __device__ __forceinline__ void tc_epilogue_tile(const sevenn_gemm_args& g, uint
     __syncwarp();
     const int col = cc + ch * 4;                     // first of this lane's 4 columns (tile-relative)
     const int nvalid = ncols - col;                  // >= 4 -> whole float4 valid
-    float4 x[8];
+    // two passes of four rows: keeps the live set at 4 + 4 float4 (the kernel runs 576 threads at <= 96 registers)
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int row = 4 * i + sub;
-      x[i] = lds128(tbs + row * 128 + ((ch ^ (row & 7)) << 4));
-    }
-    if (vec4 && nvalid >= 4) {
-      float4 aux[8];
-      if (EPI == 1 || EPI == 3) {
+    for (int h = 0; h < 2; ++h) {
+      float4 x[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          if (roff[i] >= 0)
-            aux[i] = *reinterpret_cast<const float4*>((EPI == 1 ? g.C : g.P) + roff[i] + n0 + col);
+      for (int i = 0; i < 4; ++i) {
+        const int row = 4 * (4 * h + i) + sub;
+        x[i] = lds128(tbs + row * 128 + ((ch ^ (row & 7)) << 4));
       }
+      if (vec4 && nvalid >= 4) {
+        float4 aux[4];
+        if (EPI == 1 || EPI == 3) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        if (roff[i] < 0) continue;
-        float4* c4 = reinterpret_cast<float4*>(g.C + roff[i] + n0 + col);
-        const float4 xv = x[i];
-        if (EPI == 0) {
-          *c4 = xv;
-        } else if (EPI == 1) {
-          *c4 = make_float4(aux[i].x + xv.x, aux[i].y + xv.y, aux[i].z + xv.z, aux[i].w + xv.w);
-        } else if (EPI == 2) {
-          *c4 = xv;
-          *reinterpret_cast<float4*>(g.C2 + roff[i] + n0 + col) =
-              make_float4(g.cst * silu_f(xv.x), g.cst * silu_f(xv.y), g.cst * silu_f(xv.z), g.cst * silu_f(xv.w));
-        } else {
-          *c4 = make_float4(xv.x * g.cst * dsilu_f(aux[i].x), xv.y * g.cst * dsilu_f(aux[i].y),
-                            xv.z * g.cst * dsilu_f(aux[i].z), xv.w * g.cst * dsilu_f(aux[i].w));
+          for (int i = 0; i < 4; ++i)
+            if (roff[4 * h + i] >= 0)
+              aux[i] = *reinterpret_cast<const float4*>((EPI == 1 ? g.C : g.P) + roff[4 * h + i] + n0 + col);
         }
-      }
-    } else if (nvalid > 0) {
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        if (roff[i] < 0) continue;
-        const float xs[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
+        for (int i = 0; i < 4; ++i) {
+          const long long ro = roff[4 * h + i];
+          if (ro < 0) continue;
+          float4* c4 = reinterpret_cast<float4*>(g.C + ro + n0 + col);
+          const float4 xv = x[i];
+          if (EPI == 0) {
+            *c4 = xv;
+          } else if (EPI == 1) {
+            *c4 = make_float4(aux[i].x + xv.x, aux[i].y + xv.y, aux[i].z + xv.z, aux[i].w + xv.w);
+          } else if (EPI == 2) {
+            *c4 = xv;
+            *reinterpret_cast<float4*>(g.C2 + ro + n0 + col) =
+                make_float4(g.cst * silu_f(xv.x), g.cst * silu_f(xv.y), g.cst * silu_f(xv.z), g.cst * silu_f(xv.w));
+          } else {
+            *c4 = make_float4(xv.x * g.cst * dsilu_f(aux[i].x), xv.y * g.cst * dsilu_f(aux[i].y),
+                              xv.z * g.cst * dsilu_f(aux[i].z), xv.w * g.cst * dsilu_f(aux[i].w));
+          }
+        }
+      } else if (nvalid > 0) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          if (e >= nvalid) break;
-          float* cp = g.C + roff[i] + n0 + col + e;
-          if (EPI == 0) *cp = xs[e];
-          else if (EPI == 1) *cp += xs[e];
-          else if (EPI == 2) { *cp = xs[e]; g.C2[roff[i] + n0 + col + e] = g.cst * silu_f(xs[e]); }
-          else *cp = xs[e] * g.cst * dsilu_f(g.P[roff[i] + n0 + col + e]);
+        for (int i = 0; i < 4; ++i) {
+          const long long ro = roff[4 * h + i];
+          if (ro < 0) continue;
+          const float xs[4] = {x[i].x, x[i].y, x[i].z, x[i].w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            if (e >= nvalid) break;
+            float* cp = g.C + ro + n0 + col + e;
+            if (EPI == 0) *cp = xs[e];
+            else if (EPI == 1) *cp += xs[e];
+            else if (EPI == 2) { *cp = xs[e]; g.C2[ro + n0 + col + e] = g.cst * silu_f(xs[e]); }
+            else *cp = xs[e] * g.cst * dsilu_f(g.P[ro + n0 + col + e]);
+          }
         }
       }
     }
@@ -202,7 +222,7 @@ __device__ __forceinline__ void tc_epilogue_tile(const sevenn_gemm_args& g, uint
   }
 }
 
-#define DBG(role, it, ev) do { if (P.dbg && blockIdx.x == 0 && (it) < 6 && (threadIdx.x & 31) == 0) \
+#define DBG(role, it, ev) do { if (P.dbg && blockIdx.x == 0 && (it) >= 0 && (it) < 6 && (threadIdx.x & 31) == 0) \
   P.dbg[((role) * 6 + (it)) * 8 + (ev)] = clock64(); } while (0)
 
 // Up to TC_MAX_GROUP independent problems per launch (the per-l blocks of one o3.Linear): each CTA serves one of
@@ -224,23 +244,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* bres = smem + (size_t)P.stages * stage_bytes;                     // resident B image [KB][2][Nt][32]
   uint8_t* epi_buf = bres + (P.resident ? (size_t)P.KB * 2 * b_bytes : 0);
-  uint64_t* bars = (uint64_t*)(epi_buf + TC_EPI_BYTES);
-  // bars: full[stages], empty[stages], tmem_full[2], tmem_empty[2], b_full; then the TMEM base address
+  uint64_t* bars = (uint64_t*)(epi_buf + TC_EPI8_BYTES);
+  // bars: full[2][stages] (one set per MMA-issuing warp: a k-block of an even row tile completes full[0][slot], of an
+  // odd one full[1][slot], so each warp sees every phase of the barriers it waits on -- a parity wait cannot tell
+  // phase p from phase p + 2), empty[stages], tmem_full[2], tmem_empty[2], b_full; then the TMEM base address
   const uint32_t bar0 = smem_u32(bars);
-  auto full_bar = [&](int s) { return bar0 + 8u * s; };
-  auto empty_bar = [&](int s) { return bar0 + 8u * (P.stages + s); };
-  auto tfull_bar = [&](int b) { return bar0 + 8u * (2 * P.stages + b); };
-  auto tempty_bar = [&](int b) { return bar0 + 8u * (2 * P.stages + 2 + b); };
-  const uint32_t bfull_bar = bar0 + 8u * (2 * P.stages + 4);
-  uint32_t* tmem_slot = (uint32_t*)(bars + 2 * P.stages + 5);
+  auto full_bar = [&](int w, int s) { return bar0 + 8u * (w * P.stages + s); };
+  auto empty_bar = [&](int s) { return bar0 + 8u * (2 * P.stages + s); };
+  auto tfull_bar = [&](int b) { return bar0 + 8u * (3 * P.stages + b); };
+  auto tempty_bar = [&](int b) { return bar0 + 8u * (3 * P.stages + 2 + b); };
+  const uint32_t bfull_bar = bar0 + 8u * (3 * P.stages + 4);
+  uint32_t* tmem_slot = (uint32_t*)(bars + 3 * P.stages + 5);
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < P.stages; ++s) { mbar_init(full_bar(s), TC_PRODUCERS); mbar_init(empty_bar(s), 1); }
-    for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 128); }
+    for (int s = 0; s < P.stages; ++s) {
+      mbar_init(full_bar(0, s), TC_PRODUCERS); mbar_init(full_bar(1, s), TC_PRODUCERS); mbar_init(empty_bar(s), 1);
+    }
+    for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 256); }
     mbar_init(bfull_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == TC_MMA_WARP) {
+  if (warp == TC_MMA2_WARP) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_slot)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -256,6 +280,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
 
   if (warp < TC_PRODUCERS / 32) {
     // ================= producers: cp.async (LDGSTS) ring, depth stages-1, in-place hi/lo split ==========
+    // All ring / row bookkeeping is incremental 32-bit arithmetic: the 64-bit `q % stages` and the per-tile
+    // (node, m) divisions of the first version cost ~1,000 clk per k-block on this (serial) path.
     const int tid = threadIdx.x;
     const int c = tid & 7;                  // 16 B chunk inside the 128 B k-block row
     const long long total_q = my_items * P.KB;
@@ -270,44 +296,53 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
       bulk_g2s(smem_u32(bres), bimg_nt, bytes, bfull_bar);
       mbar_arrive(bfull_bar);
     }
-    long long q_i = 0, it_i = 0; int kb_i = 0;
+    long long q_i = 0; int kb_i = 0, slot_i = 0, par_i = 0; uint32_t ph_i = 0;
+    RowWalk rw;                               // this thread's first row of the tile; the other three are 32 rows apart
+    rw.init((long long)bx * TC_BM + (tid >> 3), g.R, (long long)gx * TC_BM);
+    const int s32n = 32 / g.R, s32m = 32 % g.R;
     const float* rowp[4];
-    auto set_rows = [&](long long it) {
-      const long long mt = bx + it * (long long)gx;
+    auto set_rows = [&]() {
+      RowWalk t = rw;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const long long r = mt * TC_BM + i * 32 + (tid >> 3);
-        rowp[i] = (r < g.M) ? g.A + row_offset(r, g.R, g.sAn, g.sAm) : nullptr;
+        rowp[i] = (t.row(g.R) < g.M) ? g.A + t.off(g.sAn, g.sAm) : nullptr;
+        t.add(g.R, s32n, s32m);
       }
     };
-    if (total_q > 0) set_rows(0);
+    if (total_q > 0) set_rows();
+    const uint32_t dst_off = (uint32_t)((tid >> 3) * 128 + ((c ^ ((tid >> 3) & 7)) << 4));    // + i * 32 rows * 128 B
     auto issue = [&]() {
       if (q_i < total_q) {
-        const int slot = (int)(q_i % P.stages);
-        const uint32_t ph = (uint32_t)((q_i / P.stages) & 1);
-        mbar_wait(empty_bar(slot), ph ^ 1);
-        uint8_t* sbase = smem + (size_t)slot * stage_bytes;
+        mbar_wait(empty_bar(slot_i), ph_i ^ 1);
+        if (warp == 0) DBG(0, q_i - D, 5);
+        const uint32_t sbase = smem_u32(smem) + (uint32_t)slot_i * stage_bytes;
         if (!P.resident && tid == 0) {
-          mbar_expect_tx(full_bar(slot), 2 * b_bytes);
-          bulk_g2s(smem_u32(sbase + 2 * a_bytes), bimg_nt + (size_t)kb_i * (size_t)(2 * P.Nt * 32), 2 * b_bytes,
-                   full_bar(slot));
+          mbar_expect_tx(full_bar(par_i, slot_i), 2 * b_bytes);
+          bulk_g2s(sbase + 2 * a_bytes, bimg_nt + (size_t)kb_i * (size_t)(2 * P.Nt * 32), 2 * b_bytes,
+                   full_bar(par_i, slot_i));
         }
         const int k = kb_i * TC_BK + c * 4;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const int row = i * 32 + (tid >> 3);
-          const uint32_t dst = smem_u32(sbase) + row * 128 + ((c ^ (row & 7)) << 4);
+          const uint32_t dst = sbase + dst_off + i * (32 * 128);     // (row & 7) does not depend on i (32 rows apart)
           const bool ok = rowp[i] != nullptr && k < g.K;
           const float* src = ok ? rowp[i] + k : g.A;
           const uint32_t nbytes = ok ? 16u : 0u;        // src-size 0 -> zero fill
           asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
         }
+        if (warp == 0) DBG(0, q_i - D, 6);
         ++q_i;
-        if (++kb_i == P.KB) { kb_i = 0; ++it_i; if (q_i < total_q) set_rows(it_i); }
+        if (++slot_i == P.stages) { slot_i = 0; ph_i ^= 1; }
+        if (++kb_i == P.KB) {
+          kb_i = 0; par_i ^= 1;
+          rw.next(g.R);
+          if (q_i < total_q) set_rows();
+        }
       }
       asm volatile("cp.async.commit_group;" ::: "memory");
     };
     for (int d = 0; d < D; ++d) issue();
+    int slot = 0, kb_q = 0, par_q = 0;
     for (long long q = 0; q < total_q; ++q) {
       // groups q .. q+D-1 are outstanding: allow the newest D-1 to stay in flight -> k-block q has landed
       if (D == 1) asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -315,48 +350,58 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
       else if (D == 3) asm volatile("cp.async.wait_group 2;" ::: "memory");
       else asm volatile("cp.async.wait_group 3;" ::: "memory");
       if (warp == 0) DBG(0, q, 1);
-      const int slot = (int)(q % P.stages);
-      uint8_t* sbase = smem + (size_t)slot * stage_bytes;
+      const uint32_t sbase = smem_u32(smem) + (uint32_t)slot * stage_bytes + dst_off;
+      float4 v[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) v[i] = lds128(sbase + i * (32 * 128));
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        const int row = i * 32 + (tid >> 3);
-        const uint32_t off = row * 128 + ((c ^ (row & 7)) << 4);
-        const uint32_t sa = smem_u32(sbase) + off;
-        const float4 v = lds128(sa);
         float4 hi, lo;
-        hi.x = __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u); lo.x = v.x - hi.x;
-        hi.y = __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u); lo.y = v.y - hi.y;
-        hi.z = __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u); lo.z = v.z - hi.z;
-        hi.w = __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u); lo.w = v.w - hi.w;
-        sts128(sa, hi);
-        sts128(sa + a_bytes, lo);
+        hi.x = __uint_as_float(__float_as_uint(v[i].x) & 0xFFFFE000u); lo.x = v[i].x - hi.x;
+        hi.y = __uint_as_float(__float_as_uint(v[i].y) & 0xFFFFE000u); lo.y = v[i].y - hi.y;
+        hi.z = __uint_as_float(__float_as_uint(v[i].z) & 0xFFFFE000u); lo.z = v[i].z - hi.z;
+        hi.w = __uint_as_float(__float_as_uint(v[i].w) & 0xFFFFE000u); lo.w = v[i].w - hi.w;
+        sts128(sbase + i * (32 * 128), hi);
+        sts128(sbase + i * (32 * 128) + a_bytes, lo);
       }
+      if (warp == 0) DBG(0, q, 3);
       if (!(P.mode & 8)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> UMMA (async proxy)
-      mbar_arrive(full_bar(slot));                                  // 128 arrivals (+ B bytes) complete the phase
+      if (warp == 0) DBG(0, q, 4);
+      mbar_arrive(full_bar(par_q, slot));                           // 256 arrivals (+ B bytes) complete the phase
       if (warp == 0) DBG(0, q, 2);
+      if (++slot == P.stages) slot = 0;
+      if (++kb_q == P.KB) { kb_q = 0; par_q ^= 1; }
       issue();                                                      // refill: k-block q + D (blocks only on MMA back-pressure)
       if (warp == 0) DBG(0, q, 0);
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
-  } else if (warp == TC_MMA_WARP) {
-    // ================= MMA issuer =================
+  } else if (warp >= TC_MMA2_WARP) {
+    // ================= MMA issuers: warp 16 takes the even row tiles (TMEM buffer 0), warp 17 the odd ones =========
+    // One thread sustains one tcgen05.mma per ~50 clk and ~270 clk per tcgen05.commit (tools/mma_rate.cu): at
+    // K <= 64 that issue time, not the tensor pipe, bounded a tile, so two warps issue alternate tiles.
+    const int w = warp - TC_MMA2_WARP;
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(P.Nt >> 3) << 17) | ((uint32_t)(TC_BM >> 4) << 24);
-    int stage = 0; uint32_t phase = 0;
-    if (P.resident && my_items > 0) mbar_wait(bfull_bar, 0);
-    for (long long it = 0; it < my_items; ++it) {
-      const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
+    // ring position of k-block w * KB, the advance over the other warp's tile, and the parity this warp expects next
+    // on each of its full barriers (bit s: slot s)
+    int stage = (w * P.KB) % P.stages;
+    const int skip_s = P.KB % P.stages;
+    uint32_t pbits = 0;
+    if (P.resident && my_items > w) mbar_wait(bfull_bar, 0);
+    const uint32_t d_tmem = tmem_base + (uint32_t)w * 256;
+    uint32_t aphase = 0;
+    for (long long it = w; it < my_items; it += 2) {
       DBG(1, it, 0);
-      mbar_wait(tempty_bar(ab), aphase ^ 1);
+      mbar_wait(tempty_bar(w), aphase ^ 1);
       DBG(1, it, 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      const uint32_t d_tmem = tmem_base + (uint32_t)ab * 256;
       for (int kb = 0; kb < P.KB; ++kb) {
-        mbar_wait(full_bar(stage), phase);
+        mbar_wait(full_bar(w, stage), (pbits >> stage) & 1u);
+        pbits ^= 1u << stage;
         if (kb == 0) DBG(1, it, 2);
         if (kb == P.KB - 1) DBG(1, it, 3);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         if (lane == 0) {
-          const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+          const uint32_t sa = smem_u32(smem) + (uint32_t)stage * stage_bytes;
           const uint32_t sb = P.resident ? smem_u32(bres) + (uint32_t)kb * 2 * b_bytes : sa + 2 * a_bytes;
           const uint64_t a_hi = make_desc(sa), a_lo = make_desc(sa + a_bytes);
           const uint64_t b_hi = make_desc(sb), b_lo = make_desc(sb + b_bytes);
@@ -373,42 +418,52 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
             }
           }
           umma_commit(empty_bar(stage));
-          if (kb == P.KB - 1) umma_commit(tfull_bar(ab));
+          if (kb == P.KB - 1) umma_commit(tfull_bar(w));
         }
         __syncwarp();
         if (kb == P.KB - 1) DBG(1, it, 4);
-        if (++stage == P.stages) { stage = 0; phase ^= 1; }
+        if (++stage == P.stages) stage = 0;
       }
+      aphase ^= 1;
+      stage += skip_s;                                  // the other warp's tile
+      if (stage >= P.stages) stage -= P.stages;
     }
   } else {
-    // ================= epilogue (warps 4..7 -> TMEM lanes 32*(warp-4) ..) =================
-    const int ew = warp - TC_EPI_WARP0;
-    uint8_t* tb = epi_buf + ew * (32 * 128);             // this warp's 32 rows x 128 B transpose buffer
+    // ================= epilogue: warps 8..15, TMEM lanes 32 * (warp % 4) .., column chunks split even / odd ========
+    const int ew = (warp - TC_EPI_WARP0) & 3, half = (warp - TC_EPI_WARP0) >> 2;
+    uint8_t* tb = epi_buf + (warp - TC_EPI_WARP0) * (32 * 128);   // this warp's 32 rows x 128 B transpose buffer
     const int n0 = nt * P.Nt;
     const int ncols = min(P.Nt, g.N - n0);
-    const int sub = lane >> 3, ch = lane & 7;            // read phase: row 4*i + sub, 16 B chunk ch
+    const int sub = lane >> 3;                           // read phase: row 4*i + sub, 16 B chunk lane & 7
+    RowWalk rw;                               // row `sub` of this warp's 32; the other seven are 4 rows apart
+    rw.init((long long)bx * TC_BM + ew * 32 + sub, g.R, (long long)gx * TC_BM);
+    const int s4n = 4 / g.R, s4m = 4 % g.R;
     for (long long it = 0; it < my_items; ++it) {
-      const long long mt = bx + it * (long long)gx;
       const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
       long long roff[8];
+      {
+        RowWalk t = rw;
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const long long r = mt * TC_BM + ew * 32 + 4 * i + sub;
-        roff[i] = (r < g.M) ? row_offset(r, g.R, g.sCn, g.sCm) : -1;
+        for (int i = 0; i < 8; ++i) {
+          roff[i] = (t.row(g.R) < g.M) ? t.off(g.sCn, g.sCm) : -1;
+          t.add(g.R, s4n, s4m);
+        }
+        rw.next(g.R);
       }
-      if (ew == 0) DBG(2, it, 0);
+      if (warp == TC_EPI_WARP0) DBG(2, it, 0);
       mbar_wait(tfull_bar(ab), aphase);
-      if (ew == 0) DBG(2, it, 1);
+      if (warp == TC_EPI_WARP0) DBG(2, it, 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      tc_epilogue_tile<EPI>(g, tmem_base + (uint32_t)(ab * 256), tb, ew, lane, roff, n0, ncols, P.vec4, P.mode);
-      if (ew == 0) DBG(2, it, 3);
+      tc_epilogue_tile<EPI>(g, tmem_base + (uint32_t)(ab * 256), tb, ew, lane, roff, n0, ncols, P.vec4, P.mode, 0,
+                            32 * half, 64);
+      if (warp == TC_EPI_WARP0) DBG(2, it, 3);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       mbar_arrive(tempty_bar(ab));
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
-  if (warp == TC_MMA_WARP) {
+  if (warp == TC_MMA2_WARP) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
   }
 }
@@ -703,7 +758,7 @@ static int tc_prepare(const sevenn_gemm_args* args, const float* Bimg, TcParams&
   P.Bimg = Bimg;
   P.m_tiles = (g.M + TC_BM - 1) / TC_BM;
   const size_t b_bytes = (size_t)P.Nt * 128;
-  const size_t budget = 227 * 1024 - 1024 - TC_EPI_BYTES - 256;
+  const size_t budget = 227 * 1024 - 1024 - TC_EPI8_BYTES - 256;
   const size_t stage_bytes = 2 * TC_BM * 128 + (P.resident ? 0 : 2 * b_bytes);
   const size_t fixed = P.resident ? (size_t)P.KB * 2 * b_bytes : 0;
   int stages = (int)((budget - fixed) / stage_bytes);
@@ -718,7 +773,7 @@ static int tc_prepare(const sevenn_gemm_args* args, const float* Bimg, TcParams&
   static int tmema_ok = -1;
   if (tmema_ok < 0) { const char* e = getenv("SEVENN_TC_TMEMA"); tmema_ok = e ? atoi(e) : 1; }
   *tca = tmema_ok && !P.resident && P.n_tiles == 1 && P.Nt <= 64 && P.KB >= 4;
-  *smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * stages + 5) + 16;
+  *smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI8_BYTES + 8 * (3 * stages + 5) + 16;
   if (*tca)
     *smem = 1024 + (size_t)TCA_NS * 2 * b_bytes + (size_t)2 * TCA_SLOTS * TC_BM * 128 + TC_EPI_BYTES + 8 * (2 * TCA_NS + 5) + 16;
   return 0;
@@ -743,6 +798,12 @@ static int tc_set_smem_attr(K kern, bool* done) {
 extern "C" int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args, const float* const* Bimgs, void* stream) {
   if (n <= 0) return 0;
   if (n > TC_MAX_GROUP) return SEVENN_ERR_BAD_ARG;
+  if (n == 1 && args[0].M > 0 && args[0].N > 0) {      // a problem on its own may take the TMEM-A kernel (large K, N <= 64)
+    TcParams P; size_t sm; bool tca;
+    int rc = tc_prepare(&args[0], Bimgs[0], P, &sm, &tca);
+    if (rc) return rc;
+    if (tca) return sevenn_gemm_tc(&args[0], Bimgs[0], stream);
+  }
   if (n > 1) {
     // Sharing a launch pays for problems that cannot fill the GPU on their own (their launch / TMEM-allocation /
     // pipeline-fill latencies overlap).  A problem with >= 2 tiles per SM runs alone on all SMs instead: a static
@@ -781,7 +842,7 @@ extern "C" int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args, const
     const size_t b_bytes = (size_t)G.p[G.n].Nt * 128;
     const size_t stage_bytes = 2 * TC_BM * 128 + (G.p[G.n].resident ? 0 : 2 * b_bytes);
     const size_t fixed = G.p[G.n].resident ? (size_t)G.p[G.n].KB * 2 * b_bytes : 0;
-    sm = 1024 + (size_t)G.p[G.n].stages * stage_bytes + fixed + TC_EPI_BYTES + 8 * (2 * G.p[G.n].stages + 5) + 16;
+    sm = 1024 + (size_t)G.p[G.n].stages * stage_bytes + fixed + TC_EPI8_BYTES + 8 * (3 * G.p[G.n].stages + 5) + 16;
     if (sm > smem) smem = sm;
     tiles[G.n] = G.p[G.n].m_tiles * G.p[G.n].n_tiles;
     total += tiles[G.n];

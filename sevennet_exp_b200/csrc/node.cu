@@ -97,6 +97,137 @@ GKERNEL(gate_bwd_kernel)(const float* __restrict__ pre, int din, const float* __
   }
 }
 
+#ifndef SEVENN_EMU
+// 16-byte variants (every multiplicity, offset and stride a multiple of 4, rows 16 B aligned -- SevenNet-0 / l3i5 and
+// any model with channel counts divisible by 4).  threadIdx.x owns one float4 column of the row for the whole launch:
+// the piece lookup and its integer divisions happen once per thread instead of once per element, threadIdx.y /
+// blockIdx.x walk the rows.  Same expressions in the same order as the scalar kernels above => same bits.
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+
+__global__ void __launch_bounds__(512) gate_fwd_v4_kernel(const float* __restrict__ pre, int din, float* __restrict__ out,
+                                                          int dout, long long n, const GateTable T) {
+  int c = (int)threadIdx.x * 4, q = 0;
+  for (; q < T.n; ++q) {
+    const int sz = T.p[q].mul * (2 * T.p[q].l + 1);
+    if (c < sz) break;
+    c -= sz;
+  }
+  if (q == T.n) return;
+  const sevenn_gate_piece P = T.p[q];
+  const int m = c / P.mul, u = c % P.mul;
+  const int in = P.in_off + (P.kind ? m * P.in_stride : 0) + u, gt = P.gate_off + u, o = P.out_off + m * P.out_stride + u;
+  const int kind = P.kind, act = P.act; const float cst = P.cst;
+  const long long step = (long long)gridDim.x * blockDim.y;
+  for (long long i = blockIdx.x * (long long)blockDim.y + threadIdx.y; i < n; i += 2 * step) {
+    const long long j = i + step < n ? i + step : i;            // second row of the pair (repeats row i at the tail)
+    const float4 xi = ld4(pre + i * din + in), xj = ld4(pre + j * din + in);
+    float4 gi = xi, gj = xj;
+    if (kind != 0) { gi = ld4(pre + i * din + gt); gj = ld4(pre + j * din + gt); }
+    float4 vi, vj;
+    if (kind == 0) {
+      vi = make_float4(cst * act_f(act, xi.x), cst * act_f(act, xi.y), cst * act_f(act, xi.z), cst * act_f(act, xi.w));
+      vj = make_float4(cst * act_f(act, xj.x), cst * act_f(act, xj.y), cst * act_f(act, xj.z), cst * act_f(act, xj.w));
+    } else {
+      vi = make_float4(cst * act_f(act, gi.x) * xi.x, cst * act_f(act, gi.y) * xi.y, cst * act_f(act, gi.z) * xi.z,
+                       cst * act_f(act, gi.w) * xi.w);
+      vj = make_float4(cst * act_f(act, gj.x) * xj.x, cst * act_f(act, gj.y) * xj.y, cst * act_f(act, gj.z) * xj.z,
+                       cst * act_f(act, gj.w) * xj.w);
+    }
+    st4(out + i * dout + o, vi);
+    if (j != i) st4(out + j * dout + o, vj);
+  }
+}
+
+// Backward: threadIdx.x owns one float4 of the dpre row, so every thread does the same small amount of work (2-3 loads,
+// one store).  The gate-channel gradient needs sum_m dout[m,u] x[m,u]: the threads of the gated components leave their
+// products in shared memory and the gate-channel thread adds them in m order after the barrier (double buffered by
+// iteration parity: one __syncthreads per row group).  A thread per channel that walked the 2l+1 components itself
+// (first version) ran at 2.5 TB/s: few, heavy threads and not enough loads in flight.
+__global__ void __launch_bounds__(512, 3) gate_bwd_v4_kernel(const float* __restrict__ pre, int din, const float* __restrict__ dout_,
+                                                             int dout, float* __restrict__ dpre, long long n, const GateTable T,
+                                                             int npart) {
+  extern __shared__ float4 gate_part[];                 // [2][blockDim.y][npart]
+  const int c = (int)threadIdx.x * 4;
+  // role of this column: 0 scalar, 1 gated component, 2 gate channel, -1 none
+  int role = -1, go_off = 0, gate_off = 0, slot = 0, nm = 0, mstride = 0, act = 0; float cst = 0.f;
+  for (int q = 0, pbase = 0; q < T.n; ++q) {
+    const sevenn_gate_piece& P = T.p[q];
+    const int pnm = 2 * P.l + 1, w = P.mul / 4;
+    if (P.kind == 0) {
+      if (c >= P.in_off && c < P.in_off + P.mul) { role = 0; go_off = P.out_off + (c - P.in_off); act = P.act; cst = P.cst; }
+    } else {
+      if (c >= P.gate_off && c < P.gate_off + P.mul) {
+        role = 2; slot = pbase + (c - P.gate_off) / 4; nm = pnm; mstride = w; act = P.act; cst = P.cst;
+      } else if (c >= P.in_off && c < P.in_off + pnm * P.in_stride) {
+        const int m = (c - P.in_off) / P.in_stride, u = (c - P.in_off) % P.in_stride;
+        if (u < P.mul) {
+          role = 1; go_off = P.out_off + m * P.out_stride + u; gate_off = P.gate_off + u; slot = pbase + m * w + u / 4;
+          act = P.act; cst = P.cst;
+        }
+      }
+      pbase += pnm * w;
+    }
+  }
+  const int rb = (int)blockDim.y, ty = (int)threadIdx.y;
+  int buf = 0;
+  for (long long base = blockIdx.x * (long long)rb; base < n; base += (long long)gridDim.x * rb, buf ^= 1) {
+    const long long i = base + ty;
+    const bool ok = i < n;
+    float4* part = gate_part + ((size_t)buf * rb + ty) * npart;
+    float4 gp = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (ok && role == 0) {
+      const float4 x = ld4(pre + i * din + c), g = ld4(dout_ + i * dout + go_off);
+      st4(dpre + i * din + c, make_float4(g.x * cst * dact_f(act, x.x), g.y * cst * dact_f(act, x.y),
+                                          g.z * cst * dact_f(act, x.z), g.w * cst * dact_f(act, x.w)));
+    } else if (ok && role == 1) {
+      const float4 x = ld4(pre + i * din + c), g = ld4(dout_ + i * dout + go_off), p = ld4(pre + i * din + gate_off);
+      const float4 gate = make_float4(cst * act_f(act, p.x), cst * act_f(act, p.y), cst * act_f(act, p.z), cst * act_f(act, p.w));
+      st4(dpre + i * din + c, make_float4(g.x * gate.x, g.y * gate.y, g.z * gate.z, g.w * gate.w));
+      part[slot] = make_float4(g.x * x.x, g.y * x.y, g.z * x.z, g.w * x.w);
+    } else if (ok && role == 2) {
+      gp = ld4(pre + i * din + c);
+    }
+    __syncthreads();
+    if (ok && role == 2) {
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int m = 0; m < nm; ++m) {
+        const float4 p = part[slot + m * mstride];
+        acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+      }
+      st4(dpre + i * din + c, make_float4(acc.x * cst * dact_f(act, gp.x), acc.y * cst * dact_f(act, gp.y),
+                                          acc.z * cst * dact_f(act, gp.z), acc.w * cst * dact_f(act, gp.w)));
+    }
+  }
+}
+
+// the 16-byte kernels apply when every piece is 4-aligned; `cols` = float4 columns per row (threadIdx.x extent)
+static bool gate_v4_ok(const GateTable& T, int din, int dout, const void* a, const void* b, const void* c, bool bwd, int* cols,
+                       int* npart) {
+  if ((din & 3) || (dout & 3) || ((uintptr_t)a & 15) || ((uintptr_t)b & 15) || ((uintptr_t)c & 15)) return false;
+  int tot = 0, np = 0;
+  for (int k = 0; k < T.n; ++k) {
+    const sevenn_gate_piece& P = T.p[k];
+    if (P.l < 0 || P.l > 4 || (P.kind && P.l == 0) || (P.mul & 3) || (P.in_off & 3) || (P.out_off & 3) ||
+        (P.kind && ((P.gate_off & 3) || (P.in_stride & 3) || (P.out_stride & 3) || P.in_stride < P.mul)))
+      return false;
+    tot += P.mul * (2 * P.l + 1);
+    if (P.kind) np += (P.mul / 4) * (2 * P.l + 1);
+  }
+  if (tot != dout) return false;
+  *cols = (bwd ? din : dout) / 4;
+  *npart = np;
+  return *cols >= 1 && *cols <= 512;
+}
+static void gate_v4_dims(int cols, long long n, dim3* grid, dim3* block) {
+  int by = 512 / cols; if (by > 8) by = 8; if (by < 1) by = 1;
+  long long g = (n + by - 1) / by;
+  const long long cap = 148LL * 8;
+  if (g > cap) g = cap;
+  *grid = dim3((unsigned)g); *block = dim3((unsigned)cols, (unsigned)by);
+}
+#endif
+
 static int load_gate(GateTable& T, const sevenn_gate_piece* pieces, int n_pieces) {
   if (n_pieces < 0 || n_pieces > SEVENN_MAX_GATE_PIECES) return SEVENN_ERR_BAD_ARG;
   T.n = n_pieces;
@@ -113,6 +244,14 @@ extern "C" int sevenn_gate_fwd(const float* pre, int din, float* out, int dout, 
                                const sevenn_gate_piece* pieces, int n_pieces, void* stream) {
   GateTable T; int rc = load_gate(T, pieces, n_pieces); if (rc) return rc;
   if (n <= 0) return 0;
+#ifndef SEVENN_EMU
+  int cols, npart;
+  if (gate_v4_ok(T, din, dout, pre, out, nullptr, false, &cols, &npart)) {
+    dim3 grid, block; gate_v4_dims(cols, n, &grid, &block);
+    gate_fwd_v4_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(pre, din, out, dout, n, T);
+    return LAUNCH_STATUS();
+  }
+#endif
   LAUNCH1D(gate_fwd_kernel, n * dout, stream)(pre, din, out, dout, n, T);
   return LAUNCH_STATUS();
 }
@@ -121,6 +260,15 @@ extern "C" int sevenn_gate_bwd(const float* pre, int din, const float* dout_, in
   GateTable T; int rc = load_gate(T, pieces, n_pieces); if (rc) return rc;
   if (n <= 0) return 0;
   int nch = 0; for (int k = 0; k < n_pieces; ++k) nch += pieces[k].mul;
+#ifndef SEVENN_EMU
+  int cols, npart;
+  if (gate_v4_ok(T, din, dout, pre, dout_, dpre, true, &cols, &npart)) {
+    dim3 grid, block; gate_v4_dims(cols, n, &grid, &block);
+    const size_t sm = (size_t)2 * block.y * (npart > 0 ? npart : 1) * sizeof(float4);
+    gate_bwd_v4_kernel<<<grid, block, sm, (cudaStream_t)stream>>>(pre, din, dout_, dout, dpre, n, T, npart);
+    return LAUNCH_STATUS();
+  }
+#endif
   LAUNCH1D(gate_bwd_kernel, n * nch, stream)(pre, din, dout_, dout, dpre, n, T, nch);
   return LAUNCH_STATUS();
 }
