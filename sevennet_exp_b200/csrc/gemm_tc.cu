@@ -29,7 +29,8 @@
 #define TC_BM 128
 #define TC_BK 32                      // fp32 per k-block = one 128 B swizzle row
 #define TC_PRODUCERS 256
-#define TC_THREADS 576                 // gemm_tc_kernel: 8 producer + 8 epilogue + 2 MMA-issuing warps
+#define TC_THREADS 608                 // gemm_tc_kernel: 8 producer + 8 epilogue + 2 MMA-issuing warps + B loader
+#define TC_BLOAD_WARP 18               // gemm_tc_kernel: streams the B images (TMA bulk copies) in streaming mode
 #define TC_MMA_WARP 12                 // gemm_tca_kernel (448 threads): warps 12, 13 issue
 #define TC_MMA2_WARP 16                // gemm_tc_kernel: warps 16, 17 issue (even / odd row tiles)
 #define TC_EPI_WARP0 8
@@ -59,6 +60,9 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {   // no arrival: only raises tx-count
   asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
@@ -252,15 +256,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
   auto full_bar = [&](int w, int s) { return bar0 + 8u * (w * P.stages + s); };
   auto empty_bar = [&](int s) { return bar0 + 8u * (2 * P.stages + s); };
   auto tfull_bar = [&](int b) { return bar0 + 8u * (3 * P.stages + b); };
-  auto tempty_bar = [&](int b) { return bar0 + 8u * (3 * P.stages + 2 + b); };
-  const uint32_t bfull_bar = bar0 + 8u * (3 * P.stages + 4);
-  uint32_t* tmem_slot = (uint32_t*)(bars + 3 * P.stages + 5);
+  auto tempty_bar = [&](int b) { return bar0 + 8u * (3 * P.stages + 4 + b); };
+  const uint32_t bfull_bar = bar0 + 8u * (3 * P.stages + 8);
+  uint32_t* tmem_slot = (uint32_t*)(bars + 3 * P.stages + 9);
+  // accumulator buffers in TMEM: four of 128 columns when the tile is narrow enough (each MMA-issuing warp then
+  // alternates between two, so its next tile does not wait for the epilogue of its previous one), else two of 256
+  const int nbuf = P.Nt <= 128 ? 4 : 2;
+  const uint32_t buf_cols = 512u / (uint32_t)nbuf;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < P.stages; ++s) {
-      mbar_init(full_bar(0, s), TC_PRODUCERS); mbar_init(full_bar(1, s), TC_PRODUCERS); mbar_init(empty_bar(s), 1);
+      const uint32_t arrivals = TC_PRODUCERS + (P.resident ? 0u : 1u);     // + the B loader's arrive.expect_tx
+      mbar_init(full_bar(0, s), arrivals); mbar_init(full_bar(1, s), arrivals); mbar_init(empty_bar(s), 1);
     }
-    for (int b = 0; b < 2; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 256); }
+    for (int b = 0; b < 4; ++b) { mbar_init(tfull_bar(b), 1); mbar_init(tempty_bar(b), 256); }
     mbar_init(bfull_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -279,24 +288,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
   const float* bimg_nt = P.Bimg + (size_t)nt * P.KB * (size_t)(2 * P.Nt * 32);
 
   if (warp < TC_PRODUCERS / 32) {
-    // ================= producers: cp.async (LDGSTS) ring, depth stages-1, in-place hi/lo split ==========
-    // All ring / row bookkeeping is incremental 32-bit arithmetic: the 64-bit `q % stages` and the per-tile
-    // (node, m) divisions of the first version cost ~1,000 clk per k-block on this (serial) path.
+    // ================= producers: global -> registers -> (hi, lo) split -> shared memory ===================
+    // Each thread owns one 16 B chunk of four rows of every k-block.  TC_RD k-blocks are in flight in registers
+    // (plain 16 B read-only loads); when one has landed it is split in registers and stored once as the two
+    // SWIZZLE_128B K-major operand tiles.  The first version staged the raw rows in shared memory with cp.async and
+    // split them in place: 16 KB in + 16 KB out + 32 KB in per k-block, and the LDGSTS issue itself cost ~1,000 clk
+    // per k-block (pipeline traces, profiles/r02_gemm_tc_traces.txt); this way shared memory sees the 32 KB once.
+    // All ring / row bookkeeping is incremental 32-bit arithmetic (no division per k-block).
     const int tid = threadIdx.x;
     const int c = tid & 7;                  // 16 B chunk inside the 128 B k-block row
     const long long total_q = my_items * P.KB;
-    // k-blocks in flight per thread; one slot of slack so that the slot being refilled was released by a
-    // tcgen05.commit issued a full iteration earlier (its round trip is off the critical path)
-    int D = P.stages > 2 ? P.stages - 2 : 1;
-    if (P.dslack == 0) D = P.stages - 1;
-    if (D > 4) D = 4;
     if (P.resident && tid == 0 && my_items > 0) {
       const uint32_t bytes = (uint32_t)P.KB * 2 * b_bytes;
       mbar_expect_tx(bfull_bar, bytes);
       bulk_g2s(smem_u32(bres), bimg_nt, bytes, bfull_bar);
       mbar_arrive(bfull_bar);
     }
-    long long q_i = 0; int kb_i = 0, slot_i = 0, par_i = 0; uint32_t ph_i = 0;
+    long long q_i = 0; int kb_i = 0;
     RowWalk rw;                               // this thread's first row of the tile; the other three are 32 rows apart
     rw.init((long long)bx * TC_BM + (tid >> 3), g.R, (long long)gx * TC_BM);
     const int s32n = 32 / g.R, s32m = 32 % g.R;
@@ -311,49 +319,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
     };
     if (total_q > 0) set_rows();
     const uint32_t dst_off = (uint32_t)((tid >> 3) * 128 + ((c ^ ((tid >> 3) & 7)) << 4));    // + i * 32 rows * 128 B
-    auto issue = [&]() {
-      if (q_i < total_q) {
-        mbar_wait(empty_bar(slot_i), ph_i ^ 1);
-        if (warp == 0) DBG(0, q_i - D, 5);
-        const uint32_t sbase = smem_u32(smem) + (uint32_t)slot_i * stage_bytes;
-        if (!P.resident && tid == 0) {
-          mbar_expect_tx(full_bar(par_i, slot_i), 2 * b_bytes);
-          bulk_g2s(sbase + 2 * a_bytes, bimg_nt + (size_t)kb_i * (size_t)(2 * P.Nt * 32), 2 * b_bytes,
-                   full_bar(par_i, slot_i));
-        }
-        const int k = kb_i * TC_BK + c * 4;
+    // issue the loads of k-block q_i into v (never waits: the ring slot is only needed when the k-block is stored)
+    auto load = [&](float4 (&v)[4]) {
+      if (q_i >= total_q) return;
+      const int k = kb_i * TC_BK + c * 4;
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const uint32_t dst = sbase + dst_off + i * (32 * 128);     // (row & 7) does not depend on i (32 rows apart)
-          const bool ok = rowp[i] != nullptr && k < g.K;
-          const float* src = ok ? rowp[i] + k : g.A;
-          const uint32_t nbytes = ok ? 16u : 0u;        // src-size 0 -> zero fill
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nbytes) : "memory");
-        }
-        if (warp == 0) DBG(0, q_i - D, 6);
-        ++q_i;
-        if (++slot_i == P.stages) { slot_i = 0; ph_i ^= 1; }
-        if (++kb_i == P.KB) {
-          kb_i = 0; par_i ^= 1;
-          rw.next(g.R);
-          if (q_i < total_q) set_rows();
-        }
+      for (int i = 0; i < 4; ++i) {
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rowp[i] != nullptr && k < g.K)
+          asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(v[i].x), "=f"(v[i].y), "=f"(v[i].z), "=f"(v[i].w) : "l"(rowp[i] + k));
       }
-      asm volatile("cp.async.commit_group;" ::: "memory");
+      ++q_i;
+      if (++kb_i == P.KB) {
+        kb_i = 0;
+        rw.next(g.R);
+        if (q_i < total_q) set_rows();
+      }
     };
-    for (int d = 0; d < D; ++d) issue();
-    int slot = 0, kb_q = 0, par_q = 0;
-    for (long long q = 0; q < total_q; ++q) {
-      // groups q .. q+D-1 are outstanding: allow the newest D-1 to stay in flight -> k-block q has landed
-      if (D == 1) asm volatile("cp.async.wait_group 0;" ::: "memory");
-      else if (D == 2) asm volatile("cp.async.wait_group 1;" ::: "memory");
-      else if (D == 3) asm volatile("cp.async.wait_group 2;" ::: "memory");
-      else asm volatile("cp.async.wait_group 3;" ::: "memory");
+    int slot = 0, kb_q = 0, par_q = 0; uint32_t ph_q = 0;
+    long long q = 0;
+    // split k-block q (in v) into its ring slot and publish it
+    auto store = [&](const float4 (&v)[4]) {
       if (warp == 0) DBG(0, q, 1);
+      mbar_wait(empty_bar(slot), ph_q ^ 1);                         // slot released by the MMAs of k-block q - stages
+      if (warp == 0) DBG(0, q, 5);
       const uint32_t sbase = smem_u32(smem) + (uint32_t)slot * stage_bytes + dst_off;
-      float4 v[4];
-#pragma unroll
-      for (int i = 0; i < 4; ++i) v[i] = lds128(sbase + i * (32 * 128));
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         float4 hi, lo;
@@ -366,16 +357,35 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
       }
       if (warp == 0) DBG(0, q, 3);
       if (!(P.mode & 8)) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> UMMA (async proxy)
-      if (warp == 0) DBG(0, q, 4);
       mbar_arrive(full_bar(par_q, slot));                           // 256 arrivals (+ B bytes) complete the phase
       if (warp == 0) DBG(0, q, 2);
-      if (++slot == P.stages) slot = 0;
+      ++q;
+      if (++slot == P.stages) { slot = 0; ph_q ^= 1; }
       if (++kb_q == P.KB) { kb_q = 0; par_q ^= 1; }
-      issue();                                                      // refill: k-block q + D (blocks only on MMA back-pressure)
-      if (warp == 0) DBG(0, q, 0);
+    };
+    // register ring of three k-blocks
+    float4 r0[4], r1[4], r2[4];
+    load(r0); load(r1); load(r2);
+    while (q < total_q) {
+      store(r0); load(r0);
+      if (q < total_q) { store(r1); load(r1); }
+      if (q < total_q) { store(r2); load(r2); }
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-  } else if (warp >= TC_MMA2_WARP) {
+  } else if (warp == TC_BLOAD_WARP) {
+    // ================= B loader (streaming mode): one k-block image per ring slot, as far ahead as the ring allows ===
+    if (!P.resident && lane == 0) {
+      const long long total_q = my_items * P.KB;
+      int slot = 0, kb = 0, par = 0; uint32_t ph = 0;
+      for (long long q = 0; q < total_q; ++q) {
+        mbar_wait(empty_bar(slot), ph ^ 1);
+        const uint32_t sb = smem_u32(smem) + (uint32_t)slot * stage_bytes + 2 * a_bytes;
+        mbar_arrive_expect_tx(full_bar(par, slot), 2 * b_bytes);    // the 257th arrival of the phase, + the image bytes
+        bulk_g2s(sb, bimg_nt + (size_t)kb * (size_t)(2 * P.Nt * 32), 2 * b_bytes, full_bar(par, slot));
+        if (++slot == P.stages) { slot = 0; ph ^= 1; }
+        if (++kb == P.KB) { kb = 0; par ^= 1; }
+      }
+    }
+  } else if (warp == TC_MMA2_WARP || warp == TC_MMA2_WARP + 1) {
     // ================= MMA issuers: warp 16 takes the even row tiles (TMEM buffer 0), warp 17 the odd ones =========
     // One thread sustains one tcgen05.mma per ~50 clk and ~270 clk per tcgen05.commit (tools/mma_rate.cu): at
     // K <= 64 that issue time, not the tensor pipe, bounded a tile, so two warps issue alternate tiles.
@@ -387,11 +397,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
     const int skip_s = P.KB % P.stages;
     uint32_t pbits = 0;
     if (P.resident && my_items > w) mbar_wait(bfull_bar, 0);
-    const uint32_t d_tmem = tmem_base + (uint32_t)w * 256;
-    uint32_t aphase = 0;
+    // this warp's buffers: w (and w + 2 when there are four); eph bit b = parity expected next on tempty[b]
+    int ab = w; uint32_t eph = 0;
     for (long long it = w; it < my_items; it += 2) {
+      const uint32_t d_tmem = tmem_base + (uint32_t)ab * buf_cols;
       DBG(1, it, 0);
-      mbar_wait(tempty_bar(w), aphase ^ 1);
+      mbar_wait(tempty_bar(ab), ((eph >> ab) & 1u) ^ 1u);
+      eph ^= 1u << ab;
       DBG(1, it, 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       for (int kb = 0; kb < P.KB; ++kb) {
@@ -418,13 +430,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
             }
           }
           umma_commit(empty_bar(stage));
-          if (kb == P.KB - 1) umma_commit(tfull_bar(w));
+          if (kb == P.KB - 1) umma_commit(tfull_bar(ab));
         }
         __syncwarp();
         if (kb == P.KB - 1) DBG(1, it, 4);
         if (++stage == P.stages) stage = 0;
       }
-      aphase ^= 1;
+      if (nbuf == 4) ab ^= 2;
       stage += skip_s;                                  // the other warp's tile
       if (stage >= P.stages) stage -= P.stages;
     }
@@ -439,7 +451,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
     rw.init((long long)bx * TC_BM + ew * 32 + sub, g.R, (long long)gx * TC_BM);
     const int s4n = 4 / g.R, s4m = 4 % g.R;
     for (long long it = 0; it < my_items; ++it) {
-      const int ab = (int)(it & 1); const uint32_t aphase = (uint32_t)((it >> 1) & 1);
+      const int ab = (int)(it & (nbuf - 1)); const uint32_t aphase = (uint32_t)((it >> (nbuf == 4 ? 2 : 1)) & 1);
       long long roff[8];
       {
         RowWalk t = rw;
@@ -454,7 +466,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const TcGroup G)
       mbar_wait(tfull_bar(ab), aphase);
       if (warp == TC_EPI_WARP0) DBG(2, it, 1);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-      tc_epilogue_tile<EPI>(g, tmem_base + (uint32_t)(ab * 256), tb, ew, lane, roff, n0, ncols, P.vec4, P.mode, 0,
+      tc_epilogue_tile<EPI>(g, tmem_base + (uint32_t)ab * buf_cols, tb, ew, lane, roff, n0, ncols, P.vec4, P.mode, 0,
                             32 * half, 64);
       if (warp == TC_EPI_WARP0) DBG(2, it, 3);
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -693,16 +705,33 @@ __global__ void __launch_bounds__(TCA_THREADS, 1) gemm_tca_kernel(const TcParams
 }
 
 // geometry shared by the host-side image builder (engine.tc_weight_image) and the kernel
+// Shared memory left for the A ring and a resident B image: 227 KB - alignment - epilogue buffers - barriers.
+#define TC_SMEM_AVAIL (227 * 1024 - 1024 - TC_EPI8_BYTES - 256)
 static int tc_plan(int N, int K, int* Nt, int* n_tiles, int* KB, int* resident) {
   if (N <= 0 || K <= 0) return SEVENN_ERR_BAD_ARG;
   const int kb = (K + TC_BK - 1) / TC_BK;
-  int res = 0, nt = 0, tiles = 0;
-  for (int t = (N + 255) / 256;; ++t) {
-    nt = (((N + t - 1) / t) + 15) / 16 * 16;
-    if ((long long)kb * nt * 256 <= 84 * 1024) { res = 1; tiles = t; break; }
-    if (nt <= 64) break;
+  int res = 0, tiles = (N + 255) / 256, nt = (((N + tiles - 1) / tiles) + 15) / 16 * 16;
+  if ((long long)kb * nt * 256 + 2 * (2 * TC_BM * 128) <= TC_SMEM_AVAIL) {
+    res = 1;                        // whole [K, N] image resident next to a ring of >= 2 A stages: A is read once
+  } else if (N > 256) {
+    // wide outputs (radial MLP, N = 960): more column tiles until one tile's image fits beside >= 3 stages; A (K <= 64
+    // there) is re-read per column tile, which is small against the [128, N] output
+    for (int t = tiles;; ++t) {
+      const int n2 = (((N + t - 1) / t) + 15) / 16 * 16;
+      if ((long long)kb * n2 * 256 <= 84 * 1024) { res = 1; tiles = t; nt = n2; break; }
+      if (n2 <= 64) break;
+    }
   }
-  if (!res) { tiles = (N + 255) / 256; nt = (((N + tiles - 1) / tiles) + 15) / 16 * 16; }
+  { // experiments: SEVENN_TC_TILES=t forces t column tiles for N <= 256 (resident when the tile's image fits)
+    static int force = -1;
+    if (force < 0) { const char* e = getenv("SEVENN_TC_TILES"); force = e ? atoi(e) : 0; }
+    if (force > 0 && N <= 256) {
+      tiles = force; nt = (((N + tiles - 1) / tiles) + 15) / 16 * 16;
+      res = (long long)kb * nt * 256 + 2 * (2 * TC_BM * 128) <= TC_SMEM_AVAIL;
+    }
+  }
+  // otherwise: one column tile, B streamed per k-block (the node linears with K * N > 16 K: A read once; the first
+  // version split the columns until the image fitted and re-read A up to five times)
   *Nt = nt; *n_tiles = tiles; *KB = kb; *resident = res;
   return 0;
 }
@@ -758,7 +787,7 @@ static int tc_prepare(const sevenn_gemm_args* args, const float* Bimg, TcParams&
   P.Bimg = Bimg;
   P.m_tiles = (g.M + TC_BM - 1) / TC_BM;
   const size_t b_bytes = (size_t)P.Nt * 128;
-  const size_t budget = 227 * 1024 - 1024 - TC_EPI8_BYTES - 256;
+  const size_t budget = TC_SMEM_AVAIL;
   const size_t stage_bytes = 2 * TC_BM * 128 + (P.resident ? 0 : 2 * b_bytes);
   const size_t fixed = P.resident ? (size_t)P.KB * 2 * b_bytes : 0;
   int stages = (int)((budget - fixed) / stage_bytes);
@@ -772,8 +801,9 @@ static int tc_prepare(const sevenn_gemm_args* args, const float* Bimg, TcParams&
   P.dbg = nullptr;
   static int tmema_ok = -1;
   if (tmema_ok < 0) { const char* e = getenv("SEVENN_TC_TMEMA"); tmema_ok = e ? atoi(e) : 1; }
-  *tca = tmema_ok && !P.resident && P.n_tiles == 1 && P.Nt <= 64 && P.KB >= 4;
-  *smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI8_BYTES + 8 * (3 * stages + 5) + 16;
+  // TMEM-A kernel: large K, narrow N (same B image; it always streams it)
+  *tca = tmema_ok && P.n_tiles == 1 && P.Nt <= 64 && P.KB >= 4 && (long long)P.KB * P.Nt * 256 > 84 * 1024;
+  *smem = 1024 + (size_t)stages * stage_bytes + fixed + TC_EPI8_BYTES + 8 * (3 * stages + 9) + 16;
   if (*tca)
     *smem = 1024 + (size_t)TCA_NS * 2 * b_bytes + (size_t)2 * TCA_SLOTS * TC_BM * 128 + TC_EPI_BYTES + 8 * (2 * TCA_NS + 5) + 16;
   return 0;
@@ -842,7 +872,7 @@ extern "C" int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args, const
     const size_t b_bytes = (size_t)G.p[G.n].Nt * 128;
     const size_t stage_bytes = 2 * TC_BM * 128 + (G.p[G.n].resident ? 0 : 2 * b_bytes);
     const size_t fixed = G.p[G.n].resident ? (size_t)G.p[G.n].KB * 2 * b_bytes : 0;
-    sm = 1024 + (size_t)G.p[G.n].stages * stage_bytes + fixed + TC_EPI8_BYTES + 8 * (3 * G.p[G.n].stages + 5) + 16;
+    sm = 1024 + (size_t)G.p[G.n].stages * stage_bytes + fixed + TC_EPI8_BYTES + 8 * (3 * G.p[G.n].stages + 9) + 16;
     if (sm > smem) smem = sm;
     tiles[G.n] = G.p[G.n].m_tiles * G.p[G.n].n_tiles;
     total += tiles[G.n];
