@@ -78,6 +78,12 @@ typedef struct {
   float* C2; const float* P;                 /* aux out / aux in, strides of C */
 } sevenn_gemm_args;
 int sevenn_gemm_f32(const sevenn_gemm_args* args /* host */, void* stream);   /* exact fp32 (SIMT) */
+/* up to SEVENN_GEMM_GROUP_MAX independent problems with disjoint outputs in one launch (the per-l blocks of one or two
+ * o3.Linear on a small system); beyond SEVENN_GEMM_GROUP_MAX_TILES 16 x 32 output tiles in total it falls back to one
+ * sevenn_gemm_f32 launch per problem.  Results are bit-identical to sevenn_gemm_f32 either way. */
+#define SEVENN_GEMM_GROUP_MAX 8
+#define SEVENN_GEMM_GROUP_MAX_TILES 2048
+int sevenn_gemm_f32_grouped(int n, const sevenn_gemm_args* args /* host */, void* stream);
 /* tcgen05/TMEM 3xTF32 arm (fp32-accurate).  B is passed as the pre-swizzled (hi, lo) K-major image
  * [n_tiles][KB][2][Nt][32] whose geometry sevenn_gemm_tc_plan returns; args->B is ignored.
  * Needs K % 4 == 0 and 16-byte aligned A rows; returns SEVENN_ERR_BAD_ARG otherwise. */

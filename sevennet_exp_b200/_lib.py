@@ -39,6 +39,7 @@ SIGNATURES = {
     'sevenn_edge_fwd_tab': ([c_p, c_ll, c_i, c_i, c_f, c_i, c_p, c_p], c_i),
     'sevenn_edge_bwd_tab': ([c_p, c_ll, c_i, c_i, c_f, c_p, c_i, c_ll, c_p, c_p], c_i),
     'sevenn_gemm_f32': ([ctypes.POINTER(GemmArgs), c_p], c_i),
+    'sevenn_gemm_f32_grouped': ([c_i, ctypes.POINTER(GemmArgs), c_p], c_i),
     'sevenn_gemm_tc_plan': ([c_i, c_i, ctypes.POINTER(c_i), ctypes.POINTER(c_i), ctypes.POINTER(c_i),
                              ctypes.POINTER(c_ll)], c_i),
     'sevenn_gemm_tc': ([ctypes.POINTER(GemmArgs), c_p, c_p], c_i),

@@ -40,15 +40,15 @@ __device__ __forceinline__ float g_dact(int id, float x) {
 // take the small tiles: a 64 x 64 tile with K = 224 keeps ONE SM busy for ~4 us while 140 others idle, which is what a
 // 64-atom system's node linears consisted of.
 template <int TM, int TN>
-__global__ void __launch_bounds__(256) gemm_simt_kernel(sevenn_gemm_args g) {
+__device__ __forceinline__ void gemm_simt_body(const sevenn_gemm_args& g, int bx, int by) {
   constexpr int TBM = 16 * TM, TBN = 16 * TN;
   constexpr int NA = (TBM * BK + 255) / 256, NB = (TBN * BK + 255) / 256;
   __shared__ float As[BK][TBM + 4];
   __shared__ float Bs[BK][TBN + 4];
   const int tid = threadIdx.x;
   const int ty = tid / 16, tx = tid % 16;
-  const long long row0 = (long long)blockIdx.x * TBM;
-  const int col0 = blockIdx.y * TBN;
+  const long long row0 = (long long)bx * TBM;
+  const int col0 = by * TBN;
   float acc[TM][TN];
 #pragma unroll
   for (int a = 0; a < TM; ++a)
@@ -126,6 +126,26 @@ __global__ void __launch_bounds__(256) gemm_simt_kernel(sevenn_gemm_args g) {
 }
 
 template <int TM, int TN>
+__global__ void __launch_bounds__(256) gemm_simt_kernel(sevenn_gemm_args g) {
+  gemm_simt_body<TM, TN>(g, (int)blockIdx.x, (int)blockIdx.y);
+}
+
+// Several independent small problems in one launch (the per-l blocks of one or two o3.Linear on a small system, where a
+// launch costs more than the arithmetic): 16 x 32 tiles, CTA -> (problem, tile) through a prefix table.
+struct SimtGroup {
+  int n;
+  int start[SEVENN_GEMM_GROUP_MAX + 1];
+  int gx[SEVENN_GEMM_GROUP_MAX];
+  sevenn_gemm_args p[SEVENN_GEMM_GROUP_MAX];
+};
+__global__ void __launch_bounds__(256) gemm_simt_grouped_kernel(const SimtGroup G) {
+  int pi = 0;
+  while (pi + 1 < G.n && (int)blockIdx.x >= G.start[pi + 1]) ++pi;
+  const int local = (int)blockIdx.x - G.start[pi];
+  gemm_simt_body<1, 2>(G.p[pi], local % G.gx[pi], local / G.gx[pi]);
+}
+
+template <int TM, int TN>
 static int gemm_simt_launch(const sevenn_gemm_args& g, cudaStream_t st) {
   dim3 grid((unsigned)((g.M + 16 * TM - 1) / (16 * TM)), (unsigned)((g.N + 16 * TN - 1) / (16 * TN)));
   gemm_simt_kernel<TM, TN><<<grid, 256, 0, st>>>(g);
@@ -142,6 +162,34 @@ extern "C" int sevenn_gemm_f32(const sevenn_gemm_args* args, void* stream) {
   if (t64 >= 148) return gemm_simt_launch<4, 4>(g, st);
   if (t32 >= 148) return gemm_simt_launch<2, 2>(g, st);
   return gemm_simt_launch<1, 2>(g, st);
+}
+
+extern "C" int sevenn_gemm_f32_grouped(int n, const sevenn_gemm_args* args, void* stream) {
+  if (n <= 0) return 0;
+  if (n > SEVENN_GEMM_GROUP_MAX) return SEVENN_ERR_BAD_ARG;
+  SimtGroup G;
+  G.n = 0;
+  int start = 0;
+  long long big = 0;
+  for (int i = 0; i < n; ++i) {
+    const sevenn_gemm_args& g = args[i];
+    if (g.M <= 0 || g.N <= 0) continue;
+    if (g.K <= 0 || g.R <= 0 || g.epi < 0 || g.epi > 3) return SEVENN_ERR_BAD_ARG;
+    const long long gx = (g.M + 15) / 16, gy = (g.N + 31) / 32;
+    big += gx * gy;
+    if (big > SEVENN_GEMM_GROUP_MAX_TILES) break;
+    G.p[G.n] = g; G.gx[G.n] = (int)gx; G.start[G.n] = start;
+    start += (int)(gx * gy);
+    ++G.n;
+  }
+  if (big > SEVENN_GEMM_GROUP_MAX_TILES) {          // not a small-system group: one launch each, tile chosen per problem
+    for (int i = 0; i < n; ++i) { int rc = sevenn_gemm_f32(&args[i], stream); if (rc) return rc; }
+    return 0;
+  }
+  if (G.n == 0) return 0;
+  G.start[G.n] = start;
+  gemm_simt_grouped_kernel<<<(unsigned)start, 256, 0, (cudaStream_t)stream>>>(G);
+  return (int)cudaGetLastError();
 }
 #endif
 
@@ -176,6 +224,11 @@ extern "C" int sevenn_gemm_f32(const sevenn_gemm_args* args, void* stream) {
       }
     }
   }
+  return 0;
+}
+extern "C" int sevenn_gemm_f32_grouped(int n, const sevenn_gemm_args* args, void* stream) {
+  if (n > SEVENN_GEMM_GROUP_MAX) return SEVENN_ERR_BAD_ARG;
+  for (int i = 0; i < n; ++i) { int rc = sevenn_gemm_f32(&args[i], stream); if (rc) return rc; }
   return 0;
 }
 #endif

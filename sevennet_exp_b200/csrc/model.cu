@@ -84,6 +84,7 @@ struct sevenn_model {
   int lmax_sh, normalize_sph, S, tab_n, n_species, d0, species_wise, tc_min_rows, n_slab;
   float tab_inv_h, cutoff;
   float* dev = nullptr;          // all weights, one allocation
+  float* img = nullptr;          // tcgen05 operand images of the block weights, rebuilt at create time
   const float *embed, *scale, *shift;
   std::vector<Layer> layers;
   Lin read1, read2;
@@ -136,11 +137,23 @@ bool tc_eligible(const sevenn_model* m, const sevenn_gemm_args& g, const float* 
          ((uintptr_t)g.A & 15) == 0;
 }
 
+// exact-fp32 blocks with disjoint outputs: one launch for the group (engine.py::_gemm_group)
+int flush_simt(sevenn_model* m, sevenn_gemm_args* sg, int& n, cudaStream_t st) {
+  if (n == 0) return 0;
+  long long tiles = 0;
+  for (int i = 0; i < n; ++i) tiles += ((sg[i].M + 15) / 16) * ((sg[i].N + 31) / 32);
+  int rc = n == 1 ? sevenn_gemm_f32(&sg[0], st) : sevenn_gemm_f32_grouped(n, sg, st);
+  m->n_launch += (n == 1 || tiles <= SEVENN_GEMM_GROUP_MAX_TILES) ? 1 : n;
+  n = 0;
+  return rc;
+}
+
 // o3.Linear forward: y (+)= x @ W per block (engine.py::_linear_fwd)
 int linear_fwd(sevenn_model* m, Arena& A, const Lin& L, const float* x, long long n, float* y, bool accumulate,
                const int* types, cudaStream_t st) {
   if (A.dry || n <= 0) return 0;
   sevenn_gemm_args grp[4]; const float* img[4]; int ng = 0;
+  sevenn_gemm_args sgrp[SEVENN_GEMM_GROUP_MAX]; int nsg = 0;
   auto flush = [&]() -> int {
     if (ng == 0) return 0;
     int rc = sevenn_gemm_tc_grouped(ng, grp, img, st);
@@ -165,12 +178,13 @@ int linear_fwd(sevenn_model* m, Arena& A, const Lin& L, const float* x, long lon
       grp[ng] = g; img[ng] = b.Wimg;
       if (++ng == 4) { int rc = flush(); if (rc) return rc; }
     } else {
-      int rc = sevenn_gemm_f32(&g, st);
-      ++m->n_launch;
-      if (rc) return rc;
+      sgrp[nsg] = g;
+      if (++nsg == SEVENN_GEMM_GROUP_MAX) { int rc = flush_simt(m, sgrp, nsg, st); if (rc) return rc; }
     }
   }
   int rc = flush();
+  if (rc) return rc;
+  rc = flush_simt(m, sgrp, nsg, st);
   if (rc) return rc;
   for (const Blk& b : L.blk)
     if (b.cst != nullptr) {
@@ -186,6 +200,7 @@ int linear_bwd(sevenn_model* m, Arena& A, const Lin& L, const float* dy, long lo
   if (A.dry || n <= 0) return 0;
   const bool acc = accumulate || L.bwd_needs_zero;
   sevenn_gemm_args grp[4]; const float* img[4]; int ng = 0;
+  sevenn_gemm_args sgrp[SEVENN_GEMM_GROUP_MAX]; int nsg = 0;
   auto flush = [&]() -> int {
     if (ng == 0) return 0;
     int rc = sevenn_gemm_tc_grouped(ng, grp, img, st);
@@ -210,6 +225,9 @@ int linear_bwd(sevenn_model* m, Arena& A, const Lin& L, const float* dy, long lo
     if (tc && !L.bwd_overlap) {
       grp[ng] = g; img[ng] = b.WTimg;
       if (++ng == 4) { int rc = flush(); if (rc) return rc; }
+    } else if (!tc && !L.bwd_overlap) {
+      sgrp[nsg] = g;
+      if (++nsg == SEVENN_GEMM_GROUP_MAX) { int rc = flush_simt(m, sgrp, nsg, st); if (rc) return rc; }
     } else {
       // blocks that accumulate into one input group stay ordered, one launch each
       int rc = tc ? sevenn_gemm_tc(&g, b.WTimg, st) : sevenn_gemm_f32(&g, st);
@@ -218,6 +236,8 @@ int linear_bwd(sevenn_model* m, Arena& A, const Lin& L, const float* dy, long lo
       if (rc) return rc;
     }
   }
+  int rc = flush_simt(m, sgrp, nsg, st);
+  if (rc) return rc;
   return flush();
 }
 
@@ -513,6 +533,36 @@ extern "C" int sevenn_model_create(const int* prog, long long n_prog, const floa
     delete m;
     return SEVENN_ERR_BAD_ARG;
   }
+  // The tcgen05 operand images depend on the tile plan of THIS library build (sevenn_gemm_tc_plan); the ones packed
+  // into the program may come from another build (a deployed artefact outlives the library), so they are rebuilt here
+  // from W / W^T on the device -- the packed images only say which blocks want the tensor-core arm.
+  {
+    std::vector<Lin*> lins;
+    for (Layer& L : m->layers) { lins.push_back(&L.sc); lins.push_back(&L.si1); lins.push_back(&L.si2); }
+    lins.push_back(&m->read1); lins.push_back(&m->read2);
+    long long total = 0;
+    auto img_floats = [](int K, int N) { int a, b, c; long long f = 0; sevenn_gemm_tc_plan(N, K, &a, &b, &c, &f); return (f + 63) / 64 * 64; };
+    for (Lin* L : lins) for (Blk& b : L->blk) {
+      if (b.Wimg != nullptr) total += img_floats(b.K, b.N);
+      if (b.WTimg != nullptr) total += img_floats(b.N, b.K);
+    }
+    int rc = 0;
+    if (total > 0 && cudaMalloc(&m->img, (size_t)total * 4) != cudaSuccess) rc = (int)cudaErrorMemoryAllocation;
+    long long off = 0;
+    for (Lin* L : lins) for (Blk& b : L->blk) {
+      if (rc) break;
+      if (b.Wimg != nullptr) {
+        rc = sevenn_gemm_tc_image(b.W, b.K, b.N, m->img + off, nullptr);
+        b.Wimg = m->img + off; off += img_floats(b.K, b.N);
+      }
+      if (!rc && b.WTimg != nullptr) {
+        rc = sevenn_gemm_tc_image(b.WT, b.N, b.K, m->img + off, nullptr);
+        b.WTimg = m->img + off; off += img_floats(b.N, b.K);
+      }
+    }
+    if (!rc && cudaDeviceSynchronize() != cudaSuccess) rc = (int)cudaGetLastError();
+    if (rc) { cudaFree(m->img); cudaFree(m->dev); delete m; return rc; }
+  }
   const char* env = std::getenv("SEVENN_TC_MIN_ROWS");
   if (env != nullptr) m->tc_min_rows = std::atoi(env);
   *out = m;
@@ -521,6 +571,7 @@ extern "C" int sevenn_model_create(const int* prog, long long n_prog, const floa
 
 extern "C" int sevenn_model_destroy(sevenn_model* m) {
   if (m == nullptr) return 0;
+  cudaFree(m->img);
   cudaFree(m->dev);
   delete m;
   return 0;

@@ -186,13 +186,24 @@ class Kernels:
     def _gemm_group(self, items):
         """items: list of _gemm argument tuples with one epilogue; the tcgen05-eligible ones share launches of up
         to 4 problems (sevenn_gemm_tc_grouped), the rest go to the SIMT arm one by one."""
-        group = []
+        group, simt = [], []
         for it in items:
             g, tc = self._gemm_args(*it)
             if tc:
                 group.append((g, self._tc_image(it[4])))
             else:
-                self.lib.call('sevenn_gemm_f32', ctypes.byref(g), self._stream())
+                simt.append(g)
+        for k in range(0, len(simt), 8):
+            part = simt[k:k + 8]
+            # small problems share one launch (sevenn_gemm_f32_grouped; same results, a launch costs more than their
+            # arithmetic); beyond 2,048 16 x 32 tiles the library launches them one by one
+            tiles = sum(((g.M + 15) // 16) * ((g.N + 31) // 32) for g in part)
+            if len(part) > 1:
+                arr = (_lib.GemmArgs * len(part))(*part)
+                self.lib.call('sevenn_gemm_f32_grouped', len(part), arr, self._stream())
+                self.n_launch += 1 if tiles <= 2048 else len(part)
+            else:
+                self.lib.call('sevenn_gemm_f32', ctypes.byref(part[0]), self._stream())
                 self.n_launch += 1
         for k in range(0, len(group), 4):
             part = group[k:k + 4]
