@@ -39,7 +39,7 @@ __device__ __forceinline__ float g_dact(int id, float x) {
 // registers while the current one is multiplied (one barrier pair per slab, global latency hidden).  Small problems
 // take the small tiles: a 64 x 64 tile with K = 224 keeps ONE SM busy for ~4 us while 140 others idle, which is what a
 // 64-atom system's node linears consisted of.
-template <int TM, int TN>
+template <int TM, int TN, int D>
 __device__ __forceinline__ void gemm_simt_body(const sevenn_gemm_args& g, int bx, int by) {
   constexpr int TBM = 16 * TM, TBN = 16 * TN;
   constexpr int NA = (TBM * BK + 255) / 256, NB = (TBN * BK + 255) / 256;
@@ -63,47 +63,55 @@ __device__ __forceinline__ void gemm_simt_body(const sevenn_gemm_args& g, int bx
     const long long ar = row0 + idx / BK;
     aptr[q] = (idx < TBM * BK && ar < g.M) ? g.A + (ar / g.R) * g.sAn + (ar % g.R) * (long long)g.sAm + idx % BK : nullptr;
   }
-  float ra[NA], rb[NB];
-  auto fetch = [&](int k0) {
+  // D k-slabs in flight in registers: a 16 x 32 tile does ~100 clk of arithmetic per slab, so with one slab of
+  // prefetch every slab cost a full global-memory round trip (K = 384: 24 of them, ~15 us for a 64-atom system)
+  float ra[D][NA], rb[D][NB];
+  auto fetch = [&](float (&fa)[NA], float (&fb)[NB], int k0) {
 #pragma unroll
     for (int q = 0; q < NA; ++q) {
       const int k = k0 + (tid + 256 * q) % BK;
-      ra[q] = (aptr[q] != nullptr && k < g.K) ? __ldg(aptr[q] + k0) : 0.f;
+      fa[q] = (aptr[q] != nullptr && k < g.K) ? __ldg(aptr[q] + k0) : 0.f;
     }
 #pragma unroll
     for (int q = 0; q < NB; ++q) {
       const int idx = tid + 256 * q;
       const int k = k0 + idx / TBN, c = col0 + idx % TBN;
-      rb[q] = (idx < TBN * BK && k < g.K && c < g.N) ? __ldg(g.B + (size_t)k * g.ldb + c) : 0.f;
+      fb[q] = (idx < TBN * BK && k < g.K && c < g.N) ? __ldg(g.B + (size_t)k * g.ldb + c) : 0.f;
     }
   };
-  fetch(0);
-  for (int k0 = 0; k0 < g.K; k0 += BK) {
 #pragma unroll
-    for (int q = 0; q < NA; ++q) {
-      const int idx = tid + 256 * q;
-      if (idx < TBM * BK) As[idx % BK][idx / BK] = ra[q];
+  for (int d = 0; d < D; ++d) fetch(ra[d], rb[d], d * BK);
+  for (int kk = 0; kk < g.K; kk += D * BK) {
+#pragma unroll
+    for (int d = 0; d < D; ++d) {
+      const int k0 = kk + d * BK;
+      if (k0 >= g.K) break;
+#pragma unroll
+      for (int q = 0; q < NA; ++q) {
+        const int idx = tid + 256 * q;
+        if (idx < TBM * BK) As[idx % BK][idx / BK] = ra[d][q];
+      }
+#pragma unroll
+      for (int q = 0; q < NB; ++q) {
+        const int idx = tid + 256 * q;
+        if (idx < TBN * BK) Bs[idx / TBN][idx % TBN] = rb[d][q];
+      }
+      __syncthreads();
+      if (k0 + D * BK < g.K) fetch(ra[d], rb[d], k0 + D * BK);
+#pragma unroll
+      for (int k = 0; k < BK; ++k) {
+        float a[TM], b[TN];
+#pragma unroll
+        for (int q = 0; q < TM; ++q) a[q] = As[k][ty * TM + q];
+#pragma unroll
+        for (int q = 0; q < TN; ++q) b[q] = Bs[k][tx * TN + q];
+#pragma unroll
+        for (int i = 0; i < TM; ++i)
+#pragma unroll
+          for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      }
+      __syncthreads();
     }
-#pragma unroll
-    for (int q = 0; q < NB; ++q) {
-      const int idx = tid + 256 * q;
-      if (idx < TBN * BK) Bs[idx / TBN][idx % TBN] = rb[q];
-    }
-    __syncthreads();
-    if (k0 + BK < g.K) fetch(k0 + BK);
-#pragma unroll
-    for (int k = 0; k < BK; ++k) {
-      float a[TM], b[TN];
-#pragma unroll
-      for (int q = 0; q < TM; ++q) a[q] = As[k][ty * TM + q];
-#pragma unroll
-      for (int q = 0; q < TN; ++q) b[q] = Bs[k][tx * TN + q];
-#pragma unroll
-      for (int i = 0; i < TM; ++i)
-#pragma unroll
-        for (int j = 0; j < TN; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
-    }
-    __syncthreads();
   }
 #pragma unroll
   for (int i = 0; i < TM; ++i) {
@@ -127,7 +135,7 @@ __device__ __forceinline__ void gemm_simt_body(const sevenn_gemm_args& g, int bx
 
 template <int TM, int TN>
 __global__ void __launch_bounds__(256) gemm_simt_kernel(sevenn_gemm_args g) {
-  gemm_simt_body<TM, TN>(g, (int)blockIdx.x, (int)blockIdx.y);
+  gemm_simt_body<TM, TN, (TM * TN <= 2 ? 4 : 1)>(g, (int)blockIdx.x, (int)blockIdx.y);
 }
 
 // Several independent small problems in one launch (the per-l blocks of one or two o3.Linear on a small system, where a
@@ -142,7 +150,7 @@ __global__ void __launch_bounds__(256) gemm_simt_grouped_kernel(const SimtGroup 
   int pi = 0;
   while (pi + 1 < G.n && (int)blockIdx.x >= G.start[pi + 1]) ++pi;
   const int local = (int)blockIdx.x - G.start[pi];
-  gemm_simt_body<1, 2>(G.p[pi], local % G.gx[pi], local / G.gx[pi]);
+  gemm_simt_body<1, 2, 4>(G.p[pi], local % G.gx[pi], local / G.gx[pi]);
 }
 
 template <int TM, int TN>

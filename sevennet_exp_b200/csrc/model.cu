@@ -149,11 +149,15 @@ int flush_simt(sevenn_model* m, sevenn_gemm_args* sg, int& n, cudaStream_t st) {
 }
 
 // o3.Linear forward: y (+)= x @ W per block (engine.py::_linear_fwd)
+// `ext`: collector shared with the caller's next linear (disjoint outputs): exact-fp32 blocks are left in it unflushed
+struct SimtBatch { sevenn_gemm_args g[SEVENN_GEMM_GROUP_MAX]; int n = 0; };
 int linear_fwd(sevenn_model* m, Arena& A, const Lin& L, const float* x, long long n, float* y, bool accumulate,
-               const int* types, cudaStream_t st) {
+               const int* types, cudaStream_t st, SimtBatch* ext = nullptr) {
   if (A.dry || n <= 0) return 0;
   sevenn_gemm_args grp[4]; const float* img[4]; int ng = 0;
-  sevenn_gemm_args sgrp[SEVENN_GEMM_GROUP_MAX]; int nsg = 0;
+  SimtBatch own;
+  SimtBatch& sb = ext != nullptr ? *ext : own;
+  sevenn_gemm_args* sgrp = sb.g; int& nsg = sb.n;
   auto flush = [&]() -> int {
     if (ng == 0) return 0;
     int rc = sevenn_gemm_tc_grouped(ng, grp, img, st);
@@ -184,8 +188,9 @@ int linear_fwd(sevenn_model* m, Arena& A, const Lin& L, const float* x, long lon
   }
   int rc = flush();
   if (rc) return rc;
-  rc = flush_simt(m, sgrp, nsg, st);
-  if (rc) return rc;
+  bool has_cst = false;
+  for (const Blk& b : L.blk) has_cst = has_cst || b.cst != nullptr;
+  if (ext == nullptr || has_cst) { rc = flush_simt(m, sgrp, nsg, st); if (rc) return rc; }
   for (const Blk& b : L.blk)
     if (b.cst != nullptr) {
       add_row_kernel<<<sevenn_grid_for(n * b.N), 256, 0, st>>>(y + b.out_off, L.dout, n, b.N, b.cst);
@@ -268,12 +273,14 @@ int evaluate_graph(sevenn_model* m, Arena& A, const GraphView& g, const sevenn_h
     Layer& L = m->layers[t];
     pre[t] = A.f32(nl * L.dgi);
     if (!L.sc.fwd_full) { int rc = zero_async(A, pre[t], (size_t)nl * L.dgi * 4, st); if (rc) return rc; }
-    int rc = linear_fwd(m, A, L.sc, x, nl, pre[t], false, g.types, st);
+    SimtBatch both;                 // sc and si1 read the same x and write different buffers: one launch on small systems
+    int rc = linear_fwd(m, A, L.sc, x, nl, pre[t], false, g.types, st, &both);
     if (rc) return rc;
     h[t] = A.f32(nn * L.dx_in);
     if (!L.si1.fwd_full) { rc = zero_async(A, h[t], (size_t)nn * L.dx_in * 4, st); if (rc) return rc; }
-    rc = linear_fwd(m, A, L.si1, x, n_x, h[t], false, nullptr, st);
+    rc = linear_fwd(m, A, L.si1, x, n_x, h[t], false, nullptr, st, &both);
     if (rc) return rc;
+    if (!A.dry) { rc = flush_simt(m, both.g, both.n, st); if (rc) return rc; }
     if (t > 0 && halo != nullptr && halo->forward != nullptr && !A.dry) {
       rc = halo->forward(halo->user, t, h[t], L.dx_in, vs);      // fills rows [n_local, n_nodes)
       if (rc) return rc;
