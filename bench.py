@@ -304,7 +304,7 @@ def gemm_roofline(spec, stage, n_atoms, peak_hbm):
     ms = stage.get('si2_fwd')
     if not ms:
         return None
-    cap = ncu_capture('gemm_tc_kernel', 0)
+    cap = ncu_capture('gemm_tc', 0)          # first captured launch: the TMEM-A kernel on the l = 1 block of si2
     return {'bound': 'hbm', 'kernel': 'gemm_tc_kernel (tcgen05 3xTF32), self_interaction_2 forward of all layers',
             'achieved': bytes_ / (ms * 1e-3) / 1e9, 'peak': peak_hbm, 'unit': 'GB/s',
             'frac': bytes_ / (ms * 1e-3) / 1e9 / peak_hbm, 'algorithmic_bytes': bytes_, 'ms': ms,
@@ -312,7 +312,8 @@ def gemm_roofline(spec, stage, n_atoms, peak_hbm):
                        'frac': 3.0 * flops / (ms * 1e-3) / 1e12 / tf32_peak,
                        'note': '3 tf32 MMAs per fp32 product (hi*hi + hi*lo + lo*hi); K <= 352 per block: these '
                                'GEMMs are bound by streaming A and C, not by the tensor pipe',
-                       'ncu_tensor_pipe_pct': cap.get('tensor_pipe_pct') if cap else None}}
+                       'ncu_tensor_pipe_pct': cap.get('tensor_pipe_pct') if cap else None,
+                       'ncu_source': cap.get('source') if cap else None}}
 
 
 def cfg5_structures(n_struct=32, seed=5):

@@ -31,7 +31,10 @@ def main(files):
                 continue
             seen.add(name)
             dram = val(r, 'dram__bytes_read.sum', True) + val(r, 'dram__bytes_write.sum', True)
-            tensor = val(r, 'sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active')
+            # tcgen05 (UTCHMMA) work shows in the tensor pipe's cycles-active counter, not in the legacy HMMA instruction counter
+            tensor = val(r, 'TPC.TriageCompute.sm__pipe_tensor_cycles_active_realtime.avg.pct_of_peak_sustained_elapsed')
+            if tensor is None:
+                tensor = val(r, 'sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active')
             lim = (f"ncu r02: issue slots {val(r, 'smsp__issue_active.avg.pct_of_peak_sustained_active'):.0f} %, fma pipe "
                    f"{val(r, 'sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active'):.0f} %, L1 {val(r, 'l1tex__throughput.avg.pct_of_peak_sustained_elapsed'):.0f} %, "
                    f"L2 {val(r, 'lts__throughput.avg.pct_of_peak_sustained_elapsed'):.0f} %, warps active "
