@@ -144,6 +144,11 @@ MIN_CTAS_TAB = {
 }
 
 
+# edge-pair backward (gen_bwd_tab_pair): per-edge temporaries double; 2 CTAs of 4 warps per SM leave 255 registers
+MIN_CTAS_TAB_EP = {}
+MIN_CTAS_TAB_EP_DEFAULT = int(_os0.environ.get('SEVENN_MIN_CTAS_EP', '2'))
+
+
 def _env_overrides():
     """Tuning runs only (tools/tune_occupancy.sh): SEVENN_MIN_CTAS / SEVENN_MIN_CTAS_TAB = 'sig:fwd,bwd;sig:fwd,bwd'."""
     import os
@@ -528,9 +533,31 @@ def dy_smem_values(spec: ConvSpec) -> int:
     return nv if DY_SMEM and 32 // nv >= 2 else 0
 
 
+# Two EDGES per loop trip in the tabulated backward: everything between the loads and the dY butterfly
+# runs on float2 = (edge e, edge e + 1) with fma.rn.f32x2 -- M, q, dx, dE/dw, w x and the dY products cost one packed
+# instruction for both edges; the output gradient g and the Clebsch-Gordan literals are free broadcast / immediate
+# operands, and the backward keeps no accumulator across edges, so nothing but per-edge temporaries doubles.
+# (forward, backward) by signature; SEVENN_TAB_EP='fwd,bwd' overrides for A/B builds.
+# MEASURED (B200, tools/gpu_ab2.sh, profiles/r02b_edge_pair_ab.txt): SLOWER.  SevenNet-0 inner backward 184 registers ->
+# 2 CTAs of 4 warps per SM: 39.9 -> 61.3 ms on the 216 k-atom cell (51.6 ms capped at 168 registers / 3 CTAs), although the
+# kernel executes ~35 % fewer instructions -- with 8-12 warps per SM the dependent chains of one warp (loads -> M -> q ->
+# dx / dY -> butterfly) are no longer covered; the scalar kernel at 120 registers / 16 warps is latency AND issue bound.
+# Kept as an opt-in generator path (SEVENN_TAB_EP=0,1), off by default.
+TAB_EP_DEFAULT = (False, False)
+TAB_EP_BY_SIG = {}
+_TAB_EP_ENV = _os.environ.get('SEVENN_TAB_EP')
+TAB_EP_XY_DEPTH = 8   # ring slots for x_j / Y in edge-pair mode (three pairs in flight)
+
+
+def tab_ep(bwd: bool) -> bool:
+    mode = tuple(v == '1' for v in _TAB_EP_ENV.split(',')) if _TAB_EP_ENV else TAB_EP_BY_SIG.get(_cur_sig[0], TAB_EP_DEFAULT)
+    return bool(mode[1 if bwd else 0]) and bwd and tab_t_regs(bwd) and TAB_POLY and not DY_SMEM
+
+
 def tab_data_floats(spec: ConvSpec, bwd: bool) -> int:
     wd = 0 if tab_t_regs(bwd) else TAB_W_DEPTH
-    return max(TAB_XY_DEPTH * _tab_xy_floats(G, spec) + wd * _tab_w_floats(G) for G in make_groups(spec, tab=True))
+    dx = TAB_EP_XY_DEPTH if tab_ep(bwd) else TAB_XY_DEPTH
+    return max(dx * _tab_xy_floats(G, spec) + wd * _tab_w_floats(G) for G in make_groups(spec, tab=True))
 
 
 def tab_ring_floats(spec: ConvSpec, bwd: bool = False) -> int:
@@ -737,6 +764,198 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
                 L.append(f'        const float wd{pi}{_sx(G, c)} = fmaf(d00, {T}.x - {T}.z, fmaf(d10, {T}.y, d11 * {T}.w));')
 
 
+def _f2(v: float) -> str:
+    return f'F2B({_f(v)})'
+
+
+def gen_bwd_tab_pair(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str]:
+    """Tabulated backward with two edges per loop trip (see TAB_EP above).  Same kernel name, arguments and outputs as
+    gen_bwd(tab=True); per-edge results differ from it in the last bits only (explicit packed fma forms)."""
+    S = (spec.lmax_sh + 1) ** 2
+    S2, SD = S + 2, S + 1
+    NP = 1
+    while NP < S:
+        NP *= 2
+    gr_in_butterfly = NP > S
+    DX = TAB_EP_XY_DEPTH
+    z4 = 'make_float4(0.f, 0.f, 0.f, 0.f)'
+    idx_of = lambda e: f'F2I(LDG(Yt + (size_t)({e}) * {S2} + {S + 1}))'   # noqa: E731
+    L = []
+    mc = MIN_CTAS_TAB_EP.get(sig, MIN_CTAS_TAB_EP_DEFAULT)
+    L.append(f'KERNEL_HEAD(conv_bwd_tab_{sig}, {mc})(const float* __restrict__ x, int ldx, const float* __restrict__ Yt,')
+    L.append('    const float4* __restrict__ tab, const int* __restrict__ rowptr, const int* __restrict__ col,')
+    L.append('    int n_dst, float inv_denom, const float* __restrict__ gout, int ldo,')
+    L.append('    float* __restrict__ dxe, int lddx, float* __restrict__ dY, long long dy_stride)')
+    L.append(f'UNIT_LOOP_BEGIN_DYN(n_dst, {sum(G.nchunk // G.cpw for G in groups)}, {tab_ring_floats(spec, True)})')
+    L.append('  float* dYu = dY + (size_t)unit * (size_t)dy_stride;')
+    for gi, G in enumerate(groups):
+        xyf = _tab_xy_floats(G, spec)
+        ybase = G.d1 * 32 * G.cpw
+        chunks = [_sx(G, c) for c in range(G.cpw)]
+        _unit_open(L, G, gi == 0, gi == len(groups) - 1)
+        L.append('    const float* grow = gout + (size_t)row * ldo + c32 + lane;')
+        for pi, p in G.paths:
+            Mg = spec.lmid.groups[p.gm][0]
+            base = spec.lmid.group_off[p.gm] + p.u_off
+            for k in range(2 * p.l3 + 1):
+                for c in range(G.cpw):
+                    ld = _on(G, f'LDG(grow + {base + k * Mg + c * 32}) * inv_denom')
+                    L.append(f'    const float g{pi}_{k}{_sx(G, c)} = {ld};')
+        L.append('    const int e0 = rowptr[row], e1 = rowptr[row + 1];')
+        L.append('    if (e0 < e1) {')
+        # ---- emulation build: plain loads
+        L.append('#ifdef SEVENN_EMU')
+        L.append('      for (int e = e0; e < e1; e += 2) {')
+        L.append('        const bool vB = e + 1 < e1; const int eB = vB ? e + 1 : e;')
+        L.append(f'        const float* xrA = x + (size_t)col[e] * ldx + {G.xoff} + c32 + lane;')
+        L.append(f'        const float* xrB = x + (size_t)col[eB] * ldx + {G.xoff} + c32 + lane;')
+        L.append(f'        const float4* trA = tab + (size_t){idx_of("e")} * {spec.wn} + c32 + lane;')
+        L.append(f'        const float4* trB = tab + (size_t){idx_of("eB")} * {spec.wn} + c32 + lane;')
+        L.append(f'        const float tA = Yt[(size_t)e * {S2} + {S}], tB = Yt[(size_t)eB * {S2} + {S}];')
+        for m in range(G.d1):
+            for c in range(G.cpw):
+                o = m * G.mul + c * 32
+                a_, b_ = _on(G, f'xrA[{o}]'), _on(G, f'xrB[{o}]')
+                L.append(f'        const float2 x{m}{_sx(G, c)} = make_float2({a_}, {b_});')
+        for pi, p in G.paths:
+            ze = 'float4{0.f, 0.f, 0.f, 0.f}'
+            for c in range(G.cpw):
+                o = p.w_off + c * 32
+                L.append(f'        const float4 TA{pi}{_sx(G, c)} = {_on(G, f"trA[{o}]", ze)}, TB{pi}{_sx(G, c)} = {_on(G, f"trB[{o}]", ze)};')
+        for jj in G.ys:
+            L.append(f'        const float2 y{jj} = make_float2(Yt[(size_t)e * {S2} + {jj}], Yt[(size_t)eB * {S2} + {jj}]);')
+        # ---- device: cp.async ring for x_j / Y (three pairs ahead), table rows of the next pair in registers
+        L.append('#else')
+        for d in range(DX // 2 - 1):
+            for h in range(2):
+                L.append(f'      if (e0 + {2 * d + h} < e1) {{')
+                _tab_issue_xy(L, G, spec, '        ', f'e0 + {2 * d + h}', f'col[e0 + {2 * d + h}]', str(2 * d + h))
+                L.append('      }')
+            L.append('      CP_ASYNC_COMMIT();')
+        L.append(f'      const float4* trA0 = tab + (size_t)({idx_of("e0")}) * {spec.wn} + c32 + lane;')
+        L.append(f'      const float4* trB0 = tab + (size_t)({idx_of("(e0 + 1 < e1 ? e0 + 1 : e1 - 1)")}) * {spec.wn} + c32 + lane;')
+        for pi, p in G.paths:
+            for c in range(G.cpw):
+                o = p.w_off + c * 32
+                L.append(f'      float4 TnA{pi}{_sx(G, c)} = {_on(G, f"__ldg(trA0 + {o})", z4)}, '
+                         f'TnB{pi}{_sx(G, c)} = {_on(G, f"__ldg(trB0 + {o})", z4)};')
+        L.append(f'      int jnA = col[e0 + {DX - 2} < e1 ? e0 + {DX - 2} : e1 - 1], jnB = col[e0 + {DX - 1} < e1 ? e0 + {DX - 1} : e1 - 1];')
+        L.append(f'      int inA = {idx_of("(e0 + 2 < e1 ? e0 + 2 : e1 - 1)")}, inB = {idx_of("(e0 + 3 < e1 ? e0 + 3 : e1 - 1)")};')
+        L.append('      int slot = 0;')
+        L.append('      for (int e = e0; e < e1; e += 2) {')
+        L.append('        const bool vB = e + 1 < e1;')
+        for pi, p in G.paths:
+            for c in range(G.cpw):
+                L.append(f'        const float4 TA{pi}{_sx(G, c)} = TnA{pi}{_sx(G, c)}, TB{pi}{_sx(G, c)} = TnB{pi}{_sx(G, c)};')
+        L.append(f'        {{ const float4* trA = tab + (size_t)(inA) * {spec.wn} + c32 + lane;')
+        L.append(f'          const float4* trB = tab + (size_t)(inB) * {spec.wn} + c32 + lane;')
+        for pi, p in G.paths:
+            for c in range(G.cpw):
+                o = p.w_off + c * 32
+                L.append(f'          TnA{pi}{_sx(G, c)} = {_on(G, f"__ldg(trA + {o})", z4)}; TnB{pi}{_sx(G, c)} = {_on(G, f"__ldg(trB + {o})", z4)};')
+        L.append('        }')
+        L.append(f'        CP_ASYNC_WAIT({DX // 2 - 2});')
+        L.append('        __syncwarp();')
+        for h, jn in ((0, 'jnA'), (1, 'jnB')):
+            L.append(f'        if (e + {DX - 2 + h} < e1) {{')
+            _tab_issue_xy(L, G, spec, '          ', f'e + {DX - 2 + h}', jn, f'(slot + {DX - 2 + h}) & {DX - 1}')
+            L.append('        }')
+        L.append('        CP_ASYNC_COMMIT();')
+        L.append(f'        jnA = col[e + {DX} < e1 ? e + {DX} : e1 - 1]; jnB = col[e + {DX + 1} < e1 ? e + {DX + 1} : e1 - 1];')
+        L.append(f'        inA = {idx_of("(e + 4 < e1 ? e + 4 : e1 - 1)")}; inB = {idx_of("(e + 5 < e1 ? e + 5 : e1 - 1)")};')
+        L.append(f'        const float* srA = ring + slot * {xyf};')
+        L.append(f'        const float* srB = ring + (vB ? ((slot + 1) & {DX - 1}) : slot) * {xyf};')
+        L.append(f'        slot = (slot + 2) & {DX - 1};')
+        for m in range(G.d1):
+            for c in range(G.cpw):
+                o = (m * G.cpw + c) * 32
+                a_, b_ = _on(G, f'srA[{o} + lane]'), _on(G, f'srB[{o} + lane]')
+                L.append(f'        const float2 x{m}{_sx(G, c)} = make_float2({a_}, {b_});')
+        for jj in G.ys:
+            L.append(f'        const float2 y{jj} = make_float2(srA[{ybase + jj}], srB[{ybase + jj}]);')
+        L.append(f'        const float tA = srA[{ybase + S}], tB = srB[{ybase + S}];')
+        L.append('#endif')
+        # ---- radial weights and their derivative (monomial table rows), scalar per edge, paired afterwards
+        L.append('        const float t2A = tA + tA, t3A = 3.f * tA * tA, t2B = tB + tB, t3B = 3.f * tB * tB;')
+        for pi, p in G.paths:
+            for sx in chunks:
+                A, B = f'TA{pi}{sx}', f'TB{pi}{sx}'
+                L.append(f'        const float2 w{pi}{sx} = make_float2(fmaf(fmaf(fmaf({A}.w, tA, {A}.z), tA, {A}.y), tA, {A}.x), '
+                         f'fmaf(fmaf(fmaf({B}.w, tB, {B}.z), tB, {B}.y), tB, {B}.x));')
+                L.append(f'        const float2 wd{pi}{sx} = make_float2(fmaf(t3A, {A}.w, fmaf(t2A, {A}.z, {A}.y)), '
+                         f'fmaf(t3B, {B}.w, fmaf(t2B, {B}.z, {B}.y)));')
+        zero2 = 'make_float2(0.f, 0.f)'
+        L.append(f'        float2 dyv[{NP}];')
+        L.append(f'#pragma unroll\n        for (int q_ = 0; q_ < {NP}; ++q_) dyv[q_] = {zero2};')
+        L.append('        float2 ' + ', '.join(f'dx{m}{sx} = {zero2}' for m in range(G.d1) for sx in chunks) + f', gr2 = {zero2};')
+        touched = set()
+        for pi, p in G.paths:
+            ent, nnz = _m_terms(p.l1, p.l2, p.l3)
+            L.append(f'        {{ // path {pi}: {p.l1} x {p.l2} -> {p.l3}')
+            for (i, k), terms in ent.items():
+                j0, c0 = terms[0]
+                expr = f'__fmul2_rn({_f2(c0)}, y{p.l2 * p.l2 + j0})'
+                for j, c in terms[1:]:
+                    expr = f'__ffma2_rn({_f2(c)}, y{p.l2 * p.l2 + j}, {expr})'
+                L.append(f'          const float2 M_{i}_{k} = {expr};')
+            rows = [i for i in range(G.d1) if any((i, k) in ent for k in range(2 * p.l3 + 1))]
+            for sx in chunks:
+                for i in rows:
+                    kk = [k for k in range(2 * p.l3 + 1) if (i, k) in ent]
+                    t = f'__fmul2_rn(M_{i}_{kk[0]}, F2B(g{pi}_{kk[0]}{sx}))'
+                    for k in kk[1:]:
+                        t = f'__ffma2_rn(M_{i}_{k}, F2B(g{pi}_{k}{sx}), {t})'
+                    L.append(f'          const float2 q{i}{sx} = {t};')
+                    L.append(f'          dx{i}{sx} = __ffma2_rn(w{pi}{sx}, q{i}{sx}, dx{i}{sx});')
+                if rows:
+                    t = f'__fmul2_rn(x{rows[0]}{sx}, q{rows[0]}{sx})'
+                    for i in rows[1:]:
+                        t = f'__ffma2_rn(x{i}{sx}, q{i}{sx}, {t})'
+                    L.append(f'          gr2 = __ffma2_rn({t}, wd{pi}{sx}, gr2);')
+                for i in rows:
+                    L.append(f'          const float2 X{i}{sx} = __fmul2_rn(w{pi}{sx}, x{i}{sx});')
+            # the chunks of a warp share c_ijk: their products are added before the coefficient is applied
+            for (i, k) in ent:
+                t = f'__fmul2_rn(X{i}{chunks[0]}, F2B(g{pi}_{k}{chunks[0]}))'
+                for sx in chunks[1:]:
+                    t = f'__ffma2_rn(X{i}{sx}, F2B(g{pi}_{k}{sx}), {t})'
+                L.append(f'          const float2 P_{i}_{k} = {t};')
+            for (i, j, k, cf) in nnz:
+                q = p.l2 * p.l2 + j
+                if q not in touched:
+                    touched.add(q)
+                    L.append(f'          dyv[{q}] = P_{i}_{k};' if abs(cf - 1.0) < 1e-12 else
+                             f'          dyv[{q}] = __fmul2_rn({_f2(cf)}, P_{i}_{k});')
+                else:
+                    L.append(f'          dyv[{q}] = __ffma2_rn({_f2(cf)}, P_{i}_{k}, dyv[{q}]);')
+            L.append('        }')
+        # ---- per-edge outputs: dx_e rows, dY (+ radial term) through the butterfly, edge B only when it exists
+        L.append(f'        float* dxrA = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
+        L.append('        float* dxrB = dxrA + lddx;')
+        for m in range(G.d1):
+            for c in range(G.cpw):
+                o = m * G.mul + c * 32
+                sx = _sx(G, c)
+                cond = 'on' if G.masked else None
+                L.append(f'        {"if (on) " if cond else ""}dxrA[{o}] = dx{m}{sx}.x;')
+                L.append(f'        if ({"on && " if cond else ""}vB) dxrB[{o}] = dx{m}{sx}.y;')
+        L.append(f'        float dyA[{NP}], dyB[{NP}];')
+        L.append(f'#pragma unroll\n        for (int q_ = 0; q_ < {NP}; ++q_) {{ dyA[q_] = dyv[q_].x; dyB[q_] = dyv[q_].y; }}')
+        if gr_in_butterfly:
+            L.append(f'        dyA[{S}] = gr2.x; dyB[{S}] = gr2.y;')
+        nacc = SD if gr_in_butterfly else S
+        L.append(f'        sevenn_dy_accumulate<{NP}>(dyA, lane, dYu + (size_t)e * {SD}, {nacc});')
+        L.append(f'        if (vB) sevenn_dy_accumulate<{NP}>(dyB, lane, dYu + (size_t)(e + 1) * {SD}, {nacc});')
+        if not gr_in_butterfly:
+            L.append(f'        sevenn_gr_accumulate(gr2.x, lane, dYu + (size_t)e * {SD} + {S});')
+            L.append(f'        if (vB) sevenn_gr_accumulate(gr2.y, lane, dYu + (size_t)(e + 1) * {SD} + {S});')
+        L.append('      }')
+        L.append('    }')
+        L.append('  }')
+    L.append('UNIT_LOOP_END')
+    return L
+
+
 def pack_table(spec: ConvSpec, tab):
     """Table layout the packed (TAB_F2) kernels read: for every channel pair (c, c' = c + 32) of a two-chunk unit the
     two float4 (f_i, g_i, f_i+1, g_i+1)[c], [c'] become (f_i[c], f_i[c'], g_i[c], g_i[c']) at column c and the same
@@ -773,7 +992,7 @@ def generate(spec: ConvSpec) -> str:
     out += gen_fwd(spec, groups, sig) + ['']
     out += gen_bwd(spec, groups, sig) + ['']
     out += gen_fwd(spec, groups_tab, sig, tab=True) + ['']
-    out += gen_bwd(spec, groups_tab, sig, tab=True) + ['']
+    out += (gen_bwd_tab_pair(spec, groups_tab, sig) if tab_ep(True) else gen_bwd(spec, groups_tab, sig, tab=True)) + ['']
     rf, rb = tab_ring_floats(spec, False), tab_ring_floats(spec, True)
     out.append(f'extern "C" int sevenn_conv_fwd_tab_{sig}(const float* x, int ldx, const float* Yt, const float* tab,')
     out.append('    const int* rowptr, const int* col, int n_dst, float inv_denom, float* out, int ldo, void* stream) {')

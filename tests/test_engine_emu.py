@@ -82,7 +82,7 @@ def test_engine_emu_two_chunk_units(monkeypatch, packed):
     cfg['channel'] = 64
     conv = sp.build_spec(cfg).layers[1].conv
     assert [G.cpw for G in conv_codegen.make_groups(conv, True)] == [2, 1, 1]
-    assert ('float2' in conv_codegen.generate(conv)) == packed
+    assert ('= make_float2(g' in conv_codegen.generate(conv)) == packed      # channel pairs of the output gradient
     torch.manual_seed(777)
     model = S.build_model(cfg).eval()
     numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=4)
