@@ -484,7 +484,7 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
 # step), hurts SevenNet-0's (cfg2 3.75 -> 4.10 ms: the doubled loop body falls out of the instruction cache)
 TAB_UNROLL_BY_SIG = {'c703e622066': 2}
 _TAB_UNROLL_ENV = _os0.environ.get('SEVENN_TAB_UNROLL')
-TAB_XY_DEPTH = 4     # ring slots for x_j / Y (3 edges in flight)
+TAB_XY_DEPTH = int(_os0.environ.get('SEVENN_TAB_XY_DEPTH', '4'))     # ring slots for x_j / Y (depth - 1 edges in flight); power of two
 TAB_W_DEPTH = 2      # ring slots for the table rows (1 edge in flight: they come from L2)
 
 
