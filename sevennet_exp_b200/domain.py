@@ -259,9 +259,22 @@ class Halo:
         return t
 
 
-def evaluate_decomposed(calc, dec: Decomposition, halo: Halo, types_dev=None, pos_dev=None):
-    """One E/F/S evaluation of this rank's sub-domain; returns (E_total, forces of owned atoms, virial6)
-    with energy and virial already summed over ranks."""
+class _NativeStepInfo:
+    """What callers read off the graph of a step (edge count) when the C++ host built it on the device."""
+
+    def __init__(self, native, header):
+        self._native, self._header = native, header
+
+    @property
+    def n_edges(self):
+        return self._native.parse_header(self._header.cpu().numpy())[3]
+
+
+def evaluate_decomposed(calc, dec: Decomposition, halo: Halo, types_dev=None, pos_dev=None, host='auto'):
+    """One E/F/S evaluation of this rank's sub-domain; returns (E_total, forces of owned atoms, virial6, graph info)
+    with energy and virial already summed over ranks.  host='auto': the C++ whole-model host (one C call per step, the
+    ghost exchanges plugged in through `sevenn_halo_hooks`) when the calculator has one, else the per-launch Python
+    driver; host='python' forces the latter (stage profiling, emulation tests)."""
     dev = calc.device
     if types_dev is None:
         types_dev = torch.from_numpy(calc._lut[dec.numbers].astype(np.int32)).to(dev)
@@ -269,6 +282,16 @@ def evaluate_decomposed(calc, dec: Decomposition, halo: Halo, types_dev=None, po
     # and those come first, so the CSR is simply truncated
     # rows for the owned atoms only (they come first); ghosts are neighbours, never centres
     nl = dec.n_local
+    native = getattr(calc, 'native', None)
+    if native is not None and host != 'python':
+        if pos_dev is None:
+            pos_dev = torch.from_numpy(np.ascontiguousarray(dec.pos, dtype=np.float64)).to(dev)
+        out = native.evaluate(types_dev, pos_dev, np.eye(3), [False] * 3, pos_host=dec.pos, n_local=nl,
+                              halo=halo if halo.world > 1 else None)
+        F = halo.fold_forces(out['forces'])
+        tot = out['header'][:56].view(torch.float64).clone()          # energy, virial6 (fp64 sums of this rank)
+        halo.all_reduce_(tot)
+        return tot[0], F, tot[1:], _NativeStepInfo(native, out['header'])
     r = calc.nl.build(dec.pos, np.eye(3), [False] * 3, calc.cutoff, pos_dev=pos_dev, n_rows=nl)
     g = Graph(types_dev, r['edge_vec'], r['rowptr'], r['col'], r['cptr'], r['cedge'], nl, dec.volume)
     out = calc.engine.evaluate(g, halo=halo)

@@ -135,10 +135,17 @@ class SevenNetCalculator(_AseCalculator):
     # ---- plain-array API (also what bench.py times end to end)
     def compute(self, numbers, positions, cell, pbc):
         numbers = np.asarray(numbers)
-        types = self._lut[numbers]
-        if (types < 0).any():
-            bad = sorted({int(z) for z in numbers[types < 0]})
-            raise ValueError(f'Unknown atomic numbers {bad} for this model')   # sevennet_calculator.py:153-161
+        # species rarely change between calls (MD): the type lookup of the previous call is reused when they did not
+        last = getattr(self, '_last_types', None)
+        if last is not None and last[0].shape == numbers.shape and np.array_equal(last[0], numbers):
+            types = last[1]
+        else:
+            types = self._lut[numbers]
+            if (types < 0).any():
+                bad = sorted({int(z) for z in numbers[types < 0]})
+                raise ValueError(f'Unknown atomic numbers {bad} for this model')   # sevennet_calculator.py:153-161
+            types = types.astype(np.int32)
+            self._last_types = (numbers.copy(), types)
         pos = np.ascontiguousarray(np.asarray(positions, dtype=np.float64))
         n = len(numbers)
         if self._ts_model is not None and n > 0:
@@ -146,12 +153,14 @@ class SevenNetCalculator(_AseCalculator):
         if self.native is not None and n > 0:
             if self.native.lib.cdll.sevenn_model_set_tc_min_rows(self.native.handle, int(self.engine.tc_min_rows)):
                 raise RuntimeError('sevenn_model_set_tc_min_rows failed')
-            r = self.native.evaluate_host(types.astype(np.int32), pos, cell, pbc)
+            r = self.native.evaluate_host(types, pos, cell, pbc)
             vol = abs(float(np.linalg.det(np.asarray(cell, dtype=np.float64).reshape(3, 3))))
             vol = float(np.finfo(float).eps) if vol == 0 else vol
             stress_model = -r['virial6'] / vol
-            return {'energy': r['energy'], 'free_energy': r['energy'], 'forces': r['forces'].astype(np.float64),
-                    'stress': -stress_model[[0, 1, 2, 4, 5, 3]], 'energies': r['atomic_energy'].astype(np.float64),
+            # fp32 arrays like the reference's (`.detach().cpu().numpy()` of fp32 tensors, sevennet_calculator.py:186-201);
+            # copies, because the host's pinned result buffer is reused by the next call
+            return {'energy': r['energy'], 'free_energy': r['energy'], 'forces': r['forces'].copy(),
+                    'stress': -stress_model[[0, 1, 2, 4, 5, 3]], 'energies': r['atomic_energy'].copy(),
                     'inferred_stress': stress_model, 'n_edges': r['n_edges']}
         types_dev = torch.from_numpy(types.astype(np.int32)).to(self.device, non_blocking=True)
         g = self.nl.graph(types_dev, pos, cell, pbc, self.cutoff)
