@@ -111,6 +111,18 @@ def run(args):
     te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_t = te.item() / args.steps
+    if os.environ.get('SEVENN_E2E_DEBUG'):       # where one end-to-end step spends its wall time (printed by rank 0)
+        import sys
+        for _ in range(3):
+            marks = [time.perf_counter()]
+            pd.copy_(pos_host, non_blocking=True); torch.cuda.synchronize(); marks.append(time.perf_counter())
+            E, F, vir, g = evaluate_decomposed(calc, dec, halo, types_dev=types_dev, pos_dev=pd); marks.append(time.perf_counter())
+            torch.cuda.synchronize(); marks.append(time.perf_counter())
+            host_F.copy_(F, non_blocking=True); host_EV.copy_(torch.cat([E.reshape(1), vir]), non_blocking=True)
+            torch.cuda.synchronize(); marks.append(time.perf_counter())
+            if rank == 0:
+                print('[e2e debug] h2d %.2f ms, host side of the step %.2f ms, wait for the GPU %.2f ms, d2h %.2f ms' % tuple(
+                    1e3 * (b - a) for a, b in zip(marks[:-1], marks[1:])), file=sys.stderr, flush=True)
     stats = torch.tensor([dec.n_local, dec.n_ghost, g.n_edges], dtype=torch.float64, device=dev)
     smax = stats.clone()
     dist.all_reduce(stats)
