@@ -7,17 +7,22 @@
 // split x = hi + lo with hi = tf32(x); D += A_hi.B_hi + A_lo.B_hi + A_hi.B_lo accumulates in fp32 in TMEM,
 // which keeps ~2^-21 relative error per product (north_star tolerances are fp32 ones).
 //
-// Structure (persistent CTAs, grid = (SMs / n_tiles, n_tiles), 416 threads, one CTA per SM):
-//   warps 0-7  producers : A rows global -> smem by cp.async (ring, stages-1 k-blocks in flight per thread),
-//                          then an in-place (hi, lo) split into SWIZZLE_128B K-major tiles.
-//                          B arrives as a pre-swizzled (hi, lo) image through TMA bulk copies (cp.async.bulk):
-//                          "resident" mode = the whole [K, Nt] image once per CTA (radial-MLP forward, K = 64),
-//                          "streaming" mode = one k-block image per stage (large K).
-//   warp  12   MMA issuer: 4 k-steps x 3 tcgen05.mma.kind::tf32 (M=128, N=Nt<=256, K=8) per 32-wide k-block,
-//                          tcgen05.commit frees the stage / publishes the accumulator
-//   warps 8-11 epilogue  : tcgen05.ld 32 columns at a time -> swizzled smem transpose -> full-line coalesced
-//                          16 B accesses with the fused epilogue (store / accumulate / act / act-gradient)
-//   TMEM: 2 x 256 fp32 columns, double buffered so the epilogue of tile i overlaps loads+MMA of tile i+1.
+// Structure of gemm_tc_kernel (persistent CTAs, one per SM, 608 threads; the large-K kernel gemm_tca_kernel is
+// described where it is defined):
+//   warps 0-7   producers : each thread owns one 16 B chunk of four rows of every 32-wide k-block; three k-blocks in
+//                           flight in registers (read-only 16 B loads), split x = hi + lo in registers, stored once as
+//                           the two SWIZZLE_128B K-major operand tiles of a ring slot.
+//   warp  18    B loader  : B is a pre-swizzled (hi, lo) image.  "resident" = the whole [K, Nt] image once per CTA when
+//                           it fits beside two A stages (<= 128 KB), else "streaming" = one k-block image per ring slot
+//                           (TMA bulk copies, cp.async.bulk; mbarrier.arrive.expect_tx is the 257th arrival of the slot).
+//   warps 16,17 MMA       : alternate row tiles; 4 k-steps x 3 tcgen05.mma.kind::tf32 (M=128, N=Nt<=256, K=8) per
+//                           k-block; tcgen05.commit frees the slot / publishes the accumulator.  One thread sustains
+//                           ~50 clk per MMA and ~270 clk per commit, which bounded K <= 64 tiles with one issuer.
+//   warps 8-15  epilogue  : two per TMEM lane quadrant (even / odd 32-column chunks): tcgen05.ld -> swizzled smem
+//                           transpose -> full-line coalesced 16 B accesses with the fused epilogue (store / accumulate /
+//                           act / act-gradient).
+//   TMEM: four 128-column accumulators when Nt <= 128 (two per issuing warp), else two of 256 columns: the epilogue of
+//   a tile overlaps loads + MMAs of the next ones.
 #include "sevenn_common.cuh"
 #include "../../include/sevenn_b200.h"
 
@@ -40,7 +45,7 @@
 struct TcParams {
   sevenn_gemm_args g;
   const float* Bimg;    // [n_tiles][KB][2][Nt][32] pre-swizzled hi/lo images
-  int Nt, n_tiles, KB, stages, vec4, mode, resident, dslack;
+  int Nt, n_tiles, KB, stages, vec4, mode, resident;
   long long m_tiles;
   long long* dbg;       // optional clock64 trace of CTA (0,0) (SEVENN_TC_DBG=1)
 };
@@ -794,8 +799,9 @@ static int tc_prepare(const sevenn_gemm_args* args, const float* Bimg, TcParams&
   if (stages > 6) stages = 6;
   if (stages < 2) return SEVENN_ERR_BAD_ARG;
   P.stages = stages;
-  { const char* e = getenv("SEVENN_TC_MMA_MODE"); P.mode = e ? atoi(e) : 0; }
-  { const char* e = getenv("SEVENN_TC_DSLACK"); P.dslack = e ? atoi(e) : 1; }
+  static int mma_mode = -1;            // diagnostics (SEVENN_TC_MMA_MODE bits: 1 plain TF32, 2 no stores, 4 no MMAs, 8 no proxy fence)
+  if (mma_mode < 0) { const char* e = getenv("SEVENN_TC_MMA_MODE"); mma_mode = e ? atoi(e) : 0; }
+  P.mode = mma_mode;
   P.vec4 = !((g.sCn & 3) || (g.sCm & 3) || ((uintptr_t)g.C & 15) || (g.C2 && ((uintptr_t)g.C2 & 15)) ||
              (g.P && ((uintptr_t)g.P & 15)));
   P.dbg = nullptr;
@@ -905,7 +911,9 @@ extern "C" int sevenn_gemm_tc(const sevenn_gemm_args* args, const float* Bimg, v
   size_t smem; bool tca;
   int rc = tc_prepare(args, Bimg, P, &smem, &tca);
   if (rc) return rc;
-  const bool dbg = getenv("SEVENN_TC_DBG") != nullptr;
+  static int dbg_on = -1;
+  if (dbg_on < 0) dbg_on = getenv("SEVENN_TC_DBG") != nullptr;
+  const bool dbg = dbg_on != 0;
   if (!tca && !dbg) return sevenn_gemm_tc_grouped(1, args, &Bimg, stream);
   const sevenn_gemm_args& g = P.g;
   static long long* dbg_dev = nullptr;
