@@ -258,6 +258,7 @@ int sevenn_adam_step_dev(float* param, const float* grad, float* exp_avg, float*
  * tabulated-radial variants (w interpolated from tab[n_int][wn] float4 nodes; Yt / dY rows as for sevenn_edge_*_tab):
  *   int sevenn_conv_fwd_tab_<sig>(x, ldx, Yt, tab, rowptr, col, n_dst, inv_denom, out, ldo, stream)
  *   int sevenn_conv_bwd_tab_<sig>(x, ldx, Yt, tab, rowptr, col, n_dst, inv_denom, gout, ldo, dxe, lddx, dY, dy_stride, stream)
+ * dxe == NULL in the backward calls: the per-edge dE/dx rows are not written (first layer: x does not depend on positions).
  * replaces IrrepsConvolution.forward's TensorProduct + message_gather (sevenn/nn/convolution.py:16-25,118-137). */
 
 #ifdef __cplusplus

@@ -449,14 +449,17 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
                 else:
                     L.append(f'          dyv[{q}] = fmaf({_f(cf)}, P_{i}_{k}, dyv[{q}]);')
             L.append('        }')
-        L.append(f'        float* dxr = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
         if f2:
             L.append('        gr = gr2.x + gr2.y;')
+        # dxe == nullptr: the caller does not need dE/dx (first layer: its input does not depend on the positions)
+        L.append('        if (dxe != nullptr) {')
+        L.append(f'          float* dxr = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
         for m in range(G.d1):
             for c in range(G.cpw):
                 val = f'dx{m}.{"xy"[c]}' if f2 else f'dx{m}{_sx(G, c)}'
                 st = f'dxr[{m * G.mul + c * 32}] = {val};'
-                L.append(f'        if (on) {st}' if G.masked else f'        {st}')
+                L.append(f'          if (on) {st}' if G.masked else f'          {st}')
+        L.append('        }')
         if gr_in_butterfly:
             L.append(f'        dyv[{S}] = gr;')
         if nv_smem:
@@ -930,15 +933,17 @@ def gen_bwd_tab_pair(spec: ConvSpec, groups: List[_Group], sig: str) -> List[str
                     L.append(f'          dyv[{q}] = __ffma2_rn({_f2(cf)}, P_{i}_{k}, dyv[{q}]);')
             L.append('        }')
         # ---- per-edge outputs: dx_e rows, dY (+ radial term) through the butterfly, edge B only when it exists
-        L.append(f'        float* dxrA = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
-        L.append('        float* dxrB = dxrA + lddx;')
+        L.append('        if (dxe != nullptr) {')
+        L.append(f'          float* dxrA = dxe + (size_t)e * lddx + {G.xoff} + c32 + lane;')
+        L.append('          float* dxrB = dxrA + lddx;')
         for m in range(G.d1):
             for c in range(G.cpw):
                 o = m * G.mul + c * 32
                 sx = _sx(G, c)
                 cond = 'on' if G.masked else None
-                L.append(f'        {"if (on) " if cond else ""}dxrA[{o}] = dx{m}{sx}.x;')
-                L.append(f'        if ({"on && " if cond else ""}vB) dxrB[{o}] = dx{m}{sx}.y;')
+                L.append(f'          {"if (on) " if cond else ""}dxrA[{o}] = dx{m}{sx}.x;')
+                L.append(f'          if ({"on && " if cond else ""}vB) dxrB[{o}] = dx{m}{sx}.y;')
+        L.append('        }')
         L.append(f'        float dyA[{NP}], dyB[{NP}];')
         L.append(f'#pragma unroll\n        for (int q_ = 0; q_ < {NP}; ++q_) {{ dyA[q_] = dyv[q_].x; dyB[q_] = dyv[q_].y; }}')
         if gr_in_butterfly:

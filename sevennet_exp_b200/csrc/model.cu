@@ -332,8 +332,11 @@ int evaluate_graph(sevenn_model* m, Arena& A, const GraphView& g, const sevenn_h
     if (L.si2.bwd_needs_zero) { rc = zero_async(A, dagg, (size_t)nl * L.dmid * 4, st); if (rc) return rc; }
     rc = linear_bwd(m, A, L.si2, dpre, nl, dagg, false, nullptr, st);
     if (rc) return rc;
-    float* dxe = A.f32(E * L.dx_in);
-    if (L.zero_dxe) { rc = zero_async(A, dxe, (size_t)E * L.dx_in * 4, st); if (rc) return rc; }
+    float* dxe = nullptr;                        // layer 0: dE/dx is not needed, the kernel skips it (dxe == NULL)
+    if (t > 0) {
+      dxe = A.f32(E * L.dx_in);
+      if (L.zero_dxe) { rc = zero_async(A, dxe, (size_t)E * L.dx_in * 4, st); if (rc) return rc; }
+    }
     if (nl > 0)
       RUN(L.bwd(h[t], L.dx_in, Y, L.tab, g.rowptr, g.col, (int)nl, L.inv_denom, dagg, L.dmid, dxe, L.dx_in, dY,
                 E * SD, vs));

@@ -651,7 +651,10 @@ class Engine(Kernels):
                 w = sv['w'] if sv['w'] is not None else self._mlp_last_from(lay, sv['h_last'], E)
             self._mark(f'conv_bwd_{lay["sig"]}')
             unused = any(not any(p.gx == gi for p in L.conv.paths) for gi in range(len(L.conv.lx.groups)))
-            dxe = self._zeros(max(E, 1), dx_in) if unused else self._empty(max(E, 1), dx_in)
+            if t == 0:
+                dxe = None                # layer-0 inputs do not depend on positions: the kernel skips dE/dx (dxe == NULL)
+            else:
+                dxe = self._zeros(max(E, 1), dx_in) if unused else self._empty(max(E, 1), dx_in)
             if table:
                 dW = w = None
                 _, bwd = lib.conv_tab(lay['sig'])
