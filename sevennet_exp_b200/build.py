@@ -15,6 +15,7 @@ GEN = os.path.join(CSRC, 'generated')
 LIBDIR = os.path.join(HERE, '_build')
 LIB = os.path.join(LIBDIR, 'libsevenn_b200.so')
 TORCH_LIB = os.path.join(LIBDIR, 'libsevenn_b200_torch.so')      # torch.ops.sevenn_b200.* (csrc/torch_op.cpp)
+PAIR_HARNESS = os.path.join(LIBDIR, 'sevenn_pair_harness')        # libtorch client like pair_e3gnn.cpp (csrc/pair_harness.cpp)
 MD_HOST = os.path.join(LIBDIR, 'sevenn_md_host')                  # torch-free C++ host on the C ABI (csrc/md_host.cpp)
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17', '-Xcompiler', '-fPIC']
 STATIC_UNITS = ['misc.cu', 'nl.cu', 'edge.cu', 'node.cu', 'gemm_simt.cu', 'gemm_tc.cu', 'model.cu', 'train.cu']
@@ -135,7 +136,30 @@ def build_md_host(verbose=True):
     return MD_HOST
 
 
+def build_pair_harness(verbose=True):
+    """sevenn_pair_harness: a libtorch program that loads a deployed archive and calls it exactly like the reference's
+    LAMMPS pair style does (csrc/pair_harness.cpp); links libtorch only -- the op library is dlopen'ed at run time."""
+    import torch
+    import torch.utils.cpp_extension as ce
+    src = os.path.join(CSRC, 'pair_harness.cpp')
+    if os.path.exists(PAIR_HARNESS) and os.path.getmtime(PAIR_HARNESS) >= os.path.getmtime(src):
+        return PAIR_HARNESS
+    tlib = os.path.join(os.path.dirname(torch.__file__), 'lib')
+    cuda_home = os.environ.get('CUDA_HOME', '/usr/local/cuda')
+    cmd = ['g++', '-O2', '-std=c++17', f'-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}']
+    for inc in ce.include_paths() + [os.path.join(cuda_home, 'include')]:
+        cmd += ['-I', inc]
+    cmd += [src, '-o', PAIR_HARNESS + '.tmp', '-L', tlib, '-Wl,--no-as-needed', '-ltorch', '-ltorch_cpu', '-lc10',
+            '-ltorch_cuda', '-lc10_cuda', '-Wl,--as-needed', '-ldl', f'-Wl,-rpath,{tlib}']
+    subprocess.check_call(cmd)
+    os.replace(PAIR_HARNESS + '.tmp', PAIR_HARNESS)
+    if verbose:
+        print(f'built {PAIR_HARNESS}')
+    return PAIR_HARNESS
+
+
 if __name__ == '__main__':
     build()
     build_torch_op()
     build_md_host()
+    build_pair_harness()

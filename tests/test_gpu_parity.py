@@ -604,6 +604,34 @@ assert 'sevennet_exp_b200' not in sys.modules
     assert np.abs(out['stress'] - gold['stress']).max() * KBAR < 1e-2            # the reference ran in fp32
 
 
+def test_cpp_libtorch_client_like_the_lammps_pair_style(lib, golden_dir, tmp_path):
+    """csrc/pair_harness.cpp is a libtorch program that does what `pair_style e3gnn` does (pair_e3gnn.cpp:306-335 coeff,
+    :147-264 compute): dlopen of the op library, torch::jit::load with `_extra_files`, full neighbour list with strict
+    r < rc, the serial input dict, forward, the four outputs.  Run on the frame of the REFERENCE's own deployed model
+    (tests/golden/deployed_serial_hfo2.npz) with our archive of the same weights."""
+    import subprocess
+    from sevennet_exp_b200 import build as B, deploy as D
+    from tests.test_oracle import deployed_serial_case
+    cfg, sd, numbers, pos, cell, gold = deployed_serial_case(golden_dir)
+    path = D.deploy((cfg, sd), str(tmp_path / 'deployed_serial.pt'))
+    exe = B.build_pair_harness(verbose=False)
+    with open(tmp_path / 'structure.txt', 'w') as f:
+        f.write(f'{len(numbers)}\n' + ' '.join(repr(float(v)) for v in np.asarray(cell).reshape(-1)) + '\n')
+        for z, r in zip(numbers, pos):
+            f.write(f'{D._SYMBOLS[int(z)]} {float(r[0])!r} {float(r[1])!r} {float(r[2])!r}\n')
+    r = subprocess.run([exe, D.TORCH_OP_LIB, path, str(tmp_path / 'structure.txt'), str(tmp_path / 'result.txt')],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-500:], r.stderr[-2000:])
+    assert f'{gold["edge_index"].shape[1]} edges' in r.stdout          # same edge count as the reference's graph
+    rows = [list(map(float, ln.split())) for ln in open(tmp_path / 'result.txt')]
+    n = len(numbers)
+    energy, stress, per_atom = rows[0][0], np.array(rows[1]), np.array(rows[2:])
+    assert abs(energy - float(gold['energy'])) / n < 1e-5
+    assert np.abs(per_atom[:, 3] - gold['atomic_energy'].reshape(-1)).max() < 1e-5
+    assert np.abs(per_atom[:, :3] - gold['force']).max() < 1e-4
+    assert np.abs(stress - gold['stress']).max() * KBAR < 1e-2             # the reference ran in fp32
+
+
 def test_calculator_takes_an_nn_module_instance(lib):
     """reference sevennet_calculator.py:111-124: SevenNetCalculator(model=<AtomGraphSequential>, file_type='model_instance')."""
     from sevennet_exp_b200 import nn as bnn
