@@ -64,7 +64,20 @@ def _worker(rank, world, port, ret):
         assert (F - Fref).abs().max().item() < 1e-4
         stress = -(vir / dec.volume).float()
         assert (stress - ref[S.STRESS].detach()).abs().max().item() * 1602.1766208 < 1e-3 * 10
-        ret[rank] = (dec.n_local, dec.n_ghost)
+        # atoms move across brick faces and the periodic boundary (pair_e3gnn_parallel.cpp:684-785 relies on
+        # LAMMPS re-assigning owners and ghosts): a rigid shift of 0.37 of the cell along x and y plus a random walk,
+        # positions left unwrapped; a new Decomposition / Halo from the moved positions must again equal the oracle
+        rng = np.random.default_rng(5)
+        pos2 = pos + 0.37 * (cell[0] + cell[1]) + rng.normal(scale=0.08, size=pos.shape)
+        dec2 = Decomposition(numbers, pos2, cell, spec.cutoff, brick_grid(world), rank)
+        moved = len(set(dec.local_ids.tolist()) ^ set(dec2.local_ids.tolist()))
+        halo2 = Halo(dec2, lib, 'cpu')
+        E2, F2, vir2, _ = evaluate_decomposed(calc, dec2, halo2)
+        ref2 = model(S.atoms_to_graph(numbers, pos2, cell, [True] * 3, cfg['cutoff']))
+        assert abs(E2.item() - ref2[S.E_TOT].item()) / n < 1e-5
+        assert (F2 - ref2[S.FORCE].detach()[torch.from_numpy(dec2.local_ids)]).abs().max().item() < 1e-4
+        assert ((-(vir2 / dec2.volume).float()) - ref2[S.STRESS].detach()).abs().max().item() * 1602.1766208 < 1e-3 * 10
+        ret[rank] = (dec.n_local, dec.n_ghost, moved)
     finally:
         dist.destroy_process_group()
 
@@ -79,6 +92,7 @@ def test_decomposed_equals_single_domain(world):
     ret = mgr.dict()
     mp.spawn(_worker, args=(world, _free_port(), ret), nprocs=world, join=True)
     assert len(ret) == world and all(v[1] > 0 for v in ret.values())
+    assert all(v[2] > 10 for v in ret.values())            # ownership really changed on every rank
 
 
 def test_brick_grid():
