@@ -157,6 +157,14 @@ def run(args):
                     'elided': 'w and dW [E, wn] (tabulated radial weights)' if tab else None,
                     'touched_bytes': touched, 'touched_frac': touched / (dom_ms * 1e-3) / 1e9 / peak}
         stage_sorted = dict(sorted(((k, round(v, 4)) for k, v in stage.items()), key=lambda kv: -kv[1])[:12])
+        # ghost exchanges of one step on rank 0 (CUDA events around the exchange calls of the profiling pass: pack + NVLink
+        # write + device-side barrier, i.e. including the wait for the slowest neighbour) and the bytes this rank sends
+        n_send = int(halo.send_off[-1])
+        halo_info = {'fwd_ms': round(stage.get('halo_fwd', 0.0), 4), 'bwd_ms': round(stage.get('halo_bwd', 0.0), 4),
+                     'exchanges_per_step': 2 * (len(calc.spec.layers) - 1) + 1,
+                     'rows_sent_rank0': n_send, 'rows_received_rank0': int(halo.recv_off[-1]),
+                     'bytes_sent_per_exchange_rank0': n_send * calc.spec.layers[1].conv.lx.dim * 4,
+                     'share_of_step': round((stage.get('halo_fwd', 0.0) + stage.get('halo_bwd', 0.0)) / ms_step, 4)}
         x_dim = calc.spec.layers[1].conv.lx.dim
         line = {
             'metric': B.METRIC, 'value': n_total / (ms_step * 1e-3), 'unit': B.UNIT, 'n_gpus': world,
@@ -178,7 +186,8 @@ def run(args):
                     'h2d_bytes_per_step': int(pos_host.numel() * 8),
                     'd2h_bytes_per_step': int(7 * 8 + 3 * dec.n_local * 4)},
             'gpu_launches': int(launches), 'clocks': sampler.summary() if sampler else None,
-            'check': check, 'roofline': roofline, 'stage_ms_rank0': stage_sorted, 'cpu_baseline': None,
+            'check': check, 'roofline': roofline, 'stage_ms_rank0': stage_sorted, 'halo_rank0': halo_info,
+            'cpu_baseline': None,
         }
         print(json.dumps(line), flush=True)
     dist.barrier()

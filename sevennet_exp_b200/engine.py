@@ -563,6 +563,7 @@ class Engine(Kernels):
             self._linear_fwd(lay['si1'], x, n_x, h)
             if halo is not None and t > 0 and (n_x < nn or getattr(halo, 'world', 1) > 1):
                 # collective: every rank enters it, also one whose brick has no ghosts (vacuum side of a slab)
+                self._mark('halo_fwd')
                 halo.forward(t, h)    # fills rows [n_local, n_nodes)
             self._mark('mlp_fwd')
             if table:
@@ -696,6 +697,7 @@ class Engine(Kernels):
             self.n_launch += 1
             del dxe
             if halo is not None and (nl < nn or getattr(halo, 'world', 1) > 1):
+                self._mark('halo_bwd')
                 halo.backward(t, dh)  # ghost rows -> owners (added into rows [0, n_local))
             self._mark('si1_sc_bwd')
             dxn = self._zeros(nl, dx_in) if lay['si1'].bwd_needs_zero else self._empty(nl, dx_in)
