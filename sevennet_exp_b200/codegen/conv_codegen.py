@@ -78,7 +78,7 @@ TAB_CPW = int(_os0.environ.get('SEVENN_TAB_CPW', '2'))
 # float2; warp-uniform M entries and literals are free broadcast / immediate operands of FFMA2
 TAB_F2 = _os0.environ.get('SEVENN_TAB_F2', '0') == '1'
 # table rows as monomial coefficients (c0, c1, c2, c3) of t instead of Hermite nodes (radial_table.build_table layout='poly')
-# A/B on B200 (tools/gpu_ab2.sh, r02): cfg2 3.84 -> 3.75 ms, 216 k-atom Si 106.1 -> 103.9 ms, cfg3 32.6 -> 32.1 ms per step
+# A/B on B200 (tools/gpu.sh ab, r02): cfg2 3.84 -> 3.75 ms, 216 k-atom Si 106.1 -> 103.9 ms, cfg3 32.6 -> 32.1 ms per step
 TAB_POLY = _os0.environ.get('SEVENN_TAB_POLY', '1') == '1' and not TAB_F2
 
 
@@ -135,7 +135,7 @@ MIN_CTAS = {
     'c703e622066': (4, 3),      # SevenNet-l3i5 inner layers: 127 / 168 registers
 }
 MIN_CTAS_DEFAULT = (1, 1)
-# tabulated kernels: measured with tools/tune_occupancy.sh on B200 (profiles/r01e_occupancy_sweep.log): SevenNet-0
+# tabulated kernels: measured with tools/gpu.sh sweep-occupancy on B200 (profiles/r01e_occupancy_sweep.log): SevenNet-0
 # forward 1.090 -> 1.045 ms at 5 instead of 6; l3i5 backward 22.5 -> 18.6 ms at 4 instead of 2 (128 registers,
 # 64 B of spill; 4 CTAs is also what the 56.6 KB ring per CTA allows)
 MIN_CTAS_TAB = {
@@ -150,7 +150,7 @@ MIN_CTAS_TAB_EP_DEFAULT = int(_os0.environ.get('SEVENN_MIN_CTAS_EP', '2'))
 
 
 def _env_overrides():
-    """Tuning runs only (tools/tune_occupancy.sh): SEVENN_MIN_CTAS / SEVENN_MIN_CTAS_TAB = 'sig:fwd,bwd;sig:fwd,bwd'."""
+    """Tuning runs only (tools/gpu.sh sweep-occupancy): SEVENN_MIN_CTAS / SEVENN_MIN_CTAS_TAB = 'sig:fwd,bwd;sig:fwd,bwd'."""
     import os
     for var, table in (('SEVENN_MIN_CTAS', MIN_CTAS), ('SEVENN_MIN_CTAS_TAB', MIN_CTAS_TAB)):
         for item in filter(None, os.environ.get(var, '').split(';')):
@@ -506,7 +506,7 @@ def _tab_w_floats(G: _Group) -> int:
 
 # Where the table rows of the next edge wait: 'smem' = cp.async into the ring (rows cross the L1 data pipe twice:
 # LDGSTS write + LDS read), 'regs' = 16-byte __ldg straight into registers one edge ahead (once).  (forward, backward)
-# by signature; measured with tools/tune_tabmode.sh on B200 (profiles/r01e_table_staging_sweep.log): SevenNet-0 inner
+# by signature; measured with tools/gpu.sh sweep-tabmode on B200 (profiles/r01e_table_staging_sweep.log): SevenNet-0 inner
 # forward 1.042 -> 0.804 ms, backward 1.914 -> 1.864 ms; l3i5 inner forward 8.22 -> 7.97 ms, backward slower in
 # registers (18.6 -> 19.2 ms: 128 registers are already spilling there), first / last layers 5-25 % faster both ways.
 import os as _os
@@ -541,7 +541,7 @@ def dy_smem_values(spec: ConvSpec) -> int:
 # instruction for both edges; the output gradient g and the Clebsch-Gordan literals are free broadcast / immediate
 # operands, and the backward keeps no accumulator across edges, so nothing but per-edge temporaries doubles.
 # (forward, backward) by signature; SEVENN_TAB_EP='fwd,bwd' overrides for A/B builds.
-# MEASURED (B200, tools/gpu_ab2.sh, profiles/r02b_edge_pair_ab.txt): SLOWER.  SevenNet-0 inner backward 184 registers ->
+# MEASURED (B200, tools/gpu.sh ab, profiles/r02b_edge_pair_ab.txt): SLOWER.  SevenNet-0 inner backward 184 registers ->
 # 2 CTAs of 4 warps per SM: 39.9 -> 61.3 ms on the 216 k-atom cell (51.6 ms capped at 168 registers / 3 CTAs), although the
 # kernel executes ~35 % fewer instructions -- with 8-12 warps per SM the dependent chains of one warp (loads -> M -> q ->
 # dx / dY -> butterfly) are no longer covered; the scalar kernel at 120 registers / 16 warps is latency AND issue bound.

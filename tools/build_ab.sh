@@ -1,5 +1,5 @@
 #!/bin/bash
-# Builds library variants for same-box A/B runs (tools/gpu_ab.sh, tools/gpu_ab_f2.sh) into tools/ab/ (git-ignored, travels
+# Builds library variants for same-box A/B runs (tools/gpu.sh ab, tools/gpu.sh ab) into tools/ab/ (git-ignored, travels
 # with gpurun).  usage: tools/build_ab.sh <tag> [ENV=VALUE ...]    e.g.  tools/build_ab.sh f2 SEVENN_TAB_F2=1
 #                                                                        tools/build_ab.sh cpw1 SEVENN_TAB_CPW=1
 # The default library is rebuilt afterwards so the tree is left as it was.
