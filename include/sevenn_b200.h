@@ -193,6 +193,12 @@ typedef struct {                /* per-layer ghost exchange of a domain-decompos
   void* user;
   int (*forward)(void* user, int layer, float* h /* n_nodes x dim; fill rows >= n_local */, int dim, void* stream);
   int (*backward)(void* user, int layer, float* dh /* add ghost rows into their owners */, int dim, void* stream);
+  /* Overlap: rows [0, n_interior) have no ghost neighbour (the host orders its owned atoms that way).  When
+   * n_interior > 0 and side_stream != NULL the forward exchange of a layer is issued on side_stream while the convolution
+   * of the interior rows runs on the main stream; the boundary rows follow once the exchange has landed.  0 / NULL: the
+   * exchange runs in line on the main stream. */
+  long long n_interior;
+  void* side_stream;
 } sevenn_halo_hooks;
 int sevenn_model_create(const int* prog /* host */, long long n_prog, const float* data /* host */, long long n_data,
                         sevenn_model** out);

@@ -85,6 +85,7 @@ struct sevenn_model {
   float tab_inv_h, cutoff;
   float* dev = nullptr;          // all weights, one allocation
   float* img = nullptr;          // tcgen05 operand images of the block weights, rebuilt at create time
+  cudaEvent_t ev_main = nullptr, ev_side = nullptr;   // ordering between the main stream and a host's halo side stream
   const float *embed, *scale, *shift;
   std::vector<Layer> layers;
   Lin read1, read2;
@@ -281,13 +282,35 @@ int evaluate_graph(sevenn_model* m, Arena& A, const GraphView& g, const sevenn_h
     rc = linear_fwd(m, A, L.si1, x, n_x, h[t], false, nullptr, st, &both);
     if (rc) return rc;
     if (!A.dry) { rc = flush_simt(m, both.g, both.n, st); if (rc) return rc; }
+    // ghost exchange: in line, or on the side stream while the rows without ghost neighbours are convolved
+    long long n_int = 0;
     if (t > 0 && halo != nullptr && halo->forward != nullptr && !A.dry) {
-      rc = halo->forward(halo->user, t, h[t], L.dx_in, vs);      // fills rows [n_local, n_nodes)
-      if (rc) return rc;
+      const bool overlap = halo->side_stream != nullptr && halo->n_interior > 0 && halo->n_interior <= nl &&
+                           m->ev_main != nullptr;
+      if (overlap) {
+        cudaStream_t side = (cudaStream_t)halo->side_stream;
+        if (cudaEventRecord(m->ev_main, st) != cudaSuccess || cudaStreamWaitEvent(side, m->ev_main, 0) != cudaSuccess)
+          return (int)cudaGetLastError();
+        rc = halo->forward(halo->user, t, h[t], L.dx_in, halo->side_stream);
+        if (rc) return rc;
+        if (cudaEventRecord(m->ev_side, side) != cudaSuccess) return (int)cudaGetLastError();
+        n_int = halo->n_interior;
+      } else {
+        rc = halo->forward(halo->user, t, h[t], L.dx_in, vs);      // fills rows [n_local, n_nodes)
+        if (rc) return rc;
+      }
     }
     const size_t mk = A.mark();
     float* agg = A.f32(nl * L.dmid);
-    if (nl > 0) RUN(L.fwd(h[t], L.dx_in, Y, L.tab, g.rowptr, g.col, (int)nl, L.inv_denom, agg, L.dmid, vs));
+    if (n_int > 0) {
+      RUN(L.fwd(h[t], L.dx_in, Y, L.tab, g.rowptr, g.col, (int)n_int, L.inv_denom, agg, L.dmid, vs));
+      if (cudaStreamWaitEvent(st, m->ev_side, 0) != cudaSuccess) return (int)cudaGetLastError();
+      if (nl > n_int)
+        RUN(L.fwd(h[t], L.dx_in, Y, L.tab, g.rowptr + n_int, g.col, (int)(nl - n_int), L.inv_denom,
+                  agg + n_int * L.dmid, L.dmid, vs));
+    } else if (nl > 0) {
+      RUN(L.fwd(h[t], L.dx_in, Y, L.tab, g.rowptr, g.col, (int)nl, L.inv_denom, agg, L.dmid, vs));
+    }
     rc = linear_fwd(m, A, L.si2, agg, nl, pre[t], true, nullptr, st);
     if (rc) return rc;
     A.release(mk);
@@ -592,12 +615,19 @@ extern "C" int sevenn_model_create(const int* prog, long long n_prog, const floa
   }
   const char* env = std::getenv("SEVENN_TC_MIN_ROWS");
   if (env != nullptr) m->tc_min_rows = std::atoi(env);
+  if (cudaEventCreateWithFlags(&m->ev_main, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&m->ev_side, cudaEventDisableTiming) != cudaSuccess) {
+    m->ev_main = m->ev_side = nullptr;           // no overlap then; everything else works
+    cudaGetLastError();
+  }
   *out = m;
   return 0;
 }
 
 extern "C" int sevenn_model_destroy(sevenn_model* m) {
   if (m == nullptr) return 0;
+  if (m->ev_main != nullptr) cudaEventDestroy(m->ev_main);
+  if (m->ev_side != nullptr) cudaEventDestroy(m->ev_side);
   cudaFree(m->img);
   cudaFree(m->dev);
   delete m;

@@ -61,6 +61,12 @@ class Decomposition:
         if np.any(halo * grid > 1.0):
             raise ValueError('sub-domain thinner than the cutoff (comm_brick.cpp:1074 aborts likewise)')
         self.local_ids = np.nonzero(owner == rank)[0]
+        # owned atoms farther than the cutoff from every face of the brick have no ghost neighbour: they come first, so a
+        # host can convolve rows [0, n_interior) while the ghost rows are still in flight (SURVEY 8e "Overlap")
+        fl = frac[self.local_ids]
+        interior = np.all((fl >= lo + halo) & (fl < hi - halo), axis=1)
+        self.local_ids = np.concatenate([self.local_ids[interior], self.local_ids[~interior]])
+        self.n_interior = int(interior.sum())
         # ghost candidates: every atom, every image shift in {-1,0,1}^3 whose position falls in the
         # brick grown by the halo, except the owned atoms themselves at shift 0
         g_ids, g_shift = [], []

@@ -8,6 +8,7 @@ synchronisation before the result copy.  What it replaces in the reference: the 
 ``SevenNetCalculator.calculate`` (sevenn/sevennet_calculator.py:163-202) and of ``PairE3GNN::compute``
 (sevenn/pair_e3gnn/pair_e3gnn.cpp:71-274)."""
 import ctypes
+import os
 from typing import Optional
 
 import numpy as np
@@ -134,7 +135,8 @@ HALO_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c
 
 
 class HaloHooks(ctypes.Structure):
-    _fields_ = [('user', ctypes.c_void_p), ('forward', HALO_FN), ('backward', HALO_FN)]
+    _fields_ = [('user', ctypes.c_void_p), ('forward', HALO_FN), ('backward', HALO_FN),
+                ('n_interior', ctypes.c_longlong), ('side_stream', ctypes.c_void_p)]
 
 
 class NativeModel:
@@ -158,6 +160,7 @@ class NativeModel:
         self._res = None
         self._cap = {}             # (n_local, n_nodes) -> edge capacity
         self._hooks_keep = None
+        self._side = None
         self._graphs, self._graph_seen = {}, None
         self._replayed = [0, 0]      # library calls / tcgen05 launches executed through graph replays
         self._stage = {}
@@ -259,14 +262,28 @@ class NativeModel:
             def cb(user, layer, ptr, dim, stream):
                 try:
                     t = _tensor_from_ptr(ptr, n_nodes * dim, dev).view(n_nodes, dim)
-                    fn(layer, t)
+                    # the exchange runs on the stream the host names (the main one, or the side stream of the overlap)
+                    if stream:
+                        with torch.cuda.stream(torch.cuda.ExternalStream(int(stream), device=dev)):
+                            fn(layer, t)
+                    else:                      # NULL = the legacy default stream
+                        with torch.cuda.stream(torch.cuda.default_stream(dev)):
+                            fn(layer, t)
                     return 0
                 except Exception as e:  # noqa: BLE001
                     import sys
                     print(f'[halo hook] {type(e).__name__}: {e}', file=sys.stderr, flush=True)
                     return 10003
             return HALO_FN(cb)
-        hooks = HaloHooks(None, wrap(halo.forward), wrap(halo.backward))
+        # SURVEY 8e "Overlap": when the decomposition put the owned atoms without ghost neighbours first, the forward
+        # exchange of a layer runs on a side stream under the convolution of those rows (SEVENN_HALO_OVERLAP=0: in line)
+        n_int = int(getattr(getattr(halo, 'dec', None), 'n_interior', 0))
+        side = None
+        if n_int > 0 and os.environ.get('SEVENN_HALO_OVERLAP', '1') != '0':
+            if self._side is None:
+                self._side = torch.cuda.Stream(device=dev)
+            side = self._side.cuda_stream
+        hooks = HaloHooks(None, wrap(halo.forward), wrap(halo.backward), n_int if side else 0, side)
         self._hooks_keep = hooks
         return hooks
 
