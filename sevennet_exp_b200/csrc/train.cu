@@ -228,46 +228,57 @@ extern "C" int sevenn_edge_train(const float* edge_vec, long long n_edges, int l
 // sevenn_gemm_args).  types != nullptr keeps only the nodes of species `type_sel` (species-indexed linears).
 // Two stages, fixed order: split s sums its rows into part[s][K][N], then the splits are added in order.
 #ifndef SEVENN_EMU
-#define TN_T 64          // output tile (K x N) per CTA
+#define TN_T 64          // output tile: TN_T rows of K x (NJ * TN_T) columns of N per CTA
 #define TN_R 16          // rows staged per iteration
+// 256 threads as 16 (k) x 16 (n); each thread owns 4 k x (NJ x 4) n outputs: n = n0 + 64 j + 4 tx + {0..3}, so the 16-byte
+// shared-memory reads of eight neighbouring threads cover 128 contiguous bytes (conflict free).  NJ = 2 (wide N: the
+// [64, 960] radial-MLP weight gradients over all edges) does 32 FMAs per 3 vector loads; NJ = 1 keeps narrow N dense.
+template <int NJ>
 __global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ A, long long sAn, int sAm,
                                                       const float* __restrict__ B, long long sBn, int sBm, long long M,
                                                       int R, int K, int N, const int* __restrict__ types, int type_sel,
                                                       int n_split, float* __restrict__ part) {
-  __shared__ float As[TN_R][TN_T + 4];
-  __shared__ float Bs[TN_R][TN_T + 4];
-  const int k0 = blockIdx.x * TN_T, n0 = blockIdx.y * TN_T, sp = blockIdx.z;
+  constexpr int TNW = NJ * TN_T;
+  __shared__ __align__(16) float As[TN_R][TN_T + 4];
+  __shared__ __align__(16) float Bs[TN_R][TNW + 4];
+  const int k0 = blockIdx.x * TN_T, n0 = blockIdx.y * TNW, sp = blockIdx.z;
   const int tid = threadIdx.x, ty = tid / 16, tx = tid % 16;
   const long long per = (M + n_split - 1) / n_split;
   const long long r_begin = sp * per, r_end = (r_begin + per < M) ? r_begin + per : M;
-  float acc[4][4];
+  float acc[4][4 * NJ];
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  // loader: 4 elements of A and 4 of B per thread and iteration; consecutive threads read consecutive columns
-  const int lr = tid / 64, lc = tid % 64;          // rows lr, lr + 4, lr + 8, lr + 12; column lc
+    for (int j = 0; j < 4 * NJ; ++j) acc[i][j] = 0.f;
+  // loader: 4 elements of A and 4 NJ of B per thread and iteration; consecutive threads read consecutive columns
+  const int lr = tid / 64, lc = tid % 64;          // rows lr, lr + 4, lr + 8, lr + 12; columns lc (+ 64 for NJ = 2)
   // (node, m) of this thread's four rows, advanced incrementally (a 64-bit division per element would cost more
-  // instructions than the 64 FMAs it feeds)
+  // instructions than the FMAs it feeds)
   long long node_q[4]; int m_q[4];
 #pragma unroll
   for (int q = 0; q < 4; ++q) { const long long r = r_begin + lr + 4 * q; node_q[q] = r / R; m_q[q] = (int)(r - node_q[q] * R); }
   const int step_n = TN_R / R, step_m = TN_R % R;
-  float ra[4], rb[4];
+  float ra[4], rb[4][NJ];
   auto fetch = [&](long long r0) {            // next slab into registers while the current one is multiplied
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
       const long long r = r0 + lr + 4 * q;
-      float a = 0.f, b = 0.f;
+      float a = 0.f, b[NJ];
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) b[j] = 0.f;
       if (r < r_end) {
         const long long node = node_q[q];
         const int m = m_q[q];
         if (types == nullptr || types[node] == type_sel) {
           if (k0 + lc < K) a = __ldg(A + node * sAn + (long long)m * sAm + k0 + lc);
-          if (n0 + lc < N) b = __ldg(B + node * sBn + (long long)m * sBm + n0 + lc);
+#pragma unroll
+          for (int j = 0; j < NJ; ++j)
+            if (n0 + 64 * j + lc < N) b[j] = __ldg(B + node * sBn + (long long)m * sBm + n0 + 64 * j + lc);
         }
       }
-      ra[q] = a; rb[q] = b;
+      ra[q] = a;
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) rb[q][j] = b[j];
       node_q[q] += step_n; m_q[q] += step_m;
       if (m_q[q] >= R) { m_q[q] -= R; ++node_q[q]; }
     }
@@ -275,26 +286,35 @@ __global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ 
   fetch(r_begin);
   for (long long r0 = r_begin; r0 < r_end; r0 += TN_R) {
 #pragma unroll
-    for (int q = 0; q < 4; ++q) { As[lr + 4 * q][lc] = ra[q]; Bs[lr + 4 * q][lc] = rb[q]; }
+    for (int q = 0; q < 4; ++q) {
+      As[lr + 4 * q][lc] = ra[q];
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) Bs[lr + 4 * q][64 * j + lc] = rb[q][j];
+    }
     __syncthreads();
     if (r0 + TN_R < r_end) fetch(r0 + TN_R);
 #pragma unroll
     for (int rr = 0; rr < TN_R; ++rr) {
-      float a[4], b[4];
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[rr][ty * 4]);
+      const float a[4] = {a4.x, a4.y, a4.z, a4.w};
+      float b[4 * NJ];
 #pragma unroll
-      for (int q = 0; q < 4; ++q) { a[q] = As[rr][ty * 4 + q]; b[q] = Bs[rr][tx * 4 + q]; }
+      for (int j = 0; j < NJ; ++j) {
+        const float4 b4 = *reinterpret_cast<const float4*>(&Bs[rr][64 * j + tx * 4]);
+        b[4 * j] = b4.x; b[4 * j + 1] = b4.y; b[4 * j + 2] = b4.z; b[4 * j + 3] = b4.w;
+      }
 #pragma unroll
       for (int i = 0; i < 4; ++i)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        for (int j = 0; j < 4 * NJ; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
     }
     __syncthreads();
   }
 #pragma unroll
   for (int i = 0; i < 4; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const int k = k0 + ty * 4 + i, nn = n0 + tx * 4 + j;
+    for (int j = 0; j < 4 * NJ; ++j) {
+      const int k = k0 + ty * 4 + i, nn = n0 + 64 * (j / 4) + tx * 4 + (j % 4);
       if (k < K && nn < N) part[((size_t)sp * K + k) * N + nn] = acc[i][j];
     }
 }
@@ -333,9 +353,15 @@ extern "C" int sevenn_gemm_tn(const float* A, long long sAn, int sAm, const floa
   return 0;
 #else
   const int n_split = sevenn_gemm_tn_splits(M);
-  dim3 grid((K + TN_T - 1) / TN_T, (N + TN_T - 1) / TN_T, n_split);
-  gemm_tn_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(A, sAn, sAm, B, sBn, sBm, M, R, K, N, types, type_sel, n_split,
-                                                         part);
+  if (N >= 96) {
+    dim3 grid((K + TN_T - 1) / TN_T, (N + 2 * TN_T - 1) / (2 * TN_T), n_split);
+    gemm_tn_kernel<2><<<grid, 256, 0, (cudaStream_t)stream>>>(A, sAn, sAm, B, sBn, sBm, M, R, K, N, types, type_sel,
+                                                              n_split, part);
+  } else {
+    dim3 grid((K + TN_T - 1) / TN_T, (N + TN_T - 1) / TN_T, n_split);
+    gemm_tn_kernel<1><<<grid, 256, 0, (cudaStream_t)stream>>>(A, sAn, sAm, B, sBn, sBm, M, R, K, N, types, type_sel,
+                                                              n_split, part);
+  }
   gemm_tn_reduce_kernel<<<sevenn_grid_for((long long)K * N), 256, 0, (cudaStream_t)stream>>>(part, n_split, (long long)K * N,
                                                                                              scale, accumulate, out);
   return (int)cudaGetLastError();
