@@ -92,7 +92,8 @@ int sevenn_gemm_tc(const sevenn_gemm_args* args /* host */, const float* Bimg, v
 /* builds that image on the device from a row-major W[K, N] (img: img_floats of sevenn_gemm_tc_plan); for weights that
  * change every step (training) */
 int sevenn_gemm_tc_image(const float* W, int K, int N, float* img, void* stream);
-/* up to 4 independent problems with the same epilogue in one launch (the per-l blocks of one o3.Linear) */
+/* up to SEVENN_GEMM_GROUP_MAX independent problems with the same epilogue in one launch (the per-l blocks of one or two
+ * o3.Linear with disjoint outputs); members with >= 2 tiles per SM are launched on their own */
 int sevenn_gemm_tc_grouped(int n, const sevenn_gemm_args* args /* host array */, const float* const* Bimgs /* host array */,
                            void* stream);
 

@@ -49,7 +49,7 @@ struct TcParams {
   long long m_tiles;
   long long* dbg;       // optional clock64 trace of CTA (0,0) (SEVENN_TC_DBG=1)
 };
-#define TC_MAX_GROUP 4
+#define TC_MAX_GROUP SEVENN_GEMM_GROUP_MAX      // 8: the per-l blocks of up to two o3.Linear with disjoint outputs
 struct TcGroup {
   int n;
   int cta_start[TC_MAX_GROUP + 1];

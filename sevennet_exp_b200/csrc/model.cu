@@ -151,20 +151,25 @@ int flush_simt(sevenn_model* m, sevenn_gemm_args* sg, int& n, cudaStream_t st) {
 
 // o3.Linear forward: y (+)= x @ W per block (engine.py::_linear_fwd)
 // `ext`: collector shared with the caller's next linear (disjoint outputs): exact-fp32 blocks are left in it unflushed
-struct SimtBatch { sevenn_gemm_args g[SEVENN_GEMM_GROUP_MAX]; int n = 0; };
+struct SimtBatch {
+  sevenn_gemm_args g[SEVENN_GEMM_GROUP_MAX]; int n = 0;                                       // exact-fp32 arm
+  sevenn_gemm_args tg[SEVENN_GEMM_GROUP_MAX]; const float* timg[SEVENN_GEMM_GROUP_MAX]; int nt = 0;   // tcgen05 arm
+};
+int flush_tc(sevenn_model* m, SimtBatch& b, cudaStream_t st) {
+  if (b.nt == 0) return 0;
+  int rc = sevenn_gemm_tc_grouped(b.nt, b.tg, b.timg, st);
+  ++m->n_launch; ++m->n_tc_launch; b.nt = 0;
+  return rc;
+}
 int linear_fwd(sevenn_model* m, Arena& A, const Lin& L, const float* x, long long n, float* y, bool accumulate,
                const int* types, cudaStream_t st, SimtBatch* ext = nullptr) {
   if (A.dry || n <= 0) return 0;
-  sevenn_gemm_args grp[4]; const float* img[4]; int ng = 0;
   SimtBatch own;
   SimtBatch& sb = ext != nullptr ? *ext : own;
   sevenn_gemm_args* sgrp = sb.g; int& nsg = sb.n;
-  auto flush = [&]() -> int {
-    if (ng == 0) return 0;
-    int rc = sevenn_gemm_tc_grouped(ng, grp, img, st);
-    ++m->n_launch; ++m->n_tc_launch; ng = 0;
-    return rc;
-  };
+  sevenn_gemm_args* grp = sb.tg; const float** img = sb.timg; int& ng = sb.nt;
+  const int tc_cap = ext != nullptr ? SEVENN_GEMM_GROUP_MAX : 4;      // a linear on its own keeps groups of <= 4 (one per l)
+  auto flush = [&]() -> int { return flush_tc(m, sb, st); };
   for (const Blk& b : L.blk) {
     const int R = 2 * b.l + 1;
     if (L.by_type_S) {
@@ -180,18 +185,21 @@ int linear_fwd(sevenn_model* m, Arena& A, const Lin& L, const float* x, long lon
     g.C = y + b.out_off; g.sCn = L.dout; g.sCm = b.out_mul; g.M = n * R; g.R = R; g.N = b.N; g.K = b.K;
     g.epi = accumulate ? 1 : 0; g.cst = 1.f;
     if (tc_eligible(m, g, b.Wimg)) {
+      if (ng > 0 && grp[0].epi != g.epi) { int rc = flush(); if (rc) return rc; }     // one epilogue per launch
       grp[ng] = g; img[ng] = b.Wimg;
-      if (++ng == 4) { int rc = flush(); if (rc) return rc; }
+      if (++ng == tc_cap) { int rc = flush(); if (rc) return rc; }
     } else {
       sgrp[nsg] = g;
       if (++nsg == SEVENN_GEMM_GROUP_MAX) { int rc = flush_simt(m, sgrp, nsg, st); if (rc) return rc; }
     }
   }
-  int rc = flush();
-  if (rc) return rc;
+  int rc = 0;
   bool has_cst = false;
   for (const Blk& b : L.blk) has_cst = has_cst || b.cst != nullptr;
-  if (ext == nullptr || has_cst) { rc = flush_simt(m, sgrp, nsg, st); if (rc) return rc; }
+  if (ext == nullptr || has_cst) {
+    rc = flush(); if (rc) return rc;
+    rc = flush_simt(m, sgrp, nsg, st); if (rc) return rc;
+  }
   for (const Blk& b : L.blk)
     if (b.cst != nullptr) {
       add_row_kernel<<<sevenn_grid_for(n * b.N), 256, 0, st>>>(y + b.out_off, L.dout, n, b.N, b.cst);
@@ -281,7 +289,10 @@ int evaluate_graph(sevenn_model* m, Arena& A, const GraphView& g, const sevenn_h
     if (!L.si1.fwd_full) { rc = zero_async(A, h[t], (size_t)nn * L.dx_in * 4, st); if (rc) return rc; }
     rc = linear_fwd(m, A, L.si1, x, n_x, h[t], false, nullptr, st, &both);
     if (rc) return rc;
-    if (!A.dry) { rc = flush_simt(m, both.g, both.n, st); if (rc) return rc; }
+    if (!A.dry) {
+      rc = flush_tc(m, both, st); if (rc) return rc;
+      rc = flush_simt(m, both.g, both.n, st); if (rc) return rc;
+    }
     // ghost exchange: in line, or on the side stream while the rows without ghost neighbours are convolved
     long long n_int = 0;
     if (t > 0 && halo != nullptr && halo->forward != nullptr && !A.dry) {
