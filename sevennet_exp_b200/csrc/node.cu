@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(512) gate_fwd_v4_kernel(const float* __restric
 // products in shared memory and the gate-channel thread adds them in m order after the barrier (double buffered by
 // iteration parity: one __syncthreads per row group).  A thread per channel that walked the 2l+1 components itself
 // (first version) ran at 2.5 TB/s: few, heavy threads and not enough loads in flight.
-__global__ void __launch_bounds__(512, 3) gate_bwd_v4_kernel(const float* __restrict__ pre, int din, const float* __restrict__ dout_,
+__global__ void __launch_bounds__(512, 2) gate_bwd_v4_kernel(const float* __restrict__ pre, int din, const float* __restrict__ dout_,
                                                              int dout, float* __restrict__ dpre, long long n, const GateTable T,
                                                              int npart) {
   extern __shared__ float4 gate_part[];                 // [2][blockDim.y][npart]
@@ -170,34 +170,42 @@ __global__ void __launch_bounds__(512, 3) gate_bwd_v4_kernel(const float* __rest
     }
   }
   const int rb = (int)blockDim.y, ty = (int)threadIdx.y;
+  const long long stride = (long long)gridDim.x * rb;
+  // the loads of the next row group are issued before this group's barrier (two groups of loads in flight per thread)
+  float4 x = make_float4(0.f, 0.f, 0.f, 0.f), g = x, p = x;
+  auto load = [&](long long i, float4& x_, float4& g_, float4& p_) {
+    if (i >= n || role < 0) return;
+    x_ = ld4(pre + i * din + c);                                   // role 2: the gate pre-activation itself
+    if (role != 2) g_ = ld4(dout_ + i * dout + go_off);
+    if (role == 1) p_ = ld4(pre + i * din + gate_off);
+  };
+  load(blockIdx.x * (long long)rb + ty, x, g, p);
   int buf = 0;
-  for (long long base = blockIdx.x * (long long)rb; base < n; base += (long long)gridDim.x * rb, buf ^= 1) {
+  for (long long base = blockIdx.x * (long long)rb; base < n; base += stride, buf ^= 1) {
     const long long i = base + ty;
     const bool ok = i < n;
+    float4 xn = x, gn = g, pn = p;
+    load(i + stride, xn, gn, pn);
     float4* part = gate_part + ((size_t)buf * rb + ty) * npart;
-    float4 gp = make_float4(0.f, 0.f, 0.f, 0.f);
     if (ok && role == 0) {
-      const float4 x = ld4(pre + i * din + c), g = ld4(dout_ + i * dout + go_off);
       st4(dpre + i * din + c, make_float4(g.x * cst * dact_f(act, x.x), g.y * cst * dact_f(act, x.y),
                                           g.z * cst * dact_f(act, x.z), g.w * cst * dact_f(act, x.w)));
     } else if (ok && role == 1) {
-      const float4 x = ld4(pre + i * din + c), g = ld4(dout_ + i * dout + go_off), p = ld4(pre + i * din + gate_off);
       const float4 gate = make_float4(cst * act_f(act, p.x), cst * act_f(act, p.y), cst * act_f(act, p.z), cst * act_f(act, p.w));
       st4(dpre + i * din + c, make_float4(g.x * gate.x, g.y * gate.y, g.z * gate.z, g.w * gate.w));
       part[slot] = make_float4(g.x * x.x, g.y * x.y, g.z * x.z, g.w * x.w);
-    } else if (ok && role == 2) {
-      gp = ld4(pre + i * din + c);
     }
     __syncthreads();
     if (ok && role == 2) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int m = 0; m < nm; ++m) {
-        const float4 p = part[slot + m * mstride];
-        acc.x += p.x; acc.y += p.y; acc.z += p.z; acc.w += p.w;
+        const float4 q = part[slot + m * mstride];
+        acc.x += q.x; acc.y += q.y; acc.z += q.z; acc.w += q.w;
       }
-      st4(dpre + i * din + c, make_float4(acc.x * cst * dact_f(act, gp.x), acc.y * cst * dact_f(act, gp.y),
-                                          acc.z * cst * dact_f(act, gp.z), acc.w * cst * dact_f(act, gp.w)));
+      st4(dpre + i * din + c, make_float4(acc.x * cst * dact_f(act, x.x), acc.y * cst * dact_f(act, x.y),
+                                          acc.z * cst * dact_f(act, x.z), acc.w * cst * dact_f(act, x.w)));
     }
+    x = xn; g = gn; p = pn;
   }
 }
 
