@@ -99,3 +99,21 @@ def test_brick_grid():
     from sevennet_exp_b200.domain import brick_grid
     assert brick_grid(1) == (1, 1, 1) and brick_grid(2) == (2, 1, 1)
     assert brick_grid(4) == (2, 2, 1) and brick_grid(8) == (2, 2, 2)
+
+
+def test_interior_atoms_have_no_ghost_neighbours():
+    """domain.Decomposition puts the owned atoms farther than the cutoff from every brick face first (n_interior): a host
+    may convolve those rows while the ghost rows are still in flight (SURVEY 8e "Overlap")."""
+    from sevennet_exp_b200.domain import Decomposition
+    from tests.structures import random_cell
+    numbers, pos, cell = random_cell(600, [72, 8], density=0.05, seed=3, triclinic=False)
+    rc = 4.0
+    for grid, world in (((2, 1, 1), 2), ((2, 2, 1), 4)):
+        for rank in range(world):
+            dec = Decomposition(numbers, pos, cell, rc, grid, rank)
+            assert 0 < dec.n_interior < dec.n_local
+            owned, ghosts = dec.pos[:dec.n_local], dec.pos[dec.n_local:]
+            d = np.linalg.norm(owned[:dec.n_interior, None, :] - ghosts[None, :, :], axis=2)
+            assert d.min() >= rc                    # no ghost within the cutoff of an interior atom
+            d2 = np.linalg.norm(owned[dec.n_interior:, None, :] - ghosts[None, :, :], axis=2)
+            assert (d2.min(axis=1) < rc).mean() > 0.5     # most boundary atoms do have one
