@@ -320,6 +320,7 @@ def gen_fwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
                         if terms:
                             L.append(f'          a{pi}_{k}{sx} = fmaf(w{pi}{sx}, {" + ".join(terms)}, a{pi}_{k}{sx});')
             L.append('        }')
+        L += getattr(G, 'loop_tail', [])
         L.append('      }')   # for e
         L.append('    }')     # if e0 < e1
         L.append('    float* orow = out + (size_t)row * ldo + c32 + lane;')
@@ -468,6 +469,7 @@ def gen_bwd(spec: ConvSpec, groups: List[_Group], sig: str, tab: bool = False) -
             L.append(f'        sevenn_dy_accumulate<{NP}>(dyv, lane, dYu + (size_t)e * {SD}, {SD if gr_in_butterfly else S});')
         if tab and not gr_in_butterfly:
             L.append(f'        sevenn_gr_accumulate(gr, lane, dYu + (size_t)e * {SD} + {S});')
+        L += getattr(G, 'loop_tail', [])
         L.append('      }')
         L.append('    }')
         L.append('  }')
@@ -547,6 +549,28 @@ def dy_smem_values(spec: ConvSpec) -> int:
 # dx / dY -> butterfly) are no longer covered; the scalar kernel at 120 registers / 16 warps is latency AND issue bound.
 # Kept as an opt-in generator path (SEVENN_TAB_EP=0,1), off by default.
 TAB_EP_DEFAULT = (False, False)
+# Radial weights carried across the edge loop (regs table mode, monomial rows): w (and h dw/dr) of edge e + 1 are
+# evaluated at the END of trip e from the rows fetched at its top, so the 4-register rows never cross the back edge --
+# the (T = Tn) copies were 24 of the 196 SASS instructions of the l1 = 1 forward loop.  (forward, backward);
+# SEVENN_TAB_WCARRY='f,b' for A/B builds.
+# Same-box A/B on B200 (tools/gpu.sh ab, profiles/r02b_wcarry_ab.txt): it pays where the loop is short -- the LAST layers
+# (scalar outputs only: SevenNet-0 backward 4.74 -> 3.85 ms, forward 2.53 -> 2.28 ms on 216 k atoms; l3i5 1.09 -> 0.83 /
+# 0.54 -> 0.46 ms) and the l3i5 first-layer backward -- and not in the inner layers (SevenNet-0 forward 20.40 -> 20.51 ms
+# although the loops lose 4-18 % of their instructions; l3i5 forward 6.16 -> 7.25 ms): there the rows fetched at the top
+# of a trip are not back by its end.
+TAB_WCARRY_DEFAULT = (False, False)
+TAB_WCARRY_BY_SIG = {
+    'cddfea4828d': (True, True),     # SevenNet-0 last layer
+    'cc7e5576d9a': (True, True),     # SevenNet-l3i5 last layer
+    'c0845e94934': (False, True),    # SevenNet-l3i5 first layer
+}
+_TAB_WCARRY_ENV = _os.environ.get('SEVENN_TAB_WCARRY')
+
+
+def tab_wcarry(bwd: bool) -> bool:
+    mode = (tuple(v == '1' for v in _TAB_WCARRY_ENV.split(',')) if _TAB_WCARRY_ENV
+            else TAB_WCARRY_BY_SIG.get(_cur_sig[0], TAB_WCARRY_DEFAULT))
+    return bool(mode[1 if bwd else 0]) and tab_t_regs(bwd) and TAB_POLY and not (bwd and tab_ep(True))
 TAB_EP_BY_SIG = {}
 _TAB_EP_ENV = _os.environ.get('SEVENN_TAB_EP')
 TAB_EP_XY_DEPTH = 8   # ring slots for x_j / Y in edge-pair mode (three pairs in flight)
@@ -686,6 +710,69 @@ def _tab_pipeline_regs(L, G: _Group, spec: ConvSpec, idx_of, xyf):
             L.append(f'        const float x{m}{_sx(G, c)} = {_on(G, f"sr[{(m * G.cpw + c) * 32} + lane]")};')
 
 
+def _poly_lines(G: _Group, bwd: bool, tpre: str, t: str, decl: str, ind: str) -> List[str]:
+    """w (and wd = h dw/dr when ``bwd``) of every (path, chunk) from monomial table rows named ``tpre<pi><sx>`` at ``t``."""
+    out = []
+    scoped = decl == ''                       # assignments to carried variables: the temporaries get their own scope
+    if bwd:
+        out.append(f'{ind}{"{ " if scoped else ""}const float t2_ = {t} + {t}, t3_ = 3.f * {t} * {t};')
+    for pi, p in G.paths:
+        for c in range(G.cpw):
+            T = f'{tpre}{pi}{_sx(G, c)}'
+            out.append(f'{ind}{decl}w{pi}{_sx(G, c)} = fmaf(fmaf(fmaf({T}.w, {t}, {T}.z), {t}, {T}.y), {t}, {T}.x);')
+            if bwd:
+                out.append(f'{ind}{decl}wd{pi}{_sx(G, c)} = fmaf(t3_, {T}.w, fmaf(t2_, {T}.z, {T}.y));')
+    if bwd and scoped:
+        out.append(f'{ind}}}')
+    return out
+
+
+def _tab_pipeline_regs_carry(L, G: _Group, spec: ConvSpec, idx_of, xyf, bwd: bool):
+    """Like _tab_pipeline_regs, but the radial weights are what crosses the back edge (TAB_WCARRY): the rows of edge e + 1
+    are fetched at the top of trip e together with its t (read straight from Yt) and evaluated in G.loop_tail."""
+    S = (spec.lmax_sh + 1) ** 2
+    S2 = S + 2
+    DX = TAB_XY_DEPTH
+    z = 'make_float4(0.f, 0.f, 0.f, 0.f)'
+    names = [f'{v}{pi}{_sx(G, c)}' for pi, p in G.paths for c in range(G.cpw) for v in (('w', 'wd') if bwd else ('w',))]
+    for d in range(DX - 1):
+        L.append(f'      if (e0 + {d} < e1) {{')
+        _tab_issue_xy(L, G, spec, '        ', f'e0 + {d}', f'col[e0 + {d}]', str(d))
+        L.append('      }')
+        L.append('      CP_ASYNC_COMMIT();')
+    L.append('      float ' + ', '.join(names) + ';')
+    L.append(f'      {{ const float4* tr0 = tab + (size_t)({idx_of("e0")}) * {spec.wn} + c32 + lane;')
+    L.append(f'        const float t0_ = LDG(Yt + (size_t)e0 * {S2} + {S});')
+    for pi, p in G.paths:
+        for c in range(G.cpw):
+            L.append(f'        const float4 T0_{pi}{_sx(G, c)} = {_on(G, f"__ldg(tr0 + {p.w_off + c * 32})", z)};')
+    L += _poly_lines(G, bwd, 'T0_', 't0_', '', '        ')
+    L.append('      }')
+    L.append(f'      int jn = col[e0 + {DX - 1} < e1 ? e0 + {DX - 1} : e1 - 1];')
+    L.append(f'      int in = {idx_of("(e0 + 1 < e1 ? e0 + 1 : e1 - 1)")};')
+    L.append('      int slot = 0;')
+    L.append('      for (int e = e0; e < e1; ++e) {')
+    L.append(f'        const float4* tr = tab + (size_t)(in) * {spec.wn} + c32 + lane;')
+    L.append(f'        const float tn_ = LDG(Yt + (size_t)(e + 1 < e1 ? e + 1 : e1 - 1) * {S2} + {S});')
+    for pi, p in G.paths:
+        for c in range(G.cpw):
+            L.append(f'        const float4 Tn{pi}{_sx(G, c)} = {_on(G, f"__ldg(tr + {p.w_off + c * 32})", z)};')
+    L.append(f'        CP_ASYNC_WAIT({DX - 2});')
+    L.append('        __syncwarp();')
+    L.append(f'        if (e + {DX - 1} < e1) {{')
+    _tab_issue_xy(L, G, spec, '          ', f'e + {DX - 1}', 'jn', f'(slot + {DX - 1}) & {DX - 1}')
+    L.append('        }')
+    L.append('        CP_ASYNC_COMMIT();')
+    L.append(f'        jn = col[e + {DX} < e1 ? e + {DX} : e1 - 1];')
+    L.append(f'        in = {idx_of("(e + 2 < e1 ? e + 2 : e1 - 1)")};')
+    L.append(f'        const float* sr = ring + slot * {xyf};')
+    L.append(f'        slot = (slot + 1) & {DX - 1};')
+    for m in range(G.d1):
+        for c in range(G.cpw):
+            L.append(f'        const float x{m}{_sx(G, c)} = {_on(G, f"sr[{(m * G.cpw + c) * 32} + lane]")};')
+    G.loop_tail = ['#ifndef SEVENN_EMU'] + _poly_lines(G, bwd, 'Tn', 'tn_', '', '        ') + ['#endif']
+
+
 def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
     """Opens ``if (e0 < e1) { for (e) {`` with x*, y*, w* (and wd* = h dw/dr when ``bwd``) of edge e defined.
     cp.async groups alternate  ... X(e+2) | T(e+1) | X(e+3) | T(e+2) ...  so that ``wait_group 1`` at the top of
@@ -712,16 +799,25 @@ def _tab_pipeline_open(L, G: _Group, spec: ConvSpec, bwd: bool):
             L.append(f'        const float4 T{pi}{_sx(G, c)} = {_on(G, f"tr[{p.w_off + c * 32}]", z)};')
     for jj in G.ys:
         L.append(f'        const float y{jj} = Yt[(size_t)e * {S2} + {jj}];')
+    G.loop_tail = []
+    carry = tab_wcarry(bwd)
+    if carry:
+        L += _poly_lines(G, bwd, 'T', 't', 'const float ', '        ')
     L.append('#else')
-    if tab_t_regs(bwd):
+    if carry:
+        _tab_pipeline_regs_carry(L, G, spec, idx_of, xyf, bwd)
+    elif tab_t_regs(bwd):
         _tab_pipeline_regs(L, G, spec, idx_of, xyf)
     else:
         _tab_pipeline_smem(L, G, spec, idx_of, xyf, wf, wbase)
     ybase = G.d1 * 32 * G.cpw
     for jj in G.ys:
         L.append(f'        const float y{jj} = sr[{ybase + jj}];')
-    L.append(f'        const float t = sr[{ybase + S}];')
+    if not carry:
+        L.append(f'        const float t = sr[{ybase + S}];')
     L.append('#endif')
+    if carry:
+        return
     # cubic Hermite basis (and its derivative) at t
     if TAB_POLY:
         for pi, p in G.paths:

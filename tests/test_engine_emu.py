@@ -89,6 +89,23 @@ def test_engine_emu_two_chunk_units(monkeypatch, packed):
     print(_compare(cfg, model.state_dict(), numbers, pos, cell, [True] * 3, model))
 
 
+def test_engine_emu_carried_radial_weights(monkeypatch):
+    """conv_codegen.TAB_WCARRY: the tabulated kernels evaluate w (and h dw/dr) of the next edge at the end of a loop trip
+    instead of carrying the table rows across it.  The emulation build shares the generated algebra and the weight
+    evaluation with the device code; the pipelined loads themselves only exist on the device (GPU parity tests)."""
+    from sevennet_exp_b200.codegen import conv_codegen
+    monkeypatch.setattr(conv_codegen, 'TAB_WCARRY_DEFAULT', (True, True))
+    monkeypatch.setattr(conv_codegen, 'TAB_WCARRY_BY_SIG', {})
+    cfg = dict(presets.PRESETS['test-so3-l2'])
+    conv = sp.build_spec(cfg).layers[1].conv
+    src = conv_codegen.generate(conv)
+    assert 'tn_' in src and 'T0_' in src
+    torch.manual_seed(777)
+    model = S.build_model(cfg).eval()
+    numbers, pos, cell = random_cell(20, list(cfg['_type_map']), density=0.05, seed=4)
+    print(_compare(cfg, model.state_dict(), numbers, pos, cell, [True] * 3, model))
+
+
 @pytest.mark.parametrize('bias', [False, True])
 def test_engine_emu_modality_and_bias(bias):
     """SevenNet-MF style model (model_build.py:198-244, nn/linear.py:65-92, nn/scale.py:165-330): modality one-hot
