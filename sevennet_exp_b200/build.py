@@ -2,11 +2,9 @@
 
     python -m sevennet_exp_b200.build            # prebuilt signatures (SevenNet-0, l3i5, test models)
 """
-import hashlib
 import os
 import shutil
 import subprocess
-import sys
 from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))

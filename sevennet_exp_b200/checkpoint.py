@@ -2,7 +2,6 @@
 import os
 from typing import Dict, Tuple
 
-import numpy as np
 import torch
 
 from . import irreps as ir

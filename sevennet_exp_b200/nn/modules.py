@@ -7,7 +7,7 @@ layout and are permuted to the library's ``[2l+1][mul]`` layout inside.  Gradien
 only (see functional.py)."""
 import math
 from collections import OrderedDict
-from typing import Dict, Optional
+from typing import Dict
 
 import numpy as np
 import torch

@@ -14,7 +14,7 @@ point is a node (the Hermite pieces are then smooth inside every interval).
 Weight preprocessing only: nothing here runs per evaluation.
 """
 import math
-from typing import List, Sequence, Tuple
+from typing import Sequence, Tuple
 
 import numpy as np
 

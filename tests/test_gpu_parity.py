@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import sevenn_ref as S
-from sevennet_exp_b200 import presets, spec as sp
+from sevennet_exp_b200 import presets
 from tests.structures import diamond_si, fluorite_hfo2, random_cell
 
 pytestmark = pytest.mark.gpu

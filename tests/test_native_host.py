@@ -8,7 +8,6 @@ import pytest
 import torch
 
 from oracle import sevenn_ref as S
-from sevennet_exp_b200 import presets
 from tests.structures import diamond_si, fluorite_hfo2, random_cell
 from tests.test_gpu_parity import _random_model
 
