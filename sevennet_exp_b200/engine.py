@@ -401,6 +401,7 @@ class Engine(Kernels):
                     for c in (spec.multi_cutoff or []):              # every layer cutoff (and XPLOR switch-on) a node
                         extra += [c, c - 1.0] if xplor else [c]
                     self.tab_n = radial_table.choose_intervals(spec.cutoff, spec.cutoff_fn, spec.cutoff_on,
+                                                               n_min=int(os.environ.get('SEVENN_TAB_NMIN', '1000')),
                                                                extra_nodes=extra)
                     self.tab_inv_h = self.tab_n / spec.cutoff
                     t_first = False
