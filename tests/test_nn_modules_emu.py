@@ -250,3 +250,36 @@ def test_sequential_multi_modal_matches_oracle():
     g = S.atoms_to_graph(numbers, pos, cell, [True] * 3, cfg['cutoff'])
     g[S.X] = model._atomic_numbers_to_onehot(g[S.Z])          # _ModalInputPrepare reads data['x'].device
     assert abs(model(g)[S.E_TOT].item() - energies[0]) < 1e-4
+
+
+def test_grouped_fp32_gemm_equals_single_calls_emulation():
+    """sevenn_gemm_f32_grouped (small systems: the blocks of one or two o3.Linear in one launch) against one
+    sevenn_gemm_f32 call per problem and against numpy, through the emulation build; more than SEVENN_GEMM_GROUP_MAX
+    problems are refused."""
+    import ctypes
+    from sevennet_exp_b200 import _lib as L
+    from tests.emu_util import build_full_emu
+    lib = build_full_emu([])
+    rng = np.random.default_rng(0)
+    n = 11
+    probs = []
+    for (R, K, N, epi) in [(1, 12, 20, 0), (3, 8, 8, 1), (5, 4, 6, 0)]:
+        A = rng.normal(size=(n, R * K + 2)).astype(np.float32)
+        B = rng.normal(size=(K, N)).astype(np.float32)
+        probs.append((R, K, N, epi, A, B))
+    outs = []
+    for grouped in (False, True):
+        Cs = [np.full((n, R * N), 0.5, dtype=np.float32) for (R, K, N, *_r) in probs]
+        gs = [L.GemmArgs(A.ctypes.data, R * K + 2, K, B.ctypes.data, N, C.ctypes.data, R * N, N, n * R, R, N, K, epi, 0, 1.0, None, None)
+              for (R, K, N, epi, A, B), C in zip(probs, Cs)]
+        if grouped:
+            lib.call('sevenn_gemm_f32_grouped', len(gs), (L.GemmArgs * len(gs))(*gs), None)
+        else:
+            for g in gs:
+                lib.call('sevenn_gemm_f32', ctypes.byref(g), None)
+        outs.append(Cs)
+    for (R, K, N, epi, A, B), a, b in zip(probs, *outs):
+        assert np.array_equal(a, b)
+        ref = np.einsum('nrk,kc->nrc', A[:, :R * K].reshape(n, R, K).astype(np.float64), B.astype(np.float64)).reshape(n, R * N)
+        assert np.abs(a - (ref + (0.5 if epi else 0.0))).max() < 1e-5
+    assert lib.cdll.sevenn_gemm_f32_grouped(9, (L.GemmArgs * 9)(), None) != 0
