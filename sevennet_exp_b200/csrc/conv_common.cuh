@@ -92,10 +92,14 @@ __device__ __forceinline__ void sevenn_gr_accumulate(float v, int lane, float* d
     float* ring = ring_all + (threadIdx.x >> 5) * (ringf); (void)ring; \
     const int lane = threadIdx.x & 31; const int unit = blockIdx.y; \
     const int row = blockIdx.x * CONV_WARPS_PER_CTA + (threadIdx.x >> 5); if (row < (n)) {
-#define LAUNCH_DYN(kern, n, nunits, ringf, stream) \
+// carve: preferred shared-memory carveout in percent of the SM's 228 KB (just enough for the resident CTAs' rings, so the
+// rest of the array serves as L1 for the radial-table rows), or < 0 to leave the driver's default
+#define LAUNCH_DYN(kern, n, nunits, ringf, carve, stream) \
     { static bool attr_done = false; const int smem_bytes = CONV_WARPS_PER_CTA * (ringf) * 4; \
-      if (!attr_done && smem_bytes > 48 * 1024) { \
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes); attr_done = true; } } \
+      if (!attr_done) { \
+        if (smem_bytes > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes); \
+        if ((carve) >= 0) cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (carve)); \
+        attr_done = true; } } \
     kern<<<dim3(((n) + CONV_WARPS_PER_CTA - 1) / CONV_WARPS_PER_CTA, (nunits)), 32 * CONV_WARPS_PER_CTA, \
            CONV_WARPS_PER_CTA * (ringf) * 4, (cudaStream_t)(stream)>>>
 #define LAUNCH(kern, n, nunits, stream) kern<<<dim3(((n) + CONV_WARPS_PER_CTA - 1) / CONV_WARPS_PER_CTA, (nunits)), 32 * CONV_WARPS_PER_CTA, 0, (cudaStream_t)(stream)>>>
@@ -127,7 +131,7 @@ static inline float2 make_float2(float x, float y) { float2 r = {x, y}; return r
 static inline float2 __ffma2_rn(float2 a, float2 b, float2 c) { return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
 static inline float2 __fmul2_rn(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
 #define UNIT_LOOP_BEGIN_DYN(n, nunits, ringf) UNIT_LOOP_BEGIN(n, nunits, ringf)
-#define LAUNCH_DYN(kern, n, nunits, ringf, stream) kern
+#define LAUNCH_DYN(kern, n, nunits, ringf, carve, stream) kern
 #define LAUNCH(kern, n, nunits, stream) kern
 #define LAUNCH_STATUS() 0
 #define __restrict__
